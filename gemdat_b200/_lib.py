@@ -1,0 +1,94 @@
+"""ctypes binding of ``csrc/libgemdat_b200.so`` (declared in ``include/gemdat_b200.h``).
+
+The shared library is the product: there is no Python or CPU fallback.  Importing
+this module without the built library raises, and every compute entry point
+returns ``GD_ERR_CUDA`` when no CUDA device is usable.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = Path(os.environ.get('GEMDAT_B200_LIB', _HERE / 'csrc' / 'libgemdat_b200.so'))
+
+GD_OK = 0
+GD_ERR_CUDA = 1
+GD_ERR_INVALID = 2
+GD_ERR_ALIGNMENT = 3
+GD_ERR_TRICLINIC = 4
+GD_ERR_CAPACITY = 5
+GD_ERR_RADIUS_GT_CUTOFF = 6
+GD_ERR_INNER_CONSTANT = 7
+GD_ERR_NO_EVENTS = 8
+GD_ERR_NO_JUMPS = 9
+GD_ERR_RANGE = 10
+
+
+class GemdatB200Error(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f'libgemdat_b200 error {code}: {message}')
+        self.code = code
+        self.message = message
+
+
+def _load() -> C.CDLL:
+    if not LIB_PATH.exists():
+        raise ImportError(
+            f'{LIB_PATH} is missing: build it with `python -c "import __graft_entry__ as g; g.build()"` '
+            'or gemdat_b200/csrc/build.sh (nvcc, sm_100a). gemdat_b200 has no CPU fallback.'
+        )
+    return C.CDLL(str(LIB_PATH))
+
+
+lib = _load()
+
+_p = C.c_void_p
+_i32 = C.c_int32
+_i64 = C.c_int64
+_u64 = C.c_uint64
+_sz = C.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/gemdat_b200.h declares
+SIGNATURES = {
+    'gd_last_error': (C.c_char_p, []),
+    'gd_version': (C.c_int, []),
+    'gd_sm_count': (C.c_int, []),
+    'gd_sitegrid_build': (C.c_int, [_p, _p, _p, _i32, _p, _p, _i32, _p, _sz, C.POINTER(_sz)]),
+    'gd_site_states': (C.c_int, [_p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_remap_states': (C.c_int, [_p, _i64, _p, _i32, _p]),
+    'gd_widen_i32_i64': (C.c_int, [_p, _p, _i64, _p]),
+    'gd_events_work_elems': (_i64, [_i64, _i32]),
+    'gd_events_count': (C.c_int, [_p, _p, _i64, _i32, _p, _p, _p, _p, _p]),
+    'gd_events_scan': (C.c_int, [_p, _i64, _i32, _p, _p, C.POINTER(_i64), _p]),
+    'gd_events_fill': (C.c_int, [_p, _p, _i64, _i32, _p, _p, _p, _p, _p, _i64, _p, _p]),
+    'gd_fill_states': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p, _p]),
+    'gd_jumps_count': (C.c_int, [_p, _p, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
+    'gd_jumps_fill': (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _p]),
+    'gd_pair_matrix': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p]),
+    'gd_unwrap_chunks': (_i64, [_i64, _i32]),
+    'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_transpose_soa': (C.c_int, [_p, _i64, _i32, _p, _p]),
+    'gd_msd_direct': (C.c_int, [_p, _i64, _i32, _i64, _i64, _p, _p]),
+    'gd_density': (C.c_int, [_p, _i64, _p, _p, _p, _p]),
+    'gd_pbc_distances': (C.c_int, [_p, _p, _i32, _p, _i32, _p, _p]),
+    'gd_synth_positions': (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _p, _u64, _i64, _i64, _p, _p]),
+    'gd_fp64_peak': (C.c_int, [_i64, C.POINTER(C.c_double), _p]),
+}
+
+for _name, (_res, _args) in SIGNATURES.items():
+    _fn = getattr(lib, _name)  # AttributeError here = the .so is stale: rebuild
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+def last_error() -> str:
+    return lib.gd_last_error().decode('utf-8', 'replace')
+
+
+def check(status: int) -> None:
+    """Raise for any non-zero status (callers map specific codes to the reference's exceptions first)."""
+    if status != GD_OK:
+        raise GemdatB200Error(status, last_error())

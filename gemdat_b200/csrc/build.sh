@@ -1,0 +1,19 @@
+#!/bin/bash
+# Build libgemdat_b200.so in-tree for sm_100a (cross-compiles without a GPU).
+set -euo pipefail
+cd "$(dirname "$0")"
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17
+       --fmad=false -Xcompiler -fPIC,-ffp-contract=off,-Wall -Xptxas -v)
+mkdir -p _build
+pids=()
+for f in gd_*.cu; do
+  o=_build/${f%.cu}.o
+  if [[ ! -f $o || $f -nt $o || gd_common.cuh -nt $o || ../../include/gemdat_b200.h -nt $o ]]; then
+    ( "$NVCC" "${FLAGS[@]}" -c "$f" -o "$o" > "_build/${f%.cu}.log" 2>&1 || { cat "_build/${f%.cu}.log"; exit 1; } ) &
+    pids+=($!)
+  fi
+done
+for p in "${pids[@]:-}"; do [[ -n "$p" ]] && wait "$p"; done
+"$NVCC" -shared -o libgemdat_b200.so _build/gd_*.o -lcudart
+echo "built $(pwd)/libgemdat_b200.so"

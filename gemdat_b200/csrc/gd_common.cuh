@@ -1,0 +1,138 @@
+// Shared plumbing for libgemdat_b200.so: error reporting, launch helpers and the
+// sm_100a PTX wrappers (mbarrier + TMA bulk copy) the streaming kernels use.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/gemdat_b200.h"
+
+#define GD_NOSITE (-1)
+
+void gd_set_error(const char *fmt, ...);
+
+#define GD_CUDA_CHECK(expr)                                                                  \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            gd_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__,   \
+                         __LINE__);                                                          \
+            return GD_ERR_CUDA;                                                              \
+        }                                                                                    \
+    } while (0)
+
+#define GD_REQUIRE(cond, code, ...)                                                          \
+    do {                                                                                     \
+        if (!(cond)) {                                                                       \
+            gd_set_error(__VA_ARGS__);                                                       \
+            return (code);                                                                   \
+        }                                                                                    \
+    } while (0)
+
+#define GD_LAUNCH_CHECK()                                                                    \
+    do {                                                                                     \
+        cudaError_t _e = cudaGetLastError();                                                 \
+        if (_e != cudaSuccess) {                                                             \
+            gd_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e),         \
+                         __FILE__, __LINE__);                                                \
+            return GD_ERR_CUDA;                                                              \
+        }                                                                                    \
+    } while (0)
+
+struct GdDeviceInfo {
+    int sm_count;
+    int max_smem_optin;
+};
+// cached per process; sm_count < 0 when no device is usable
+const GdDeviceInfo &gd_device_info();
+
+static inline int64_t gd_ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+#ifdef __CUDACC__
+
+// ---------------------------------------------------------------- mbarrier / TMA (sm_90+)
+__device__ __forceinline__ uint32_t gd_smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void gd_mbar_init(uint64_t *bar, uint32_t arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(gd_smem_u32(bar)), "r"(arrivals)
+                 : "memory");
+}
+
+// make barrier initialisation visible to the async (TMA) proxy
+__device__ __forceinline__ void gd_fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void gd_mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(gd_smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+
+__device__ __forceinline__ void gd_mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(gd_smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ bool gd_mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        "  .reg .pred p;\n"
+        "  mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "  selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(gd_smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+__device__ __forceinline__ void gd_mbar_wait(uint64_t *bar, uint32_t parity) {
+    while (!gd_mbar_try_wait(bar, parity)) {
+    }
+}
+
+// 1-D TMA bulk copy global -> shared, completion reported on an mbarrier.
+// dst/src 16-byte aligned, bytes a non-zero multiple of 16.  SASS: UBLKCP.
+__device__ __forceinline__ void gd_tma_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes,
+                                               uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(gd_smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(gd_smem_u32(bar))
+        : "memory");
+}
+
+// 1-D TMA bulk copy shared -> global (bulk async-group completion).
+__device__ __forceinline__ void gd_tma_store_1d(void *gmem_dst, const void *smem_src,
+                                                uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst),
+                 "r"(gd_smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void gd_tma_store_commit() {
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void gd_tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void gd_tma_store_wait() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+// generic-proxy smem writes -> visible to the async proxy (before a TMA store)
+__device__ __forceinline__ void gd_fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ int gd_warp_sum(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+#endif  // __CUDACC__

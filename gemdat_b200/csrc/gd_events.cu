@@ -1,0 +1,348 @@
+// K2 -- transition events and forward/backward fill over the [n_frames, n_atoms]
+// int32 state arrays produced by K1.
+//
+// Replaces _calculate_transition_events (reference src/gemdat/transitions.py:413-482:
+// a Python loop over atoms with np.roll/np.nonzero/np.unique inside) and
+// ffill/bfill (src/gemdat/utils.py:59-98).
+//
+// The frame axis is cut into chunks of F frames; one thread owns one (chunk, atom)
+// column segment, so a warp reads 32 neighbouring atoms of the same frame (one
+// coalesced 128-byte line per state array per step) and keeps the previous row in
+// registers: every state is read exactly once per pass.  Rows come out sorted by
+// (atom, time) through a count -> per-atom block scan -> fill sequence; the row
+// offsets live in the caller's scratch (atom-major so the scan is contiguous).
+//
+// Algorithmic traffic: 8 B read per atom-frame per pass (count, fill); events are
+// O(1e-2) of the atom-frames.
+#include "gd_common.cuh"
+
+namespace {
+
+// frames per chunk: ~2^18 (chunk, atom) items in flight
+__host__ __device__ inline int64_t chunk_frames(int64_t n_frames, int32_t n_atoms) {
+    int64_t want = (n_frames * (int64_t)n_atoms) >> 18;
+    int64_t f = 8;
+    while (f < want && f < 1024) f <<= 1;
+    return f;
+}
+
+struct Geometry {
+    int64_t n_frames;
+    int32_t n_atoms;
+    int64_t f;         // frames per chunk
+    int64_t n_chunks;
+};
+
+inline Geometry geometry(int64_t n_frames, int32_t n_atoms) {
+    Geometry g;
+    g.n_frames = n_frames;
+    g.n_atoms = n_atoms;
+    g.f = chunk_frames(n_frames, n_atoms);
+    g.n_chunks = gd_ceil_div(n_frames, g.f);
+    return g;
+}
+
+// ---------------------------------------------------------------- events: count / fill
+
+template <bool kFill>
+__global__ void __launch_bounds__(256)
+    k_events(const int32_t *__restrict__ so, const int32_t *__restrict__ si, Geometry g,
+             const int32_t *__restrict__ next_o, const int32_t *__restrict__ next_i,
+             int32_t *__restrict__ work, uint8_t *__restrict__ changed,
+             const uint8_t *__restrict__ changed_global, const int64_t *__restrict__ atom_offsets,
+             int64_t frame0, int32_t *__restrict__ events) {
+    const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= g.n_chunks * g.n_atoms) return;
+    const int64_t c = item / g.n_atoms;
+    const int32_t a = (int32_t)(item - c * g.n_atoms);
+    const int64_t t0 = c * g.f;
+    const int64_t t1 = min(g.n_frames, t0 + g.f);
+    const int64_t A = g.n_atoms;
+
+    int64_t row = 0;
+    if (kFill) {
+        if (!changed_global[a]) return;  // outer state never changes: atom is skipped
+        row = atom_offsets[a] + work[(int64_t)a * g.n_chunks + c];
+    }
+
+    int32_t po = so[t0 * A + a];
+    int32_t pi = si[t0 * A + a];
+    int cnt = 0;
+    bool ch_o = false, ch_i = false;
+#pragma unroll 4
+    for (int64_t t = t0; t < t1; ++t) {
+        int32_t no, ni;
+        if (t + 1 < g.n_frames) {
+            no = so[(t + 1) * A + a];
+            ni = si[(t + 1) * A + a];
+        } else if (next_o != nullptr) {
+            no = next_o[a];
+            ni = next_i[a];
+        } else {
+            break;  // last frame of the trajectory: the np.roll wrap-around is dropped
+        }
+        const bool d_o = no != po, d_i = ni != pi;
+        if (d_o | d_i) {
+            if (kFill) {
+                int32_t *e = events + row * 6;
+                e[0] = a;
+                e[1] = po;
+                e[2] = no;
+                e[3] = pi;
+                e[4] = ni;
+                e[5] = (int32_t)(frame0 + t);
+                ++row;
+            }
+            ++cnt;
+        }
+        ch_o |= d_o;
+        ch_i |= d_i;
+        po = no;
+        pi = ni;
+    }
+    if (!kFill) {
+        work[(int64_t)a * g.n_chunks + c] = cnt;
+        if (ch_o) changed[a] = 1;
+        if (ch_i) changed[A + a] = 1;
+    }
+}
+
+// one block per atom: exclusive scan of the chunk counts (zeroed when the atom is
+// skipped), total -> totals[a]
+__global__ void __launch_bounds__(256)
+    k_scan_chunks(int32_t *__restrict__ work, int64_t n_chunks, const uint8_t *__restrict__ changed,
+                  int32_t n_atoms, int64_t *__restrict__ totals, int32_t *__restrict__ err_flag) {
+    const int a = blockIdx.x;
+    int32_t *col = work + (int64_t)a * n_chunks;
+    const bool keep = changed[a] != 0;
+    if (threadIdx.x == 0 && keep && !changed[n_atoms + a]) atomicExch(err_flag, 1);
+    __shared__ int64_t warp_tot[8];
+    __shared__ int64_t running_s;
+    if (threadIdx.x == 0) running_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n_chunks; base += 256) {
+        const int64_t idx = base + threadIdx.x;
+        int64_t v = (idx < n_chunks && keep) ? col[idx] : 0;
+        int64_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        int64_t warp_base = 0;
+        for (int w = 0; w < warp; ++w) warp_base += warp_tot[w];
+        const int64_t running = running_s;
+        if (idx < n_chunks) col[idx] = (int32_t)(running + warp_base + incl - v);
+        __syncthreads();
+        if (threadIdx.x == 255) running_s = running + warp_base + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) totals[a + 1] = running_s;
+}
+
+// single block: in-place exclusive scan over atoms of totals[1..n] -> offsets[0..n]
+__global__ void __launch_bounds__(1024) k_scan_atoms(int64_t *__restrict__ off, int32_t n_atoms) {
+    __shared__ int64_t warp_tot[32];
+    __shared__ int64_t running_s;
+    if (threadIdx.x == 0) {
+        running_s = 0;
+        off[0] = 0;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < n_atoms; base += 1024) {
+        const int idx = base + threadIdx.x;
+        int64_t v = idx < n_atoms ? off[idx + 1] : 0;
+        int64_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t n = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += n;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        int64_t warp_base = 0;
+        for (int w = 0; w < warp; ++w) warp_base += warp_tot[w];
+        const int64_t running = running_s;
+        __syncthreads();
+        if (idx < n_atoms) off[idx + 1] = running + warp_base + incl;  // inclusive = offset of a+1
+        if (threadIdx.x == 1023) running_s = running + warp_base + incl;
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------- ffill / bfill
+
+// phase 1: last valid state of every (chunk, atom) segment, in scan direction
+__global__ void __launch_bounds__(256)
+    k_fill_summary(const int32_t *__restrict__ s, Geometry g, int direction,
+                   int32_t *__restrict__ work) {
+    const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= g.n_chunks * g.n_atoms) return;
+    const int64_t c = item / g.n_atoms;
+    const int32_t a = (int32_t)(item - c * g.n_atoms);
+    const int64_t t0 = c * g.f, t1 = min(g.n_frames, t0 + g.f);
+    int32_t last = GD_NOSITE;
+    if (direction > 0) {
+#pragma unroll 4
+        for (int64_t t = t0; t < t1; ++t) {
+            const int32_t v = s[t * g.n_atoms + a];
+            last = v != GD_NOSITE ? v : last;
+        }
+    } else {
+#pragma unroll 4
+        for (int64_t t = t1 - 1; t >= t0; --t) {
+            const int32_t v = s[t * g.n_atoms + a];
+            last = v != GD_NOSITE ? v : last;
+        }
+    }
+    work[c * g.n_atoms + a] = last;
+}
+
+// phase 2: one thread per atom walks the chunk summaries and turns them into carry-ins
+__global__ void __launch_bounds__(128)
+    k_fill_carry(Geometry g, int direction, const int32_t *__restrict__ carry_in,
+                 int32_t *__restrict__ carry_out, int32_t *__restrict__ work) {
+    const int32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= g.n_atoms) return;
+    int32_t carry = carry_in ? carry_in[a] : GD_NOSITE;
+    if (direction > 0) {
+#pragma unroll 8
+        for (int64_t c = 0; c < g.n_chunks; ++c) {
+            const int32_t v = work[c * g.n_atoms + a];
+            work[c * g.n_atoms + a] = carry;
+            carry = v != GD_NOSITE ? v : carry;
+        }
+    } else {
+#pragma unroll 8
+        for (int64_t c = g.n_chunks - 1; c >= 0; --c) {
+            const int32_t v = work[c * g.n_atoms + a];
+            work[c * g.n_atoms + a] = carry;
+            carry = v != GD_NOSITE ? v : carry;
+        }
+    }
+    if (carry_out) carry_out[a] = carry;
+}
+
+// phase 3: apply
+__global__ void __launch_bounds__(256)
+    k_fill_apply(const int32_t *__restrict__ s, Geometry g, int direction,
+                 const int32_t *__restrict__ work, int32_t *__restrict__ out) {
+    const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= g.n_chunks * g.n_atoms) return;
+    const int64_t c = item / g.n_atoms;
+    const int32_t a = (int32_t)(item - c * g.n_atoms);
+    const int64_t t0 = c * g.f, t1 = min(g.n_frames, t0 + g.f);
+    int32_t last = work[c * g.n_atoms + a];
+    if (direction > 0) {
+#pragma unroll 4
+        for (int64_t t = t0; t < t1; ++t) {
+            const int32_t v = s[t * g.n_atoms + a];
+            last = v != GD_NOSITE ? v : last;
+            out[t * g.n_atoms + a] = last;
+        }
+    } else {
+#pragma unroll 4
+        for (int64_t t = t1 - 1; t >= t0; --t) {
+            const int32_t v = s[t * g.n_atoms + a];
+            last = v != GD_NOSITE ? v : last;
+            out[t * g.n_atoms + a] = last;
+        }
+    }
+}
+
+inline unsigned blocks_for(int64_t items, int threads) { return (unsigned)gd_ceil_div(items, threads); }
+
+}  // namespace
+
+extern "C" int64_t gd_events_work_elems(int64_t n_frames, int32_t n_atoms) {
+    if (n_frames <= 0 || n_atoms <= 0) return 16;
+    Geometry g = geometry(n_frames, n_atoms);
+    return g.n_chunks * g.n_atoms + 16;  // + error flag / padding
+}
+
+extern "C" gd_status_t gd_events_count(const int32_t *d_states_outer, const int32_t *d_states_inner,
+                                       int64_t n_frames, int32_t n_atoms,
+                                       const int32_t *d_next_outer, const int32_t *d_next_inner,
+                                       int32_t *d_work, uint8_t *d_changed, void *stream) {
+    GD_REQUIRE(d_states_outer && d_states_inner && d_work && d_changed, GD_ERR_INVALID,
+               "gd_events_count: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_events_count: empty input");
+    GD_REQUIRE((d_next_outer == nullptr) == (d_next_inner == nullptr), GD_ERR_INVALID,
+               "gd_events_count: halo rows must both be given or both be NULL");
+    Geometry g = geometry(n_frames, n_atoms);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    k_events<false><<<blocks_for(items, 256), 256, 0, (cudaStream_t)stream>>>(
+        d_states_outer, d_states_inner, g, d_next_outer, d_next_inner, d_work, d_changed, nullptr,
+        nullptr, 0, nullptr);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_events_scan(int32_t *d_work, int64_t n_frames, int32_t n_atoms,
+                                      const uint8_t *d_changed_global, int64_t *d_atom_offsets,
+                                      int64_t *h_n_events, void *stream) {
+    GD_REQUIRE(d_work && d_changed_global && d_atom_offsets && h_n_events, GD_ERR_INVALID,
+               "gd_events_scan: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_events_scan: empty input");
+    cudaStream_t st = (cudaStream_t)stream;
+    Geometry g = geometry(n_frames, n_atoms);
+    int32_t *err_flag = d_work + g.n_chunks * g.n_atoms;
+    GD_CUDA_CHECK(cudaMemsetAsync(err_flag, 0, sizeof(int32_t), st));
+    k_scan_chunks<<<(unsigned)n_atoms, 256, 0, st>>>(d_work, g.n_chunks, d_changed_global, n_atoms,
+                                                    d_atom_offsets, err_flag);
+    GD_LAUNCH_CHECK();
+    k_scan_atoms<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms);
+    GD_LAUNCH_CHECK();
+    int32_t h_err = 0;
+    GD_CUDA_CHECK(cudaMemcpyAsync(h_n_events, d_atom_offsets + n_atoms, sizeof(int64_t),
+                                  cudaMemcpyDeviceToHost, st));
+    GD_CUDA_CHECK(cudaMemcpyAsync(&h_err, err_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    GD_CUDA_CHECK(cudaStreamSynchronize(st));
+    GD_REQUIRE(h_err == 0, GD_ERR_INNER_CONSTANT,
+               "index -1 is out of bounds for axis 0 with size 0");
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_events_fill(const int32_t *d_states_outer, const int32_t *d_states_inner,
+                                      int64_t n_frames, int32_t n_atoms,
+                                      const int32_t *d_next_outer, const int32_t *d_next_inner,
+                                      const int32_t *d_work, const uint8_t *d_changed_global,
+                                      const int64_t *d_atom_offsets, int64_t frame0,
+                                      int32_t *d_events, void *stream) {
+    GD_REQUIRE(d_states_outer && d_states_inner && d_work && d_changed_global && d_atom_offsets &&
+                   d_events,
+               GD_ERR_INVALID, "gd_events_fill: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_events_fill: empty input");
+    Geometry g = geometry(n_frames, n_atoms);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    k_events<true><<<blocks_for(items, 256), 256, 0, (cudaStream_t)stream>>>(
+        d_states_outer, d_states_inner, g, d_next_outer, d_next_inner,
+        const_cast<int32_t *>(d_work), nullptr, d_changed_global, d_atom_offsets, frame0, d_events);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames, int32_t n_atoms,
+                                      int direction, const int32_t *d_carry_in,
+                                      int32_t *d_carry_out, int32_t *d_work, int32_t *d_out,
+                                      void *stream) {
+    GD_REQUIRE(d_states && d_work && d_out, GD_ERR_INVALID, "gd_fill_states: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_fill_states: empty input");
+    GD_REQUIRE(direction == 1 || direction == -1, GD_ERR_INVALID,
+               "gd_fill_states: direction must be +1 (ffill) or -1 (bfill)");
+    cudaStream_t st = (cudaStream_t)stream;
+    Geometry g = geometry(n_frames, n_atoms);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    k_fill_summary<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work);
+    GD_LAUNCH_CHECK();
+    k_fill_carry<<<blocks_for(n_atoms, 128), 128, 0, st>>>(g, direction, d_carry_in, d_carry_out,
+                                                          d_work);
+    GD_LAUNCH_CHECK();
+    k_fill_apply<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work, d_out);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}

@@ -1,0 +1,271 @@
+/*
+ * gemdat_b200 -- C ABI of the B200-native GEMDAT hot path (libgemdat_b200.so).
+ *
+ * GEMDAT (the reference, pure Python) has no FFI of its own: the seams these
+ * entry points sit behind are private Python functions and the third-party
+ * native code they reach.  Each entry point below names the reference
+ * interface it replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *  - every pointer named d_* is DEVICE memory owned by the caller; h_* is host
+ *    memory.  The library never allocates device memory and never frees
+ *    anything; variable-length tables are two-phase (count -> caller
+ *    allocates -> fill).
+ *  - `stream` is a cudaStream_t passed as void* (0 = legacy default stream).
+ *    Calls are asynchronous on that stream unless stated otherwise.
+ *  - return value: GD_OK (0) or a GD_ERR_* code; gd_last_error() gives a
+ *    thread-local human readable message for the last failing call.
+ *  - NOSITE is -1 everywhere (src/gemdat/transitions.py:27).
+ *  - no CPU fallback exists: without a CUDA device every compute entry point
+ *    returns GD_ERR_CUDA.
+ */
+#ifndef GEMDAT_B200_H
+#define GEMDAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int gd_status_t;
+
+enum {
+    GD_OK = 0,
+    GD_ERR_CUDA = 1,           /* CUDA runtime error (message has the detail)            */
+    GD_ERR_INVALID = 2,        /* bad argument (null pointer, negative size, ...)         */
+    GD_ERR_ALIGNMENT = 3,      /* a device pointer is not aligned as documented           */
+    GD_ERR_TRICLINIC = 4,      /* lattice angles are not all 90 deg in float32  */
+    GD_ERR_CAPACITY = 5,       /* caller-provided buffer too small; needed size returned  */
+    GD_ERR_RADIUS_GT_CUTOFF = 6, /* radius*fraction > max radius: MDAnalysis RuntimeError   */
+    GD_ERR_INNER_CONSTANT = 7, /* transitions.py:451 IndexError (outer changes, inner not) */
+    GD_ERR_NO_EVENTS = 8,      /* transitions.py:470 ValueError (np.vstack of nothing)    */
+    GD_ERR_NO_JUMPS = 9,       /* jumps.py:107-108 ValueError('No jumps found')           */
+    GD_ERR_RANGE = 10          /* volume.py:476-477 AssertionError (coords not in [0,1))  */
+};
+
+const char *gd_last_error(void);
+int gd_version(void);
+/* number of SMs of the current device (148 on B200); <0 on error */
+int gd_sm_count(void);
+
+/* ------------------------------------------------------------------------- *
+ * K1  site-state assignment
+ * replaces: _calculate_atom_states, src/gemdat/transitions.py:736-809, i.e.
+ *   MDAnalysis PeriodicKDTree.set_coords/search_tree (float32 wrap + periodic
+ *   images + scipy cKDTree.query_ball_tree) and the last-write-wins scatter
+ *   (transitions.py:802-807), for the outer (fraction 1.0, :160-165) and the
+ *   inner (:167-172) call in ONE pass.
+ * ------------------------------------------------------------------------- */
+
+/* Build the site search structure ("site grid") on the host.
+ *
+ *  h_lattice      3x3 row-major lattice matrix (Angstrom); must be orthorhombic
+ *                 in the sense MDAnalysis uses (all angles == 90 as float32).
+ *  h_sites_frac   [n_sites,3] fractional site coordinates (Structure.frac_coords)
+ *  h_site_group   [n_sites] index of the site_radius dict entry the site belongs
+ *                 to, in dict order (later groups overwrite earlier ones,
+ *                 transitions.py:785-807); -1 = site carries no listed label.
+ *  h_group_radius [n_groups] site_radius[label] (Angstrom)
+ *  h_group_inner  [n_groups] site_inner_fraction[label]
+ *  h_blob/cap     output buffer (host) and its capacity in bytes.  On
+ *                 GD_ERR_CAPACITY *needed holds the required size; call again.
+ *
+ * The blob is position independent: copy it to the device verbatim
+ * (256-byte aligned) and hand that pointer to gd_site_states.
+ */
+gd_status_t gd_sitegrid_build(const double *h_lattice, const double *h_sites_frac,
+                              const int32_t *h_site_group, int32_t n_sites,
+                              const double *h_group_radius, const double *h_group_inner,
+                              int32_t n_groups, void *h_blob, size_t cap, size_t *needed);
+
+/* One pass over all atom-frames.
+ *
+ *  d_pos_frac     [n_atom_frames,3] float64 fractional positions, C order
+ *                 ([T,A,3] flattened; Trajectory.positions); 16-byte aligned.
+ *  d_blob         device copy of the gd_sitegrid_build blob
+ *  d_states_outer [n_atom_frames] int32 site index or -1  (Transitions.states)
+ *  d_states_inner [n_atom_frames] int32                   (Transitions.inner_states)
+ *  d_visited      [2*n_sites] uint8, zero-initialised by the caller: set to 1 for
+ *                 every site that contains at least one atom-frame (outer: first
+ *                 n_sites bytes, inner: next n_sites).  Feeds the reference's
+ *                 "No floating species in range" warning (transitions.py:798-800)
+ *                 and the integer_remap quirk (gd_remap_states).
+ *  d_band_counts  [4] uint64, zero-initialised: atom-frames with | |d|-r | < 1e-12 A
+ *                 (outer, inner) and < 4e-6 A (outer, inner) for some site; the
+ *                 float32 staging of the reference makes the latter band the one
+ *                 where a pure-fp64 method would disagree.  May be NULL.
+ */
+gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_atom_frames, const void *d_blob,
+                           const void *h_blob, int32_t *d_states_outer, int32_t *d_states_inner,
+                           uint8_t *d_visited, unsigned long long *d_band_counts, void *stream);
+
+/* integer_remap quirk (src/gemdat/utils.py:101-125 via transitions.py:804-805):
+ * d_lut [n_sites] int32 maps the natural site index to the index the reference
+ * reports; applied in place.  Only needed when a labelled group has a site that
+ * was never visited. */
+gd_status_t gd_remap_states(int32_t *d_states, int64_t n, const int32_t *d_lut, int32_t n_sites,
+                            void *stream);
+
+/* int32 -> int64 widening for the host-facing arrays (the reference returns int64). */
+gd_status_t gd_widen_i32_i64(const int32_t *d_in, int64_t *d_out, int64_t n, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * K2  transition events, forward / backward fill
+ * replaces: _calculate_transition_events, src/gemdat/transitions.py:413-482;
+ *           ffill / bfill, src/gemdat/utils.py:59-98 (Transitions.states_prev/next,
+ *           transitions.py:254-278)
+ * ------------------------------------------------------------------------- */
+
+/* Scratch sizing: number of int32 elements gd_events_count needs in d_work. */
+int64_t gd_events_work_elems(int64_t n_frames, int32_t n_atoms);
+
+/* Phase 1.  d_states_* are [n_frames,n_atoms] int32.  d_next_outer/inner
+ * ([n_atoms], may be NULL) is the first row of the FOLLOWING frame shard
+ * (multi-GPU halo); NULL means this shard ends the trajectory.
+ * d_changed [2*n_atoms] uint8 (zero-initialised by caller): outer / inner state of
+ * the atom changes somewhere in this shard.  Asynchronous. */
+gd_status_t gd_events_count(const int32_t *d_states_outer, const int32_t *d_states_inner,
+                            int64_t n_frames, int32_t n_atoms, const int32_t *d_next_outer,
+                            const int32_t *d_next_inner, int32_t *d_work, uint8_t *d_changed,
+                            void *stream);
+
+/* Phase 2.  d_changed_global is d_changed OR-reduced over all shards (same
+ * buffer on one GPU).  Computes row offsets, returns the number of events of
+ * this shard in *h_n_events and the status of the reference's error paths
+ * (GD_ERR_INNER_CONSTANT, GD_ERR_NO_EVENTS is left to the caller because it
+ * is a whole-trajectory property).  d_atom_offsets [n_atoms+1] int64 receives
+ * the first row of every atom.  Synchronises the stream. */
+gd_status_t gd_events_scan(int32_t *d_work, int64_t n_frames, int32_t n_atoms,
+                           const uint8_t *d_changed_global, int64_t *d_atom_offsets,
+                           int64_t *h_n_events, void *stream);
+
+/* Phase 3.  d_events [n_events,6] int32, reference column order
+ * (atom index, start site, destination site, start inner site,
+ *  destination inner site, time), sorted by atom then time; `frame0` is added
+ * to the time column (global frame index of the shard's first frame). */
+gd_status_t gd_events_fill(const int32_t *d_states_outer, const int32_t *d_states_inner,
+                           int64_t n_frames, int32_t n_atoms, const int32_t *d_next_outer,
+                           const int32_t *d_next_inner, const int32_t *d_work,
+                           const uint8_t *d_changed_global, const int64_t *d_atom_offsets,
+                           int64_t frame0, int32_t *d_events, void *stream);
+
+/* ffill (direction=+1, states_prev) / bfill (direction=-1, states_next) along the
+ * frame axis.  d_carry_in [n_atoms] (may be NULL) is the last valid state before
+ * (after, for bfill) this shard; d_carry_out [n_atoms] (may be NULL) receives the
+ * last valid state at the end of the shard.  d_work: gd_events_work_elems ints. */
+gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames, int32_t n_atoms, int direction,
+                           const int32_t *d_carry_in, int32_t *d_carry_out, int32_t *d_work,
+                           int32_t *d_out, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * K3  transitions -> jumps
+ * replaces: _generic_transitions_to_jumps, src/gemdat/jumps.py:24-119 (the
+ *           pandas groupby/iterrows state machine)
+ * ------------------------------------------------------------------------- */
+
+/* d_events [n_events,6] int32 sorted by atom then time, d_atom_offsets
+ * [n_atoms+1] int64.  n_frames_total = len(transitions.trajectory) (jumps.py:39).
+ * d_jump_counts [n_atoms+1] int64 scratch.  Writes *h_n_jumps; synchronises. */
+gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_atom_offsets, int32_t n_atoms,
+                           int64_t n_frames_total, int64_t minimal_residence,
+                           int64_t *d_jump_counts, int64_t *h_n_jumps, void *stream);
+
+/* d_jumps [n_jumps,6] int32: atom index, start site, destination site,
+ * start time, stop time, residence_time (jumps.py:110-119). */
+gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets, int32_t n_atoms,
+                          int64_t n_frames_total, int64_t minimal_residence,
+                          const int64_t *d_jump_counts, int32_t *d_jumps, void *stream);
+
+/* (start, destination) count matrix: _calculate_transitions_matrix,
+ * src/gemdat/transitions.py:812-834.  d_rows [n_rows,row_stride] int32 with the
+ * start site in column col_start and the destination in col_dest; d_scratch
+ * [(n_sites+1)^2] uint64 zero-initialised by the caller; d_matrix [n_sites,n_sites]
+ * int64 (fully written).  Index -1 (NOSITE) aliases n_sites-1 and, as with
+ * numpy's fancy assignment of np.unique rows, the last source pair wins. */
+gd_status_t gd_pair_matrix(const int32_t *d_rows, int64_t n_rows, int32_t row_stride,
+                           int32_t col_start, int32_t col_dest, int32_t n_sites,
+                           unsigned long long *d_scratch, long long *d_matrix, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * K0  displacement / unwrap
+ * replaces: pymatgen Trajectory.to_displacements via Trajectory.displacements
+ *           (src/gemdat/trajectory.py:182-193), cumulative_displacements
+ *           (:705-713), distances_from_base_position (:715-730), _lengths (:40-60)
+ * ------------------------------------------------------------------------- */
+
+/* d_pos_frac [n_frames,n_atoms,3] wrapped fractional positions.
+ * d_prev_row [n_atoms,3] last row of the preceding shard (NULL: first shard, d[0]=0).
+ * d_base_winding [n_atoms,3] int32 lattice translations accumulated before this
+ *   shard (NULL = 0); d_base_pos [n_atoms,3] positions of GLOBAL frame 0 (NULL:
+ *   row 0 of this shard).
+ * Outputs (any may be NULL): d_cum_frac [n_frames,n_atoms,3] cumulative fractional
+ *   displacement; d_cum_cart same in Angstrom (cum_frac @ lattice); d_dist
+ *   [n_atoms,n_frames] distance from the base position (note: atom-major, as the
+ *   reference returns it); d_winding_out [n_atoms,3] int32 winding at shard end.
+ * d_work: n_chunks*n_atoms*3 int32, n_chunks = gd_unwrap_chunks(n_frames, n_atoms). */
+int64_t gd_unwrap_chunks(int64_t n_frames, int32_t n_atoms);
+gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                      const double *h_lattice, const double *d_prev_row,
+                      const int32_t *d_base_winding, const double *d_base_pos, int32_t *d_work,
+                      double *d_cum_frac, double *d_cum_cart, double *d_dist,
+                      int32_t *d_winding_out, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * K4  all-lag mean squared displacement
+ * replaces: Trajectory.mean_squared_displacement, src/gemdat/trajectory.py:896-933
+ *           (numpy FFT autocorrelation); computed here by direct summation.
+ * ------------------------------------------------------------------------- */
+
+/* [n_frames,n_atoms,3] -> component-major per atom [n_atoms,3,n_frames] (the layout
+ * gd_msd_direct streams). */
+gd_status_t gd_transpose_soa(const double *d_in, int64_t n_frames, int32_t n_atoms, double *d_out,
+                             void *stream);
+
+/* d_soa [n_atoms,3,n_frames] unwrapped Cartesian displacement (gd_unwrap d_cum_cart
+ * through gd_transpose_soa).  Lags lag0 .. lag0+n_lags-1.  d_msd [n_atoms,n_lags]
+ * float64: msd[a,j] = mean_t |r[t+lag0+j]-r[t]|^2 (0 for lag 0). */
+gd_status_t gd_msd_direct(const double *d_soa, int64_t n_frames, int32_t n_atoms, int64_t lag0,
+                          int64_t n_lags, double *d_msd, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * K5  density histogram
+ * replaces: trajectory_to_volume, src/gemdat/volume.py:449-509
+ *           (np.digitize against np.linspace edges + np.unique(axis=0) counting)
+ * ------------------------------------------------------------------------- */
+
+/* nedges[3] = int(1 + length // resolution) per axis (volume.py:482-484); the
+ * grid has (nedges-1) voxels per axis.  d_grid [(nx-1)*(ny-1)*(nz-1)] uint32,
+ * accumulated into (caller zero-initialises).  d_range_flag [1] int32 is set to 1
+ * if any coordinate is outside [0,1) (the reference asserts). */
+gd_status_t gd_density(const double *d_pos_frac, int64_t n_atom_frames, const int32_t *h_nedges,
+                       uint32_t *d_grid, int32_t *d_range_flag, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * helpers
+ * ------------------------------------------------------------------------- */
+
+/* minimum-image distance matrix between two fractional coordinate sets
+ * (pymatgen Lattice.get_all_distances as used at transitions.py:543,595 and
+ * jumps.py:203).  d_out [n1,n2] float64. */
+gd_status_t gd_pbc_distances(const double *h_lattice, const double *d_frac1, int32_t n1,
+                             const double *d_frac2, int32_t n2, double *d_out, void *stream);
+
+/* Synthetic trajectory generator (bench / tests only; see gemdat_b200/synth.py for
+ * the recipe, which numpy replays bit-identically for any frame window).
+ * d_centre/d_delta [n_atoms,n_epochs,3], frames [frame0, frame0+n_frames). */
+gd_status_t gd_synth_positions(const double *d_centre, const double *d_delta, int32_t n_atoms,
+                               int32_t n_epochs, int32_t epoch_len, int32_t knot_len,
+                               const double *h_noise_scale, uint64_t seed, int64_t frame0,
+                               int64_t n_frames, double *d_pos_frac, void *stream);
+
+/* fp64 pipe micro-benchmark: runs `iters` dependent DFMA per thread on a full
+ * grid and returns the achieved DFMA/s in *h_dfma_per_s (roofline denominator
+ * for the fp64-bound kernels; MEASURED_PEAKS.json has no fp64 entry). */
+gd_status_t gd_fp64_peak(int64_t iters, double *h_dfma_per_s, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GEMDAT_B200_H */
