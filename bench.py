@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- site-assignment + jump throughput (atom-frames/s) of the hot path.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm
+    python bench.py --impl reference --gpus N --steps K ...   # CPU reference arm (oracle port)
+
+A step = one pass of the hot path (K1 site states, K2 events, K3 jumps) over the
+whole synthetic trajectory, resident in HBM (``value``), and through the public
+Python API with pinned HOST buffers incl. host<->device copies (``e2e``).
+Workload at N=1: BASELINE config 3 (LLZO-like, 1008 Li x 10^6 frames, 2160 sites);
+at N>1 the frame axis of the same trajectory is sharded over the ranks.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = 'site_assignment_plus_jumps_atom_frames_per_s'
+UNIT = 'atom-frames/s'
+RADIUS, INNER, MIN_RES = 0.6, 0.5, 3
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--frames', type=int, default=1_000_000, help='total frames of the C3 trajectory')
+    ap.add_argument('--e2e-frames', type=int, default=100_000, help='frames per e2e step (host buffers)')
+    ap.add_argument('--cpu-frames', type=int, default=2_000, help='frames of the CPU baseline sample')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------ clocks
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+             'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+             'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+        self._thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(
+                    ['nvidia-smi', f'--id={self.index}', f'--query-gpu={self.QUERY}',
+                     '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(',')]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._thread.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unavailable']}
+        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(s[2 + k].lower().startswith('active') for s in self.samples)]
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None,
+                'sm_max_mhz': int(self.samples[0][1]) if self.samples[0][1].isdigit() else None,
+                'reasons': reasons, 'samples': len(self.samples)}
+
+
+# ------------------------------------------------------------------------------ CPU arm
+
+
+def cpu_reference_pass(rec, frame0, n_frames):
+    """The reference's CPU path on one window: restated oracle (scipy cKDTree ball query,
+    two calls like transitions.py:160-172), events, jumps.  Returns seconds."""
+    import warnings
+
+    from oracle import events as oevents
+    from oracle import jumps as ojumps
+    from oracle import states as ostates
+
+    pos = rec.host_positions(frame0, n_frames)
+    kw = dict(site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels, positions=pos,
+              lattice_matrix=rec.lattice, site_radius={'': RADIUS})
+    t0 = time.perf_counter()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        so = ostates.calculate_atom_states(**kw, site_inner_fraction={'': 1.0})
+        si = ostates.calculate_atom_states(**kw, site_inner_fraction={'': INNER})
+    ev = oevents.calculate_transition_events(so, si)
+    try:
+        ojumps.transitions_to_jumps(ev, n_frames, MIN_RES)
+    except ValueError:
+        pass
+    return time.perf_counter() - t0, pos.shape[0] * pos.shape[1]
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    from gemdat_b200 import synth  # recipe only (numpy); no GPU work in this arm
+
+    rec = synth.config_c3(n_frames=args.frames)
+    times, units = [], 0
+    for i in range(args.warmup + args.steps):
+        dt, units = cpu_reference_pass(rec, (i * args.cpu_frames) % max(1, args.frames - args.cpu_frames),
+                                       args.cpu_frames)
+        if i >= args.warmup:
+            times.append(dt)
+    value = units * len(times) / sum(times)
+    sample = f'{args.cpu_frames} frames x {rec.n_atoms} atoms of C3 per step, oracle port (numpy + scipy cKDTree)'
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * sum(times) / len(times),
+        'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64',
+        'data': 'synthetic', 'config': workload_config(rec, args),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': 1, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(rec, args):
+    return {
+        'workload': f'C3 synthetic LLZO-like garnet {rec.n_atoms} Li x {args.frames} frames, '
+                    f'{len(rec.sites)} sites, site_radius={RADIUS}, inner_fraction={INNER}, '
+                    f'minimal_residence={MIN_RES}',
+        'frame_sharding': f'{args.gpus} rank(s), contiguous frame blocks',
+        'l2': 'inputs (24 B/atom-frame) exceed the 126 MB L2 by >100x; no explicit flush',
+    }
+
+
+# ------------------------------------------------------------------------------ GPU arm
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from gemdat_b200 import _lib, synth
+    from gemdat_b200.pipeline import HotPath
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
+    rec = synth.config_c3(n_frames=args.frames)
+    n_atoms = rec.n_atoms
+    # contiguous frame shard of this rank
+    f0 = args.frames * rank // world
+    f1 = args.frames * (rank + 1) // world
+    pos = rec.device_positions(f0, f1 - f0)
+    hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=n_atoms, site_radius=RADIUS,
+                 site_inner_fraction=INNER, minimal_residence=MIN_RES, n_frames_total=args.frames,
+                 frame0=f0, world=world, rank=rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        res = hp.run(pos)
+    barrier()
+    k1_ms = []
+    sampler = ClockSampler(local_rank)
+    with sampler:
+        barrier()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            res = hp.run(pos)
+            k1_ms.append(hp.last_k1_events)
+        e1.record()
+        barrier()
+    total_ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([total_ms], device='cuda', dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    k1_avg_ms = float(np.mean([a.elapsed_time(b) for a, b in k1_ms]))
+    ms_per_step = total_ms / args.steps
+    n_af_total = args.frames * n_atoms
+    value = n_af_total / (ms_per_step * 1e-3)
+
+    line = None
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.loads((ROOT / 'MEASURED_PEAKS.json').read_text())
+        except Exception:
+            pass
+        peak = float(peaks.get('hbm_gbs', 6650.0))
+        k1_bytes = 32.0 * (f1 - f0) * n_atoms
+        achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': workload_config(rec, args),
+            'roofline': {'bound': 'hbm', 'kernel': 'k_site_states', 'achieved': achieved, 'peak': peak,
+                         'unit': 'GB/s', 'frac': achieved / peak, 'traffic': None,
+                         'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback',
+                         'algorithmic_bytes_per_atom_frame': 32, 'launch_ms': k1_avg_ms},
+            'gpu_launches': hp.launches_per_run * args.steps,
+            'clocks': sampler.summary(),
+            'results': {'n_events': int(res['n_events']), 'n_jumps': int(res['n_jumps'])},
+        }
+
+    # ---- e2e through the public API with pinned host buffers (rank-local window)
+    from gemdat_b200 import Trajectory
+
+    e2e_frames = min(args.e2e_frames, f1 - f0)
+    host = torch.empty((e2e_frames, n_atoms, 3), dtype=torch.float64, pin_memory=True)
+    host.copy_(pos[:e2e_frames])
+    torch.cuda.synchronize()
+    host_np = host.numpy()
+    e2e_times = []
+    for i in range(args.warmup + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        traj = Trajectory(species=['Li'] * n_atoms, coords=host_np, lattice=rec.lattice, time_step=2e-15)
+        tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=RADIUS, site_inner_fraction=INNER)
+        jumps = tr.jumps(minimal_residence=MIN_RES)
+        states, inner_states = tr.states, tr.inner_states  # device -> host, int64 like the reference
+        n_j = jumps.n_jumps
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            e2e_times.append(dt)
+    e2e_dt = float(np.mean(e2e_times))
+    if world > 1:
+        t = torch.tensor([e2e_dt], device='cuda', dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_dt = float(t.item())
+    if rank == 0:
+        line['e2e'] = {
+            'value': world * e2e_frames * n_atoms / e2e_dt, 'unit': UNIT,
+            'h2d_bytes_per_step': int(host_np.nbytes),
+            'd2h_bytes_per_step': int(states.nbytes + inner_states.nbytes + tr.events.to_numpy().nbytes
+                                      + jumps.data.to_numpy().nbytes),
+            'frames_per_step': e2e_frames, 'ms_per_step': 1e3 * e2e_dt,
+            'api': 'Trajectory.transitions_between_sites + Transitions.jumps (numpy in, numpy/pandas out)',
+        }
+        if not args.no_cpu_baseline:
+            t_cpu, units, reps = 0.0, 0, 0
+            while t_cpu < 10.0 and reps < 4:
+                dt, u = cpu_reference_pass(rec, reps * args.cpu_frames, args.cpu_frames)
+                t_cpu += dt
+                units += u
+                reps += 1
+            line['cpu_baseline'] = {
+                'value': units / t_cpu, 'unit': UNIT, 'cores': 1, 'kind': 'port',
+                'sample': f'{reps} x {args.cpu_frames} frames x {n_atoms} atoms of C3 '
+                          f'({t_cpu:.1f} s; numpy + scipy cKDTree oracle, host has {os.cpu_count()} cores)',
+            }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

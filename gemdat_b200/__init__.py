@@ -1,0 +1,30 @@
+"""gemdat_b200 -- B200-native implementation of GEMDAT's data-parallel hot path.
+
+Site assignment -> transition events -> jumps, the displacement / MSD path and the
+density histogram, behind GEMDAT's own Python API.  All arithmetic runs in
+hand-written sm_100a CUDA kernels (``csrc/``, C ABI in ``include/gemdat_b200.h``);
+there is no CPU fallback.
+"""
+
+from __future__ import annotations
+
+from . import _lib  # fails loudly if libgemdat_b200.so is missing
+from .jumps import Jumps
+from .lattice import FloatWithUnit, Lattice, Sites
+from .metrics import TrajectoryMetrics
+from .trajectory import Trajectory
+from .transitions import SiteRadius, Transitions
+from .volume import Volume, trajectory_to_volume
+
+__version__ = '0.1.0'
+__all__ = [
+    'Jumps',
+    'Lattice',
+    'Sites',
+    'SiteRadius',
+    'Trajectory',
+    'TrajectoryMetrics',
+    'Transitions',
+    'Volume',
+    'trajectory_to_volume',
+]

@@ -254,6 +254,17 @@ __global__ void __launch_bounds__(256)
     }
 }
 
+// one block per atom: copy this shard's rows of the atom to their place in the merged table
+__global__ void __launch_bounds__(128)
+    k_merge_rows(const int32_t *__restrict__ src, const int64_t *__restrict__ src_off,
+                 const int64_t *__restrict__ dst_start, int32_t *__restrict__ dst) {
+    const int a = blockIdx.x;
+    const int64_t r0 = src_off[a], n = (src_off[a + 1] - r0) * 6;
+    const int32_t *s = src + r0 * 6;
+    int32_t *d = dst + dst_start[a] * 6;
+    for (int64_t k = threadIdx.x; k < n; k += blockDim.x) d[k] = s[k];
+}
+
 inline unsigned blocks_for(int64_t items, int threads) { return (unsigned)gd_ceil_div(items, threads); }
 
 }  // namespace
@@ -343,6 +354,17 @@ extern "C" gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames,
                                                           d_work);
     GD_LAUNCH_CHECK();
     k_fill_apply<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work, d_out);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom_offsets,
+                                       const int64_t *d_dst_start, int32_t n_atoms,
+                                       int32_t *d_dst_rows, void *stream) {
+    GD_REQUIRE(d_src_atom_offsets && d_dst_start && d_dst_rows && n_atoms > 0, GD_ERR_INVALID,
+               "gd_events_merge: bad argument");
+    k_merge_rows<<<(unsigned)n_atoms, 128, 0, (cudaStream_t)stream>>>(
+        d_src_rows, d_src_atom_offsets, d_dst_start, d_dst_rows);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

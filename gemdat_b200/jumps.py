@@ -1,0 +1,137 @@
+"""Jumps: host-side mirror of reference src/gemdat/jumps.py for the hot path.
+
+``Jumps(transitions, conversion_method=..., minimal_residence=0)`` (:123-151) keeps the
+reference's plug-in hook: any ``Callable[[Transitions, minimal_residence=int],
+DataFrame]``.  The default method is the CUDA state machine (``gd_jumps_count`` /
+``gd_jumps_fill``, K3) standing in for the pandas ``groupby``/``iterrows`` loop of
+``_generic_transitions_to_jumps`` (:24-119).  ``matrix`` (:212-221) and
+``jump_diffusivity`` (:185-210) follow the reference formulae.  Collective jumps,
+rates, activation energies and graphs are consumers of this table and out of scope
+(DESIGN.md "next rows").
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from collections import Counter
+from itertools import product
+from typing import Callable
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import _device as dv
+from . import _lib
+from .caching import weak_lru_cache
+from .lattice import FloatWithUnit, site_arrays
+from .transitions import Transitions, _pair_matrix_device
+
+ANGSTROM = 1e-10  # scipy.constants.angstrom
+
+JUMP_COLUMNS = [
+    'atom index',
+    'start site',
+    'destination site',
+    'start time',
+    'stop time',
+    'residence_time',
+]
+
+
+def _jumps_device(transitions: Transitions, minimal_residence: int) -> torch.Tensor:
+    """int32 [J, 6] device table; raises ValueError('No jumps found') like jumps.py:107-108."""
+    ev = transitions.d_events
+    n_atoms = ev.n_atoms
+    n_frames_total = len(transitions.trajectory)  # jumps.py:39
+    lib = _lib.lib
+    counts = dv.empty((n_atoms + 1,), torch.int64)
+    n_jumps = C.c_int64(0)
+    s = dv.stream_ptr()
+    _lib.check(lib.gd_jumps_count(dv.ptr(ev.rows), dv.ptr(ev.atom_offsets), n_atoms, n_frames_total,
+                                  int(minimal_residence), dv.ptr(counts), C.byref(n_jumps), s))
+    if n_jumps.value == 0:
+        raise ValueError('No jumps found')
+    out = dv.empty((n_jumps.value, 6), torch.int32)
+    _lib.check(lib.gd_jumps_fill(dv.ptr(ev.rows), dv.ptr(ev.atom_offsets), n_atoms, n_frames_total,
+                                 int(minimal_residence), dv.ptr(counts), dv.ptr(out), s))
+    return out
+
+
+def _generic_transitions_to_jumps(transitions: Transitions, *, minimal_residence: int = 0) -> pd.DataFrame:
+    """Drop-in for jumps.py:24-119."""
+    table = _jumps_device(transitions, minimal_residence)
+    transitions._dev['jumps'] = table
+    return pd.DataFrame(data=dv.to_host(table).astype(np.int64), columns=JUMP_COLUMNS)
+
+
+class Jumps:
+    def __init__(
+        self,
+        transitions: Transitions,
+        *,
+        conversion_method: Callable[..., pd.DataFrame] = _generic_transitions_to_jumps,
+        minimal_residence: int = 0,
+    ):
+        self.transitions = transitions
+        self.trajectory = transitions.diff_trajectory
+        self.sites = transitions.sites
+        self.conversion_method = conversion_method
+        self.data = conversion_method(transitions, minimal_residence=minimal_residence)
+        self.minimal_residence = minimal_residence
+
+    @property
+    def n_jumps(self) -> int:
+        return len(self.data)
+
+    @property
+    def n_floating(self) -> int:
+        return len(self.trajectory.species)
+
+    @property
+    def site_pairs(self) -> list[tuple[str, str]]:
+        _, labels, _ = site_arrays(self.sites)
+        return list(product(labels, repeat=2))
+
+    @property
+    def jump_names(self) -> list[str]:
+        return ['->'.join(key) for key in self.site_pairs]
+
+    @weak_lru_cache()
+    def jump_diffusivity(self, dimensions: int) -> float:
+        """jumps.py:185-210: sum(pdist^2 * matrix) * A^2 / (2 d n_floating total_time), m^2/s."""
+        frac, _, _ = site_arrays(self.sites)
+        pdist = self.trajectory.get_lattice().get_all_distances(frac, frac)
+        jump_diff = np.sum(pdist**2 * self.matrix())
+        jump_diff *= ANGSTROM**2 / (2 * dimensions * self.n_floating * self.trajectory.total_time)
+        return FloatWithUnit(jump_diff, 'm^2 s^-1')
+
+    @weak_lru_cache()
+    def matrix(self) -> np.ndarray:
+        """jumps.py:212-221: [n_sites, n_sites] jump counts."""
+        pairs = np.ascontiguousarray(
+            self.data[['start site', 'destination site']].to_numpy(dtype=np.int32)
+        )
+        rows = dv.to_device(pairs) if len(pairs) else None
+        return _pair_matrix_device(rows, len(pairs), 2, 0, 1, self.transitions.n_sites)
+
+    @weak_lru_cache()
+    def counter(self) -> Counter:
+        """jumps.py:310-324: jump counts keyed by (start label, destination label)."""
+        _, labels, _ = site_arrays(self.sites)
+        out: Counter = Counter()
+        for (i, j), val in self._counter().items():
+            out[labels[i], labels[j]] += val
+        return out
+
+    @weak_lru_cache()
+    def _counter(self) -> Counter:
+        return Counter(zip(self.data['start site'], self.data['destination site']))
+
+    def split(self, n_parts: int) -> list['Jumps']:
+        """jumps.py:412-433."""
+        return [
+            Jumps(part, conversion_method=self.conversion_method,
+                  minimal_residence=self.minimal_residence)
+            for part in self.transitions.split(n_parts)
+        ]

@@ -1,0 +1,71 @@
+"""TrajectoryMetrics: the displacement-derived scalars on the hot path.
+
+Mirror of reference src/gemdat/metrics.py:21-231 for ``speed`` (:35-47),
+``tracer_diffusivity`` (:76-97), ``amplitudes`` (:209-231), ``vibration_amplitude``
+(:190-207) and ``particle_density`` (:49-62).  The per-frame distances come from the K0
+kernel (``gd_unwrap``) instead of the reference's Python loop over frames; the
+amplitude run-length bookkeeping is O(sign flips) host work on the returned array.
+Attempt frequency, conductivity, Haven ratio and the Arrhenius helpers are out of
+scope (DESIGN.md "next rows").
+"""
+
+from __future__ import annotations
+
+import numpy as np
+
+from .caching import weak_lru_cache
+from .lattice import FloatWithUnit
+
+ANGSTROM = 1e-10
+
+
+class TrajectoryMetrics:
+    def __init__(self, trajectory):
+        self.trajectory = trajectory
+
+    @weak_lru_cache()
+    def _distances(self) -> np.ndarray:
+        return self.trajectory.distances_from_base_position()
+
+    @weak_lru_cache()
+    def speed(self) -> np.ndarray:
+        """metrics.py:35-47: change of the distance from the base position per step, [A, T]."""
+        return np.diff(self._distances(), prepend=0)
+
+    @weak_lru_cache()
+    def particle_density(self) -> FloatWithUnit:
+        volume_m3 = self.trajectory.get_lattice().volume * ANGSTROM**3
+        return FloatWithUnit(len(self.trajectory.species) / volume_m3, 'm^-3')
+
+    @weak_lru_cache()
+    def tracer_diffusivity(self, *, dimensions: int = 3) -> FloatWithUnit:
+        """metrics.py:76-97: mean |r(T-1)-r(0)|^2 / (2 d total_time), m^2/s.
+
+        Only the final frame matters, so this reads the winding totals of K0 and never
+        materialises the [A, T] distance array the reference builds.
+        """
+        msd = float(np.mean(self.trajectory.final_displacement_sq()))
+        tracer = (msd * ANGSTROM**2) / (2 * dimensions * self.trajectory.total_time)
+        return FloatWithUnit(tracer, 'm^2 s^-1')
+
+    @weak_lru_cache()
+    def amplitudes(self) -> np.ndarray:
+        """metrics.py:209-231: sums of ``speed`` over runs of equal sign.
+
+        The reference splits each atom's speed at every sign flip except the first and
+        the last one (``splits[1:-1]``) and sums each piece.
+        """
+        out = []
+        for row in self.speed():
+            signs = np.sign(row)
+            flips = np.nonzero(signs != np.roll(signs, shift=-1))[0]
+            cuts = flips[1:-1] + 1
+            starts = np.concatenate([[0], cuts])
+            if len(row):
+                out.append(np.add.reduceat(row, starts))
+        return np.concatenate(out) if out else np.zeros(0)
+
+    @weak_lru_cache()
+    def vibration_amplitude(self) -> FloatWithUnit:
+        """metrics.py:190-207: standard deviation of the amplitudes, Angstrom."""
+        return FloatWithUnit(np.std(self.amplitudes()), 'ang')

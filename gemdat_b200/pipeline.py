@@ -1,0 +1,189 @@
+"""Device-resident, frame-sharded run of the hot path (K1 -> K2 -> K3).
+
+One process per GPU; each rank owns a contiguous block of frames.  K1 needs no
+communication.  K2 needs the first state row of the following shard (halo) and the
+OR of the per-atom "state changes at all" flags; the compacted event tables are
+all-gathered and merged per atom, after which every rank holds the whole table and
+runs K3 on it.  All exchanges are O(n_atoms) or O(n_events) and go through
+``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in the CPU tests of the
+host logic).  The single-GPU public API (``Trajectory.transitions_between_sites``) runs
+the same kernels through ``gemdat_b200.transitions``.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import warnings
+
+import numpy as np
+import torch
+
+from . import _device as dv
+from . import _lib
+from .lattice import site_arrays
+from .transitions import SiteGrid, _radius_to_dict
+
+
+def merge_plan(counts: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
+    """Per-atom placement of per-shard event rows in the merged (atom, time)-sorted table.
+
+    ``counts`` [n_shards, n_atoms] rows per shard and atom.  Returns ``(atom_offsets
+    [n_atoms + 1], dst_start [n_shards, n_atoms])``: shard ``r``'s rows of atom ``a`` start at
+    ``dst_start[r, a]`` -- after all rows of atoms < a and after earlier shards' rows of a.
+    """
+    counts = np.asarray(counts, dtype=np.int64)
+    per_atom = counts.sum(axis=0)
+    atom_offsets = np.concatenate([[0], np.cumsum(per_atom)])
+    before = np.cumsum(counts, axis=0) - counts
+    return atom_offsets, atom_offsets[:-1][None, :] + before
+
+
+class HotPath:
+    def __init__(self, *, sites, lattice, n_atoms: int, site_radius, site_inner_fraction=1.0,
+                 minimal_residence: int = 0, n_frames_total: int, frame0: int = 0,
+                 world: int = 1, rank: int = 0, group=None):
+        frac, labels, _ = site_arrays(sites)
+        r, f = _radius_to_dict(site_radius, site_inner_fraction)
+        self.radius = r
+        self.grid = SiteGrid(lattice_matrix=lattice, site_frac=frac, site_labels=labels,
+                             site_radius=r, site_inner_fraction=f)
+        self.n_atoms = n_atoms
+        self.n_sites = len(frac)
+        self.minimal_residence = int(minimal_residence)
+        self.n_frames_total = int(n_frames_total)
+        self.frame0 = int(frame0)
+        self.world, self.rank, self.group = world, rank, group
+        self.launches_per_run = 0
+        self.last_k1_events = None
+        self._buf = {}
+
+    # ------------------------------------------------------------------ helpers
+    def _dist(self):
+        import torch.distributed as dist
+
+        return dist
+
+    def _tensor(self, name, shape, dtype):
+        t = self._buf.get(name)
+        if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
+            t = dv.empty(shape, dtype)
+            self._buf[name] = t
+        return t
+
+    def _all_gather(self, t: torch.Tensor) -> torch.Tensor:
+        out = dv.empty((self.world,) + tuple(t.shape), t.dtype)
+        self._dist().all_gather_into_tensor(out, t.contiguous(), group=self.group)
+        return out
+
+    # ------------------------------------------------------------------ the pass
+    def run(self, pos: torch.Tensor) -> dict:
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+        assert n_atoms == self.n_atoms
+        launches = 0
+        outer = self._tensor('outer', (n_frames, n_atoms), torch.int32)
+        inner = self._tensor('inner', (n_frames, n_atoms), torch.int32)
+        visited = self._tensor('visited', (2 * self.n_sites,), torch.uint8)
+        band = self._tensor('band', (4,), torch.int64)
+        visited.zero_()
+        band.zero_()
+
+        # ---- K1
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.gd_site_states(dv.ptr(pos), n_frames * n_atoms, dv.ptr(self.grid.d_blob),
+                                      self.grid.h_blob.ctypes.data, dv.ptr(outer), dv.ptr(inner),
+                                      dv.ptr(visited), dv.ptr(band), s))
+        e1.record()
+        self.last_k1_events = (e0, e1)
+        launches += 1
+
+        if self.world > 1:
+            self._dist().all_reduce(visited, op=self._dist().ReduceOp.MAX, group=self.group)
+        vis = dv.to_host(visited).astype(bool).reshape(2, self.n_sites)
+        for arr, v in ((outer, vis[0]), (inner, vis[1])):
+            for label, key in zip(self.grid.group_labels, self.grid.group_keys):
+                if not (v.any() if key is None else v[key].any()):
+                    radius = self.radius[label]
+                    warnings.warn(f'No floating species in range of {label} ({radius=})', stacklevel=2)
+            lut = self.grid.remap_lut(v)
+            if lut is not None:
+                d_lut = dv.to_device(lut)
+                _lib.check(lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut), self.n_sites, s))
+                launches += 1
+
+        # ---- K2
+        next_o = next_i = None
+        if self.world > 1:
+            rows = self._all_gather(torch.stack([outer[0], inner[0]]))  # [W, 2, A]
+            if self.rank + 1 < self.world:
+                next_o, next_i = rows[self.rank + 1, 0].contiguous(), rows[self.rank + 1, 1].contiguous()
+        work = self._tensor('work', (int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+        changed = self._tensor('changed', (2 * n_atoms,), torch.uint8)
+        changed.zero_()
+        _lib.check(lib.gd_events_count(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, dv.ptr(next_o),
+                                       dv.ptr(next_i), dv.ptr(work), dv.ptr(changed), s))
+        launches += 1
+        if self.world > 1:
+            self._dist().all_reduce(changed, op=self._dist().ReduceOp.MAX, group=self.group)
+        offsets = self._tensor('offsets', (n_atoms + 1,), torch.int64)
+        n_events = C.c_int64(0)
+        st = lib.gd_events_scan(dv.ptr(work), n_frames, n_atoms, dv.ptr(changed), dv.ptr(offsets),
+                                C.byref(n_events), s)
+        if st == _lib.GD_ERR_INNER_CONSTANT:
+            raise IndexError('index -1 is out of bounds for axis 0 with size 0')
+        _lib.check(st)
+        launches += 2
+        if not bool(changed[:n_atoms].any()):
+            raise ValueError('need at least one array to concatenate')
+        rows = dv.empty((max(n_events.value, 1), 6), torch.int32)
+        if n_events.value:
+            _lib.check(lib.gd_events_fill(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, dv.ptr(next_o),
+                                          dv.ptr(next_i), dv.ptr(work), dv.ptr(changed), dv.ptr(offsets),
+                                          self.frame0, dv.ptr(rows), s))
+            launches += 1
+        rows = rows[: n_events.value]
+
+        if self.world > 1:
+            rows, offsets, n_total = self._merge_events(rows, offsets, n_atoms)
+            launches += self.world
+        else:
+            n_total = n_events.value
+
+        # ---- K3
+        counts = self._tensor('jcounts', (n_atoms + 1,), torch.int64)
+        n_jumps = C.c_int64(0)
+        _lib.check(lib.gd_jumps_count(dv.ptr(rows), dv.ptr(offsets), n_atoms, self.n_frames_total,
+                                      self.minimal_residence, dv.ptr(counts), C.byref(n_jumps), s))
+        launches += 2
+        jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
+        if n_jumps.value:
+            _lib.check(lib.gd_jumps_fill(dv.ptr(rows), dv.ptr(offsets), n_atoms, self.n_frames_total,
+                                         self.minimal_residence, dv.ptr(counts), dv.ptr(jumps), s))
+            launches += 1
+        self.launches_per_run = launches
+        return {'outer': outer, 'inner': inner, 'events': rows, 'atom_offsets': offsets,
+                'jumps': jumps[: n_jumps.value], 'n_events': n_total, 'n_jumps': n_jumps.value,
+                'visited': vis, 'band': band}
+
+    def _merge_events(self, rows, offsets, n_atoms):
+        """All-gather the per-shard tables and merge them per atom (every rank gets the whole table)."""
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        all_off = self._all_gather(offsets)  # [W, A+1]
+        off_h = dv.to_host(all_off)
+        counts = np.diff(off_h, axis=1)
+        n_per = off_h[:, -1]
+        cap = int(max(1, n_per.max()))
+        padded = dv.zeros((cap, 6), torch.int32)
+        padded[: rows.shape[0]] = rows
+        gathered = self._all_gather(padded)  # [W, cap, 6]
+        atom_offsets, dst_start = merge_plan(counts)
+        merged = dv.empty((max(int(atom_offsets[-1]), 1), 6), torch.int32)
+        d_dst = dv.to_device(np.ascontiguousarray(dst_start))
+        for r in range(self.world):
+            if n_per[r]:
+                _lib.check(lib.gd_events_merge(dv.ptr(gathered[r]), dv.ptr(all_off[r]), dv.ptr(d_dst[r]),
+                                               n_atoms, dv.ptr(merged), s))
+        return merged[: int(atom_offsets[-1])], dv.to_device(atom_offsets.astype(np.int64)), int(atom_offsets[-1])

@@ -1,0 +1,282 @@
+"""Trajectory: the input contract of the hot path and its displacement / MSD / density methods.
+
+Mirrors the parts of ``gemdat.Trajectory`` (reference src/gemdat/trajectory.py) the
+path touches: construction kwargs, ``positions`` / ``displacements`` (:170-193),
+``filter`` (:833-864), ``get_lattice`` (:686-703), ``split`` (:866-894),
+``cumulative_displacements`` (:705-713), ``distances_from_base_position`` (:715-730),
+``mean_squared_displacement`` (:896-933), ``to_volume`` (:129-150),
+``transitions_between_sites`` (:1066-1110), ``metrics`` (:1112-1116).
+
+File readers, drift correction, plotting and the kinisi bridge are out of scope
+(DESIGN.md).  ``coords`` may be a numpy array (copied to the GPU per call) or a
+CUDA ``torch.Tensor`` (device resident: the 24 GB C3 trajectory never visits the
+host).  All arithmetic on the path runs in ``libgemdat_b200.so``.
+"""
+
+from __future__ import annotations
+
+from itertools import pairwise
+from typing import Collection
+
+import numpy as np
+import torch
+
+from . import _device as dv
+from . import _lib
+from .lattice import Lattice, as_lattice_matrix
+
+
+def _symbol(sp) -> str:
+    """Element symbol of a species given as 'Li', 'Li+', pymatgen Species/Element, ..."""
+    s = getattr(sp, 'symbol', None)
+    if s is not None:
+        return str(s)
+    s = str(sp)
+    out = ''
+    for ch in s:
+        if ch.isalpha():
+            out += ch
+        else:
+            break
+    return out or s
+
+
+class Trajectory:
+    def __init__(
+        self,
+        *,
+        species,
+        coords,
+        lattice,
+        metadata: dict | None = None,
+        time_step: float | None = None,
+        constant_lattice: bool = True,
+        coords_are_displacement: bool = False,
+        base_positions=None,
+        **_ignored,
+    ):
+        if not constant_lattice:
+            raise NotImplementedError(
+                'only constant-lattice trajectories are on the accelerated path '
+                '(the reference calls get_lattice() without an index, transitions.py:769)'
+            )
+        self.species = list(species)
+        self.coords = coords if dv.is_device(coords) else np.asarray(coords, dtype=np.float64)
+        if self.coords.ndim != 3 or self.coords.shape[2] != 3:
+            raise ValueError('coords must have shape [n_frames, n_atoms, 3]')
+        if self.coords.shape[1] != len(self.species):
+            raise ValueError('len(species) must equal coords.shape[1]')
+        self.lattice = as_lattice_matrix(lattice)
+        self.constant_lattice = True
+        self.metadata = metadata if metadata else {}
+        self.time_step = time_step
+        self.coords_are_displacement = coords_are_displacement
+        if coords_are_displacement:
+            self.base_positions = self.coords[0] if base_positions is None else base_positions
+        else:
+            self.base_positions = self.coords[0]
+
+    # ------------------------------------------------------------------ container protocol
+    def __len__(self) -> int:
+        return int(self.coords.shape[0])
+
+    def __getitem__(self, frames):
+        if not isinstance(frames, slice):
+            raise TypeError('only slicing along the frame axis is supported')
+        self.to_positions()
+        return self.__class__(
+            species=self.species,
+            coords=self.coords[frames],
+            lattice=self.lattice,
+            metadata=self.metadata,
+            time_step=self.time_step,
+        )
+
+    def __repr__(self):
+        return (
+            f'Trajectory({len(self.species)} sites, {len(self)} time steps, '
+            f'abc={Lattice(self.lattice).lengths}, device_resident={dv.is_device(self.coords)})'
+        )
+
+    # ------------------------------------------------------------------ representations
+    def to_positions(self):
+        """trajectory.py:121-127 (base + cumsum, then mod 1).  Data-model accessor, host numpy."""
+        if not self.coords_are_displacement:
+            return
+        coords = self._host_coords()
+        base = np.asarray(dv.to_host(self.base_positions) if dv.is_device(self.base_positions)
+                          else self.base_positions)
+        self.coords = np.mod(base + np.cumsum(coords, axis=0), 1)
+        self.coords_are_displacement = False
+
+    def to_displacements(self):
+        """pymatgen ``to_displacements``: wrapped frame-to-frame steps, frame 0 = 0."""
+        if self.coords_are_displacement:
+            return
+        coords = self._host_coords()
+        d = np.subtract(coords, np.roll(coords, 1, axis=0))
+        d[0] = 0.0
+        self.coords = np.subtract(d, np.around(d))
+        self.coords_are_displacement = True
+
+    def _host_coords(self) -> np.ndarray:
+        return dv.to_host(self.coords) if dv.is_device(self.coords) else self.coords
+
+    @property
+    def positions(self):
+        """Fractional positions [n_frames, n_atoms, 3] (numpy, or the CUDA tensor if device resident)."""
+        self.to_positions()
+        return self.coords
+
+    @property
+    def displacements(self) -> np.ndarray:
+        self.to_displacements()
+        return self.coords
+
+    def _device_positions(self) -> torch.Tensor:
+        """float64 CUDA tensor [T, A, 3] of wrapped positions (uploads host arrays)."""
+        self.to_positions()
+        return dv.to_device(self.coords, torch.float64)
+
+    # ------------------------------------------------------------------ scalars
+    @property
+    def time_step_ps(self) -> float:
+        assert self.time_step
+        return self.time_step * 1e12
+
+    @property
+    def total_time(self) -> float:
+        assert self.time_step
+        return len(self) * self.time_step
+
+    @property
+    def sampling_frequency(self) -> float:
+        assert self.time_step
+        return 1 / self.time_step
+
+    def get_lattice(self, idx: int | None = None) -> Lattice:
+        return Lattice(self.lattice)
+
+    # ------------------------------------------------------------------ selection
+    def filter(self, species: str | Collection[str]) -> 'Trajectory':
+        """trajectory.py:833-864: keep the atoms whose element symbol is in ``species``."""
+        if isinstance(species, str):
+            species = [species]
+        wanted = {_symbol(s) for s in species}
+        idx = [_symbol(sp) in wanted for sp in self.species]
+        pos = self.positions
+        if dv.is_device(pos):
+            sel = torch.nonzero(torch.tensor(idx, device=pos.device)).flatten()
+            new_coords = pos.index_select(1, sel) if len(sel) != pos.shape[1] else pos
+        else:
+            new_coords = pos[:, idx]
+        return self.__class__(
+            species=[sp for sp, keep in zip(self.species, idx) if keep],
+            coords=new_coords,
+            lattice=self.lattice,
+            metadata=self.metadata,
+            time_step=self.time_step,
+        )
+
+    def split(self, n_parts: int = 10, equal_parts: bool = False) -> list['Trajectory']:
+        """trajectory.py:866-894."""
+        interval = np.linspace(0, len(self) - 1, n_parts + 1, dtype=int)
+        parts = [self[int(a):int(b)] for a, b in pairwise(interval)]
+        if equal_parts:
+            minsize = min(int(b - a) for a, b in pairwise(interval))
+            parts = [p[0:minsize] for p in parts]
+        return parts
+
+    # ------------------------------------------------------------------ K0: displacement path
+    def _unwrap(self, *, want_frac=False, want_cart=False, want_dist=False, keep_on_device=False):
+        pos = self._device_positions()
+        n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+        n_chunks = int(_lib.lib.gd_unwrap_chunks(n_frames, n_atoms))
+        work = dv.empty((n_chunks * n_atoms * 3,), torch.int32)
+        frac = dv.empty((n_frames, n_atoms, 3), torch.float64) if want_frac else None
+        cart = dv.empty((n_frames, n_atoms, 3), torch.float64) if want_cart else None
+        dist = dv.empty((n_atoms, n_frames), torch.float64) if want_dist else None
+        wind = dv.empty((n_atoms, 3), torch.int32)
+        _lib.check(
+            _lib.lib.gd_unwrap(
+                dv.ptr(pos), n_frames, n_atoms, self.lattice.ctypes.data, None, None, None,
+                dv.ptr(work), dv.ptr(frac), dv.ptr(cart), dv.ptr(dist), dv.ptr(wind),
+                dv.stream_ptr(),
+            )
+        )
+        out = {'frac': frac, 'cart': cart, 'dist': dist, 'winding': wind, 'pos': pos}
+        if not keep_on_device:
+            out = {k: (dv.to_host(v) if v is not None and k != 'pos' else v) for k, v in out.items()}
+        return out
+
+    @property
+    def cumulative_displacements(self) -> np.ndarray:
+        """trajectory.py:705-713, [n_frames, n_atoms, 3] fractional."""
+        return self._unwrap(want_frac=True)['frac']
+
+    def distances_from_base_position(self) -> np.ndarray:
+        """trajectory.py:715-730, [n_atoms, n_frames] in Angstrom."""
+        return self._unwrap(want_dist=True)['dist']
+
+    def final_displacement_sq(self) -> np.ndarray:
+        """|r(T-1) - r(0)|^2 per atom (Angstrom^2) from the winding counts alone."""
+        res = self._unwrap(keep_on_device=True)
+        pos = res['pos']
+        first, last = dv.to_host(pos[0]), dv.to_host(pos[-1])
+        frac = (last - first) - dv.to_host(res['winding']).astype(np.float64)
+        g = Lattice(self.lattice).metric_tensor
+        return np.einsum('ij,ij->i', frac @ g, frac)
+
+    # ------------------------------------------------------------------ K4: MSD
+    def mean_squared_displacement(self, lags: tuple[int, int] | None = None) -> np.ndarray:
+        """trajectory.py:896-933: per-atom MSD for every lag, [n_atoms, n_frames] Angstrom^2.
+
+        ``lags=(first, count)`` restricts the computation to a contiguous lag range
+        (extension; the reference always returns all lags).
+        """
+        res = self._unwrap(want_cart=True, keep_on_device=True)
+        cart = res['cart']
+        n_frames, n_atoms = int(cart.shape[0]), int(cart.shape[1])
+        soa = dv.empty((n_atoms, 3, n_frames), torch.float64)
+        _lib.check(_lib.lib.gd_transpose_soa(dv.ptr(cart), n_frames, n_atoms, dv.ptr(soa), dv.stream_ptr()))
+        del cart, res
+        lag0, n_lags = (0, n_frames) if lags is None else (int(lags[0]), int(lags[1]))
+        msd = dv.empty((n_atoms, n_lags), torch.float64)
+        _lib.check(
+            _lib.lib.gd_msd_direct(dv.ptr(soa), n_frames, n_atoms, lag0, n_lags, dv.ptr(msd), dv.stream_ptr())
+        )
+        return dv.to_host(msd)
+
+    # ------------------------------------------------------------------ K5: density
+    def to_volume(self, resolution: float = 0.2):
+        from .volume import trajectory_to_volume
+
+        return trajectory_to_volume(self, resolution=resolution)
+
+    # ------------------------------------------------------------------ K1-K3
+    def transitions_between_sites(
+        self,
+        sites,
+        floating_specie: str,
+        site_radius: float | dict[str, float] | None = None,
+        site_inner_fraction: float | dict[str, float] = 1.0,
+        remove_part_occup_from_structure: bool = False,
+        fraction_of_overlap: float = 0.0,
+    ):
+        """trajectory.py:1066-1110."""
+        from .transitions import Transitions
+
+        return Transitions.from_trajectory(
+            trajectory=self,
+            sites=sites,
+            floating_specie=floating_specie,
+            site_radius=site_radius,
+            site_inner_fraction=site_inner_fraction,
+            remove_part_occup_from_structure=remove_part_occup_from_structure,
+            fraction_of_overlap=fraction_of_overlap,
+        )
+
+    def metrics(self):
+        from .metrics import TrajectoryMetrics
+
+        return TrajectoryMetrics(trajectory=self)

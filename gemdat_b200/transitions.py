@@ -1,0 +1,670 @@
+"""Transitions between sites: host-side mirror of reference src/gemdat/transitions.py.
+
+Same names, kwargs, return types, warnings and exceptions as the reference for the
+hot path: ``Transitions.from_trajectory`` (:96-186), ``Transitions.jumps`` (:188-202),
+``matrix`` / ``states_next`` / ``states_prev`` (:243-278), ``occupancy*`` /
+``atom_locations`` / ``residence_time`` / ``split`` (:280-410), ``SiteRadius``
+(:485-733) and the three private seams the CUDA kernels sit behind:
+
+* ``_calculate_atom_states``        (:736-809)  -> ``gd_sitegrid_build`` + ``gd_site_states`` (K1)
+* ``_calculate_transition_events``  (:413-482)  -> ``gd_events_count/scan/fill`` (K2)
+* ``_calculate_transitions_matrix`` (:812-834)  -> ``gd_pair_matrix``
+
+All arithmetic on the path runs in ``libgemdat_b200.so``; this file only prepares
+small host-side tables, maps status codes to the reference's exceptions and wraps
+results in numpy / pandas.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import typing
+from collections import defaultdict
+from dataclasses import dataclass
+from itertools import combinations_with_replacement, pairwise
+from warnings import warn
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import _device as dv
+from . import _lib
+from .caching import weak_lru_cache
+from .lattice import Sites, site_arrays
+
+if typing.TYPE_CHECKING:
+    from .jumps import Jumps
+    from .trajectory import Trajectory
+
+NOSITE = -1
+
+EVENT_COLUMNS = [
+    'atom index',
+    'start site',
+    'destination site',
+    'start inner site',
+    'destination inner site',
+    'time',
+]
+
+
+# --------------------------------------------------------------------------- K1 host side
+
+
+class SiteGrid:
+    """Host + device copy of the search structure built by ``gd_sitegrid_build``."""
+
+    def __init__(self, *, lattice_matrix, site_frac, site_labels, site_radius: dict,
+                 site_inner_fraction: dict):
+        labels = np.asarray(list(site_labels), dtype=object)
+        self.group_labels = list(site_radius.keys())
+        self.n_sites = len(site_frac)
+        group = np.full(self.n_sites, -1, dtype=np.int32)
+        self.group_keys: list[np.ndarray | None] = []
+        for g, label in enumerate(self.group_labels):
+            if label:
+                key = np.nonzero(labels == label)[0]
+                if key.size == 0:
+                    # the reference does `key, site_group = zip(*empty)` -> ValueError
+                    raise ValueError('not enough values to unpack (expected 2, got 0)')
+                group[key] = g
+                self.group_keys.append(key)
+            else:
+                group[:] = g
+                self.group_keys.append(None)
+        radius = np.array([site_radius[k] for k in self.group_labels], dtype=np.float64)
+        inner = np.array([site_inner_fraction[k] for k in self.group_labels], dtype=np.float64)
+        lat = dv.host_f64(lattice_matrix)
+        frac = dv.host_f64(site_frac)
+        needed = C.c_size_t(0)
+        args = (lat.ctypes.data, frac.ctypes.data, group.ctypes.data, self.n_sites,
+                radius.ctypes.data, inner.ctypes.data, len(radius))
+        st = _lib.lib.gd_sitegrid_build(*args, None, 0, C.byref(needed))
+        if st == _lib.GD_ERR_CAPACITY:
+            self.h_blob = np.zeros(needed.value, dtype=np.uint8)
+            st = _lib.lib.gd_sitegrid_build(*args, self.h_blob.ctypes.data, self.h_blob.nbytes,
+                                            C.byref(needed))
+        if st == _lib.GD_ERR_RADIUS_GT_CUTOFF:
+            raise RuntimeError('Set cutoff greater or equal to the radius.')
+        if st == _lib.GD_ERR_TRICLINIC:
+            raise NotImplementedError(_lib.last_error())
+        _lib.check(st)
+        self.radius = radius
+        self.group = group
+        self._d_blob = None
+
+    @property
+    def d_blob(self) -> torch.Tensor:
+        if self._d_blob is None:
+            self._d_blob = dv.to_device(self.h_blob)
+        return self._d_blob
+
+    def remap_lut(self, visited: np.ndarray) -> np.ndarray | None:
+        """LUT natural index -> reported index for the integer_remap quirk, None if identity.
+
+        transitions.py:804-805 maps a group's local site number through
+        ``integer_remap(siteno, key, palette=np.unique(siteno))``: the palette holds only
+        the sites that were hit, so the i-th *visited* site of a labelled group is
+        reported as ``key[i]``.
+        """
+        lut = np.arange(self.n_sites, dtype=np.int32)
+        for key in self.group_keys:
+            if key is None:
+                continue
+            v = visited[key]
+            rank = np.cumsum(v) - 1
+            lut[key[v]] = key[rank[v]]
+        return None if np.array_equal(lut, np.arange(self.n_sites)) else lut
+
+
+def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_fraction: dict,
+                        which: str = 'both'):
+    """K1 on the device.  Returns (outer int32 [T,A], inner int32 [T,A], info dict)."""
+    site_frac, site_labels, _ = site_arrays(sites)
+    grid = SiteGrid(
+        lattice_matrix=trajectory.get_lattice().matrix,
+        site_frac=site_frac,
+        site_labels=site_labels,
+        site_radius=site_radius,
+        site_inner_fraction=site_inner_fraction,
+    )
+    pos = trajectory._device_positions()
+    n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+    outer = dv.empty((n_frames, n_atoms), torch.int32)
+    inner = dv.empty((n_frames, n_atoms), torch.int32)
+    visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
+    band = dv.zeros((4,), torch.int64)
+    st = _lib.lib.gd_site_states(
+        dv.ptr(pos), n_frames * n_atoms, dv.ptr(grid.d_blob), grid.h_blob.ctypes.data,
+        dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band), dv.stream_ptr(),
+    )
+    _lib.check(st)
+    visited_h = dv.to_host(visited).astype(bool).reshape(2, grid.n_sites)
+    band_h = dv.to_host(band)
+    for which_i, (arr, vis) in enumerate(((outer, visited_h[0]), (inner, visited_h[1]))):
+        if which == 'outer' and which_i == 1 or which == 'inner' and which_i == 0:
+            continue
+        for label, key in zip(grid.group_labels, grid.group_keys):
+            hit = vis.any() if key is None else vis[key].any()
+            if not hit:
+                radius = site_radius[label]
+                warn(f'No floating species in range of {label} ({radius=})', stacklevel=3)
+        lut = grid.remap_lut(vis)
+        if lut is not None:
+            d_lut = dv.to_device(lut)
+            _lib.check(_lib.lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut),
+                                                grid.n_sites, dv.stream_ptr()))
+    info = {
+        'visited_outer': visited_h[0],
+        'visited_inner': visited_h[1],
+        'band_1e-12': (int(band_h[0]), int(band_h[1])),
+        'band_4e-6': (int(band_h[2]), int(band_h[3])),
+    }
+    return outer, inner, info
+
+
+def widen_to_host(t: torch.Tensor) -> np.ndarray:
+    """int32 device array -> int64 numpy (the reference's dtype), widened on the device."""
+    out = dv.empty(tuple(t.shape), torch.int64)
+    _lib.check(_lib.lib.gd_widen_i32_i64(dv.ptr(t), dv.ptr(out), t.numel(), dv.stream_ptr()))
+    return dv.to_host(out)
+
+
+def _calculate_atom_states(
+    sites,
+    trajectory: 'Trajectory',
+    site_radius: dict[str, float],
+    site_inner_fraction: dict[str, float],
+) -> np.ndarray:
+    """Drop-in for transitions.py:736-809: int64 [time, atom] site index, -1 = no site."""
+    _, inner, _ = _site_states_device(
+        sites=sites, trajectory=trajectory, site_radius=site_radius,
+        site_inner_fraction=site_inner_fraction, which='inner',
+    )
+    return widen_to_host(inner)
+
+
+# --------------------------------------------------------------------------- K2 host side
+
+
+class EventTable:
+    """Device-resident event table: int32 [E, 6] rows sorted by (atom, time) + per-atom offsets."""
+
+    def __init__(self, rows: torch.Tensor, atom_offsets: torch.Tensor, n_atoms: int):
+        self.rows = rows
+        self.atom_offsets = atom_offsets
+        self.n_atoms = n_atoms
+
+    def __len__(self):
+        return int(self.rows.shape[0])
+
+    def to_dataframe(self) -> pd.DataFrame:
+        data = dv.to_host(self.rows).astype(np.int64)
+        return pd.DataFrame(data=data, columns=EVENT_COLUMNS)
+
+    @classmethod
+    def from_dataframe(cls, events: pd.DataFrame, n_atoms: int | None = None) -> 'EventTable':
+        data = np.ascontiguousarray(events[EVENT_COLUMNS].to_numpy(dtype=np.int64))
+        order = np.argsort(data[:, 0], kind='stable')
+        data = data[order]
+        if n_atoms is None:
+            n_atoms = int(data[:, 0].max()) + 1 if len(data) else 1
+        counts = np.bincount(data[:, 0], minlength=n_atoms)
+        offsets = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+        return cls(dv.to_device(data.astype(np.int32)), dv.to_device(offsets), n_atoms)
+
+
+def _events_device(outer: torch.Tensor, inner: torch.Tensor) -> EventTable:
+    n_frames, n_atoms = int(outer.shape[0]), int(outer.shape[1])
+    lib = _lib.lib
+    work = dv.empty((int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+    changed = dv.zeros((2 * n_atoms,), torch.uint8)
+    s = dv.stream_ptr()
+    _lib.check(lib.gd_events_count(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, None, None,
+                                   dv.ptr(work), dv.ptr(changed), s))
+    offsets = dv.empty((n_atoms + 1,), torch.int64)
+    n_events = C.c_int64(0)
+    st = lib.gd_events_scan(dv.ptr(work), n_frames, n_atoms, dv.ptr(changed), dv.ptr(offsets),
+                            C.byref(n_events), s)
+    if st == _lib.GD_ERR_INNER_CONSTANT:
+        raise IndexError('index -1 is out of bounds for axis 0 with size 0')
+    _lib.check(st)
+    if not bool(changed[:n_atoms].any()):
+        # np.vstack([]) in the reference (transitions.py:470)
+        raise ValueError('need at least one array to concatenate')
+    rows = dv.empty((n_events.value, 6), torch.int32)
+    if n_events.value:
+        _lib.check(lib.gd_events_fill(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, None, None,
+                                      dv.ptr(work), dv.ptr(changed), dv.ptr(offsets), 0,
+                                      dv.ptr(rows), s))
+    return EventTable(rows, offsets, n_atoms)
+
+
+def _calculate_transition_events(*, atom_sites, atom_inner_sites) -> pd.DataFrame:
+    """Drop-in for transitions.py:413-482 (accepts numpy or CUDA int arrays)."""
+    outer = dv.to_device(atom_sites, torch.int32)
+    inner = dv.to_device(atom_inner_sites, torch.int32)
+    return _events_device(outer, inner).to_dataframe()
+
+
+def _calculate_transitions_matrix(events, n_sites: int) -> np.ndarray:
+    """Drop-in for transitions.py:812-834 (``events`` = DataFrame with start/destination site)."""
+    pairs = np.ascontiguousarray(events[['start site', 'destination site']].to_numpy(dtype=np.int32))
+    return _pair_matrix_device(dv.to_device(pairs) if len(pairs) else None, len(pairs), 2, 0, 1, n_sites)
+
+
+def _pair_matrix_device(rows, n_rows: int, stride: int, cs: int, cd: int, n_sites: int) -> np.ndarray:
+    scratch = dv.zeros(((n_sites + 1) * (n_sites + 1),), torch.int64)
+    out = dv.empty((n_sites, n_sites), torch.int64)
+    _lib.check(_lib.lib.gd_pair_matrix(dv.ptr(rows), n_rows, stride, cs, cd, n_sites,
+                                       dv.ptr(scratch), dv.ptr(out), dv.stream_ptr()))
+    return dv.to_host(out).astype(int)
+
+
+def _fill_device(states: torch.Tensor, direction: int) -> torch.Tensor:
+    n_frames, n_atoms = int(states.shape[0]), int(states.shape[1])
+    work = dv.empty((int(_lib.lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+    out = dv.empty((n_frames, n_atoms), torch.int32)
+    _lib.check(_lib.lib.gd_fill_states(dv.ptr(states), n_frames, n_atoms, direction, None, None,
+                                       dv.ptr(work), dv.ptr(out), dv.stream_ptr()))
+    return out
+
+
+def ffill(arr, fill_val: int = -1, axis=-1) -> np.ndarray:
+    """Drop-in for utils.py:59-84 on the GPU (2-D integer arrays, fill value -1)."""
+    return _fill_host(arr, fill_val, axis, +1)
+
+
+def bfill(arr, fill_val: int = -1, axis=-1) -> np.ndarray:
+    """Drop-in for utils.py:87-98."""
+    return _fill_host(arr, fill_val, axis, -1)
+
+
+def _fill_host(arr, fill_val, axis, direction):
+    arr = np.asarray(arr)
+    if arr.ndim > 2:
+        raise ValueError
+    if fill_val != NOSITE:
+        raise NotImplementedError('the device kernel fills the NOSITE (-1) value only')
+    time_major = arr if axis == 0 else arr.T  # kernel scans along axis 0
+    out = widen_to_host(_fill_device(dv.to_device(np.ascontiguousarray(time_major), torch.int32), direction))
+    out = out if axis == 0 else out.T
+    return out.astype(arr.dtype, copy=False)
+
+
+# --------------------------------------------------------------------------- Transitions
+
+
+class Transitions:
+    """Container for transitions between sites (reference transitions.py:30-410).
+
+    ``states`` / ``inner_states`` / ``events`` are materialised on first access from
+    the device-resident int32 arrays (``d_states`` ...), which the downstream
+    kernels (jumps, fills, matrices) consume directly.
+    """
+
+    DISORDER_ERROR_MSG = (
+        'Input `sites` has partial occupancies. In GEMDAT, '
+        '`sites` is treated as the set of all possible sites '
+        'for the floating species, and partial occupancies '
+        'can lead to ambiguous site assignments. '
+        'Remove partial occupancies manually, or set '
+        '`remove_part_occup_from_structure=True` '
+        'to do it automatically.'
+    )
+
+    def __init__(self, *, trajectory, diff_trajectory, sites, events, states, inner_states,
+                 site_radius, _device=None):
+        if not getattr(sites, 'is_ordered', True):
+            warn(self.DISORDER_ERROR_MSG, stacklevel=2)
+        self.sites = sites
+        self.trajectory = trajectory
+        self.diff_trajectory = diff_trajectory
+        self.site_radius = site_radius
+        self._states = states
+        self._inner_states = inner_states
+        self._events = events
+        self._dev = _device or {}
+        self.info = self._dev.get('info', {})
+
+    # -- lazily materialised host views
+    @property
+    def states(self) -> np.ndarray:
+        if self._states is None:
+            self._states = widen_to_host(self._dev['outer'])
+        return self._states
+
+    @property
+    def inner_states(self) -> np.ndarray:
+        if self._inner_states is None:
+            self._inner_states = widen_to_host(self._dev['inner'])
+        return self._inner_states
+
+    @property
+    def events(self) -> pd.DataFrame:
+        if self._events is None:
+            self._events = self._dev['events'].to_dataframe()
+        return self._events
+
+    @property
+    def d_states(self) -> torch.Tensor:
+        if 'outer' not in self._dev:
+            self._dev['outer'] = dv.to_device(self._states, torch.int32)
+        return self._dev['outer']
+
+    @property
+    def d_inner_states(self) -> torch.Tensor:
+        if 'inner' not in self._dev:
+            self._dev['inner'] = dv.to_device(self._inner_states, torch.int32)
+        return self._dev['inner']
+
+    @property
+    def d_events(self) -> EventTable:
+        if 'events' not in self._dev:
+            self._dev['events'] = EventTable.from_dataframe(self._events, self.n_floating)
+        return self._dev['events']
+
+    @classmethod
+    def from_trajectory(
+        cls,
+        *,
+        trajectory,
+        sites,
+        floating_specie: str,
+        site_radius: float | dict[str, float] | None = None,
+        site_inner_fraction: float | dict[str, float] = 1.0,
+        remove_part_occup_from_structure: bool = False,
+        fraction_of_overlap: float = 0.0,
+    ) -> 'Transitions':
+        """transitions.py:96-186."""
+        from .metrics import TrajectoryMetrics
+
+        if not getattr(sites, 'is_ordered', True):
+            if remove_part_occup_from_structure:
+                sites = remove_partial_occupancies_from_structure(sites)
+            else:
+                warn(cls.DISORDER_ERROR_MSG, stacklevel=2)
+
+        diff_trajectory = trajectory.filter(floating_specie)
+
+        if site_radius is None:
+            vibration_amplitude = TrajectoryMetrics(diff_trajectory).vibration_amplitude()
+            site_radius_obj = SiteRadius.from_vibration_amplitude(
+                trajectory=trajectory, sites=sites, vibration_amplitude=vibration_amplitude,
+                inner_fraction=site_inner_fraction,
+            )
+        else:
+            site_radius_obj = SiteRadius.from_given_radius(
+                trajectory=trajectory, sites=sites, radius=site_radius,
+                inner_fraction=site_inner_fraction, fraction_of_overlap=fraction_of_overlap,
+            )
+
+        # the reference runs _calculate_atom_states twice (outer fraction 1.0, then inner);
+        # K1 produces both in one pass over the positions
+        outer, inner, info = _site_states_device(
+            sites=sites, trajectory=diff_trajectory, site_radius=site_radius_obj.radius,
+            site_inner_fraction=site_radius_obj.inner_fraction,
+        )
+        events = _events_device(outer, inner)
+
+        return cls(
+            sites=sites, trajectory=trajectory, diff_trajectory=diff_trajectory,
+            events=None, states=None, inner_states=None, site_radius=site_radius_obj,
+            _device={'outer': outer, 'inner': inner, 'events': events, 'info': info},
+        )
+
+    def jumps(self, **kwargs) -> 'Jumps':
+        """transitions.py:188-202."""
+        from .jumps import Jumps
+
+        return Jumps(self, **kwargs)
+
+    @property
+    def n_floating(self) -> int:
+        return len(self.diff_trajectory.species)
+
+    @property
+    def n_states(self) -> int:
+        if self._states is not None:
+            return len(self._states)
+        return int(self._dev['outer'].shape[0])
+
+    @property
+    def n_events(self) -> int:
+        if self._events is not None:
+            return len(self._events)
+        return len(self._dev['events'])
+
+    @property
+    def n_sites(self) -> int:
+        return len(self.sites)
+
+    @weak_lru_cache()
+    def matrix(self) -> np.ndarray:
+        """transitions.py:243-252: [n_sites, n_sites] counts of (start, destination) events."""
+        ev = self.d_events
+        return _pair_matrix_device(ev.rows if len(ev) else None, len(ev), 6, 1, 2, self.n_sites)
+
+    @weak_lru_cache()
+    def states_next(self) -> np.ndarray:
+        """transitions.py:254-265 (bfill along time)."""
+        return widen_to_host(_fill_device(self.d_states, -1))
+
+    @weak_lru_cache()
+    def states_prev(self) -> np.ndarray:
+        """transitions.py:267-278 (ffill along time)."""
+        return widen_to_host(_fill_device(self.d_states, +1))
+
+    def occupancy(self) -> Sites:
+        """transitions.py:280-306: fraction of frames each site is occupied."""
+        frac, labels, _ = site_arrays(self.sites)
+        unq, counts = np.unique(self.states, return_counts=True)
+        occ = dict(zip(unq.tolist(), (counts / self.n_states).tolist()))
+        symbols = getattr(self.sites, 'symbols', None) or [
+            str(getattr(getattr(s, 'specie', None), 'name', 'X')) for s in self.sites
+        ]
+        return Sites(
+            getattr(self.sites, 'lattice'), symbols, frac, labels,
+            occupancies=[occ.get(i, 0) for i in range(len(frac))],
+        )
+
+    def occupancy_by_site_type(self) -> dict[str, float]:
+        """transitions.py:308-321."""
+        by_label = defaultdict(list)
+        occ = self.occupancy()
+        for label, value in zip(occ.labels, occ.occupancies):
+            by_label[label].append(float(value))
+        return {k: sum(v) / len(v) for k, v in by_label.items()}
+
+    def atom_locations(self) -> dict[str, float]:
+        """transitions.py:323-337."""
+        n = self.n_floating
+        by_label = defaultdict(list)
+        occ = self.occupancy()
+        for label, value in zip(occ.labels, occ.occupancies):
+            by_label[label].append(float(value))
+        return {k: sum(v) / n for k, v in by_label.items()}
+
+    def residence_time(self) -> pd.DataFrame:
+        """transitions.py:339-373: one row per completed site visit."""
+        states = self.states
+        _, labels, _ = site_arrays(self.sites)
+        rows = []
+        for atom in range(states.shape[1]):
+            col = states[:, atom]
+            boundaries = np.nonzero(np.diff(col))[0] + 1
+            starts, ends = boundaries[:-1], boundaries[1:]
+            site = col[starts]
+            keep = site != NOSITE
+            for s, e, k in zip(starts[keep], ends[keep], site[keep]):
+                rows.append((atom, k, labels[k], int(e - s)))
+        return pd.DataFrame(rows, columns=['atom index', 'site', 'label', 'time'])
+
+    def split(self, n_parts: int = 10) -> list['Transitions']:
+        """transitions.py:375-410."""
+        split_states = np.array_split(self.states, n_parts)
+        split_inner_states = np.array_split(self.inner_states, n_parts)
+        split_events = _split_transitions_events(self.events, self.n_states, n_parts)
+        split_trajectory = self.trajectory.split(n_parts)
+        split_diff_trajectory = self.diff_trajectory.split(n_parts)
+        return [
+            self.__class__(
+                sites=self.sites, trajectory=split_trajectory[i],
+                diff_trajectory=split_diff_trajectory[i], states=split_states[i],
+                inner_states=split_inner_states[i], events=split_events[i],
+                site_radius=self.site_radius,
+            )
+            for i in range(n_parts)
+        ]
+
+
+def _split_transitions_events(events: pd.DataFrame, n_states: int, n_parts=10, split_key='time',
+                              dependent_keys='time') -> list[pd.DataFrame]:
+    """transitions.py:837-879."""
+    if len(events) < n_parts:
+        raise ValueError(f'Not enough transitions per part to split into {n_parts}')
+    bins = np.linspace(0, n_states + 1, n_parts + 1, dtype=int)
+    parts = [
+        events[(events[split_key] >= start) & (events[split_key] < stop)].copy()
+        for start, stop in pairwise(bins)
+    ]
+    for offset, part in zip(bins[:-1], parts):
+        part[dependent_keys] -= offset
+    return parts
+
+
+def remove_partial_occupancies_from_structure(structure):
+    """utils.py:310-330 for the ``Sites`` stand-in: set every occupancy to 1."""
+    new = structure.copy()
+    if hasattr(new, 'occupancies'):
+        new.occupancies = np.ones(len(new))
+        return new
+    raise NotImplementedError('pass a gemdat_b200.Sites object or an ordered pymatgen Structure')
+
+
+# --------------------------------------------------------------------------- SiteRadius
+
+
+@dataclass
+class SiteRadius:
+    """transitions.py:485-711 (scalar host prep feeding K1; the S x S distance matrix is a kernel)."""
+
+    radius: dict[str, float]
+    inner_fraction: dict[str, float]
+    pdist: np.ndarray
+    site_pairs: dict
+    min_dist: dict
+
+    @classmethod
+    def from_given_radius(cls, *, trajectory, sites, radius, inner_fraction,
+                          fraction_of_overlap: float = 0.0) -> 'SiteRadius':
+        if fraction_of_overlap > 1:
+            raise ValueError('fraction_of_overlap must be <= 1.0')
+        frac, _, _ = site_arrays(sites)
+        pdist = trajectory.get_lattice().get_all_distances(frac, frac)
+        r, f = _radius_to_dict(radius=radius, inner_fraction=inner_fraction)
+        obj = cls(radius=r, inner_fraction=f, pdist=pdist, site_pairs={}, min_dist={})
+        obj._site_pairs()
+        obj._min_dist(sites)
+        factor = 1 + fraction_of_overlap
+        if obj.sites_are_overlapping(factor=factor):
+            obj.raise_if_overlapping(sites=sites, factor=factor)
+        return obj
+
+    @classmethod
+    def from_vibration_amplitude(cls, *, trajectory, sites, vibration_amplitude: float,
+                                 inner_fraction=1.0) -> 'SiteRadius':
+        frac, labels, _ = site_arrays(sites)
+        site_radius = 2 * vibration_amplitude
+        pdist = trajectory.get_lattice().get_all_distances(frac, frac)
+        min_dist = np.min(pdist[np.triu_indices_from(pdist, k=1)])
+        if min_dist < 2 * site_radius:
+            site_radius = (0.5 * min_dist) - 0.005
+            if site_radius * 2 < 0.5:
+                idx = np.argwhere(np.triu(pdist, k=1) == min_dist)
+                lines = []
+                for i, j in idx:
+                    lines.append('\nToo close:')
+                    lines.append(f'({i}) {labels[i]} {frac[i]}')
+                    lines.append(' - ')
+                    lines.append(f'({j}) {labels[i]} {frac[j]}')
+                msg = ''.join(lines)
+                raise ValueError(
+                    'Two sites are within half an Angstrom of each other. '
+                    'This is not realistic, check/change the given sites. '
+                    f'Expected: > {site_radius * 2:.4f}, '
+                    f'got: {min_dist:.4f} for {msg}'
+                )
+        r, f = _radius_to_dict(radius=float(site_radius), inner_fraction=inner_fraction)
+        obj = cls(radius=r, pdist=pdist, inner_fraction=f, site_pairs={}, min_dist={})
+        obj._site_pairs()
+        obj._min_dist(sites)
+        return obj
+
+    def outer_states_fraction(self) -> dict[str, float]:
+        return {label: 1.0 for label in self.radius}
+
+    def _site_pairs(self):
+        pairs = list(combinations_with_replacement(self.radius.keys(), 2))
+        self.site_pairs = {(i, j): self.radius[i] + self.radius[j] for (i, j) in pairs}
+
+    def _min_dist(self, sites):
+        self.min_dist = {}
+        _, labels, _ = site_arrays(sites)
+        site_labels = np.array(labels)
+        for (i, j), _pair_dist in self.site_pairs.items():
+            ii = np.where(site_labels == i)[0]
+            jj = np.where(site_labels == j)[0]
+            if ii.size == 0 or jj.size == 0:
+                self.min_dist[(i, j)] = float('inf')
+                continue
+            sub = self.pdist[np.ix_(ii, jj)]
+            _, a, b = np.intersect1d(ii, jj, return_indices=True)
+            if a.size:
+                sub[a, b] = np.inf
+            self.min_dist[(i, j)] = float(sub.min(initial=np.inf))
+
+    def sites_are_overlapping(self, factor: float = 1.0) -> bool:
+        return any(factor * self.min_dist[key] < pair for key, pair in self.site_pairs.items())
+
+    def raise_if_overlapping(self, sites, factor: float = 1.0) -> None:
+        frac, labels, _ = site_arrays(sites)
+        lines = []
+        for key, pair_dist in self.site_pairs.items():
+            min_dist = self.min_dist[key]
+            if factor * min_dist < pair_dist:
+                for i, j in np.argwhere(np.triu(self.pdist, k=1) == min_dist):
+                    lines.append('\nOverlapping: ')
+                    lines.append(f'({i}) {frac[i]}')
+                    lines.append(' - ')
+                    lines.append(f'({j}) {frac[j]}, ')
+                    lines.append(f'expected < {min_dist / 2:.2f}, ')
+                    lines.append(f'got {labels[i]}: {self.radius[labels[i]]} ')
+                    lines.append(f'and {labels[j]}: {self.radius[labels[j]]}')
+        msg = ''.join(lines)
+        raise ValueError(
+            'Sites are overlapping with the chosen site_radius '
+            'and fraction_of_overlap, make site_radius smaller '
+            f'for {msg}'
+        )
+
+
+def _radius_to_dict(radius, inner_fraction):
+    """transitions.py:713-733."""
+    if isinstance(radius, (int, float)):
+        if isinstance(inner_fraction, dict):
+            r = {label: radius for label in inner_fraction.keys()}
+        elif isinstance(inner_fraction, (int, float)):
+            r = {'': radius}
+    elif isinstance(radius, dict):
+        r = radius
+    else:
+        raise TypeError(f'Invalid type for `site_radius`: {type(radius)}')
+    if isinstance(inner_fraction, (int, float)):
+        f = {label: inner_fraction for label in r.keys()}
+    elif isinstance(inner_fraction, dict):
+        f = inner_fraction
+    else:
+        raise TypeError(f'Invalid type for `site_inner_fraction`: {type(inner_fraction)}')
+    return r, f

@@ -151,6 +151,13 @@ gd_status_t gd_events_fill(const int32_t *d_states_outer, const int32_t *d_state
                            const uint8_t *d_changed_global, const int64_t *d_atom_offsets,
                            int64_t frame0, int32_t *d_events, void *stream);
 
+/* Frame-sharded runs: place one shard's rows (sorted by atom, then time) into the
+ * merged table.  d_dst_start [n_atoms] int64 = first merged row for this shard's
+ * rows of each atom (rows of earlier shards of the same atom come first). */
+gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom_offsets,
+                            const int64_t *d_dst_start, int32_t n_atoms, int32_t *d_dst_rows,
+                            void *stream);
+
 /* ffill (direction=+1, states_prev) / bfill (direction=-1, states_next) along the
  * frame axis.  d_carry_in [n_atoms] (may be NULL) is the last valid state before
  * (after, for bfill) this shard; d_carry_out [n_atoms] (may be NULL) receives the

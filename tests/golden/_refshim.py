@@ -202,7 +202,7 @@ def install_stubs():
     pm = _module('pymatgen', core=core)
     pm.__path__ = []
     _module('pymatgen.core.trajectory', Trajectory=PymatgenTrajectory)
-    _module('pymatgen.core.units', FloatWithUnit=FloatWithUnit, Unit=object)
+    _module('pymatgen.core.units', FloatWithUnit=FloatWithUnit, Unit=str)
     vasp = _module('pymatgen.io.vasp', VolumetricData=object, Vasprun=object)
     io = _module('pymatgen.io', vasp=vasp)
     io.__path__ = []

@@ -1,0 +1,145 @@
+"""CPU-side checks of the C ABI: every declared symbol is exported, and the host-built
+site grid is a conservative superset of the exact matches (so K1's exact test decides)."""
+
+from __future__ import annotations
+
+import ctypes as C
+import re
+import struct
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from gemdat_b200 import _lib
+from gemdat_b200.transitions import SiteGrid
+from oracle import states as ostates
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def header_symbols():
+    text = (ROOT / 'include' / 'gemdat_b200.h').read_text()
+    text = re.sub(r'/\*.*?\*/', '', text, flags=re.S)
+    return sorted(set(re.findall(r'\b(gd_[a-z0-9_]+)\s*\(', text)))
+
+
+def test_every_declared_symbol_is_exported_and_bound():
+    syms = header_symbols()
+    assert len(syms) >= 20
+    for name in syms:
+        assert hasattr(_lib.lib, name), f'{name} declared in include/gemdat_b200.h but not exported'
+    assert sorted(_lib.SIGNATURES) == syms
+
+
+def test_version_and_error_string():
+    assert _lib.lib.gd_version() == 100
+    assert isinstance(_lib.last_error(), str)
+
+
+def parse_blob(blob: np.ndarray):
+    raw = blob.tobytes()
+    magic, version, n_sites, n_total, n_groups = struct.unpack_from('<IIiii', raw, 0)
+    dims = struct.unpack_from('<3i', raw, 20)
+    n_entries, is_diag, max_count = struct.unpack_from('<3i', raw, 32)
+    box = np.frombuffer(raw, dtype=np.float32, count=3, offset=44)
+    cutoff32 = np.frombuffer(raw, dtype=np.float32, count=1, offset=56)[0]
+    inv_cell = np.frombuffer(raw, dtype=np.float32, count=3, offset=60)
+    off = 76 + 4  # pad0 -> 80
+    inv_box = np.frombuffer(raw, dtype=np.float64, count=3, offset=off)
+    matrix = np.frombuffer(raw, dtype=np.float64, count=9, offset=off + 24)
+    o_sites, o_cells, o_entries, o_groups, total = struct.unpack_from('<5Q', raw, off + 24 + 72)
+    assert magic == 0x47534447 and version == 1 and total == len(raw)
+    sites = np.frombuffer(raw, dtype=np.float32, count=4 * n_sites, offset=o_sites).reshape(-1, 4)
+    natgrp = sites[:, 3].copy().view(np.int32)
+    ncell = dims[0] * dims[1] * dims[2]
+    cells = np.frombuffer(raw, dtype=np.uint32, count=2 * ncell, offset=o_cells).reshape(-1, 2)
+    entries = np.frombuffer(raw, dtype=np.int32, count=max(n_entries, 1), offset=o_entries)
+    groups = np.frombuffer(raw, dtype=np.float64, count=4 * n_groups, offset=o_groups).reshape(-1, 4)
+    return dict(n_sites=n_sites, n_total=n_total, dims=dims, box=box, cutoff32=cutoff32,
+                inv_cell=inv_cell, matrix=matrix.reshape(3, 3), xyz=sites[:, :3],
+                natural=natgrp & 0xFFFFFF, group=natgrp >> 24, cells=cells, entries=entries,
+                groups=groups, is_diag=is_diag, max_count=max_count)
+
+
+CASES = [
+    # lattice diag, n_sites, radius dict, inner dict, label pattern
+    ((19.848, 9.924, 9.924), 96, {'': 0.9}, {'': 0.5}, None),
+    ((7.31, 5.07, 6.43), 24, {'Q': 1.1, 'P': 0.8}, {'Q': 0.7, 'P': 1.0}, 'QP'),
+    ((38.91, 38.91, 25.94), 400, {'B': 0.5, 'A': 0.6}, {'B': 1.0, 'A': 0.4}, 'AB'),
+    ((3.0, 40.0, 2.5), 12, {'': 1.2}, {'': 1.0}, None),  # box narrower than 2*cutoff along x, z
+]
+
+
+@pytest.mark.parametrize('lengths,n_sites,radius,inner,pattern', CASES)
+def test_site_grid_is_conservative(lengths, n_sites, radius, inner, pattern):
+    rng = np.random.default_rng(n_sites)
+    lattice = np.diag(lengths)
+    site_frac = rng.random((n_sites, 3)) * 1.2 - 0.1  # some outside [0, 1)
+    labels = ['X'] * n_sites if pattern is None else [pattern[i % len(pattern)] for i in range(n_sites)]
+    grid = SiteGrid(lattice_matrix=lattice, site_frac=site_frac, site_labels=labels,
+                    site_radius=radius, site_inner_fraction=inner)
+    b = parse_blob(grid.h_blob)
+    assert b['n_total'] == n_sites and b['is_diag'] == 1
+    # staged site centres equal the oracle's float32 staging, in overwrite (rank) order
+    s32 = ostates.staged_sites(site_frac, lattice)
+    np.testing.assert_array_equal(b['xyz'], s32[b['natural']])
+    np.testing.assert_array_equal(b['box'], np.array(lengths, dtype=np.float32))
+    assert b['cutoff32'] == np.float32(max(radius.values()))
+    # rank order: groups in dict order, ascending natural index inside a group
+    order = []
+    for g, label in enumerate(radius):
+        order += [i for i in range(n_sites) if (label == '' or labels[i] == label)]
+    np.testing.assert_array_equal(b['natural'], order)
+
+    # atoms: uniform + hugging faces / edges / site surfaces
+    pos = rng.random((6000, 1, 3))
+    pos[:500, 0] = rng.choice([0.0, 1e-9, 1 - 1e-9, 0.5], size=(500, 3))
+    near = site_frac[rng.integers(n_sites, size=1500)] + rng.normal(scale=0.03, size=(1500, 3))
+    pos[500:2000, 0] = np.mod(near, 1)
+    cutoff = max(radius.values())
+    c0, c1, box3 = ostates.staged_atoms(pos, lattice, cutoff)
+    # device cell index: float32 multiply, truncate, clamp
+    idx = np.empty((len(c0), 3), dtype=np.int64)
+    for j in range(3):
+        idx[:, j] = np.clip((c0[:, j] * b['inv_cell'][j]).astype(np.float32).astype(np.int64), 0, b['dims'][j] - 1)
+    cell = (idx[:, 0] * b['dims'][1] + idx[:, 1]) * b['dims'][2] + idx[:, 2]
+    reach2 = np.maximum(b['groups'][:, 0], b['groups'][:, 1])  # max(r2_outer, r2_inner)
+    missing = 0
+    for e in range(b['n_sites']):
+        d2 = ostates.min_d2(b['xyz'][e], c0, c1)
+        hit = np.nonzero(d2 <= reach2[b['group'][e]])[0]
+        for n in hit:
+            cnt, payload = b['cells'][cell[n]]
+            cand = [payload] if cnt == 1 else list(b['entries'][payload:payload + cnt])
+            missing += e not in cand
+    assert missing == 0
+    # candidate lists ascend in rank (last match = overwrite winner)
+    for cnt, payload in b['cells'][b['cells'][:, 0] > 1][:2000]:
+        lst = b['entries'][payload:payload + cnt]
+        assert np.all(np.diff(lst) > 0)
+
+
+def test_sitegrid_error_paths():
+    frac = np.random.default_rng(0).random((5, 3))
+    with pytest.raises(NotImplementedError):
+        SiteGrid(lattice_matrix=np.array([[5.0, 0, 0], [1.0, 5.0, 0], [0, 0, 5.0]]), site_frac=frac,
+                 site_labels=['a'] * 5, site_radius={'': 0.5}, site_inner_fraction={'': 1.0})
+    with pytest.raises(RuntimeError, match='Set cutoff greater or equal to the radius'):
+        SiteGrid(lattice_matrix=np.eye(3) * 5, site_frac=frac, site_labels=['a'] * 5,
+                 site_radius={'': 0.5}, site_inner_fraction={'': 1.5})
+    with pytest.raises(ValueError):
+        SiteGrid(lattice_matrix=np.eye(3) * 5, site_frac=frac, site_labels=['a'] * 5,
+                 site_radius={'zzz': 0.5}, site_inner_fraction={'zzz': 1.0})
+
+
+def test_compute_entry_points_fail_loudly_without_gpu():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip('GPU present')
+    from gemdat_b200 import Trajectory
+
+    t = Trajectory(species=['Li'], coords=np.zeros((4, 1, 3)), lattice=np.eye(3), time_step=1.0)
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        t.distances_from_base_position()

@@ -1,0 +1,316 @@
+"""Parity of the CUDA path (through the C ABI / ctypes, via the public API) against the
+fixtures produced by executing the reference and against the oracle.  Integer and
+index results are compared bit-exactly; floating-point results within the
+tolerance written at each assertion (north_star: 1e-10 relative)."""
+
+from __future__ import annotations
+
+import warnings
+
+import numpy as np
+import pytest
+from numpy.testing import assert_allclose, assert_array_equal
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip('torch')
+
+
+@pytest.fixture(scope='module', autouse=True)
+def _need_cuda():
+    if not torch.cuda.is_available():
+        pytest.skip('no CUDA device')
+
+
+def _product(case):
+    from gemdat_b200 import Sites, Trajectory
+
+    species = [str(s) for s in case['species']] if 'species' in case else ['Li'] * case['positions'].shape[1]
+    traj = Trajectory(species=species, coords=case['positions'], lattice=case['lattice'],
+                      metadata={'temperature': 650.0}, time_step=2e-15)
+    sites = Sites(case['lattice'], 'Li', case['site_frac'], labels=case['labels'])
+    return traj, sites
+
+
+def _radius_args(case):
+    name = case['name']
+    if name == 'pipeline_c2_default_radius':
+        return None, 1.0
+    if list(case['site_radius']) == ['']:
+        return case['site_radius'][''], case['inner_fraction']['']
+    return case['site_radius'], case['inner_fraction']
+
+
+def test_pipeline_matches_reference(pipeline_case):
+    c = pipeline_case
+    traj, sites = _product(c)
+    radius, inner = _radius_args(c)
+    with warnings.catch_warnings(record=True) as caught:
+        warnings.simplefilter('always')
+        tr = traj.transitions_between_sites(
+            sites, 'Li', site_radius=radius, site_inner_fraction=inner,
+            fraction_of_overlap=float(c['fraction_of_overlap']),
+        )
+    assert sorted(str(w.message) for w in caught) == sorted(str(w) for w in c['warnings'])
+    if radius is None:
+        assert_allclose(tr.site_radius.radius[''], c['site_radius'][''], rtol=1e-12)
+    assert tr.states.dtype == np.int64 and tr.states.shape == c['states'].shape
+    assert_array_equal(tr.states, c['states'])
+    assert_array_equal(tr.inner_states, c['inner_states'])
+    assert list(tr.events.columns) == [str(x) for x in c['event_columns']]
+    assert_array_equal(tr.events.to_numpy(), c['events'])
+    assert tr.n_events == len(c['events']) and tr.n_states == len(c['states'])
+    assert_array_equal(tr.matrix(), c['matrix'])
+    assert_array_equal(tr.states_next(), c['states_next'])
+    assert_array_equal(tr.states_prev(), c['states_prev'])
+    for key in [k for k in c if k.startswith('jumps_') and k[6:].isdigit()]:
+        mr = int(key[6:])
+        jumps = tr.jumps(minimal_residence=mr)
+        assert list(jumps.data.columns) == [str(x) for x in c['jump_columns']]
+        assert_array_equal(jumps.data.to_numpy(), c[key])
+        assert_array_equal(jumps.matrix(), c[f'{key}_matrix'])
+        assert_allclose(float(jumps.jump_diffusivity(3)), float(c[f'{key}_diffusivity']), rtol=1e-10)
+
+
+def test_private_seams_match_reference(pipeline_case):
+    """_calculate_atom_states / _calculate_transition_events keep the reference signatures."""
+    from gemdat_b200.transitions import _calculate_atom_states, _calculate_transition_events
+
+    c = pipeline_case
+    traj, sites = _product(c)
+    diff = traj.filter('Li')
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        inner = _calculate_atom_states(sites, diff, c['site_radius'], c['inner_fraction'])
+    assert_array_equal(inner, c['inner_states'])
+    ev = _calculate_transition_events(atom_sites=c['states'], atom_inner_sites=c['inner_states'])
+    assert_array_equal(ev.to_numpy(), c['events'])
+
+
+@pytest.mark.parametrize('tag', ['unit', 'walk', 'c2'])
+def test_displacement_path(displacement_golden, tag):
+    from gemdat_b200 import Trajectory, TrajectoryMetrics
+    from oracle import msd as omsd
+
+    g = displacement_golden
+    pos, lat, ts = g[f'{tag}_positions'], g[f'{tag}_lattice'], float(g[f'{tag}_time_step'])
+    traj = Trajectory(species=['Li'] * pos.shape[1], coords=pos, lattice=lat, time_step=ts)
+    # integer-winding unwrap vs the reference's sequential cumsum: 1e-12 absolute (fractional units)
+    assert_allclose(traj.cumulative_displacements, g[f'{tag}_cumulative'], rtol=0, atol=1e-12)
+    scale = max(1.0, float(np.abs(g[f'{tag}_distances']).max()))
+    assert_allclose(traj.distances_from_base_position(), g[f'{tag}_distances'], rtol=1e-10, atol=1e-11 * scale)
+    m = TrajectoryMetrics(traj)
+    assert_allclose(m.speed(), g[f'{tag}_speed'], rtol=0, atol=1e-11 * scale)
+    assert_allclose(float(m.tracer_diffusivity(dimensions=3)), float(g[f'{tag}_tracer_diffusivity']), rtol=1e-10)
+    amp = m.amplitudes()
+    assert amp.shape == g[f'{tag}_amplitudes'].shape
+    assert_allclose(amp, g[f'{tag}_amplitudes'], rtol=0, atol=1e-10 * scale)
+    assert_allclose(float(m.vibration_amplitude()), float(g[f'{tag}_vibration_amplitude']), rtol=1e-10, atol=1e-12)
+    # MSD: vs the compensated direct oracle at 1e-10 relative; vs the reference's FFT form at the
+    # FFT form's own accuracy (it loses ~<r^2>/msd digits at small lags)
+    msd = traj.mean_squared_displacement()
+    direct = omsd.msd_direct(pos, lat)
+    assert msd.shape == g[f'{tag}_msd'].shape
+    assert_allclose(msd, direct, rtol=1e-10, atol=1e-18)
+    peak = max(1.0, float(np.abs(g[f'{tag}_msd']).max()))
+    assert_allclose(msd, g[f'{tag}_msd'], rtol=1e-9, atol=1e-11 * peak)
+
+
+@pytest.mark.parametrize('tag,res', [('unit', 0.2), ('walk', 0.2), ('walk', 0.5), ('c2', 0.2), ('c2', 0.5)])
+def test_density_volume(displacement_golden, tag, res):
+    from gemdat_b200 import Trajectory, trajectory_to_volume
+
+    g = displacement_golden
+    pos, lat = g[f'{tag}_positions'], g[f'{tag}_lattice']
+    traj = Trajectory(species=['Li'] * pos.shape[1], coords=pos, lattice=lat, time_step=1.0)
+    vol = trajectory_to_volume(traj, resolution=res)
+    assert vol.data.shape == g[f'{tag}_volume_{res}'].shape
+    assert_array_equal(vol.data, g[f'{tag}_volume_{res}'])
+    assert_array_equal(traj.to_volume(resolution=res).data, vol.data)
+
+
+def test_density_rejects_out_of_range():
+    from gemdat_b200 import Trajectory
+
+    pos = np.full((3, 2, 3), 0.5)
+    pos[1, 1, 2] = 1.0
+    traj = Trajectory(species=['Li'] * 2, coords=pos, lattice=np.eye(3) * 4, time_step=1.0)
+    traj.coords_are_displacement = False
+    with pytest.raises(AssertionError):
+        traj.to_volume(0.5)
+
+
+def test_fill_and_matrix_helpers(utils_golden):
+    from gemdat_b200.transitions import _calculate_transitions_matrix, bfill, ffill
+    import pandas as pd
+
+    u = utils_golden
+    assert_array_equal(ffill(u['arr']), u['ffill'])
+    assert_array_equal(bfill(u['arr']), u['bfill'])
+    assert_array_equal(ffill(u['arr'], axis=0), u['ffill0'])
+    assert_array_equal(bfill(u['arr'], axis=0), u['bfill0'])
+    assert_array_equal(ffill(u['rnd'], axis=0), u['rnd_ffill0'])
+    assert_array_equal(bfill(u['rnd'], axis=0), u['rnd_bfill0'])
+    assert_array_equal(ffill(u['rnd']), u['rnd_ffill1'])
+    assert_array_equal(bfill(u['rnd']), u['rnd_bfill1'])
+    ev = pd.DataFrame(u['matrix_events'], columns=['atom index', 'start site', 'destination site', 'time'])
+    m = _calculate_transitions_matrix(ev, n_sites=3)
+    assert m.dtype == int
+    assert_array_equal(m, u['matrix'])
+
+
+def test_event_and_jump_error_paths():
+    """transitions.py:442-443, 451, 470 and jumps.py:107-108."""
+    from gemdat_b200.transitions import _calculate_transition_events
+
+    const = np.zeros((6, 2), dtype=np.int64)
+    with pytest.raises(ValueError):
+        _calculate_transition_events(atom_sites=const, atom_inner_sites=const)
+    outer = const.copy()
+    outer[3:, 0] = 1
+    with pytest.raises(IndexError):
+        _calculate_transition_events(atom_sites=outer, atom_inner_sites=const)
+    inner = const.copy()
+    inner[2, 1] = 5
+    inner[4:, 0] = 1
+    ev = _calculate_transition_events(atom_sites=outer, atom_inner_sites=inner)
+    assert_array_equal(ev.to_numpy(), [[0, 0, 1, 0, 0, 2], [0, 1, 1, 0, 1, 3]])
+
+
+def test_no_jumps_found():
+    from gemdat_b200 import Sites, Trajectory
+
+    # one atom leaves its site and never arrives anywhere: events but no jumps
+    pos = np.full((8, 1, 3), 0.1)
+    pos[4:, 0, 0] = 0.5
+    traj = Trajectory(species=['Li'], coords=pos, lattice=np.eye(3) * 10.0, time_step=1e-15)
+    sites = Sites(np.eye(3) * 10.0, 'Li', [[0.1, 0.1, 0.1], [0.9, 0.9, 0.9]], labels=['a', 'a'])
+    tr = traj.transitions_between_sites(sites, 'Li', site_radius=0.5)
+    assert_array_equal(tr.events.to_numpy(), [[0, 0, -1, 0, -1, 3]])
+    with pytest.raises(ValueError, match='No jumps found'):
+        tr.jumps()
+
+
+@pytest.mark.parametrize('n_frames,n_atoms', [(1, 1), (2, 3), (7, 1), (511, 1), (513, 3), (1025, 7)])
+def test_ragged_sizes_against_oracle(n_frames, n_atoms):
+    """Odd atom-frame counts exercise the 16-byte tail of the TMA bulk copies and partial chunks."""
+    from gemdat_b200 import Sites, Trajectory
+    from oracle import cstates
+
+    rng = np.random.default_rng(n_frames * 31 + n_atoms)
+    lat = np.diag([6.0, 7.5, 5.25])
+    site_frac = np.array([[0.1, 0.1, 0.1], [0.6, 0.6, 0.6], [0.98, 0.02, 0.5], [0.3, 0.8, 0.99]])
+    pos = rng.random((n_frames, n_atoms, 3))
+    traj = Trajectory(species=['Li'] * n_atoms, coords=pos, lattice=lat, time_step=1e-15)
+    sites = Sites(lat, 'Li', site_frac, labels=['s'] * 4)
+    from gemdat_b200.transitions import _site_states_device, widen_to_host
+
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        o, i, _ = _site_states_device(sites=sites, trajectory=traj, site_radius={'': 1.4},
+                                      site_inner_fraction={'': 0.6})
+        eo, ei = cstates.calculate_atom_states_pair(
+            site_frac=site_frac, site_labels=['s'] * 4, positions=pos, lattice_matrix=lat,
+            site_radius={'': 1.4}, site_inner_fraction={'': 0.6})
+    assert_array_equal(widen_to_host(o), eo)
+    assert_array_equal(widen_to_host(i), ei)
+
+
+def test_synth_device_equals_host_replay():
+    from gemdat_b200 import synth
+
+    rec = synth.config_c2(n_frames=3000, seed=5)
+    dev = rec.device_positions().cpu().numpy()
+    assert_array_equal(dev, rec.host_positions())
+    window = rec.device_positions(1999, 300).cpu().numpy()
+    assert_array_equal(window, rec.host_positions(1999, 300))
+
+
+def test_c2_20k_frames_against_oracles():
+    """BASELINE config 2 shape (48 Li, 96 argyrodite sites) at 2*10^4 frames: states vs the C
+    oracle, events / jumps vs the numpy oracle, boundary-band counts vs the numpy oracle."""
+    from gemdat_b200 import synth
+    from oracle import cstates, events as oevents, jumps as ojumps, states as ostates
+
+    rec = synth.config_c2(n_frames=20_000, seed=20260101)
+    traj = rec.trajectory(device=True)
+    tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=0.9, site_inner_fraction=0.5)
+    pos = traj.positions.cpu().numpy()
+    kw = dict(site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels, positions=pos,
+              lattice_matrix=rec.lattice, site_radius={'': 0.9})
+    eo, ei = cstates.calculate_atom_states_pair(**kw, site_inner_fraction={'': 0.5})
+    assert_array_equal(tr.states, eo)
+    assert_array_equal(tr.inner_states, ei)
+    ev = oevents.calculate_transition_events(eo, ei)
+    assert_array_equal(tr.events.to_numpy(), ev)
+    for mr in (0, 3, 100):
+        assert_array_equal(tr.jumps(minimal_residence=mr).data.to_numpy(),
+                           ojumps.transitions_to_jumps(ev, len(traj), mr))
+    sub = dict(kw, positions=pos[:2000])
+    b12, bf32 = ostates.boundary_band_counts(**sub, site_inner_fraction={'': 1.0})
+    tr_sub = traj[:2000].transitions_between_sites(rec.sites, 'Li', site_radius=0.9, site_inner_fraction=1.0)
+    assert tr_sub.info['band_1e-12'][0] == b12
+    assert tr_sub.info['band_4e-6'][0] == bf32
+
+
+def test_c3_two_label_radii_full_parity():
+    """BASELINE config 3 shape (1008 Li, 2160 sites), per-label radii (SURVEY.md Q1/Q2 paths):
+    whole-trajectory comparison with the C oracle, including the integer_remap quirk."""
+    from gemdat_b200 import synth
+    from oracle import cstates
+
+    rec = synth.config_c3(n_frames=1500)
+    traj = rec.trajectory(device=True)
+    radius = {'24d': 0.6, '96h': 0.5}
+    inner = {'24d': 0.5, '96h': 0.8}
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=radius, site_inner_fraction=inner)
+        eo, ei = cstates.calculate_atom_states_pair(
+            site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels,
+            positions=traj.positions.cpu().numpy(), lattice_matrix=rec.lattice,
+            site_radius=radius, site_inner_fraction=inner)
+    assert not tr.info['visited_outer'].all()  # short run: the remap quirk is active
+    assert_array_equal(tr.states, eo)
+    assert_array_equal(tr.inner_states, ei)
+
+
+def test_c3_shape_properties_and_window_parity():
+    """BASELINE config 3 shape on a device-resident trajectory: sampled frame windows vs the C
+    oracle (replayed on the host from the recipe), plus size-independent invariants of the
+    event / jump tables."""
+    from gemdat_b200 import synth
+    from oracle import cstates
+
+    rec = synth.config_c3(n_frames=20_000)
+    traj = rec.trajectory(device=True)
+    tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=0.6, site_inner_fraction=0.5)
+    states, inner_states = tr.states, tr.inner_states
+    n_sites = len(rec.sites)
+    assert states.min() >= -1 and states.max() < n_sites
+    # inner sphere inside the outer sphere of the same site -> inner state is the outer one or -1
+    assert np.all((inner_states == -1) | (inner_states == states))
+    for frame0 in (0, 7777, 19_900):
+        pos = rec.host_positions(frame0, 100)
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            eo, ei = cstates.calculate_atom_states_pair(
+                site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels, positions=pos,
+                lattice_matrix=rec.lattice, site_radius={'': 0.6}, site_inner_fraction={'': 0.5})
+        assert_array_equal(states[frame0:frame0 + 100], eo)
+        assert_array_equal(inner_states[frame0:frame0 + 100], ei)
+    ev = tr.events.to_numpy()
+    # every event row is consistent with the state arrays it was cut from
+    a, t = ev[:, 0], ev[:, 5]
+    assert_array_equal(states[t, a], ev[:, 1])
+    assert_array_equal(states[t + 1, a], ev[:, 2])
+    assert_array_equal(inner_states[t, a], ev[:, 3])
+    assert_array_equal(inner_states[t + 1, a], ev[:, 4])
+    assert np.all((ev[:, 1] != ev[:, 2]) | (ev[:, 3] != ev[:, 4]))
+    assert np.all(np.diff(a) >= 0) and np.all(np.diff(t)[np.diff(a) == 0] > 0)
+    changed = (states[1:] != states[:-1]) | (inner_states[1:] != inner_states[:-1])
+    keep = (states[1:] != states[:-1]).any(axis=0)  # atoms whose outer state never changes are skipped
+    assert len(ev) == int(changed[:, keep].sum())
+    jumps = tr.jumps().data.to_numpy()
+    assert np.all(jumps[:, 1] != jumps[:, 2]) and np.all(jumps[:, 4] > jumps[:, 3])
+    assert int(tr.jumps().matrix().sum()) == len(jumps)

@@ -1,0 +1,164 @@
+"""The oracle against fixtures produced by executing the reference (tests/golden/make_golden.py)
+and against the reference's own unit-test constants.  CPU only."""
+
+from __future__ import annotations
+
+import warnings
+
+import numpy as np
+import pytest
+from numpy.testing import assert_allclose, assert_array_equal
+
+from oracle import displ, events, fill, jumps, msd, radius, states, volume
+from oracle.pmg import Lattice
+
+
+def _states(case, fn, fraction):
+    pos = case['positions'][:, case['floating_mask']]
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        return fn(
+            site_frac=case['site_frac'], site_labels=case['labels'], positions=pos,
+            lattice_matrix=case['lattice'], site_radius=case['site_radius'],
+            site_inner_fraction=fraction,
+        )
+
+
+def test_states_kdtree_oracle_matches_reference(pipeline_case):
+    c = pipeline_case
+    outer = {k: 1.0 for k in c['site_radius']}
+    assert_array_equal(_states(c, states.calculate_atom_states, outer), c['states'])
+    assert_array_equal(_states(c, states.calculate_atom_states, c['inner_fraction']), c['inner_states'])
+
+
+def test_states_bruteforce_oracle_matches_reference(pipeline_case):
+    c = pipeline_case
+    outer = {k: 1.0 for k in c['site_radius']}
+    assert_array_equal(_states(c, states.calculate_atom_states_bruteforce, outer), c['states'])
+    assert_array_equal(
+        _states(c, states.calculate_atom_states_bruteforce, c['inner_fraction']), c['inner_states']
+    )
+
+
+def test_events_match_reference(pipeline_case):
+    c = pipeline_case
+    ev = events.calculate_transition_events(c['states'], c['inner_states'])
+    assert_array_equal(ev, c['events'])
+    assert list(c['event_columns']) == events.EVENT_COLUMNS
+
+
+def test_fill_matches_reference(pipeline_case):
+    c = pipeline_case
+    assert_array_equal(fill.ffill(c['states'], axis=0), c['states_prev'])
+    assert_array_equal(fill.bfill(c['states'], axis=0), c['states_next'])
+
+
+def test_jumps_match_reference(pipeline_case):
+    c = pipeline_case
+    n_frames = c['positions'].shape[0]
+    for key in [k for k in c if k.startswith('jumps_') and k[6:].isdigit()]:
+        mr = int(key[6:])
+        j = jumps.transitions_to_jumps(c['events'], n_frames, mr)
+        assert_array_equal(j, c[key])
+        n_sites = len(c['site_frac'])
+        m = jumps.transitions_matrix(j[:, 1:3], n_sites)
+        assert_array_equal(m, c[f'{key}_matrix'])
+        pdist = Lattice(c['lattice']).get_all_distances(c['site_frac'], c['site_frac'])
+        d = jumps.jump_diffusivity(
+            pdist=pdist, matrix=m, dimensions=3, n_floating=int(c['floating_mask'].sum()),
+            total_time=n_frames * 2e-15,
+        )
+        assert_allclose(d, float(c[f'{key}_diffusivity']), rtol=1e-12)
+    assert list(c['jump_columns']) == jumps.JUMP_COLUMNS
+
+
+def test_event_matrix_matches_reference(pipeline_case):
+    c = pipeline_case
+    assert_array_equal(jumps.transitions_matrix(c['events'][:, 1:3], len(c['site_frac'])), c['matrix'])
+
+
+def test_default_radius_matches_reference():
+    from conftest import load_golden
+
+    c = load_golden('pipeline_c2_default_radius')
+    vib = displ.vibration_amplitude(c['positions'], c['lattice'])
+    r = radius.radius_from_vibration_amplitude(c['site_frac'], c['lattice'], vib)
+    assert_allclose(r, float(c['radius_values'][0]), rtol=1e-13)
+
+
+@pytest.mark.parametrize('tag', ['unit', 'walk', 'c2'])
+def test_displacement_path_matches_reference(displacement_golden, tag):
+    g = displacement_golden
+    pos, lat, ts = g[f'{tag}_positions'], g[f'{tag}_lattice'], float(g[f'{tag}_time_step'])
+    assert_array_equal(displ.cumulative_displacements(pos), g[f'{tag}_cumulative'])
+    assert_allclose(displ.distances_from_base_position(pos, lat), g[f'{tag}_distances'], rtol=1e-14, atol=1e-15)
+    assert_allclose(displ.speed(pos, lat), g[f'{tag}_speed'], rtol=1e-12, atol=1e-14)
+    assert_allclose(displ.amplitudes(g[f'{tag}_speed']), g[f'{tag}_amplitudes'], rtol=1e-13, atol=1e-15)
+    assert_allclose(displ.vibration_amplitude(pos, lat), float(g[f'{tag}_vibration_amplitude']), rtol=1e-12, atol=1e-15)
+    assert_allclose(
+        displ.tracer_diffusivity(pos, lat, time_step=ts), float(g[f'{tag}_tracer_diffusivity']), rtol=1e-12
+    )
+
+
+@pytest.mark.parametrize('tag', ['unit', 'walk', 'c2'])
+def test_msd_matches_reference(displacement_golden, tag):
+    g = displacement_golden
+    pos, lat = g[f'{tag}_positions'], g[f'{tag}_lattice']
+    ref = g[f'{tag}_msd']
+    assert_allclose(msd.msd_fft(pos, lat), ref, rtol=1e-12, atol=1e-12)
+    # the direct definition agrees with the reference's FFT form to the FFT form's own accuracy
+    direct = msd.msd_direct(pos, lat)
+    assert_allclose(direct, ref, rtol=1e-9, atol=1e-11 * max(1.0, float(np.abs(ref).max())))
+
+
+@pytest.mark.parametrize('tag,res', [('unit', 0.2), ('walk', 0.2), ('walk', 0.5), ('c2', 0.2), ('c2', 0.5)])
+def test_volume_matches_reference(displacement_golden, tag, res):
+    g = displacement_golden
+    v = volume.trajectory_to_volume(g[f'{tag}_positions'], g[f'{tag}_lattice'], res)
+    assert_array_equal(v, g[f'{tag}_volume_{res}'])
+    assert v.sum() == g[f'{tag}_positions'].shape[0] * g[f'{tag}_positions'].shape[1]
+
+
+def test_reference_unit_test_constants(displacement_golden):
+    """Constants asserted by the reference's own tests (tests/trajectory_test.py:65-163,
+    tests/metrics_test.py:35,41)."""
+    pos, lat = displacement_golden['unit_positions'], displacement_golden['unit_lattice']
+    assert_allclose(displ.displacements(pos[:, [0, 3]])[:, 0, 0], [0.0, 0.2, 0.2, 0.2, 0.3])
+    assert_allclose(displ.distances_from_base_position(pos[:, :2], lat),
+                    [[0.0, 0.2, 0.4, 0.6, 0.9], [0.0, 0.0, 0.0, 0.0, 0.0]])
+    m = msd.msd_fft(pos, lat)
+    assert_allclose(m[0], [0.0, 0.0525, 0.19, 0.425, 0.81], atol=1e-15)
+    assert_allclose(m.mean(), 0.073875)
+    assert_allclose(displ.speed(pos[:, :1], lat), [[0.0, 0.2, 0.2, 0.2, 0.3]])
+    assert_allclose(displ.amplitudes(displ.speed(pos[:, :1], lat)), [0.9])
+
+
+def test_utils_match_reference(utils_golden):
+    """tests/utils_test.py:17-85 and tests/sites_test.py:9-26 of the reference."""
+    u = utils_golden
+    assert_array_equal(fill.ffill(u['arr']), [[5, 5, 5, 7, 2], [3, 3, 1, 8, 8], [4, 9, 6, 6, 6]])
+    assert_array_equal(fill.bfill(u['arr']), [[5, 7, 7, 7, 2], [3, 1, 1, 8, -1], [4, 9, 6, -1, -1]])
+    assert_array_equal(fill.ffill(u['arr'], axis=0), [[5, -1, -1, 7, 2], [3, -1, 1, 8, 2], [4, 9, 6, 8, 2]])
+    assert_array_equal(fill.bfill(u['arr'], axis=0), [[5, 9, 1, 7, 2], [3, 9, 1, 8, -1], [4, 9, 6, -1, -1]])
+    for key, fn, kw in (('rnd_ffill0', fill.ffill, {'axis': 0}), ('rnd_bfill0', fill.bfill, {'axis': 0}),
+                        ('rnd_ffill1', fill.ffill, {}), ('rnd_bfill1', fill.bfill, {})):
+        assert_array_equal(fn(u['rnd'], **kw), u[key])
+    assert_array_equal(fill.integer_remap(np.array([4, 2, 1, 3]), key=np.array([10, 20, 30, 40])), u['remap'])
+    assert_array_equal(jumps.transitions_matrix(u['matrix_events'][:, 1:3], 3), [[0, 1, 0], [2, 0, 0], [1, 1, 0]])
+    assert_array_equal(u['matrix'], [[0, 1, 0], [2, 0, 0], [1, 1, 0]])
+
+
+def test_event_quirks():
+    """transitions.py:442-443, 451, 470."""
+    const = np.zeros((6, 2), dtype=np.int64)
+    with pytest.raises(ValueError):
+        events.calculate_transition_events(const, const)
+    outer = const.copy()
+    outer[3:, 0] = 1
+    with pytest.raises(IndexError):
+        events.calculate_transition_events(outer, const)
+    inner = const.copy()
+    inner[2, 1] = 5  # inner-only change on an atom whose outer state is constant: skipped
+    inner[4:, 0] = 1
+    ev = events.calculate_transition_events(outer, inner)
+    assert_array_equal(ev, [[0, 0, 1, 0, 0, 2], [0, 1, 1, 0, 1, 3]])
