@@ -219,6 +219,11 @@ __global__ void __launch_bounds__(kThreads, 2)
                 f2 = __ldg(gp + 2);
             }
         }
+        // The slot is refilled by the async proxy (TMA) once all 512 arrivals are in.  The
+        // reads above are generic-proxy LDS: without this cross-proxy fence the arrive can
+        // overtake a still-queued LDS and the refill lands first (observed on B200: whole
+        // warps saw the data of chunk i+4).
+        gd_fence_proxy_async();
         gd_mbar_arrive(&empty[slot]);
         if (!active) continue;
 

@@ -275,6 +275,35 @@ def test_c3_two_label_radii_full_parity():
     assert_array_equal(tr.inner_states, ei)
 
 
+def test_k1_repeatable_under_pipeline_pressure():
+    """The TMA ring of K1 is refilled by the async proxy while warps read it through the
+    generic proxy; a missing cross-proxy fence showed up as whole warps reading the data of a
+    later chunk, a few times in ten runs.  Many short launches + one long one, all identical."""
+    from gemdat_b200 import synth
+    from gemdat_b200.transitions import _site_states_device
+    from oracle import cstates
+
+    rec = synth.config_c3(n_frames=1500)
+    traj = rec.trajectory(device=True)
+    kw = dict(sites=rec.sites, trajectory=traj, site_radius={'': 0.6}, site_inner_fraction={'': 0.5})
+    eo, ei = cstates.calculate_atom_states_pair(
+        site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels,
+        positions=traj.positions.cpu().numpy(), lattice_matrix=rec.lattice,
+        site_radius={'': 0.6}, site_inner_fraction={'': 0.5})
+    eo_d = torch.from_numpy(eo.astype(np.int32)).cuda()
+    ei_d = torch.from_numpy(ei.astype(np.int32)).cuda()
+    for _ in range(25):
+        o, i, _ = _site_states_device(**kw)
+        assert bool((o == eo_d).all()) and bool((i == ei_d).all())
+    big = synth.config_c3(n_frames=40_000).trajectory(device=True)
+    kw['trajectory'] = big
+    o1, i1, _ = _site_states_device(**kw)
+    o1, i1 = o1.clone(), i1.clone()
+    for _ in range(3):
+        o2, i2, _ = _site_states_device(**kw)
+        assert bool((o1 == o2).all()) and bool((i1 == i2).all())
+
+
 def test_c3_shape_properties_and_window_parity():
     """BASELINE config 3 shape on a device-resident trajectory: sampled frame windows vs the C
     oracle (replayed on the host from the recipe), plus size-independent invariants of the
