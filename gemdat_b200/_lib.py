@@ -57,7 +57,7 @@ SIGNATURES = {
     'gd_version': (C.c_int, []),
     'gd_sm_count': (C.c_int, []),
     'gd_sitegrid_build': (C.c_int, [_p, _p, _p, _i32, _p, _p, _i32, _p, _sz, C.POINTER(_sz)]),
-    'gd_site_states': (C.c_int, [_p, _i64, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_site_states': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     'gd_remap_states': (C.c_int, [_p, _i64, _p, _i32, _p]),
     'gd_widen_i32_i64': (C.c_int, [_p, _p, _i64, _p]),
     'gd_events_work_elems': (_i64, [_i64, _i32]),
@@ -66,8 +66,9 @@ SIGNATURES = {
     'gd_events_fill': (C.c_int, [_p, _p, _i64, _i32, _p, _p, _p, _p, _p, _i64, _p, _p]),
     'gd_events_merge': (C.c_int, [_p, _p, _p, _i32, _p, _p]),
     'gd_fill_states': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p, _p]),
-    'gd_jumps_count': (C.c_int, [_p, _p, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
-    'gd_jumps_fill': (C.c_int, [_p, _p, _i32, _i64, _i64, _p, _p, _p]),
+    'gd_jumps_work_bytes': (_i64, [_i64, _i32]),
+    'gd_jumps_count': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
+    'gd_jumps_fill': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _p]),
     'gd_pair_matrix': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),
     'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -49,6 +49,28 @@ const GdDeviceInfo &gd_device_info();
 
 static inline int64_t gd_ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// Frame-chunk geometry shared by K1 (fused event count), K2 (events, fills) and the
+// scans: the frame axis is cut into chunks of f frames, f a power of two in [32, 256]
+// chosen so that a 10^9 atom-frame shard gives ~4*10^6 (chunk, atom) segments.
+struct GdChunks {
+    int64_t n_frames;
+    int32_t n_atoms;
+    int32_t f;         // frames per chunk
+    int64_t n_chunks;  // ceil(n_frames / f)
+};
+static inline GdChunks gd_chunks(int64_t n_frames, int32_t n_atoms) {
+    GdChunks g;
+    g.n_frames = n_frames;
+    g.n_atoms = n_atoms;
+    const int64_t want = (n_frames * (int64_t)n_atoms) >> 20;
+    int32_t f = 32;
+    while (f < want && f < 256) f <<= 1;
+    g.f = f;
+    g.n_chunks = (n_frames + f - 1) / f;
+    if (g.n_chunks < 1) g.n_chunks = 1;
+    return g;
+}
+
 #ifdef __CUDACC__
 
 // ---------------------------------------------------------------- mbarrier / TMA (sm_90+)

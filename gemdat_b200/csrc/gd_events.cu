@@ -5,45 +5,37 @@
 // a Python loop over atoms with np.roll/np.nonzero/np.unique inside) and
 // ffill/bfill (src/gemdat/utils.py:59-98).
 //
-// The frame axis is cut into chunks of F frames; one thread owns one (chunk, atom)
-// column segment, so a warp reads 32 neighbouring atoms of the same frame (one
-// coalesced 128-byte line per state array per step) and keeps the previous row in
-// registers: every state is read exactly once per pass.  Rows come out sorted by
-// (atom, time) through a count -> per-atom block scan -> fill sequence; the row
-// offsets live in the caller's scratch (atom-major so the scan is contiguous).
+// The frame axis is cut into chunks of f frames (gd_chunks, shared with K1); one thread
+// owns one (chunk, atom) column segment, so a warp reads 32 neighbouring atoms of the
+// same frame (one coalesced 128-byte piece per state array per step) and keeps the
+// previous row in registers: every state is read exactly once per pass.  Rows come
+// out sorted by (atom, time) through a count -> per-atom block scan -> fill sequence;
+// the row offsets live in the caller's scratch (atom-major so the scan is contiguous).
+// On the fused path the count pass is free: K1 (gd_site_states) produces the per-segment
+// counts while the states are still in registers, and only the fill pass re-reads them.
 //
-// Algorithmic traffic: 8 B read per atom-frame per pass (count, fill); events are
-// O(1e-2) of the atom-frames.
+// Algorithmic traffic: 8 B read per atom-frame per pass; events are O(1e-2) of the
+// atom-frames (24 B each).
 #include "gd_common.cuh"
 
 namespace {
 
-// frames per chunk: ~2^18 (chunk, atom) items in flight
-__host__ __device__ inline int64_t chunk_frames(int64_t n_frames, int32_t n_atoms) {
-    int64_t want = (n_frames * (int64_t)n_atoms) >> 18;
-    int64_t f = 8;
-    while (f < want && f < 1024) f <<= 1;
-    return f;
-}
-
-struct Geometry {
-    int64_t n_frames;
-    int32_t n_atoms;
-    int64_t f;         // frames per chunk
-    int64_t n_chunks;
-};
-
-inline Geometry geometry(int64_t n_frames, int32_t n_atoms) {
-    Geometry g;
-    g.n_frames = n_frames;
-    g.n_atoms = n_atoms;
-    g.f = chunk_frames(n_frames, n_atoms);
-    g.n_chunks = gd_ceil_div(n_frames, g.f);
-    return g;
-}
+typedef GdChunks Geometry;
+inline Geometry geometry(int64_t n_frames, int32_t n_atoms) { return gd_chunks(n_frames, n_atoms); }
 
 // ---------------------------------------------------------------- events: count / fill
 
+__device__ __forceinline__ void put_event(int32_t *__restrict__ events, int64_t row, int32_t a,
+                                          int32_t po, int32_t no, int32_t pi, int32_t ni, int32_t t) {
+    int2 *e = reinterpret_cast<int2 *>(events + row * 6);  // rows are 24 B: 8-byte aligned
+    e[0] = make_int2(a, po);
+    e[1] = make_int2(no, pi);
+    e[2] = make_int2(ni, t);
+}
+
+// One thread owns one (chunk, atom) column segment; a warp reads 32 neighbouring atoms of
+// the same frame (one coalesced 128-byte row piece per state array per step) and keeps the
+// previous row in registers: every state is read once per pass.
 template <bool kFill>
 __global__ void __launch_bounds__(256)
     k_events(const int32_t *__restrict__ so, const int32_t *__restrict__ si, Geometry g,
@@ -52,53 +44,63 @@ __global__ void __launch_bounds__(256)
              const uint8_t *__restrict__ changed_global, const int64_t *__restrict__ atom_offsets,
              int64_t frame0, int32_t *__restrict__ events) {
     const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (item >= g.n_chunks * g.n_atoms) return;
-    const int64_t c = item / g.n_atoms;
-    const int32_t a = (int32_t)(item - c * g.n_atoms);
+    const bool on = item < g.n_chunks * g.n_atoms;
+    const int64_t c = on ? item / g.n_atoms : 0;
+    const int32_t a = on ? (int32_t)(item - c * g.n_atoms) : 0;
     const int64_t t0 = c * g.f;
     const int64_t t1 = min(g.n_frames, t0 + g.f);
     const int64_t A = g.n_atoms;
 
     int64_t row = 0;
     if (kFill) {
-        if (!changed_global[a]) return;  // outer state never changes: atom is skipped
-        row = atom_offsets[a] + work[(int64_t)a * g.n_chunks + c];
+        // rows of this segment: [first, last) in the atom's block of the table
+        int32_t first = 0, last = 0;
+        if (on && changed_global[a]) {  // outer state never changes: atom is skipped
+            const int32_t *w = work + (int64_t)a * g.n_chunks + c;
+            first = w[0];
+            last = (c + 1 < g.n_chunks) ? w[1] : (int32_t)(atom_offsets[a + 1] - atom_offsets[a]);
+            row = atom_offsets[a] + first;
+        }
+        const bool mine = last > first;
+        if (!__any_sync(0xffffffffu, mine)) return;  // nothing happens to these 32 atoms here
+        if (!mine) return;
+    } else if (!on) {
+        return;
     }
 
-    int32_t po = so[t0 * A + a];
-    int32_t pi = si[t0 * A + a];
+    const int32_t *qo = so + t0 * A + a;
+    const int32_t *qi = si + t0 * A + a;
+    int32_t po = *qo, pi = *qi;
     int cnt = 0;
     bool ch_o = false, ch_i = false;
-#pragma unroll 4
-    for (int64_t t = t0; t < t1; ++t) {
-        int32_t no, ni;
-        if (t + 1 < g.n_frames) {
-            no = so[(t + 1) * A + a];
-            ni = si[(t + 1) * A + a];
-        } else if (next_o != nullptr) {
-            no = next_o[a];
-            ni = next_i[a];
-        } else {
-            break;  // last frame of the trajectory: the np.roll wrap-around is dropped
-        }
+    // transitions t -> t+1 with both frames inside this shard
+    const int64_t t_in = min(t1, g.n_frames - 1);
+#pragma unroll 8
+    for (int64_t t = t0; t < t_in; ++t) {
+        qo += A;
+        qi += A;
+        const int32_t no = *qo, ni = *qi;
         const bool d_o = no != po, d_i = ni != pi;
         if (d_o | d_i) {
-            if (kFill) {
-                int32_t *e = events + row * 6;
-                e[0] = a;
-                e[1] = po;
-                e[2] = no;
-                e[3] = pi;
-                e[4] = ni;
-                e[5] = (int32_t)(frame0 + t);
-                ++row;
-            }
+            if (kFill) put_event(events, row++, a, po, no, pi, ni, (int32_t)(frame0 + t));
             ++cnt;
         }
         ch_o |= d_o;
         ch_i |= d_i;
         po = no;
         pi = ni;
+    }
+    // last frame of the shard: needs the first row of the following shard; without one the
+    // np.roll wrap-around pseudo event of the reference is dropped (transitions.py:439-452)
+    if (t1 == g.n_frames && next_o != nullptr) {
+        const int32_t no = next_o[a], ni = next_i[a];
+        const bool d_o = no != po, d_i = ni != pi;
+        if (d_o | d_i) {
+            if (kFill) put_event(events, row++, a, po, no, pi, ni, (int32_t)(frame0 + g.n_frames - 1));
+            ++cnt;
+        }
+        ch_o |= d_o;
+        ch_i |= d_i;
     }
     if (!kFill) {
         work[(int64_t)a * g.n_chunks + c] = cnt;

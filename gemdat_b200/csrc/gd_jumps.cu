@@ -5,10 +5,10 @@
 // (src/gemdat/transitions.py:812-834: np.unique(axis=0) + fancy assignment).
 //
 // The conversion is a per-atom sequential state machine over that atom's events
-// (already contiguous and time-ordered in the K2 table), so atoms run in parallel:
-// one warp per atom streams the rows with coalesced 128-bit loads into shared
-// memory and lane 0 steps the machine.  Two phases (count, fill) give the exact
-// output size without any allocation in the library.
+// (already contiguous and time-ordered in the K2 table).  Atoms run in parallel, and so
+// do segments of 512 events of the same atom (speculate / chain / fill, see below).
+// Two phases (count, fill) give the exact output size without any allocation in the
+// library.
 #include "gd_common.cuh"
 
 namespace {
@@ -74,62 +74,249 @@ struct JumpMachine {
     }
 };
 
-constexpr int kWarpsPerBlock = 4;
-constexpr int kRowsPerBatch = 128;  // 128 rows * 24 B = 3 KiB per warp
+// ---------------------------------------------------------------- time-parallel conversion
+//
+// The machine is sequential per atom, but its state forgets the past quickly: after any
+// "departure" event (start site != NOSITE and != destination site) the pending `from`
+// is overwritten by that event and a pending candidate has been closed by it, so the state
+// is a function of that event alone.  An atom's events are therefore cut into segments of
+// kSeg rows that run in parallel:
+//   1. k_jumps_spec   (thread per segment) runs the machine from the EMPTY state, records
+//      the row after which its state can no longer depend on the true entry state (the
+//      first departure), the jumps it emits after that row, and its exit state;
+//   2. k_jumps_chain  (thread per atom) walks the atom's segments in order with the TRUE
+//      state, replaying only each segment's short prefix (in lockstep with the speculative
+//      run until both states are equal -- so odd inputs degrade to sequential, never to
+//      wrong), and leaves the true entry state and jump count of every segment;
+//   3. an exclusive scan of the counts, then k_jumps_fill (thread per segment) re-runs
+//      each segment from its true entry state and writes its jumps in place.
+// Output order = segment order = (atom, time), exactly the reference's.
 
-template <bool kFill>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
-    k_jumps(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
-            int32_t n_atoms, int64_t n_frames_total, int64_t minimal_residence,
-            int64_t *__restrict__ counts, int32_t *__restrict__ jumps) {
-    __shared__ int32_t rows[kWarpsPerBlock][kRowsPerBatch * 6];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int32_t a = blockIdx.x * kWarpsPerBlock + warp;
-    if (a >= n_atoms) return;
-    const int64_t r0 = atom_offsets[a], r1 = atom_offsets[a + 1];
-    int64_t out = kFill ? counts[a] : 0;  // counts hold exclusive offsets in the fill phase
-    int64_t n_out = 0;
-    JumpMachine m(minimal_residence);
-    auto emit = [&](const Jump &j) {
-        if (kFill) {
-            int32_t *o = jumps + (out + n_out) * 6;
-            o[0] = j.atom;
-            o[1] = j.start_site;
-            o[2] = j.dest_site;
-            o[3] = j.start_time;
-            o[4] = j.stop_time;
-            o[5] = j.residence;
-        }
-        ++n_out;
-    };
-    for (int64_t base = r0; base < r1; base += kRowsPerBatch) {
-        const int n_rows = (int)min((int64_t)kRowsPerBatch, r1 - base);
-        const int32_t *src = events + base * 6;
-        for (int k = lane; k < n_rows * 6; k += 32) rows[warp][k] = __ldg(src + k);
-        __syncwarp();
-        if (lane == 0) {
-            for (int r = 0; r < n_rows; ++r) {
-                const int32_t *e = &rows[warp][r * 6];
-                m.step(e[0], e[1], e[2], e[4], e[5], emit);
-            }
-        }
-        __syncwarp();
-    }
-    if (lane == 0) {
-        if (m.have_cand) m.close_candidate(n_frames_total, emit);  // jumps.py:97-105
-        if (!kFill) counts[a] = n_out;
-    }
+constexpr int kSeg = 512;  // event rows per segment
+
+struct PackedState {  // 40 bytes
+    int32_t have;  // bit 0: from pending, bit 1: candidate pending
+    int32_t f_start, f_dest, f_time;
+    int32_t c_start, c_dest, c_inner, c_start_time, c_stop_time;
+    int32_t pad;
+};
+
+__device__ __forceinline__ PackedState pack(const JumpMachine &m) {
+    PackedState s;
+    s.have = (m.have_from ? 1 : 0) | (m.have_cand ? 2 : 0);
+    s.f_start = m.from_start_site;
+    s.f_dest = m.from_dest_site;
+    s.f_time = m.from_start_time;
+    s.c_start = m.c_start_site;
+    s.c_dest = m.c_dest_site;
+    s.c_inner = m.c_dest_inner;
+    s.c_start_time = m.c_start_time;
+    s.c_stop_time = m.c_stop_time;
+    s.pad = 0;
+    return s;
 }
 
-// single block exclusive scan, counts[0..n) -> offsets, counts[n] = total
-__global__ void __launch_bounds__(1024) k_scan_counts(int64_t *__restrict__ c, int32_t n) {
+__device__ __forceinline__ void unpack(JumpMachine &m, const PackedState &s, int32_t atom) {
+    m.have_from = (s.have & 1) != 0;
+    m.have_cand = (s.have & 2) != 0;
+    m.from_start_site = s.f_start;
+    m.from_dest_site = s.f_dest;
+    m.from_start_time = s.f_time;
+    m.c_atom = atom;
+    m.c_start_site = s.c_start;
+    m.c_dest_site = s.c_dest;
+    m.c_dest_inner = s.c_inner;
+    m.c_start_time = s.c_start_time;
+    m.c_stop_time = s.c_stop_time;
+}
+
+__device__ __forceinline__ bool same_state(const JumpMachine &x, const JumpMachine &y) {
+    if (x.have_from != y.have_from || x.have_cand != y.have_cand) return false;
+    if (x.have_from && (x.from_start_site != y.from_start_site || x.from_dest_site != y.from_dest_site ||
+                        x.from_start_time != y.from_start_time))
+        return false;
+    if (x.have_cand && (x.c_start_site != y.c_start_site || x.c_dest_site != y.c_dest_site ||
+                        x.c_dest_inner != y.c_dest_inner || x.c_start_time != y.c_start_time ||
+                        x.c_stop_time != y.c_stop_time))
+        return false;
+    return true;
+}
+
+struct Row {
+    int32_t atom, s0, s1, i0, i1, t;
+};
+__device__ __forceinline__ Row load_row(const int32_t *__restrict__ events, int64_t r) {
+    const int2 *e = reinterpret_cast<const int2 *>(events + r * 6);
+    const int2 a = __ldg(e), b = __ldg(e + 1), c = __ldg(e + 2);
+    return Row{a.x, a.y, b.x, b.y, c.x, c.y};
+}
+
+struct SegSpec {  // 48 bytes: result of the speculative run of one segment
+    PackedState exit;
+    int32_t sync;     // rows [0, sync) must be replayed from the true entry state
+    int32_t n_after;  // jumps the speculative run emits in rows [sync, n)
+};
+
+// segment bookkeeping: seg_off[a] = first segment of atom a (exclusive scan of
+// ceil(n_events_a / kSeg)); single block
+__global__ void __launch_bounds__(1024)
+    k_seg_offsets(const int64_t *__restrict__ atom_offsets, int32_t n_atoms, int64_t *__restrict__ seg_off) {
     __shared__ int64_t warp_tot[32];
     __shared__ int64_t running_s;
     if (threadIdx.x == 0) running_s = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < n; base += 1024) {
+    for (int base = 0; base < n_atoms; base += 1024) {
         const int idx = base + threadIdx.x;
+        const int64_t v = idx < n_atoms ? (atom_offsets[idx + 1] - atom_offsets[idx] + kSeg - 1) / kSeg : 0;
+        int64_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int64_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        int64_t warp_base = 0;
+        for (int w = 0; w < warp; ++w) warp_base += warp_tot[w];
+        const int64_t running = running_s;
+        __syncthreads();
+        if (idx < n_atoms) seg_off[idx] = running + warp_base + incl - v;
+        if (threadIdx.x == 1023) running_s = running + warp_base + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) seg_off[n_atoms] = running_s;
+}
+
+// (atom, first row, row count) of global segment `seg`
+__device__ __forceinline__ bool locate_segment(int64_t seg, const int64_t *__restrict__ seg_off,
+                                               const int64_t *__restrict__ atom_offsets, int32_t n_atoms,
+                                               int32_t &atom, int64_t &r0, int &n) {
+    if (seg >= seg_off[n_atoms]) return false;
+    int lo = 0, hi = n_atoms;  // last atom with seg_off[atom] <= seg
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (seg_off[mid] <= seg) lo = mid; else hi = mid;
+    }
+    atom = lo;
+    const int64_t j = seg - seg_off[lo];
+    r0 = atom_offsets[lo] + j * kSeg;
+    const int64_t left = atom_offsets[lo + 1] - r0;
+    n = (int)(left < kSeg ? left : kSeg);
+    return true;
+}
+
+__global__ void __launch_bounds__(128)
+    k_jumps_spec(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
+                 const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t minimal_residence,
+                 SegSpec *__restrict__ spec) {
+    const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int32_t atom;
+    int64_t r0;
+    int n;
+    if (!locate_segment(seg, seg_off, atom_offsets, n_atoms, atom, r0, n)) return;
+    JumpMachine m(minimal_residence);
+    int sync = n, n_after = 0;
+    bool synced = false;
+    auto emit = [&](const Jump &) { n_after += synced ? 1 : 0; };
+    for (int k = 0; k < n; ++k) {
+        const Row e = load_row(events, r0 + k);
+        m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+        if (!synced && e.s0 != GD_NOSITE && e.s0 != e.s1) {
+            synced = true;
+            sync = k + 1;
+        }
+    }
+    SegSpec out;
+    out.exit = pack(m);
+    out.sync = sync;
+    out.n_after = n_after;
+    spec[seg] = out;
+}
+
+__global__ void __launch_bounds__(64)
+    k_jumps_chain(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
+                  const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
+                  int64_t minimal_residence, const SegSpec *__restrict__ spec,
+                  PackedState *__restrict__ entry, int64_t *__restrict__ counts) {
+    const int32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n_atoms) return;
+    const int64_t s0 = seg_off[a], s1 = seg_off[a + 1];
+    const int64_t row_end = atom_offsets[a + 1];
+    JumpMachine truth(minimal_residence);
+    truth.c_atom = a;
+    for (int64_t seg = s0; seg < s1; ++seg) {
+        entry[seg] = pack(truth);
+        const int64_t r0 = atom_offsets[a] + (seg - s0) * kSeg;
+        const int n = (int)min((int64_t)kSeg, row_end - r0);
+        const SegSpec sp = spec[seg];
+        JumpMachine guess(minimal_residence);
+        int64_t n_true = 0;
+        int n_guess_after = 0;  // jumps of the speculative run in rows [sync, k)
+        int k = 0;
+        bool merged = false;
+        auto emit_true = [&](const Jump &) { ++n_true; };
+        for (; k < n; ++k) {
+            if (k >= sp.sync && same_state(truth, guess)) {
+                merged = true;
+                break;
+            }
+            const bool after = k >= sp.sync;
+            auto emit_guess = [&](const Jump &) { n_guess_after += after ? 1 : 0; };
+            const Row e = load_row(events, r0 + k);
+            truth.step(e.atom, e.s0, e.s1, e.i1, e.t, emit_true);
+            guess.step(e.atom, e.s0, e.s1, e.i1, e.t, emit_guess);
+        }
+        if (merged || same_state(truth, guess)) {
+            // from here on the speculative run is the true run
+            n_true += sp.n_after - n_guess_after;
+            unpack(truth, sp.exit, a);
+        }
+        // (otherwise the whole segment was replayed and `truth` already is its exit state)
+        if (seg + 1 == s1 && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
+        counts[seg] = n_true;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+    k_jumps_fill(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
+                 const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
+                 int64_t minimal_residence, const PackedState *__restrict__ entry,
+                 const int64_t *__restrict__ counts, int32_t *__restrict__ jumps) {
+    const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int32_t atom;
+    int64_t r0;
+    int n;
+    if (!locate_segment(seg, seg_off, atom_offsets, n_atoms, atom, r0, n)) return;
+    const int64_t out0 = counts[seg], out1 = counts[seg + 1];  // exclusive offsets after the scan
+    if (out1 == out0) return;
+    JumpMachine m(minimal_residence);
+    unpack(m, entry[seg], atom);
+    int64_t out = out0;
+    auto emit = [&](const Jump &j) {
+        int2 *o = reinterpret_cast<int2 *>(jumps + out * 6);
+        o[0] = make_int2(j.atom, j.start_site);
+        o[1] = make_int2(j.dest_site, j.start_time);
+        o[2] = make_int2(j.stop_time, j.residence);
+        ++out;
+    };
+    for (int k = 0; k < n && out < out1; ++k) {
+        const Row e = load_row(events, r0 + k);
+        m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+    }
+    const bool last_of_atom = r0 + n == atom_offsets[atom + 1];
+    if (last_of_atom && m.have_cand && out < out1) m.close_candidate(n_frames_total, emit);
+}
+
+// single block exclusive scan, c[0..n) -> offsets, c[n] = total
+__global__ void __launch_bounds__(1024) k_scan_counts(int64_t *__restrict__ c, int64_t n) {
+    __shared__ int64_t warp_tot[32];
+    __shared__ int64_t running_s;
+    if (threadIdx.x == 0) running_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int64_t idx = base + threadIdx.x;
         const int64_t v = idx < n ? c[idx] : 0;
         int64_t incl = v;
 #pragma unroll
@@ -148,6 +335,33 @@ __global__ void __launch_bounds__(1024) k_scan_counts(int64_t *__restrict__ c, i
         __syncthreads();
     }
     if (threadIdx.x == 0) c[n] = running_s;
+}
+
+// scratch layout inside the caller's d_work (all 16-byte aligned)
+struct JumpWork {
+    int64_t max_segs;
+    int64_t *seg_off;    // [n_atoms + 1]
+    int64_t *counts;     // [max_segs + 1]
+    SegSpec *spec;       // [max_segs]
+    PackedState *entry;  // [max_segs]
+    size_t bytes;
+};
+inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
+    auto up = [](size_t x) { return (x + 15) & ~size_t(15); };
+    JumpWork w;
+    w.max_segs = n_events / kSeg + n_atoms + 1;
+    unsigned char *p = static_cast<unsigned char *>(base);
+    size_t off = 0;
+    w.seg_off = reinterpret_cast<int64_t *>(p + off);
+    off += up((size_t)(n_atoms + 1) * 8);
+    w.counts = reinterpret_cast<int64_t *>(p + off);
+    off += up((size_t)(w.max_segs + 1) * 8);
+    w.spec = reinterpret_cast<SegSpec *>(p + off);
+    off += up((size_t)w.max_segs * sizeof(SegSpec));
+    w.entry = reinterpret_cast<PackedState *>(p + off);
+    off += up((size_t)w.max_segs * sizeof(PackedState));
+    w.bytes = off;
+    return w;
 }
 
 // ---------------------------------------------------------------- pair matrix
@@ -184,38 +398,52 @@ __global__ void __launch_bounds__(256)
 
 }  // namespace
 
+extern "C" int64_t gd_jumps_work_bytes(int64_t n_events, int32_t n_atoms) {
+    if (n_events < 0 || n_atoms <= 0) return 0;
+    return (int64_t)jump_work(nullptr, n_events, n_atoms).bytes;
+}
+
 extern "C" gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_atom_offsets,
-                                      int32_t n_atoms, int64_t n_frames_total,
-                                      int64_t minimal_residence, int64_t *d_jump_counts,
-                                      int64_t *h_n_jumps, void *stream) {
-    GD_REQUIRE(d_events && d_atom_offsets && d_jump_counts && h_n_jumps, GD_ERR_INVALID,
-               "gd_jumps_count: null argument");
+                                      int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                      int64_t minimal_residence, void *d_work, int64_t *h_n_jumps,
+                                      void *stream) {
+    GD_REQUIRE(d_atom_offsets && d_work && h_n_jumps, GD_ERR_INVALID, "gd_jumps_count: null argument");
+    GD_REQUIRE(n_events >= 0 && (n_events == 0 || d_events), GD_ERR_INVALID,
+               "gd_jumps_count: bad event table");
     GD_REQUIRE(n_atoms > 0, GD_ERR_INVALID, "gd_jumps_count: n_atoms must be positive");
+    GD_REQUIRE((reinterpret_cast<uintptr_t>(d_work) & 15) == 0, GD_ERR_ALIGNMENT,
+               "gd_jumps_count: d_work must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
-    const unsigned blocks = (unsigned)gd_ceil_div(n_atoms, kWarpsPerBlock);
-    k_jumps<false><<<blocks, kWarpsPerBlock * 32, 0, st>>>(d_events, d_atom_offsets, n_atoms,
-                                                          n_frames_total, minimal_residence,
-                                                          d_jump_counts, nullptr);
+    const JumpWork w = jump_work(d_work, n_events, n_atoms);
+    k_seg_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms, w.seg_off);
     GD_LAUNCH_CHECK();
-    k_scan_counts<<<1, 1024, 0, st>>>(d_jump_counts, n_atoms);
+    k_jumps_spec<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
+        d_events, d_atom_offsets, w.seg_off, n_atoms, minimal_residence, w.spec);
     GD_LAUNCH_CHECK();
-    GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, d_jump_counts + n_atoms, sizeof(int64_t),
+    GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
+    k_jumps_chain<<<(unsigned)gd_ceil_div(n_atoms, 64), 64, 0, st>>>(
+        d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence, w.spec,
+        w.entry, w.counts);
+    GD_LAUNCH_CHECK();
+    k_scan_counts<<<1, 1024, 0, st>>>(w.counts, w.max_segs);
+    GD_LAUNCH_CHECK();
+    GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
                                   cudaMemcpyDeviceToHost, st));
     GD_CUDA_CHECK(cudaStreamSynchronize(st));
     return GD_OK;
 }
 
 extern "C" gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets,
-                                     int32_t n_atoms, int64_t n_frames_total,
-                                     int64_t minimal_residence, const int64_t *d_jump_counts,
+                                     int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                     int64_t minimal_residence, const void *d_work,
                                      int32_t *d_jumps, void *stream) {
-    GD_REQUIRE(d_events && d_atom_offsets && d_jump_counts && d_jumps, GD_ERR_INVALID,
+    GD_REQUIRE(d_events && d_atom_offsets && d_work && d_jumps, GD_ERR_INVALID,
                "gd_jumps_fill: null argument");
-    GD_REQUIRE(n_atoms > 0, GD_ERR_INVALID, "gd_jumps_fill: n_atoms must be positive");
-    const unsigned blocks = (unsigned)gd_ceil_div(n_atoms, kWarpsPerBlock);
-    k_jumps<true><<<blocks, kWarpsPerBlock * 32, 0, (cudaStream_t)stream>>>(
-        d_events, d_atom_offsets, n_atoms, n_frames_total, minimal_residence,
-        const_cast<int64_t *>(d_jump_counts), d_jumps);
+    GD_REQUIRE(n_atoms > 0 && n_events >= 0, GD_ERR_INVALID, "gd_jumps_fill: bad size");
+    const JumpWork w = jump_work(const_cast<void *>(d_work), n_events, n_atoms);
+    k_jumps_fill<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, (cudaStream_t)stream>>>(
+        d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence, w.entry,
+        w.counts, d_jumps);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

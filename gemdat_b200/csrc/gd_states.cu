@@ -1,27 +1,39 @@
-// K1 -- site-state assignment for every (frame, floating atom).
+// K1 -- site-state assignment for every (frame, floating atom), fused with the event
+// count of K2.
 //
 // Replaces _calculate_atom_states (reference src/gemdat/transitions.py:736-809): the
 // MDAnalysis PeriodicKDTree build + query (float32 wrap, periodic images,
 // scipy cKDTree ball query) and the last-write-wins scatter, for the outer and the
-// inner sphere in one pass over the positions.
+// inner sphere in one pass over the positions; and the change detection of
+// _calculate_transition_events (:439-452) on the states while they are still in
+// registers.
 //
-// B200 design
-//  * positions stream HBM -> shared memory through a 1-D TMA bulk-copy ring
-//    (cp.async.bulk + mbarrier, SASS UBLKCP); every thread then owns one
-//    atom-frame (3 doubles, bank-conflict free at a 24-byte stride);
-//  * the site list (16 B / site) and the per-label radii live in shared memory;
+// B200 design ("strip walker")
+//  * one warp owns a strip of 32 neighbouring atoms and walks it down one chunk of
+//    frames: lane = atom, so the state of frame t and t+1 of an atom meet in the same
+//    lane and the event count / "ever changes" flags cost no memory traffic;
+//  * each frame row of a strip is 32 x 24 B = 768 contiguous bytes of the [T, A, 3]
+//    float64 array; it streams HBM -> shared memory through a warp-private ring of
+//    1-D TMA bulk copies (cp.async.bulk + mbarrier, SASS UBLKCP) kStages rows deep,
+//    so no warp ever waits for another warp; every lane then reads its 3 doubles
+//    with conflict-free LDS at a 24-byte stride;
+//  * a CTA = 8 neighbouring strips of the same frame chunk (6 KB contiguous per
+//    row); CTAs are ordered strip-group-major, so the CTAs resident at any time work
+//    on the same few hundred atoms at different times and their cell / site records
+//    stay in L1;
 //  * instead of a KD-tree, a uniform cell grid over the wrapped float32 box maps a
-//    position to the few sites whose sphere can reach that cell (conservative
-//    superset built on the host, L1/L2 resident); the exact test below decides;
+//    position to the few sites whose sphere can reach that cell (exact sphere/box
+//    test on the host, 4 B per cell); each (cell, site) entry carries 3 flag bits
+//    saying on which axes a periodic image of the atom can matter, so the common
+//    path evaluates one plain distance;
 //  * the exact test reproduces the reference's arithmetic bit for bit:
 //    float64 frac*L -> float32, float32 wrap, float32 periodic image (+L if
 //    x <= cutoff else -L if L-x <= cutoff), float64 dx*dx+dy*dy+dz*dz <= r*r with
-//    every operation individually rounded (no FMA);
-//  * persistent CTAs, each walking a contiguous range of 512-atom-frame chunks so
-//    the cell records of "its" frames stay in L1.
+//    every operation individually rounded (no FMA).
 //
 // Algorithmic traffic: 24 B read + 8 B written per atom-frame.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -32,15 +44,19 @@
 namespace {
 
 constexpr uint32_t kMagic = 0x47534447u;  // "GDSG"
+constexpr uint32_t kBlobVersion = 2;
 constexpr int kMaxGroups = 64;
-constexpr int kThreads = 512;  // atom-frames per pipeline stage
-constexpr int kStages = 4;
-constexpr float kNoImage = 1.0e30f;
+constexpr int kWarps = 8;  // strips per CTA
+constexpr int kThreads = kWarps * 32;
+constexpr int kStages = 4;        // frame rows in flight per warp
+constexpr int kRowDoubles = 96;   // 32 atoms x 3
+constexpr int kVisSmemMax = 24 * 1024;  // visited flags kept in shared memory up to this size
+constexpr uint32_t kRankMask = 0xFFFFFu;  // 20 bits of rank, 3 bits of image flags above
 
 struct GdGridHeader {  // 256 bytes, little endian, position independent
     uint32_t magic;
     uint32_t version;
-    int32_t n_sites;   // sites that belong to a group (= rows of the site table)
+    int32_t n_sites;  // sites that belong to a group (= rows of the site table)
     int32_t n_sites_total;
     int32_t n_groups;
     int32_t dims[3];
@@ -62,17 +78,19 @@ struct GdGridHeader {  // 256 bytes, little endian, position independent
 };
 static_assert(sizeof(GdGridHeader) == 256, "header layout");
 
-struct GdGroupRec {  // 32 bytes
+struct GdGroupRec {  // 48 bytes
     double r2_outer;
     double r2_inner;
+    // pre-filter of the boundary-band diagnostics on the high word of d2 (monotone for
+    // d2 >= 0): (unsigned)(hi(d2) - band_lo) <= band_span  <=>  d2 within ~1.1e-3 of r^2
+    int32_t band_lo_o, band_span_o, band_lo_i, band_span_i;
     double r_outer;
     double r_inner;
 };
+static_assert(sizeof(GdGroupRec) == 48, "group record layout");
 
 inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 
-// MDAnalysis _ortho_pbc, float32 (lib/src/calc_distances.h) [recalled]
-__host__ __device__ inline float wrap_ortho(float c, float L, double invL) {
 #ifdef __CUDA_ARCH__
 #define GD_FADD(a, b) __fadd_rn((a), (b))
 #define GD_FSUB(a, b) __fsub_rn((a), (b))
@@ -82,6 +100,9 @@ __host__ __device__ inline float wrap_ortho(float c, float L, double invL) {
 #define GD_FSUB(a, b) ((a) - (b))
 #define GD_FMUL(a, b) ((a) * (b))
 #endif
+
+// MDAnalysis _ortho_pbc, float32 (lib/src/calc_distances.h) [recalled]
+__host__ __device__ inline float wrap_ortho(float c, float L, double invL) {
     if (c < 0.0f) {
         float once = GD_FADD(c, L);
         if (once < 0.0f) {
@@ -103,211 +124,300 @@ __host__ __device__ inline float wrap_ortho(float c, float L, double invL) {
         }
     }
     return c;
-#undef GD_FADD
-#undef GD_FSUB
-#undef GD_FMUL
 }
+
+// device cell index along one axis: float32 multiply, truncate (clamped by the caller)
+__host__ __device__ inline int cell_raw(float x, float inv_cell) { return (int)GD_FMUL(x, inv_cell); }
 
 struct StatesParams {
     const double *pos;
-    int64_t n_af;
+    const double *next_row;  // [n_atoms,3] first row of the following shard, or null
+    int64_t n_frames;
     int64_t n_chunks;
+    int64_t n_cblocks;       // chunk blocks = ceil(n_chunks / cpg)
+    int32_t n_atoms;
+    int32_t f;               // frames per chunk
+    int32_t n_strips;
+    int32_t spg_shift;       // log2(strips per CTA)
     const float4 *sites;     // [n_sites] x, y, z, bits(natural | group << 24)
-    const uint2 *cells;      // [ncell] {count, payload}
-    const int32_t *entries;  // ranks, ascending inside a cell
+    const uint32_t *cells;   // [ncell] count << 24 | payload
+    const uint32_t *entries; // rank | flags << 20, ranks ascending inside a cell
     const GdGroupRec *groups;
     int32_t *out_o;
     int32_t *out_i;
     uint8_t *visited;  // [2*n_sites_total] or null
     unsigned long long *band;
-    int32_t n_sites;
+    int32_t *work;     // [n_atoms, n_chunks] event counts, or null
+    uint8_t *changed;  // [2*n_atoms]
     int32_t n_sites_total;
     int32_t n_groups;
     int32_t dims[3];
     int32_t is_diag;
+    int32_t vis_mode;  // visited flags: 0 none, 1 staged in shared memory, 2 global stores
     float box[3];
     float cutoff32;
     float inv_cell[3];
     double inv_box[3];
     double m[9];
+    GdGroupRec g0;  // the only group when n_groups == 1 (read from the constant bank)
 };
 
-template <bool kSmemSites>
-__global__ void __launch_bounds__(kThreads, 2)
+struct BandCounters {
+    unsigned int o12 = 0, i12 = 0, of = 0, fi = 0;
+};
+
+// periodic image of the atom along one axis, if it has one (lib/_augment.pyx [recalled])
+__device__ __forceinline__ double axis_delta_image(double d, double s, float a, float L, float r32) {
+    float img;
+    if (a <= r32)
+        img = __fadd_rn(a, L);
+    else if (__fsub_rn(L, a) <= r32)
+        img = __fsub_rn(a, L);
+    else
+        return d;
+    const double e = __dsub_rn(s, (double)img);
+    return fabs(e) < fabs(d) ? e : d;
+}
+
+// rare path: bit 0/1 = outer sphere within 1e-12 / 4e-6 A, bit 2/3 = inner sphere
+__device__ __noinline__ unsigned band_diag(double d2, const GdGroupRec *g) {
+    unsigned r = 0;
+    if (fabs(d2 - g->r2_outer) < g->r2_outer * 1e-3) {
+        const double dd = fabs(sqrt(d2) - g->r_outer);
+        r |= (dd < 1e-12 ? 1u : 0u) | (dd < 4e-6 ? 2u : 0u);
+    }
+    if (fabs(d2 - g->r2_inner) < g->r2_inner * 1e-3) {
+        const double dd = fabs(sqrt(d2) - g->r_inner);
+        r |= (dd < 1e-12 ? 4u : 0u) | (dd < 4e-6 ? 8u : 0u);
+    }
+    return r;
+}
+
+__device__ __noinline__ float wrap_slow(float c, float L, double invL) { return wrap_ortho(c, L, invL); }
+
+// site states of one atom-frame
+template <bool kOneGroup>
+__device__ __forceinline__ void classify(const StatesParams &p, const GdGroupRec *s_groups,
+                                         uint8_t *s_vis, double f0, double f1, double f2,
+                                         int32_t &best_o, int32_t &best_i, BandCounters &bc) {
+    // ---- reference staging: float64 Cartesian -> float32 -> wrap
+    double cx, cy, cz;
+    if (p.is_diag) {
+        cx = __dmul_rn(f0, p.m[0]);
+        cy = __dmul_rn(f1, p.m[4]);
+        cz = __dmul_rn(f2, p.m[8]);
+    } else {
+        cx = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[0]), __dmul_rn(f1, p.m[3])), __dmul_rn(f2, p.m[6]));
+        cy = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[1]), __dmul_rn(f1, p.m[4])), __dmul_rn(f2, p.m[7]));
+        cz = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[2]), __dmul_rn(f1, p.m[5])), __dmul_rn(f2, p.m[8]));
+    }
+    float ax = __double2float_rn(cx), ay = __double2float_rn(cy), az = __double2float_rn(cz);
+    const float Lx = p.box[0], Ly = p.box[1], Lz = p.box[2];
+    if (!(ax >= 0.0f && ax < Lx)) ax = wrap_slow(ax, Lx, p.inv_box[0]);
+    if (!(ay >= 0.0f && ay < Ly)) ay = wrap_slow(ay, Ly, p.inv_box[1]);
+    if (!(az >= 0.0f && az < Lz)) az = wrap_slow(az, Lz, p.inv_box[2]);
+    const double a0x = (double)ax, a0y = (double)ay, a0z = (double)az;
+
+    // ---- candidate sites of this cell
+    const unsigned ix = min((unsigned)cell_raw(ax, p.inv_cell[0]), (unsigned)(p.dims[0] - 1));
+    const unsigned iy = min((unsigned)cell_raw(ay, p.inv_cell[1]), (unsigned)(p.dims[1] - 1));
+    const unsigned iz = min((unsigned)cell_raw(az, p.inv_cell[2]), (unsigned)(p.dims[2] - 1));
+    const uint32_t cell = __ldg(p.cells + ((ix * (unsigned)p.dims[1] + iy) * (unsigned)p.dims[2] + iz));
+    const uint32_t count = cell >> 24, payload = cell & 0xFFFFFFu;
+
+    best_o = GD_NOSITE;
+    best_i = GD_NOSITE;
+    for (uint32_t k = 0; k < count; ++k) {
+        const uint32_t word = (count == 1) ? payload : __ldg(p.entries + payload + k);
+        const float4 rec = __ldg(p.sites + (word & kRankMask));
+        const int natgrp = __float_as_int(rec.w);
+        const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[natgrp >> 24];
+        const double sx = (double)rec.x, sy = (double)rec.y, sz = (double)rec.z;
+        double dx = __dsub_rn(sx, a0x), dy = __dsub_rn(sy, a0y), dz = __dsub_rn(sz, a0z);
+        if (word >> 20) {  // a periodic image of the atom can be the closer one (rare)
+            if (word & (1u << 20)) dx = axis_delta_image(dx, sx, ax, Lx, p.cutoff32);
+            if (word & (1u << 21)) dy = axis_delta_image(dy, sy, ay, Ly, p.cutoff32);
+            if (word & (1u << 22)) dz = axis_delta_image(dz, sz, az, Lz, p.cutoff32);
+        }
+        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+        const int natural = natgrp & 0x00FFFFFF;
+        const bool hit_o = d2 <= g.r2_outer, hit_i = d2 <= g.r2_inner;
+        if (hit_o) best_o = natural;  // entries ascend in overwrite order: last match wins
+        if (hit_i) best_i = natural;
+        if (p.vis_mode == 1) {
+            if (hit_o) s_vis[natural] = 1;
+            if (hit_i) s_vis[p.n_sites_total + natural] = 1;
+        } else if (p.vis_mode == 2) {
+            if (hit_o) p.visited[natural] = 1;
+            if (hit_i) p.visited[p.n_sites_total + natural] = 1;
+        }
+        // boundary-band diagnostics: integer pre-filter on the high word, exact test on the
+        // rare path
+        const int hi = __double2hiint(d2);
+        if ((unsigned)(hi - g.band_lo_o) <= (unsigned)g.band_span_o ||
+            (unsigned)(hi - g.band_lo_i) <= (unsigned)g.band_span_i) {
+            const unsigned b = band_diag(d2, &g);
+            bc.o12 += b & 1u;
+            bc.of += (b >> 1) & 1u;
+            bc.i12 += (b >> 2) & 1u;
+            bc.fi += (b >> 3) & 1u;
+        }
+    }
+}
+
+template <bool kTma, bool kOneGroup>
+__global__ void __launch_bounds__(kThreads, 4)
     k_site_states(const __grid_constant__ StatesParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
-    double *ring = reinterpret_cast<double *>(smem);
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)kStages * kThreads * 24);
-    uint64_t *empty = full + kStages;
-    GdGroupRec *s_groups = reinterpret_cast<GdGroupRec *>(empty + kStages);
-    float4 *s_sites = reinterpret_cast<float4 *>(s_groups + kMaxGroups);
+    double *ring = reinterpret_cast<double *>(smem);  // [kWarps][kStages][96]
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)kWarps * kStages * kRowDoubles * 8);
+    GdGroupRec *s_groups = reinterpret_cast<GdGroupRec *>(full + kWarps * kStages);
+    uint8_t *s_vis = reinterpret_cast<uint8_t *>(s_groups + kMaxGroups);
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // contiguous chunk range of this CTA
-    const int64_t per = p.n_chunks / gridDim.x;
-    const int64_t rem = p.n_chunks % gridDim.x;
-    const int64_t bid = blockIdx.x;
-    const int64_t chunk0 = bid * per + (bid < rem ? bid : rem);
-    const int64_t n_my = per + (bid < rem ? 1 : 0);
-
-    if (tid == 0) {
-        for (int s = 0; s < kStages; ++s) {
-            gd_mbar_init(&full[s], 1);
-            gd_mbar_init(&empty[s], kThreads);
-        }
-        gd_fence_barrier_init();
-    }
     for (int g = tid; g < p.n_groups; g += kThreads) s_groups[g] = p.groups[g];
-    if (kSmemSites) {
-        for (int e = tid; e < p.n_sites; e += kThreads) s_sites[e] = __ldg(p.sites + e);
+    const int n_vis = 2 * p.n_sites_total;
+    if (p.vis_mode == 1)
+        for (int i = tid; i < (n_vis + 3) / 4; i += kThreads) reinterpret_cast<uint32_t *>(s_vis)[i] = 0;
+    if (kTma && lane == 0) {
+        for (int s = 0; s < kStages; ++s) gd_mbar_init(&full[warp * kStages + s], 1);
+        gd_fence_barrier_init();
     }
     __syncthreads();
 
-    auto issue = [&](int64_t local_chunk, int slot) {
-        const int64_t chunk = chunk0 + local_chunk;
-        const int64_t first = chunk * kThreads;
-        int64_t valid = p.n_af - first;
-        if (valid > kThreads) valid = kThreads;
-        const uint32_t bytes = (uint32_t)(valid * 24) & ~15u;
-        gd_mbar_arrive_expect_tx(&full[slot], bytes);
-        gd_tma_load_1d(ring + (size_t)slot * kThreads * 3, p.pos + first * 3, bytes, &full[slot]);
-    };
+    // ---- which (strip, chunk) this warp owns: CTAs are strip-group-major
+    const int spg = 1 << p.spg_shift;
+    const int64_t grp = blockIdx.x / p.n_cblocks;
+    const int64_t cb = blockIdx.x - grp * p.n_cblocks;
+    const int32_t strip = (int32_t)(grp << p.spg_shift) + (warp & (spg - 1));
+    const int64_t chunk = cb * (kWarps >> p.spg_shift) + (warp >> p.spg_shift);
+    BandCounters bc;
 
-    if (tid == 0) {
-        for (int s = 0; s < kStages && s < n_my; ++s) issue(s, s);
-    }
+    if (strip < p.n_strips && chunk < p.n_chunks) {
+        const int32_t a0 = strip * 32;
+        const int32_t a = a0 + lane;
+        const bool lane_on = a < p.n_atoms;
+        const int r = min(32, p.n_atoms - a0);  // atoms in this strip
+        const int64_t t0 = chunk * p.f;
+        const int64_t t1 = min(p.n_frames, t0 + (int64_t)p.f);
+        const int n_own = (int)(t1 - t0);
+        // halo row for the event at the chunk's last frame
+        const bool halo = p.work != nullptr && (t1 < p.n_frames || p.next_row != nullptr);
+        const int n_rows = n_own + (halo ? 1 : 0);
+        const int64_t A3 = (int64_t)p.n_atoms * 3;
+        const double *row0 = p.pos + t0 * A3 + (int64_t)a0 * 3;
+        const double *halo_row = (t1 < p.n_frames) ? p.pos + t1 * A3 + (int64_t)a0 * 3
+                                                   : (p.next_row ? p.next_row + (int64_t)a0 * 3 : nullptr);
+        auto row_ptr = [&](int k) { return k < n_own ? row0 + (int64_t)k * A3 : halo_row; };
 
-    const float Lx = p.box[0], Ly = p.box[1], Lz = p.box[2];
-    const float r32 = p.cutoff32;
-    const int dimx = p.dims[0], dimy = p.dims[1], dimz = p.dims[2];
-    const float4 *sites = kSmemSites ? s_sites : p.sites;
+        // bytes of a row that the bulk copy moves (multiple of 16); an odd strip leaves the
+        // last atom's z to a plain load
+        const uint32_t row_bytes = (uint32_t)(r * 24) & ~15u;
+        const int covered = (int)(row_bytes >> 3);  // doubles in shared memory
+        double *my_ring = ring + (size_t)warp * kStages * kRowDoubles;
+        uint64_t *my_full = full + warp * kStages;
 
-    unsigned int band_o12 = 0, band_i12 = 0, band_of = 0, band_if = 0;
-
-    for (int64_t i = 0; i < n_my; ++i) {
-        const int slot = (int)(i % kStages);
-        const uint32_t phase = (uint32_t)((i / kStages) & 1);
-
-        // producer duty: refill the slot everybody consumed in the previous iteration
-        if (tid == 0 && i >= 1 && (i - 1 + kStages) < n_my) {
-            const int ps = (int)((i - 1) % kStages);
-            const uint32_t pp = (uint32_t)(((i - 1) / kStages) & 1);
-            gd_mbar_wait(&empty[ps], pp);
-            issue(i - 1 + kStages, ps);
-        }
-
-        gd_mbar_wait(&full[slot], phase);
-
-        const int64_t n = (chunk0 + i) * kThreads + tid;
-        const bool active = n < p.n_af;
-        int64_t valid = p.n_af - (chunk0 + i) * kThreads;
-        if (valid > kThreads) valid = kThreads;
-        const int covered = (int)(((uint32_t)(valid * 24) & ~15u) / 24);  // whole triples in smem
-
-        double f0 = 0.0, f1 = 0.0, f2 = 0.0;
-        if (active) {
-            if (tid < covered) {
-                const double *sp = ring + (size_t)slot * kThreads * 3 + 3 * tid;
-                f0 = sp[0];
-                f1 = sp[1];
-                f2 = sp[2];
-            } else {  // odd tail element: its last 8 bytes were not part of the bulk copy
-                const double *gp = p.pos + n * 3;
-                f0 = __ldg(gp);
-                f1 = __ldg(gp + 1);
-                f2 = __ldg(gp + 2);
+        if (kTma && lane == 0) {
+            for (int s = 0; s < kStages && s < n_rows; ++s) {
+                gd_mbar_arrive_expect_tx(&my_full[s], row_bytes);
+                gd_tma_load_1d(my_ring + s * kRowDoubles, row_ptr(s), row_bytes, &my_full[s]);
             }
         }
-        // The slot is refilled by the async proxy (TMA) once all 512 arrivals are in.  The
-        // reads above are generic-proxy LDS: without this cross-proxy fence the arrive can
-        // overtake a still-queued LDS and the refill lands first (observed on B200: whole
-        // warps saw the data of chunk i+4).
-        gd_fence_proxy_async();
-        gd_mbar_arrive(&empty[slot]);
-        if (!active) continue;
-
-        // ---- reference staging: float64 Cartesian -> float32 -> wrap -> images
-        double cx, cy, cz;
-        if (p.is_diag) {
-            cx = __dmul_rn(f0, p.m[0]);
-            cy = __dmul_rn(f1, p.m[4]);
-            cz = __dmul_rn(f2, p.m[8]);
-        } else {
-            cx = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[0]), __dmul_rn(f1, p.m[3])), __dmul_rn(f2, p.m[6]));
-            cy = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[1]), __dmul_rn(f1, p.m[4])), __dmul_rn(f2, p.m[7]));
-            cz = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[2]), __dmul_rn(f1, p.m[5])), __dmul_rn(f2, p.m[8]));
+        // register prefetch of the non-TMA variant (odd n_atoms: rows are only 8-byte aligned)
+        double n0 = 0.0, n1 = 0.0, n2 = 0.0;
+        if (!kTma && lane_on) {
+            const double *q = row_ptr(0) + 3 * lane;
+            n0 = __ldg(q);
+            n1 = __ldg(q + 1);
+            n2 = __ldg(q + 2);
         }
-        const float ax = wrap_ortho(__double2float_rn(cx), Lx, p.inv_box[0]);
-        const float ay = wrap_ortho(__double2float_rn(cy), Ly, p.inv_box[1]);
-        const float az = wrap_ortho(__double2float_rn(cz), Lz, p.inv_box[2]);
 
-        const bool lox = ax <= r32, loy = ay <= r32, loz = az <= r32;
-        const float bx = lox ? __fadd_rn(ax, Lx) : ((__fsub_rn(Lx, ax) <= r32) ? __fsub_rn(ax, Lx) : kNoImage);
-        const float by = loy ? __fadd_rn(ay, Ly) : ((__fsub_rn(Ly, ay) <= r32) ? __fsub_rn(ay, Ly) : kNoImage);
-        const float bz = loz ? __fadd_rn(az, Lz) : ((__fsub_rn(Lz, az) <= r32) ? __fsub_rn(az, Lz) : kNoImage);
+        int32_t prev_o = GD_NOSITE, prev_i = GD_NOSITE;
+        int cnt = 0;
+        int chg = 0;  // bit 0: outer state changed somewhere, bit 1: inner
+        const bool tail_lane = 3 * lane + 2 >= covered;  // z of an odd strip's last atom
+        const double *my_row = my_ring + 3 * lane;
+        int slot = 0;
+        uint32_t phase = 0;
+        int32_t *po = p.out_o + t0 * p.n_atoms + a;
+        int32_t *pi = p.out_i + t0 * p.n_atoms + a;
 
-        const double a0x = (double)ax, a0y = (double)ay, a0z = (double)az;
-        const double a1x = (double)bx, a1y = (double)by, a1z = (double)bz;
-
-        // ---- candidate sites of this cell
-        int ix = (int)(ax * p.inv_cell[0]);
-        int iy = (int)(ay * p.inv_cell[1]);
-        int iz = (int)(az * p.inv_cell[2]);
-        ix = min(max(ix, 0), dimx - 1);
-        iy = min(max(iy, 0), dimy - 1);
-        iz = min(max(iz, 0), dimz - 1);
-        const uint2 cell = __ldg(p.cells + ((int64_t)ix * dimy + iy) * dimz + iz);
-
-        int32_t best_o = GD_NOSITE, best_i = GD_NOSITE;
-        for (uint32_t k = 0; k < cell.x; ++k) {
-            const int e = (cell.x == 1) ? (int)cell.y : __ldg(p.entries + cell.y + k);
-            const float4 rec = sites[e];
-            const int natgrp = __float_as_int(rec.w);
-            const GdGroupRec g = s_groups[natgrp >> 24];
-            const double sx = (double)rec.x, sy = (double)rec.y, sz = (double)rec.z;
-            double dx = __dsub_rn(sx, a0x), ex = __dsub_rn(sx, a1x);
-            double dy = __dsub_rn(sy, a0y), ey = __dsub_rn(sy, a1y);
-            double dz = __dsub_rn(sz, a0z), ez = __dsub_rn(sz, a1z);
-            const double qx = fmin(__dmul_rn(dx, dx), __dmul_rn(ex, ex));
-            const double qy = fmin(__dmul_rn(dy, dy), __dmul_rn(ey, ey));
-            const double qz = fmin(__dmul_rn(dz, dz), __dmul_rn(ez, ez));
-            const double d2 = __dadd_rn(__dadd_rn(qx, qy), qz);
-            const int natural = natgrp & 0x00ffffff;
-            if (d2 <= g.r2_outer) {
-                best_o = natural;  // entries ascend in overwrite order: last match wins
-                if (p.visited && !p.visited[natural]) p.visited[natural] = 1;
+        for (int k = 0; k < n_rows; ++k) {
+            double f0 = 0.0, f1 = 0.0, f2 = 0.0;
+            if (kTma) {
+                gd_mbar_wait(&my_full[slot], phase);
+                if (lane_on) {
+                    const double *sp = my_row + slot * kRowDoubles;
+                    f0 = sp[0];
+                    f1 = sp[1];
+                    f2 = tail_lane ? __ldg(row_ptr(k) + 3 * lane + 2) : sp[2];
+                }
+                // The slot is refilled by the async proxy (TMA); the reads above are
+                // generic-proxy LDS.  Order them before the refill (observed on B200
+                // without the fence: whole warps read the data of a later row).
+                gd_fence_proxy_async();
+                __syncwarp();
+                if (lane == 0 && k + kStages < n_rows) {
+                    gd_mbar_arrive_expect_tx(&my_full[slot], row_bytes);
+                    gd_tma_load_1d(my_ring + slot * kRowDoubles, row_ptr(k + kStages), row_bytes,
+                                   &my_full[slot]);
+                }
+                if (++slot == kStages) {
+                    slot = 0;
+                    phase ^= 1u;
+                }
+            } else {
+                f0 = n0;
+                f1 = n1;
+                f2 = n2;
+                if (lane_on && k + 1 < n_rows) {
+                    const double *q = row_ptr(k + 1) + 3 * lane;
+                    n0 = __ldg(q);
+                    n1 = __ldg(q + 1);
+                    n2 = __ldg(q + 2);
+                }
             }
-            if (d2 <= g.r2_inner) {
-                best_i = natural;
-                if (p.visited && !p.visited[p.n_sites_total + natural])
-                    p.visited[p.n_sites_total + natural] = 1;
+            if (!lane_on) continue;
+
+            int32_t so, si;
+            classify<kOneGroup>(p, s_groups, s_vis, f0, f1, f2, so, si, bc);
+
+            if (k > 0) {
+                const int d_o = so != prev_o, d_i = si != prev_i;
+                cnt += d_o | d_i;
+                chg |= d_o | (d_i << 1);
             }
-            // boundary-band diagnostics (rare path)
-            if (fabs(d2 - g.r2_outer) < g.r2_outer * 1e-3) {
-                const double dd = fabs(sqrt(d2) - g.r_outer);
-                band_o12 += dd < 1e-12;
-                band_of += dd < 4e-6;
-            }
-            if (fabs(d2 - g.r2_inner) < g.r2_inner * 1e-3) {
-                const double dd = fabs(sqrt(d2) - g.r_inner);
-                band_i12 += dd < 1e-12;
-                band_if += dd < 4e-6;
+            prev_o = so;
+            prev_i = si;
+            if (k < n_own) {
+                *po = so;
+                *pi = si;
+                po += p.n_atoms;
+                pi += p.n_atoms;
             }
         }
-        p.out_o[n] = best_o;
-        p.out_i[n] = best_i;
+        if (p.work && lane_on) {
+            p.work[(int64_t)a * p.n_chunks + chunk] = cnt;
+            if (chg & 1) p.changed[a] = 1;
+            if (chg & 2) p.changed[p.n_atoms + a] = 1;
+        }
     }
 
     if (p.band) {
-        const int o12 = gd_warp_sum((int)band_o12), i12 = gd_warp_sum((int)band_i12);
-        const int of = gd_warp_sum((int)band_of), fi = gd_warp_sum((int)band_if);
-        if ((tid & 31) == 0) {
+        const int o12 = gd_warp_sum((int)bc.o12), i12 = gd_warp_sum((int)bc.i12);
+        const int of = gd_warp_sum((int)bc.of), fi = gd_warp_sum((int)bc.fi);
+        if (lane == 0) {
             if (o12) atomicAdd(p.band + 0, (unsigned long long)o12);
             if (i12) atomicAdd(p.band + 1, (unsigned long long)i12);
             if (of) atomicAdd(p.band + 2, (unsigned long long)of);
             if (fi) atomicAdd(p.band + 3, (unsigned long long)fi);
         }
+    }
+    if (p.vis_mode == 1) {
+        __syncthreads();
+        for (int i = tid; i < n_vis; i += kThreads)
+            if (s_vis[i]) p.visited[i] = 1;
     }
 }
 
@@ -322,8 +432,8 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
                                          size_t *needed) {
     GD_REQUIRE(h_lattice && h_sites_frac && h_site_group && h_group_radius && h_group_inner && needed,
                GD_ERR_INVALID, "gd_sitegrid_build: null argument");
-    GD_REQUIRE(n_sites > 0 && n_sites < (1 << 24), GD_ERR_INVALID,
-               "gd_sitegrid_build: n_sites must be in [1, 2^24)");
+    GD_REQUIRE(n_sites > 0 && n_sites <= (int32_t)kRankMask, GD_ERR_INVALID,
+               "gd_sitegrid_build: n_sites must be in [1, 2^20)");
     GD_REQUIRE(n_groups > 0 && n_groups <= kMaxGroups, GD_ERR_INVALID,
                "gd_sitegrid_build: n_groups must be in [1, %d]", kMaxGroups);
 
@@ -352,14 +462,28 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     for (int g = 1; g < n_groups; ++g) cutoff = std::max(cutoff, h_group_radius[g]);
     GD_REQUIRE(cutoff > 0.0, GD_ERR_INVALID, "gd_sitegrid_build: radii must be positive");
     std::vector<GdGroupRec> groups(n_groups);
-    double reach_max = 0.0;
     for (int g = 0; g < n_groups; ++g) {
         const double ro = h_group_radius[g] * 1.0;
         const double ri = h_group_radius[g] * h_group_inner[g];
         GD_REQUIRE(!(cutoff < ri), GD_ERR_RADIUS_GT_CUTOFF,
                    "Set cutoff greater or equal to the radius.");
-        groups[g] = GdGroupRec{ro * ro, ri * ri, ro, ri};
-        reach_max = std::max(reach_max, std::max(ro, ri));
+        GdGroupRec rec;
+        rec.r2_outer = ro * ro;
+        rec.r2_inner = ri * ri;
+        // band_diag applies the exact filter |d2 - r2| < r2 * 1e-3; a window of 1.1e-3
+        // widened by one unit of the high word is a superset of it
+        auto hi_word = [](double v) {
+            int64_t bits;
+            memcpy(&bits, &v, 8);
+            return (int32_t)(bits >> 32);
+        };
+        rec.band_lo_o = hi_word(rec.r2_outer * (1.0 - 1.1e-3)) - 1;
+        rec.band_span_o = hi_word(rec.r2_outer * (1.0 + 1.1e-3)) + 1 - rec.band_lo_o;
+        rec.band_lo_i = hi_word(rec.r2_inner * (1.0 - 1.1e-3)) - 1;
+        rec.band_span_i = hi_word(rec.r2_inner * (1.0 + 1.1e-3)) + 1 - rec.band_lo_i;
+        rec.r_outer = ro;
+        rec.r_inner = ri;
+        groups[g] = rec;
     }
 
     float box[3];
@@ -368,21 +492,22 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
         box[i] = (float)len[i];
         inv_box[i] = 1.0 / (double)box[i];
     }
+    const float r32 = (float)cutoff;
 
     // rank order = overwrite order of the reference: groups in dict order, ascending
     // site index inside a group
+    for (int32_t s = 0; s < n_sites; ++s)
+        GD_REQUIRE(h_site_group[s] >= -1 && h_site_group[s] < n_groups, GD_ERR_INVALID,
+                   "gd_sitegrid_build: site %d has group %d", s, h_site_group[s]);
     std::vector<int32_t> order;
     order.reserve(n_sites);
     for (int g = 0; g < n_groups; ++g)
         for (int32_t s = 0; s < n_sites; ++s)
             if (h_site_group[s] == g) order.push_back(s);
-    for (int32_t s = 0; s < n_sites; ++s)
-        GD_REQUIRE(h_site_group[s] >= -1 && h_site_group[s] < n_groups, GD_ERR_INVALID,
-                   "gd_sitegrid_build: site %d has group %d", s, h_site_group[s]);
     const int32_t n_ranked = (int32_t)order.size();
 
     // float32 staging of the site centres (float64 frac @ M -> float32 -> wrap)
-    std::vector<float> sx(n_ranked * 3);
+    std::vector<float> sx((size_t)std::max(n_ranked, 1) * 3);
     for (int32_t e = 0; e < n_ranked; ++e) {
         const double *f = h_sites_frac + 3 * (size_t)order[e];
         for (int j = 0; j < 3; ++j) {
@@ -395,9 +520,15 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
         }
     }
 
-    // grid resolution: ~0.4 * cutoff per cell, at most 256 cells per axis / 2^22 cells
+    // grid resolution: cells of ~k * cutoff (k = 0.75; GD_GRID_K overrides for tuning),
+    // at most 256 cells per axis / 2^22 cells in total
+    double kfac = 0.75;
+    if (const char *env = getenv("GD_GRID_K")) {
+        const double v = atof(env);
+        if (v > 0.05 && v < 100.0) kfac = v;
+    }
     int dims[3];
-    double target = std::max(0.4 * cutoff, 1e-3);
+    double target = std::max(kfac * cutoff, 1e-3);
     for (;;) {
         int64_t total = 1;
         for (int j = 0; j < 3; ++j) {
@@ -412,47 +543,95 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     for (int j = 0; j < 3; ++j) inv_cell[j] = (float)((double)dims[j] / (double)box[j]);
     const int64_t ncell = (int64_t)dims[0] * dims[1] * dims[2];
 
-    // cells reachable from each site (periodic), margin covers every float32 rounding
-    const double margin = 2e-3;
-    auto axis_cells = [&](double s, double reach, int j, std::vector<int> &out) {
-        out.clear();
-        const double w = (double)box[j] / dims[j];
-        long lo = (long)floor((s - reach) / w) - 1;  // one extra cell each side: the device
-        long hi = (long)floor((s + reach) / w) + 1;  // computes the cell index in float32
-        if (hi - lo + 1 >= dims[j]) {
-            for (int i = 0; i < dims[j]; ++i) out.push_back(i);
-            return;
+    // exact float32 interval of every cell along every axis: cell i of axis j holds the
+    // wrapped coordinates x with lo[i] <= x <= hi[i], evaluated with the device's own
+    // formula min(trunc(fl32(x * inv_cell)), dim - 1), which is monotone in x
+    std::vector<float> edge[3];
+    for (int j = 0; j < 3; ++j) {
+        edge[j].assign(dims[j] + 1, 0.0f);
+        for (int i = 1; i < dims[j]; ++i) {
+            float g = (float)((double)i / (double)inv_cell[j]);
+            while (g > 0.0f && cell_raw(g, inv_cell[j]) >= i) g = nextafterf(g, -INFINITY);
+            while (cell_raw(g, inv_cell[j]) < i) g = nextafterf(g, INFINITY);
+            edge[j][i] = g;  // smallest float that lands in cell >= i
         }
-        for (long i = lo; i <= hi; ++i) {
-            long c = i % dims[j];
-            if (c < 0) c += dims[j];
-            out.push_back((int)c);
-        }
-    };
+        edge[j][dims[j]] = box[j];
+    }
 
-    // pass 1: count candidates per cell
-    std::vector<uint32_t> count(ncell, 0);
-    std::vector<int> cxs, cys, czs;
-    auto for_each_cell = [&](int32_t e, auto &&fn) {
+    // (cell, site) entries by an exact sphere / box test (periodic), with the axes on
+    // which an image of the atom can be the closer one flagged.  `margin` covers every
+    // float32 rounding of the staged coordinates and images (<= 4e-6 A).
+    const double margin = 2e-3;
+    const double eps = 1e-4;
+    struct AxisHit {
+        int cell;
+        double dist;
+        bool flag;
+    };
+    std::vector<AxisHit> hits[3];
+    std::vector<uint32_t> e_cell, e_word;
+    e_cell.reserve((size_t)n_ranked * 32);
+    e_word.reserve((size_t)n_ranked * 32);
+    for (int32_t e = 0; e < n_ranked; ++e) {
         const GdGroupRec &g = groups[h_site_group[order[e]]];
         const double reach = std::max(g.r_outer, g.r_inner) + margin;
-        axis_cells(sx[3 * e + 0], reach, 0, cxs);
-        axis_cells(sx[3 * e + 1], reach, 1, cys);
-        axis_cells(sx[3 * e + 2], reach, 2, czs);
-        for (int a : cxs)
-            for (int b : cys)
-                for (int c : czs) fn(((int64_t)a * dims[1] + b) * dims[2] + c);
-    };
-    for (int32_t e = 0; e < n_ranked; ++e) for_each_cell(e, [&](int64_t cell) { ++count[cell]; });
+        for (int j = 0; j < 3; ++j) {
+            hits[j].clear();
+            const double s = (double)sx[3 * e + j];
+            const double L = (double)box[j];
+            for (int i = 0; i < dims[j]; ++i) {
+                const double lo = (double)edge[j][i], hi = (double)edge[j][i + 1];
+                double best = std::max(0.0, std::max(lo - s, s - hi));
+                bool flag = false;
+                if (lo <= (double)r32 + eps) {  // atoms here may carry the +L image
+                    const double d = std::max(0.0, lo + L - s - eps);
+                    if (d <= reach) {
+                        flag = true;
+                        best = std::min(best, d);
+                    }
+                }
+                if (hi >= L - (double)r32 - eps) {  // ... or the -L image
+                    const double d = std::max(0.0, s - (hi - L) - eps);
+                    if (d <= reach) {
+                        flag = true;
+                        best = std::min(best, d);
+                    }
+                }
+                if (best <= reach) hits[j].push_back(AxisHit{i, best, flag});
+            }
+        }
+        const double reach2 = reach * reach;
+        for (const AxisHit &hx : hits[0])
+            for (const AxisHit &hy : hits[1]) {
+                const double dxy = hx.dist * hx.dist + hy.dist * hy.dist;
+                if (dxy > reach2) continue;
+                for (const AxisHit &hz : hits[2]) {
+                    if (dxy + hz.dist * hz.dist > reach2) continue;
+                    const uint32_t flags = (hx.flag ? 1u : 0u) | (hy.flag ? 2u : 0u) | (hz.flag ? 4u : 0u);
+                    e_cell.push_back((uint32_t)(((int64_t)hx.cell * dims[1] + hy.cell) * dims[2] + hz.cell));
+                    e_word.push_back((uint32_t)e | (flags << 20));
+                }
+            }
+    }
+    const size_t n_entries = e_cell.size();
+    GD_REQUIRE(n_entries < (size_t(1) << 24), GD_ERR_INVALID,
+               "gd_sitegrid_build: %zu (cell, site) entries exceed the 2^24 limit", n_entries);
 
+    std::vector<uint32_t> count(ncell, 0);
+    for (size_t k = 0; k < n_entries; ++k) ++count[e_cell[k]];
     std::vector<uint32_t> start(ncell + 1, 0);
-    for (int64_t c = 0; c < ncell; ++c) start[c + 1] = start[c] + count[c];
-    const size_t n_entries = start[ncell];
+    uint32_t maxc = 0;
+    for (int64_t c = 0; c < ncell; ++c) {
+        start[c + 1] = start[c] + count[c];
+        maxc = std::max(maxc, count[c]);
+    }
+    GD_REQUIRE(maxc <= 255, GD_ERR_INVALID,
+               "gd_sitegrid_build: %u candidate sites in one cell exceed the limit of 255", maxc);
 
     const size_t off_sites = sizeof(GdGridHeader);
     const size_t off_groups = align256(off_sites + (size_t)n_ranked * 16);
     const size_t off_cells = align256(off_groups + (size_t)n_groups * sizeof(GdGroupRec));
-    const size_t off_entries = align256(off_cells + (size_t)ncell * 8);
+    const size_t off_entries = align256(off_cells + (size_t)ncell * 4);
     const size_t total = align256(off_entries + std::max<size_t>(n_entries, 1) * 4);
     *needed = total;
     if (!h_blob || cap < total) {
@@ -463,7 +642,7 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     unsigned char *base = static_cast<unsigned char *>(h_blob);
     GdGridHeader *h = reinterpret_cast<GdGridHeader *>(base);
     h->magic = kMagic;
-    h->version = 1;
+    h->version = kBlobVersion;
     h->n_sites = n_ranked;
     h->n_sites_total = n_sites;
     h->n_groups = n_groups;
@@ -475,7 +654,8 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     }
     h->n_entries = (int32_t)n_entries;
     h->is_diag = is_diag ? 1 : 0;
-    h->cutoff32 = (float)cutoff;
+    h->max_count = (int32_t)maxc;
+    h->cutoff32 = r32;
     for (int j = 0; j < 9; ++j) h->matrix[j] = m[j];
     h->off_sites = off_sites;
     h->off_groups = off_groups;
@@ -493,59 +673,71 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     }
     memcpy(base + off_groups, groups.data(), (size_t)n_groups * sizeof(GdGroupRec));
 
-    // pass 2: fill; sites are visited in ascending rank so every cell list ascends too
-    int32_t *entries = reinterpret_cast<int32_t *>(base + off_entries);
+    // counting sort by cell; sites were visited in ascending rank so every list ascends
+    uint32_t *entries = reinterpret_cast<uint32_t *>(base + off_entries);
     std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
-    for (int32_t e = 0; e < n_ranked; ++e)
-        for_each_cell(e, [&](int64_t cell) { entries[cursor[cell]++] = e; });
-
+    for (size_t k = 0; k < n_entries; ++k) entries[cursor[e_cell[k]]++] = e_word[k];
     uint32_t *cells = reinterpret_cast<uint32_t *>(base + off_cells);
-    uint32_t maxc = 0;
-    for (int64_t c = 0; c < ncell; ++c) {
-        cells[2 * c] = count[c];
-        cells[2 * c + 1] = count[c] == 1 ? (uint32_t)entries[start[c]] : start[c];
-        maxc = std::max(maxc, count[c]);
-    }
-    h->max_count = (int32_t)maxc;
+    for (int64_t c = 0; c < ncell; ++c)
+        cells[c] = (count[c] << 24) | (count[c] == 1 ? entries[start[c]] : start[c]);
     return GD_OK;
 }
 
 // ------------------------------------------------------------------------------------ launch
 
-extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_atom_frames,
-                                      const void *d_blob, const void *h_blob,
-                                      int32_t *d_states_outer, int32_t *d_states_inner,
-                                      uint8_t *d_visited, unsigned long long *d_band_counts,
-                                      void *stream) {
+extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                                      const double *d_next_pos_row, const void *d_blob,
+                                      const void *h_blob, int32_t *d_states_outer,
+                                      int32_t *d_states_inner, uint8_t *d_visited,
+                                      unsigned long long *d_band_counts, int32_t *d_event_work,
+                                      uint8_t *d_changed, void *stream) {
     GD_REQUIRE(d_pos_frac && d_blob && h_blob && d_states_outer && d_states_inner, GD_ERR_INVALID,
                "gd_site_states: null argument");
-    GD_REQUIRE(n_atom_frames >= 0, GD_ERR_INVALID, "gd_site_states: negative size");
+    GD_REQUIRE(n_frames >= 0 && n_atoms > 0, GD_ERR_INVALID, "gd_site_states: bad size");
+    GD_REQUIRE((d_event_work == nullptr) == (d_changed == nullptr), GD_ERR_INVALID,
+               "gd_site_states: d_event_work and d_changed must both be given or both be NULL");
     GD_REQUIRE((reinterpret_cast<uintptr_t>(d_pos_frac) & 15) == 0, GD_ERR_ALIGNMENT,
                "gd_site_states: d_pos_frac must be 16-byte aligned");
+    GD_REQUIRE((reinterpret_cast<uintptr_t>(d_next_pos_row) & 15) == 0, GD_ERR_ALIGNMENT,
+               "gd_site_states: d_next_pos_row must be 16-byte aligned");
     GD_REQUIRE((reinterpret_cast<uintptr_t>(d_blob) & 255) == 0, GD_ERR_ALIGNMENT,
                "gd_site_states: d_blob must be 256-byte aligned");
     const GdGridHeader *h = static_cast<const GdGridHeader *>(h_blob);
-    GD_REQUIRE(h->magic == kMagic && h->version == 1, GD_ERR_INVALID,
+    GD_REQUIRE(h->magic == kMagic && h->version == kBlobVersion, GD_ERR_INVALID,
                "gd_site_states: h_blob is not a site grid");
-    if (n_atom_frames == 0) return GD_OK;
+    if (n_frames == 0) return GD_OK;
     const GdDeviceInfo &dev = gd_device_info();
     GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");
 
     const unsigned char *base = static_cast<const unsigned char *>(d_blob);
+    const GdChunks geo = gd_chunks(n_frames, n_atoms);
     StatesParams p;
     memset(&p, 0, sizeof(p));
     p.pos = d_pos_frac;
-    p.n_af = n_atom_frames;
-    p.n_chunks = gd_ceil_div(n_atom_frames, kThreads);
+    p.next_row = d_next_pos_row;
+    p.n_frames = n_frames;
+    p.n_atoms = n_atoms;
+    p.f = geo.f;
+    p.n_chunks = geo.n_chunks;
+    p.n_strips = (n_atoms + 31) / 32;
+    int spg_shift = 0;
+    while ((1 << spg_shift) < kWarps && (1 << spg_shift) < p.n_strips) ++spg_shift;
+    p.spg_shift = spg_shift;
+    const int cpg = kWarps >> spg_shift;
+    p.n_cblocks = gd_ceil_div(geo.n_chunks, cpg);
+    const int64_t n_groups_of_strips = gd_ceil_div(p.n_strips, 1 << spg_shift);
+    const int64_t grid = n_groups_of_strips * p.n_cblocks;
+    GD_REQUIRE(grid < (int64_t(1) << 31), GD_ERR_INVALID, "gd_site_states: shard too large");
     p.sites = reinterpret_cast<const float4 *>(base + h->off_sites);
-    p.cells = reinterpret_cast<const uint2 *>(base + h->off_cells);
-    p.entries = reinterpret_cast<const int32_t *>(base + h->off_entries);
+    p.cells = reinterpret_cast<const uint32_t *>(base + h->off_cells);
+    p.entries = reinterpret_cast<const uint32_t *>(base + h->off_entries);
     p.groups = reinterpret_cast<const GdGroupRec *>(base + h->off_groups);
     p.out_o = d_states_outer;
     p.out_i = d_states_inner;
     p.visited = d_visited;
     p.band = d_band_counts;
-    p.n_sites = h->n_sites;
+    p.work = d_event_work;
+    p.changed = d_changed;
     p.n_sites_total = h->n_sites_total;
     p.n_groups = h->n_groups;
     p.is_diag = h->is_diag;
@@ -558,19 +750,19 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_atom_f
     }
     for (int j = 0; j < 9; ++j) p.m[j] = h->matrix[j];
 
-    const size_t fixed = (size_t)kStages * kThreads * 24 + 2 * kStages * sizeof(uint64_t) +
-                         kMaxGroups * sizeof(GdGroupRec);
-    const size_t with_sites = fixed + (size_t)h->n_sites * 16;
-    // keep two CTAs per SM when the site table fits twice, else one; fall back to global
-    const bool smem_sites = with_sites <= (size_t)dev.max_smem_optin;
-    const size_t smem = smem_sites ? with_sites : fixed;
-    auto kern = smem_sites ? k_site_states<true> : k_site_states<false>;
+    const size_t vis_bytes = 2 * (size_t)h->n_sites_total;
+    p.vis_mode = d_visited == nullptr ? 0 : (vis_bytes <= (size_t)kVisSmemMax ? 1 : 2);
+    p.g0 = *reinterpret_cast<const GdGroupRec *>(static_cast<const unsigned char *>(h_blob) + h->off_groups);
+    const size_t smem = (size_t)kWarps * kStages * kRowDoubles * 8 + kWarps * kStages * sizeof(uint64_t) +
+                        kMaxGroups * sizeof(GdGroupRec) +
+                        (p.vis_mode == 1 ? ((vis_bytes + 15) & ~size_t(15)) : 0);
+    // rows of an odd-sized atom axis start on 8-byte boundaries only: no bulk copies then
+    const bool tma = (n_atoms % 2) == 0;
+    const bool one = h->n_groups == 1;
+    void (*kern)(StatesParams) =
+        tma ? (one ? k_site_states<true, true> : k_site_states<true, false>)
+            : (one ? k_site_states<false, true> : k_site_states<false, false>);
     GD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    GD_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem));
-    GD_REQUIRE(per_sm >= 1, GD_ERR_CUDA, "gd_site_states: kernel does not fit on an SM");
-    int64_t grid = (int64_t)dev.sm_count * per_sm;
-    if (grid > p.n_chunks) grid = p.n_chunks;
     kern<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(p);
     GD_LAUNCH_CHECK();
     return GD_OK;

@@ -45,16 +45,18 @@ def _jumps_device(transitions: Transitions, minimal_residence: int) -> torch.Ten
     n_atoms = ev.n_atoms
     n_frames_total = len(transitions.trajectory)  # jumps.py:39
     lib = _lib.lib
-    counts = dv.empty((n_atoms + 1,), torch.int64)
+    n_events = len(ev)
+    work = dv.empty((int(lib.gd_jumps_work_bytes(n_events, n_atoms)),), torch.uint8)
     n_jumps = C.c_int64(0)
     s = dv.stream_ptr()
-    _lib.check(lib.gd_jumps_count(dv.ptr(ev.rows), dv.ptr(ev.atom_offsets), n_atoms, n_frames_total,
-                                  int(minimal_residence), dv.ptr(counts), C.byref(n_jumps), s))
+    _lib.check(lib.gd_jumps_count(dv.ptr(ev.rows), dv.ptr(ev.atom_offsets), n_events, n_atoms,
+                                  n_frames_total, int(minimal_residence), dv.ptr(work),
+                                  C.byref(n_jumps), s))
     if n_jumps.value == 0:
         raise ValueError('No jumps found')
     out = dv.empty((n_jumps.value, 6), torch.int32)
-    _lib.check(lib.gd_jumps_fill(dv.ptr(ev.rows), dv.ptr(ev.atom_offsets), n_atoms, n_frames_total,
-                                 int(minimal_residence), dv.ptr(counts), dv.ptr(out), s))
+    _lib.check(lib.gd_jumps_fill(dv.ptr(ev.rows), dv.ptr(ev.atom_offsets), n_events, n_atoms,
+                                 n_frames_total, int(minimal_residence), dv.ptr(work), dv.ptr(out), s))
     return out
 
 

@@ -1,8 +1,9 @@
 """Device-resident, frame-sharded run of the hot path (K1 -> K2 -> K3).
 
-One process per GPU; each rank owns a contiguous block of frames.  K1 needs no
-communication.  K2 needs the first state row of the following shard (halo) and the
-OR of the per-atom "state changes at all" flags; the compacted event tables are
+One process per GPU; each rank owns a contiguous block of frames.  K1 (site states
+fused with the event count) needs one halo row of POSITIONS from the following shard,
+exchanged before the kernel starts.  K2 needs that shard's first state row for the halo
+event itself and the OR of the per-atom "state changes at all" flags; the compacted event tables are
 all-gathered and merged per atom, after which every rank holds the whole table and
 runs K3 on it.  All exchanges are O(n_atoms) or O(n_events) and go through
 ``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in the CPU tests of the
@@ -89,12 +90,24 @@ class HotPath:
         visited.zero_()
         band.zero_()
 
-        # ---- K1
+        # ---- K1 (+ the event count of K2, fused).  The event at a shard's last frame needs the
+        # state of the next shard's first frame: positions are known up front, so the halo ROW OF
+        # POSITIONS is exchanged before K1 and its state recomputed locally -- K1 never waits for
+        # a neighbour's kernel.
+        next_pos = None
+        if self.world > 1:
+            first_rows = self._all_gather(pos[0].contiguous())  # [W, A, 3]
+            if self.rank + 1 < self.world:
+                next_pos = first_rows[self.rank + 1].contiguous()
+        work = self._tensor('work', (int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+        changed = self._tensor('changed', (2 * n_atoms,), torch.uint8)
+        changed.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        _lib.check(lib.gd_site_states(dv.ptr(pos), n_frames * n_atoms, dv.ptr(self.grid.d_blob),
-                                      self.grid.h_blob.ctypes.data, dv.ptr(outer), dv.ptr(inner),
-                                      dv.ptr(visited), dv.ptr(band), s))
+        _lib.check(lib.gd_site_states(dv.ptr(pos), n_frames, n_atoms, dv.ptr(next_pos),
+                                      dv.ptr(self.grid.d_blob), self.grid.h_blob.ctypes.data,
+                                      dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band),
+                                      dv.ptr(work), dv.ptr(changed), s))
         e1.record()
         self.last_k1_events = (e0, e1)
         launches += 1
@@ -113,19 +126,12 @@ class HotPath:
                 _lib.check(lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut), self.n_sites, s))
                 launches += 1
 
-        # ---- K2
+        # ---- K2: scan + fill (the fill writes the halo event with the neighbour's first states)
         next_o = next_i = None
         if self.world > 1:
             rows = self._all_gather(torch.stack([outer[0], inner[0]]))  # [W, 2, A]
             if self.rank + 1 < self.world:
                 next_o, next_i = rows[self.rank + 1, 0].contiguous(), rows[self.rank + 1, 1].contiguous()
-        work = self._tensor('work', (int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
-        changed = self._tensor('changed', (2 * n_atoms,), torch.uint8)
-        changed.zero_()
-        _lib.check(lib.gd_events_count(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, dv.ptr(next_o),
-                                       dv.ptr(next_i), dv.ptr(work), dv.ptr(changed), s))
-        launches += 1
-        if self.world > 1:
             self._dist().all_reduce(changed, op=self._dist().ReduceOp.MAX, group=self.group)
         offsets = self._tensor('offsets', (n_atoms + 1,), torch.int64)
         n_events = C.c_int64(0)
@@ -135,6 +141,7 @@ class HotPath:
             raise IndexError('index -1 is out of bounds for axis 0 with size 0')
         _lib.check(st)
         launches += 2
+        self.last_n_local_events = n_events.value
         if not bool(changed[:n_atoms].any()):
             raise ValueError('need at least one array to concatenate')
         rows = dv.empty((max(n_events.value, 1), 6), torch.int32)
@@ -151,16 +158,16 @@ class HotPath:
         else:
             n_total = n_events.value
 
-        # ---- K3
-        counts = self._tensor('jcounts', (n_atoms + 1,), torch.int64)
+        # ---- K3 (time-parallel state machine: 5 launches to count, 1 to fill)
+        jwork = self._tensor('jwork', (int(lib.gd_jumps_work_bytes(n_total, n_atoms)),), torch.uint8)
         n_jumps = C.c_int64(0)
-        _lib.check(lib.gd_jumps_count(dv.ptr(rows), dv.ptr(offsets), n_atoms, self.n_frames_total,
-                                      self.minimal_residence, dv.ptr(counts), C.byref(n_jumps), s))
-        launches += 2
+        _lib.check(lib.gd_jumps_count(dv.ptr(rows), dv.ptr(offsets), n_total, n_atoms, self.n_frames_total,
+                                      self.minimal_residence, dv.ptr(jwork), C.byref(n_jumps), s))
+        launches += 4
         jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
         if n_jumps.value:
-            _lib.check(lib.gd_jumps_fill(dv.ptr(rows), dv.ptr(offsets), n_atoms, self.n_frames_total,
-                                         self.minimal_residence, dv.ptr(counts), dv.ptr(jumps), s))
+            _lib.check(lib.gd_jumps_fill(dv.ptr(rows), dv.ptr(offsets), n_total, n_atoms, self.n_frames_total,
+                                         self.minimal_residence, dv.ptr(jwork), dv.ptr(jumps), s))
             launches += 1
         self.launches_per_run = launches
         return {'outer': outer, 'inner': inner, 'events': rows, 'atom_offsets': offsets,

@@ -119,8 +119,12 @@ class SiteGrid:
 
 
 def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_fraction: dict,
-                        which: str = 'both'):
-    """K1 on the device.  Returns (outer int32 [T,A], inner int32 [T,A], info dict)."""
+                        which: str = 'both', count_events: bool = False):
+    """K1 on the device.  Returns (outer int32 [T,A], inner int32 [T,A], info dict).
+
+    With ``count_events`` the same pass also leaves the per-(atom, frame chunk) event counts
+    and the "state ever changes" flags K2 needs (``info['event_work']``, ``info['changed']``).
+    """
     site_frac, site_labels, _ = site_arrays(sites)
     grid = SiteGrid(
         lattice_matrix=trajectory.get_lattice().matrix,
@@ -135,9 +139,14 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
     inner = dv.empty((n_frames, n_atoms), torch.int32)
     visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
     band = dv.zeros((4,), torch.int64)
+    work = changed = None
+    if count_events and n_frames > 0:
+        work = dv.empty((int(_lib.lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+        changed = dv.zeros((2 * n_atoms,), torch.uint8)
     st = _lib.lib.gd_site_states(
-        dv.ptr(pos), n_frames * n_atoms, dv.ptr(grid.d_blob), grid.h_blob.ctypes.data,
-        dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band), dv.stream_ptr(),
+        dv.ptr(pos), n_frames, n_atoms, None, dv.ptr(grid.d_blob), grid.h_blob.ctypes.data,
+        dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band), dv.ptr(work), dv.ptr(changed),
+        dv.stream_ptr(),
     )
     _lib.check(st)
     visited_h = dv.to_host(visited).astype(bool).reshape(2, grid.n_sites)
@@ -152,6 +161,7 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
                 warn(f'No floating species in range of {label} ({radius=})', stacklevel=3)
         lut = grid.remap_lut(vis)
         if lut is not None:
+            # injective on the visited sites, so the event pattern counted by K1 is unchanged
             d_lut = dv.to_device(lut)
             _lib.check(_lib.lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut),
                                                 grid.n_sites, dv.stream_ptr()))
@@ -160,6 +170,8 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
         'visited_inner': visited_h[1],
         'band_1e-12': (int(band_h[0]), int(band_h[1])),
         'band_4e-6': (int(band_h[2]), int(band_h[3])),
+        'event_work': work,
+        'changed': changed,
     }
     return outer, inner, info
 
@@ -215,14 +227,17 @@ class EventTable:
         return cls(dv.to_device(data.astype(np.int32)), dv.to_device(offsets), n_atoms)
 
 
-def _events_device(outer: torch.Tensor, inner: torch.Tensor) -> EventTable:
+def _events_device(outer: torch.Tensor, inner: torch.Tensor, work: torch.Tensor | None = None,
+                   changed: torch.Tensor | None = None) -> EventTable:
+    """K2: scan + fill; the count pass is skipped when K1 already produced ``work`` / ``changed``."""
     n_frames, n_atoms = int(outer.shape[0]), int(outer.shape[1])
     lib = _lib.lib
-    work = dv.empty((int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
-    changed = dv.zeros((2 * n_atoms,), torch.uint8)
     s = dv.stream_ptr()
-    _lib.check(lib.gd_events_count(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, None, None,
-                                   dv.ptr(work), dv.ptr(changed), s))
+    if work is None or changed is None:
+        work = dv.empty((int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+        changed = dv.zeros((2 * n_atoms,), torch.uint8)
+        _lib.check(lib.gd_events_count(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, None, None,
+                                       dv.ptr(work), dv.ptr(changed), s))
     offsets = dv.empty((n_atoms + 1,), torch.int64)
     n_events = C.c_int64(0)
     st = lib.gd_events_scan(dv.ptr(work), n_frames, n_atoms, dv.ptr(changed), dv.ptr(offsets),
@@ -404,9 +419,9 @@ class Transitions:
         # K1 produces both in one pass over the positions
         outer, inner, info = _site_states_device(
             sites=sites, trajectory=diff_trajectory, site_radius=site_radius_obj.radius,
-            site_inner_fraction=site_radius_obj.inner_fraction,
+            site_inner_fraction=site_radius_obj.inner_fraction, count_events=True,
         )
-        events = _events_device(outer, inner)
+        events = _events_device(outer, inner, info.pop('event_work'), info.pop('changed'))
 
         return cls(
             sites=sites, trajectory=trajectory, diff_trajectory=diff_trajectory,

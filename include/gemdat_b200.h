@@ -80,26 +80,39 @@ gd_status_t gd_sitegrid_build(const double *h_lattice, const double *h_sites_fra
                               const double *h_group_radius, const double *h_group_inner,
                               int32_t n_groups, void *h_blob, size_t cap, size_t *needed);
 
-/* One pass over all atom-frames.
+/* One pass over all atom-frames of a frame shard, fused with the event COUNT of K2
+ * (gd_events_count) so that the states are never re-read for counting.
  *
- *  d_pos_frac     [n_atom_frames,3] float64 fractional positions, C order
- *                 ([T,A,3] flattened; Trajectory.positions); 16-byte aligned.
- *  d_blob         device copy of the gd_sitegrid_build blob
- *  d_states_outer [n_atom_frames] int32 site index or -1  (Transitions.states)
- *  d_states_inner [n_atom_frames] int32                   (Transitions.inner_states)
+ *  d_pos_frac     [n_frames,n_atoms,3] float64 fractional positions, C order
+ *                 (Trajectory.positions); 16-byte aligned.
+ *  d_next_pos_row [n_atoms,3] positions of the first frame of the FOLLOWING frame
+ *                 shard (multi-GPU halo; its state is recomputed here), or NULL when
+ *                 this shard ends the trajectory; 16-byte aligned.
+ *  d_blob/h_blob  device / host copy of the gd_sitegrid_build blob
+ *  d_states_outer [n_frames,n_atoms] int32 site index or -1  (Transitions.states)
+ *  d_states_inner [n_frames,n_atoms] int32                   (Transitions.inner_states)
  *  d_visited      [2*n_sites] uint8, zero-initialised by the caller: set to 1 for
  *                 every site that contains at least one atom-frame (outer: first
  *                 n_sites bytes, inner: next n_sites).  Feeds the reference's
  *                 "No floating species in range" warning (transitions.py:798-800)
- *                 and the integer_remap quirk (gd_remap_states).
+ *                 and the integer_remap quirk (gd_remap_states).  May be NULL.
  *  d_band_counts  [4] uint64, zero-initialised: atom-frames with | |d|-r | < 1e-12 A
  *                 (outer, inner) and < 4e-6 A (outer, inner) for some site; the
  *                 float32 staging of the reference makes the latter band the one
  *                 where a pure-fp64 method would disagree.  May be NULL.
+ *  d_event_work   gd_events_work_elems(n_frames,n_atoms) int32: receives what
+ *                 gd_events_count would write (per (atom, frame chunk) event counts);
+ *  d_changed      [2*n_atoms] uint8, zero-initialised: as in gd_events_count.
+ *                 Both NULL = states only.  NOTE: counts are taken on the states as
+ *                 written here; if gd_remap_states changes them afterwards (only
+ *                 when a labelled group has never-visited sites) the event pattern is
+ *                 unchanged because the remap is injective.
  */
-gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_atom_frames, const void *d_blob,
-                           const void *h_blob, int32_t *d_states_outer, int32_t *d_states_inner,
-                           uint8_t *d_visited, unsigned long long *d_band_counts, void *stream);
+gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                           const double *d_next_pos_row, const void *d_blob, const void *h_blob,
+                           int32_t *d_states_outer, int32_t *d_states_inner, uint8_t *d_visited,
+                           unsigned long long *d_band_counts, int32_t *d_event_work,
+                           uint8_t *d_changed, void *stream);
 
 /* integer_remap quirk (src/gemdat/utils.py:101-125 via transitions.py:804-805):
  * d_lut [n_sites] int32 maps the natural site index to the index the reference
@@ -172,18 +185,23 @@ gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames, int32_t n_
  *           pandas groupby/iterrows state machine)
  * ------------------------------------------------------------------------- */
 
+/* Scratch (bytes, 16-byte aligned) the two calls below need in d_work. */
+int64_t gd_jumps_work_bytes(int64_t n_events, int32_t n_atoms);
+
 /* d_events [n_events,6] int32 sorted by atom then time, d_atom_offsets
  * [n_atoms+1] int64.  n_frames_total = len(transitions.trajectory) (jumps.py:39).
- * d_jump_counts [n_atoms+1] int64 scratch.  Writes *h_n_jumps; synchronises. */
-gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_atom_offsets, int32_t n_atoms,
-                           int64_t n_frames_total, int64_t minimal_residence,
-                           int64_t *d_jump_counts, int64_t *h_n_jumps, void *stream);
+ * The per-atom state machine runs time-parallel over segments of 512 events
+ * (speculate, chain, scan).  Writes *h_n_jumps; synchronises. */
+gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_atom_offsets, int64_t n_events,
+                           int32_t n_atoms, int64_t n_frames_total, int64_t minimal_residence,
+                           void *d_work, int64_t *h_n_jumps, void *stream);
 
 /* d_jumps [n_jumps,6] int32: atom index, start site, destination site,
- * start time, stop time, residence_time (jumps.py:110-119). */
-gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets, int32_t n_atoms,
-                          int64_t n_frames_total, int64_t minimal_residence,
-                          const int64_t *d_jump_counts, int32_t *d_jumps, void *stream);
+ * start time, stop time, residence_time (jumps.py:110-119).  d_work as left by
+ * gd_jumps_count for the same arguments. */
+gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets, int64_t n_events,
+                          int32_t n_atoms, int64_t n_frames_total, int64_t minimal_residence,
+                          const void *d_work, int32_t *d_jumps, void *stream);
 
 /* (start, destination) count matrix: _calculate_transitions_matrix,
  * src/gemdat/transitions.py:812-834.  d_rows [n_rows,row_stride] int32 with the

@@ -49,17 +49,59 @@ def parse_blob(blob: np.ndarray):
     inv_box = np.frombuffer(raw, dtype=np.float64, count=3, offset=off)
     matrix = np.frombuffer(raw, dtype=np.float64, count=9, offset=off + 24)
     o_sites, o_cells, o_entries, o_groups, total = struct.unpack_from('<5Q', raw, off + 24 + 72)
-    assert magic == 0x47534447 and version == 1 and total == len(raw)
+    assert magic == 0x47534447 and version == 2 and total == len(raw)
     sites = np.frombuffer(raw, dtype=np.float32, count=4 * n_sites, offset=o_sites).reshape(-1, 4)
     natgrp = sites[:, 3].copy().view(np.int32)
     ncell = dims[0] * dims[1] * dims[2]
-    cells = np.frombuffer(raw, dtype=np.uint32, count=2 * ncell, offset=o_cells).reshape(-1, 2)
-    entries = np.frombuffer(raw, dtype=np.int32, count=max(n_entries, 1), offset=o_entries)
-    groups = np.frombuffer(raw, dtype=np.float64, count=4 * n_groups, offset=o_groups).reshape(-1, 4)
+    cells = np.frombuffer(raw, dtype=np.uint32, count=ncell, offset=o_cells)
+    entries = np.frombuffer(raw, dtype=np.uint32, count=max(n_entries, 1), offset=o_entries)
+    grp = np.frombuffer(raw, dtype=np.uint8, count=48 * n_groups, offset=o_groups).reshape(-1, 48)
+    r2 = grp[:, :16].copy().view(np.float64).reshape(-1, 2)  # r2_outer, r2_inner
+    band = grp[:, 16:32].copy().view(np.int32).reshape(-1, 4)  # lo_o, span_o, lo_i, span_i
     return dict(n_sites=n_sites, n_total=n_total, dims=dims, box=box, cutoff32=cutoff32,
                 inv_cell=inv_cell, matrix=matrix.reshape(3, 3), xyz=sites[:, :3],
                 natural=natgrp & 0xFFFFFF, group=natgrp >> 24, cells=cells, entries=entries,
-                groups=groups, is_diag=is_diag, max_count=max_count)
+                r2=r2, band=band, is_diag=is_diag, max_count=max_count, n_entries=n_entries)
+
+
+def emulate_k1(b, c0, c1):
+    """numpy restatement of the device walk: cell -> candidate words -> flagged-axis image ->
+    exact test; returns (outer, inner, n_band_prefilter_misses)."""
+    dims = b['dims']
+    idx = np.empty((len(c0), 3), dtype=np.int64)
+    for j in range(3):
+        raw = (c0[:, j] * b['inv_cell'][j]).astype(np.float32).astype(np.int64)
+        idx[:, j] = np.minimum(raw.astype(np.uint32), dims[j] - 1)
+    cell = (idx[:, 0] * dims[1] + idx[:, 1]) * dims[2] + idx[:, 2]
+    outer = np.full(len(c0), -1, dtype=np.int64)
+    inner = np.full(len(c0), -1, dtype=np.int64)
+    prefilter_misses = 0
+    for n in range(len(c0)):
+        word = int(b['cells'][cell[n]])
+        cnt, payload = word >> 24, word & 0xFFFFFF
+        words = [payload] if cnt == 1 else [int(w) for w in b['entries'][payload:payload + cnt]]
+        for w in words:
+            e, flags = w & 0xFFFFF, w >> 20
+            s = b['xyz'][e].astype(np.float64)
+            d = s - c0[n].astype(np.float64)
+            for j in range(3):
+                if flags >> j & 1 and not np.isnan(c1[n, j]):
+                    alt = s[j] - np.float64(c1[n, j])
+                    if abs(alt) < abs(d[j]):
+                        d[j] = alt
+            d2 = (d[0] * d[0] + d[1] * d[1]) + d[2] * d[2]
+            r2o, r2i = b['r2'][b['group'][e]]
+            if d2 <= r2o:
+                outer[n] = b['natural'][e]
+            if d2 <= r2i:
+                inner[n] = b['natural'][e]
+            # the integer pre-filter must pass everything the exact band filter would look at
+            hi = int(np.float64(d2).view(np.int64) >> 32)
+            lo_o, span_o, lo_i, span_i = (int(v) for v in b['band'][b['group'][e]])
+            passed = 0 <= hi - lo_o <= span_o or 0 <= hi - lo_i <= span_i
+            exact = abs(d2 - r2o) < r2o * 1e-3 or abs(d2 - r2i) < r2i * 1e-3
+            prefilter_misses += exact and not passed
+    return outer, inner, prefilter_misses
 
 
 CASES = [
@@ -68,11 +110,16 @@ CASES = [
     ((7.31, 5.07, 6.43), 24, {'Q': 1.1, 'P': 0.8}, {'Q': 0.7, 'P': 1.0}, 'QP'),
     ((38.91, 38.91, 25.94), 400, {'B': 0.5, 'A': 0.6}, {'B': 1.0, 'A': 0.4}, 'AB'),
     ((3.0, 40.0, 2.5), 12, {'': 1.2}, {'': 1.0}, None),  # box narrower than 2*cutoff along x, z
+    ((2.0, 2.2, 1.9), 3, {'': 1.0}, {'': 0.3}, None),  # every cell sees every site through images
 ]
 
 
+@pytest.mark.parametrize('grid_k', ['0.4', '0.75', '1.5'])
 @pytest.mark.parametrize('lengths,n_sites,radius,inner,pattern', CASES)
-def test_site_grid_is_conservative(lengths, n_sites, radius, inner, pattern):
+def test_site_grid_walk_equals_bruteforce(lengths, n_sites, radius, inner, pattern, grid_k, monkeypatch):
+    """The host-built grid (exact sphere/box test + per-axis image flags) walked exactly as the
+    kernel walks it gives the brute-force oracle's states for atoms anywhere in the box."""
+    monkeypatch.setenv('GD_GRID_K', grid_k)
     rng = np.random.default_rng(n_sites)
     lattice = np.diag(lengths)
     site_frac = rng.random((n_sites, 3)) * 1.2 - 0.1  # some outside [0, 1)
@@ -92,32 +139,48 @@ def test_site_grid_is_conservative(lengths, n_sites, radius, inner, pattern):
         order += [i for i in range(n_sites) if (label == '' or labels[i] == label)]
     np.testing.assert_array_equal(b['natural'], order)
 
-    # atoms: uniform + hugging faces / edges / site surfaces
-    pos = rng.random((6000, 1, 3))
-    pos[:500, 0] = rng.choice([0.0, 1e-9, 1 - 1e-9, 0.5], size=(500, 3))
+    # atoms: uniform + hugging faces / edges / site surfaces (where the float32 staging decides)
+    pos = rng.random((4000, 1, 3))
+    pos[:500, 0] = rng.choice([0.0, 1e-9, 1 - 1e-9, 0.5, 1 - 2**-24, 2**-25], size=(500, 3))
     near = site_frac[rng.integers(n_sites, size=1500)] + rng.normal(scale=0.03, size=(1500, 3))
     pos[500:2000, 0] = np.mod(near, 1)
+    # points on the sphere surfaces, to rounding
+    pick = rng.integers(n_sites, size=700)
+    u = rng.normal(size=(700, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    rr = np.array([radius[labels[i]] if pattern is not None else radius[''] for i in pick])
+    ff = np.array([inner[labels[i]] if pattern is not None else inner[''] for i in pick])
+    rr = np.where(rng.random(700) < 0.5, rr, rr * ff)
+    pos[2000:2700, 0] = np.mod(site_frac[pick] + (u * rr[:, None]) / np.array(lengths), 1)
     cutoff = max(radius.values())
     c0, c1, box3 = ostates.staged_atoms(pos, lattice, cutoff)
-    # device cell index: float32 multiply, truncate, clamp
-    idx = np.empty((len(c0), 3), dtype=np.int64)
-    for j in range(3):
-        idx[:, j] = np.clip((c0[:, j] * b['inv_cell'][j]).astype(np.float32).astype(np.int64), 0, b['dims'][j] - 1)
-    cell = (idx[:, 0] * b['dims'][1] + idx[:, 1]) * b['dims'][2] + idx[:, 2]
-    reach2 = np.maximum(b['groups'][:, 0], b['groups'][:, 1])  # max(r2_outer, r2_inner)
-    missing = 0
-    for e in range(b['n_sites']):
-        d2 = ostates.min_d2(b['xyz'][e], c0, c1)
-        hit = np.nonzero(d2 <= reach2[b['group'][e]])[0]
-        for n in hit:
-            cnt, payload = b['cells'][cell[n]]
-            cand = [payload] if cnt == 1 else list(b['entries'][payload:payload + cnt])
-            missing += e not in cand
-    assert missing == 0
+
+    got_o, got_i, misses = emulate_k1(b, c0, c1)
+    assert misses == 0
+    kw = dict(site_frac=site_frac, site_labels=labels, positions=pos, lattice_matrix=lattice,
+              site_radius=radius)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        # every site visited -> integer_remap is the identity, the natural indices compare
+        exp_o, vis_o = ostates.calculate_atom_states_bruteforce(
+            **kw, site_inner_fraction={k: 1.0 for k in radius}, return_visited=True)
+        exp_i, vis_i = ostates.calculate_atom_states_bruteforce(
+            **kw, site_inner_fraction=inner, return_visited=True)
+    lut_o = grid.remap_lut(vis_o)
+    lut_i = grid.remap_lut(vis_i)
+    if lut_o is not None:
+        got_o = np.where(got_o >= 0, lut_o[np.clip(got_o, 0, None)], -1)
+    if lut_i is not None:
+        got_i = np.where(got_i >= 0, lut_i[np.clip(got_i, 0, None)], -1)
+    np.testing.assert_array_equal(got_o, exp_o[:, 0])
+    np.testing.assert_array_equal(got_i, exp_i[:, 0])
     # candidate lists ascend in rank (last match = overwrite winner)
-    for cnt, payload in b['cells'][b['cells'][:, 0] > 1][:2000]:
-        lst = b['entries'][payload:payload + cnt]
-        assert np.all(np.diff(lst) > 0)
+    multi = np.nonzero((b['cells'] >> 24) > 1)[0][:2000]
+    for c in multi:
+        cnt, payload = int(b['cells'][c]) >> 24, int(b['cells'][c]) & 0xFFFFFF
+        lst = b['entries'][payload:payload + cnt] & 0xFFFFF
+        assert np.all(np.diff(lst.astype(np.int64)) > 0)
 
 
 def test_sitegrid_error_paths():

@@ -343,3 +343,122 @@ def test_c3_shape_properties_and_window_parity():
     jumps = tr.jumps().data.to_numpy()
     assert np.all(jumps[:, 1] != jumps[:, 2]) and np.all(jumps[:, 4] > jumps[:, 3])
     assert int(tr.jumps().matrix().sum()) == len(jumps)
+
+
+def _jumps_via_abi(events: np.ndarray, n_atoms: int, n_frames: int, minimal_residence: int) -> np.ndarray:
+    """gd_jumps_count / gd_jumps_fill on a raw [E, 6] event table (sorted by atom, time)."""
+    import ctypes as C
+
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+
+    ev = torch.from_numpy(np.ascontiguousarray(events, dtype=np.int32)).cuda()
+    counts = np.bincount(events[:, 0], minlength=n_atoms)
+    off = torch.from_numpy(np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)).cuda()
+    work = torch.empty(int(_lib.lib.gd_jumps_work_bytes(len(events), n_atoms)), dtype=torch.uint8, device='cuda')
+    n = C.c_int64(0)
+    s = dv.stream_ptr()
+    _lib.check(_lib.lib.gd_jumps_count(ev.data_ptr(), off.data_ptr(), len(events), n_atoms, n_frames,
+                                       minimal_residence, work.data_ptr(), C.byref(n), s))
+    out = torch.empty((max(n.value, 1), 6), dtype=torch.int32, device='cuda')
+    if n.value:
+        _lib.check(_lib.lib.gd_jumps_fill(ev.data_ptr(), off.data_ptr(), len(events), n_atoms, n_frames,
+                                          minimal_residence, work.data_ptr(), out.data_ptr(), s))
+    return out[: n.value].cpu().numpy().astype(np.int64)
+
+
+def _random_event_stream(rng, n_events, n_sites, p_stay, consistent=True):
+    """Event rows of ONE atom: a random walk over outer/inner states (NOSITE = -1 included)."""
+    rows = []
+    s, i = int(rng.integers(-1, n_sites)), -1
+    t = 0
+    for _ in range(n_events):
+        t += int(rng.integers(1, 4))
+        if rng.random() < p_stay:  # inner-only change at the same outer state
+            s1 = s
+            i1 = -1 if (i != -1 or s == -1) else s
+            if i1 == i:
+                s1 = -1 if s != -1 else int(rng.integers(0, n_sites))
+                i1 = -1
+        else:
+            s1 = int(rng.integers(-1, n_sites))
+            if s1 == s:
+                s1 = -1 if s != -1 else 0
+            i1 = s1 if (s1 != -1 and rng.random() < 0.5) else -1
+        s0 = s if consistent else int(rng.integers(-1, n_sites))
+        rows.append((0, s0, s1, i, i1, t))
+        s, i = s1, i1
+    return rows, t + 2
+
+
+@pytest.mark.parametrize('mr', [0, 2, 7])
+def test_jump_machine_time_parallel_segments(mr):
+    """K3 runs 512-event segments of an atom in parallel (speculate / chain / fill).  Streams
+    that cross many segment boundaries -- frequent departures, no departure at all for
+    thousands of events (chain falls back to sequential), and inconsistent rows (start state
+    != previous destination) -- must all equal the sequential oracle."""
+    from oracle import jumps as ojumps
+
+    rng = np.random.default_rng(99 + mr)
+    streams = [
+        _random_event_stream(rng, 5000, 6, 0.5),
+        _random_event_stream(rng, 3000, 3, 0.97),     # long stretches without a departure
+        _random_event_stream(rng, 1537, 4, 0.2),
+        _random_event_stream(rng, 2100, 5, 0.6, consistent=False),
+        _random_event_stream(rng, 512, 4, 0.5),       # exactly one segment
+        _random_event_stream(rng, 513, 4, 0.5),
+        _random_event_stream(rng, 1, 4, 0.5),
+    ]
+    # atom 2 has no events at all
+    atom_ids = [0, 1, 3, 4, 5, 6, 7]
+    rows, n_frames = [], 0
+    for a, (r, t_end) in zip(atom_ids, streams):
+        rows += [(a,) + x[1:] for x in r]
+        n_frames = max(n_frames, t_end)
+    events = np.array(rows, dtype=np.int64)
+    got = _jumps_via_abi(events, 8, n_frames, mr)
+    try:
+        exp = ojumps.transitions_to_jumps(events, n_frames, mr)
+    except ValueError:
+        exp = np.zeros((0, 6), dtype=np.int64)
+    assert len(exp) > 50
+    assert_array_equal(got, exp)
+
+
+@pytest.mark.parametrize('n_frames,n_atoms', [(300, 33), (400, 65), (1000, 31), (600, 2), (260, 97), (40, 5)])
+def test_k1_strip_walker_shapes(n_frames, n_atoms):
+    """Odd atom counts take the non-TMA variant (rows only 8-byte aligned), partial strips and
+    several frame chunks; states, fused event counts and events vs the oracles."""
+    from gemdat_b200 import Sites, Trajectory
+    from oracle import cstates, events as oevents
+
+    rng = np.random.default_rng(n_frames * 131 + n_atoms)
+    lat = np.diag([6.0, 7.5, 5.25])
+    site_frac = rng.random((14, 3))
+    labels = ['p', 'q'] * 7
+    # slow random walks so that states persist for a while and change now and then
+    pos = np.mod(rng.random((1, n_atoms, 3)) + np.cumsum(rng.normal(scale=0.04, size=(n_frames, n_atoms, 3)), axis=0), 1)
+    traj = Trajectory(species=['Li'] * n_atoms, coords=pos, lattice=lat, time_step=1e-15)
+    sites = Sites(lat, 'Li', site_frac, labels=labels)
+    radius, inner = {'p': 1.3, 'q': 1.1}, {'p': 0.5, 'q': 0.8}
+    kw = dict(site_radius=radius, site_inner_fraction=inner, fraction_of_overlap=1.0)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        eo, ei = cstates.calculate_atom_states_pair(
+            site_frac=site_frac, site_labels=labels, positions=pos, lattice_matrix=lat,
+            site_radius=radius, site_inner_fraction=inner)
+        try:
+            exp_events = oevents.calculate_transition_events(eo, ei)
+        except (IndexError, ValueError) as exc:  # reference quirks Q4: same exception expected
+            with pytest.raises(type(exc)):
+                traj.transitions_between_sites(sites, 'Li', **kw)
+            return
+        tr = traj.transitions_between_sites(sites, 'Li', **kw)
+    assert_array_equal(tr.states, eo)
+    assert_array_equal(tr.inner_states, ei)
+    assert_array_equal(tr.events.to_numpy(), exp_events)
+    # the stand-alone count pass (states given as arrays) agrees with the count fused into K1
+    from gemdat_b200.transitions import _calculate_transition_events
+
+    ev2 = _calculate_transition_events(atom_sites=eo, atom_inner_sites=ei)
+    assert_array_equal(ev2.to_numpy(), tr.events.to_numpy())
