@@ -434,7 +434,15 @@ def test_k1_strip_walker_shapes(n_frames, n_atoms):
 
     rng = np.random.default_rng(n_frames * 131 + n_atoms)
     lat = np.diag([6.0, 7.5, 5.25])
-    site_frac = rng.random((14, 3))
+    # 14 random sites at least 1.3 A apart (minimum image): the spheres still overlap (tie rule
+    # Q1) but pass the reference's check at fraction_of_overlap=1.0 (2 * min_dist >= r_i + r_j)
+    site_frac = np.zeros((0, 3))
+    while len(site_frac) < 14:
+        cand = rng.random(3)
+        d = site_frac - cand
+        d -= np.round(d)
+        if len(site_frac) == 0 or np.sqrt((((d @ lat)) ** 2).sum(axis=1)).min() >= 1.3:
+            site_frac = np.vstack([site_frac, cand])
     labels = ['p', 'q'] * 7
     # slow random walks so that states persist for a while and change now and then
     pos = np.mod(rng.random((1, n_atoms, 3)) + np.cumsum(rng.normal(scale=0.04, size=(n_frames, n_atoms, 3)), axis=0), 1)
