@@ -246,19 +246,26 @@ def run_ours(args):
     host.copy_(pos[:e2e_frames])
     torch.cuda.synchronize()
     host_np = host.numpy()
-    e2e_times = []
+    e2e_times, e2e_marks = [], []
     for i in range(args.warmup + args.steps):
         barrier()
         t0 = time.perf_counter()
         traj = Trajectory(species=['Li'] * n_atoms, coords=host_np, lattice=rec.lattice, time_step=2e-15)
         tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=RADIUS, site_inner_fraction=INNER)
-        jumps = tr.jumps(minimal_residence=MIN_RES)
-        states, inner_states = tr.states, tr.inner_states  # device -> host, int64 like the reference
-        n_j = jumps.n_jumps
         torch.cuda.synchronize()
-        dt = time.perf_counter() - t0
+        t1 = time.perf_counter()
+        jumps = tr.jumps(minimal_residence=MIN_RES)
+        n_j = jumps.n_jumps
+        t2 = time.perf_counter()
+        # device -> host: int64 arrays and DataFrames like the reference returns them
+        states, inner_states = tr.states, tr.inner_states
+        t3 = time.perf_counter()
+        events_df = tr.events
+        torch.cuda.synchronize()
+        t4 = time.perf_counter()
         if i >= args.warmup:
-            e2e_times.append(dt)
+            e2e_times.append(t4 - t0)
+            e2e_marks.append((t1 - t0, t2 - t1, t3 - t2, t4 - t3))
     e2e_dt = float(np.mean(e2e_times))
     if world > 1:
         t = torch.tensor([e2e_dt], device='cuda', dtype=torch.float64)
@@ -268,8 +275,10 @@ def run_ours(args):
         line['e2e'] = {
             'value': world * e2e_frames * n_atoms / e2e_dt, 'unit': UNIT,
             'h2d_bytes_per_step': int(host_np.nbytes),
-            'd2h_bytes_per_step': int(states.nbytes + inner_states.nbytes + tr.events.to_numpy().nbytes
+            'd2h_bytes_per_step': int(states.nbytes + inner_states.nbytes + events_df.to_numpy().nbytes
                                       + jumps.data.to_numpy().nbytes),
+            'breakdown_ms': dict(zip(['upload+transitions', 'jumps', 'states_d2h', 'events_d2h'],
+                                     (1e3 * np.mean(np.array(e2e_marks), axis=0)).round(2).tolist())),
             'frames_per_step': e2e_frames, 'ms_per_step': 1e3 * e2e_dt,
             'api': 'Trajectory.transitions_between_sites + Transitions.jumps (numpy in, numpy/pandas out)',
         }

@@ -59,8 +59,22 @@ def to_device(x, dtype: torch.dtype | None = None) -> torch.Tensor:
     return t.contiguous()
 
 
+_PINNED_MIN_BYTES = 1 << 20
+
+
 def to_host(t: torch.Tensor) -> np.ndarray:
-    return t.detach().cpu().numpy()
+    """Device tensor -> numpy.  Large results land in pinned memory (torch's caching host
+    allocator recycles the blocks, so only the first call pays for cudaHostAlloc) and move by
+    DMA at PCIe speed; the returned array keeps its pinned block alive."""
+    t = t.detach()
+    if not t.is_cuda:
+        return t.numpy()
+    if t.numel() * t.element_size() < _PINNED_MIN_BYTES:
+        return t.cpu().numpy()
+    out = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    out.copy_(t, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return out.numpy()
 
 
 def host_f64(x) -> np.ndarray:

@@ -64,7 +64,7 @@ def _generic_transitions_to_jumps(transitions: Transitions, *, minimal_residence
     """Drop-in for jumps.py:24-119."""
     table = _jumps_device(transitions, minimal_residence)
     transitions._dev['jumps'] = table
-    return pd.DataFrame(data=dv.to_host(table).astype(np.int64), columns=JUMP_COLUMNS)
+    return pd.DataFrame(data=dv.to_host(table).astype(np.int64), columns=JUMP_COLUMNS, copy=False)
 
 
 class Jumps:

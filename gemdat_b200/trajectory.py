@@ -134,9 +134,23 @@ class Trajectory:
         return self.coords
 
     def _device_positions(self) -> torch.Tensor:
-        """float64 CUDA tensor [T, A, 3] of wrapped positions (uploads host arrays)."""
+        """float64 CUDA tensor [T, A, 3] of wrapped positions.
+
+        Host arrays are uploaded once per coords array: the device copy is cached on the
+        object (and shared with ``filter`` results that keep every atom), so
+        ``transitions_between_sites`` + ``metrics`` + ``to_volume`` on one trajectory pay for
+        one host->device copy, not three.
+        """
         self.to_positions()
-        return dv.to_device(self.coords, torch.float64)
+        if dv.is_device(self.coords):
+            return dv.to_device(self.coords, torch.float64)
+        holder = self.__dict__.setdefault('_dev_holder', {})
+        cached = holder.get('pos')
+        if cached is not None and cached[0] is self.coords:
+            return cached[1]
+        t = dv.to_device(self.coords, torch.float64)
+        holder['pos'] = (self.coords, t)
+        return t
 
     # ------------------------------------------------------------------ scalars
     @property
@@ -165,18 +179,26 @@ class Trajectory:
         wanted = {_symbol(s) for s in species}
         idx = [_symbol(sp) in wanted for sp in self.species]
         pos = self.positions
-        if dv.is_device(pos):
+        keep_all = all(idx)
+        if keep_all:
+            # the reference copies (trajectory.py:854); coords are never modified in place here
+            # (representation changes rebind the attribute), so the array is shared
+            new_coords = pos
+        elif dv.is_device(pos):
             sel = torch.nonzero(torch.tensor(idx, device=pos.device)).flatten()
-            new_coords = pos.index_select(1, sel) if len(sel) != pos.shape[1] else pos
+            new_coords = pos.index_select(1, sel)
         else:
-            new_coords = pos[:, idx]
-        return self.__class__(
+            new_coords = np.take(pos, np.nonzero(idx)[0], axis=1)
+        out = self.__class__(
             species=[sp for sp, keep in zip(self.species, idx) if keep],
             coords=new_coords,
             lattice=self.lattice,
             metadata=self.metadata,
             time_step=self.time_step,
         )
+        if keep_all:  # same coords object: parent and child share one device copy
+            out._dev_holder = self.__dict__.setdefault('_dev_holder', {})
+        return out
 
     def split(self, n_parts: int = 10, equal_parts: bool = False) -> list['Trajectory']:
         """trajectory.py:866-894."""

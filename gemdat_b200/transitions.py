@@ -178,6 +178,8 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
 
 def widen_to_host(t: torch.Tensor) -> np.ndarray:
     """int32 device array -> int64 numpy (the reference's dtype), widened on the device."""
+    if t.numel() == 0:
+        return np.zeros(tuple(t.shape), dtype=np.int64)
     out = dv.empty(tuple(t.shape), torch.int64)
     _lib.check(_lib.lib.gd_widen_i32_i64(dv.ptr(t), dv.ptr(out), t.numel(), dv.stream_ptr()))
     return dv.to_host(out)
@@ -212,8 +214,8 @@ class EventTable:
         return int(self.rows.shape[0])
 
     def to_dataframe(self) -> pd.DataFrame:
-        data = dv.to_host(self.rows).astype(np.int64)
-        return pd.DataFrame(data=data, columns=EVENT_COLUMNS)
+        # widened to the reference's int64 on the device, one DMA to pinned memory, no host copy
+        return pd.DataFrame(data=widen_to_host(self.rows), columns=EVENT_COLUMNS, copy=False)
 
     @classmethod
     def from_dataframe(cls, events: pd.DataFrame, n_atoms: int | None = None) -> 'EventTable':
