@@ -44,7 +44,7 @@
 namespace {
 
 constexpr uint32_t kMagic = 0x47534447u;  // "GDSG"
-constexpr uint32_t kBlobVersion = 2;
+constexpr uint32_t kBlobVersion = 3;
 constexpr int kMaxGroups = 64;
 constexpr int kWarps = 8;  // strips per CTA
 constexpr int kThreads = kWarps * 32;
@@ -129,6 +129,13 @@ __host__ __device__ inline float wrap_ortho(float c, float L, double invL) {
 // device cell index along one axis: float32 multiply, truncate (clamped by the caller)
 __host__ __device__ inline int cell_raw(float x, float inv_cell) { return (int)GD_FMUL(x, inv_cell); }
 
+struct GdSiteRec {  // 32 bytes: the float32-staged centre widened (exactly) to float64
+    double x, y, z;
+    int32_t natgrp;  // natural index | group << 24
+    int32_t pad;
+};
+static_assert(sizeof(GdSiteRec) == 32, "site record layout");
+
 struct StatesParams {
     const double *pos;
     const double *next_row;  // [n_atoms,3] first row of the following shard, or null
@@ -139,7 +146,7 @@ struct StatesParams {
     int32_t f;               // frames per chunk
     int32_t n_strips;
     int32_t spg_shift;       // log2(strips per CTA)
-    const float4 *sites;     // [n_sites] x, y, z, bits(natural | group << 24)
+    const GdSiteRec *sites;  // [n_sites] in rank (overwrite) order
     const uint32_t *cells;   // [ncell] count << 24 | payload
     const uint32_t *entries; // rank | flags << 20, ranks ascending inside a cell
     const GdGroupRec *groups;
@@ -152,7 +159,6 @@ struct StatesParams {
     int32_t n_sites_total;
     int32_t n_groups;
     int32_t dims[3];
-    int32_t is_diag;
     int32_t vis_mode;  // visited flags: 0 none, 1 staged in shared memory, 2 global stores
     float box[3];
     float cutoff32;
@@ -195,14 +201,18 @@ __device__ __noinline__ unsigned band_diag(double d2, const GdGroupRec *g) {
 
 __device__ __noinline__ float wrap_slow(float c, float L, double invL) { return wrap_ortho(c, L, invL); }
 
-// site states of one atom-frame
-template <bool kOneGroup>
-__device__ __forceinline__ void classify(const StatesParams &p, const GdGroupRec *s_groups,
-                                         uint8_t *s_vis, double f0, double f1, double f2,
-                                         int32_t &best_o, int32_t &best_i, BandCounters &bc) {
-    // ---- reference staging: float64 Cartesian -> float32 -> wrap
+// What the walk knows about one atom-frame besides its two states.
+struct Staged {
+    float ax, ay, az;  // float32-staged, wrapped Cartesian position
+    uint32_t cell;     // its cell word
+};
+
+// float64 frac -> float64 Cartesian -> float32 -> wrap (the reference's staging), then the
+// cell word.  kDiag: orthorhombic cell given as a diagonal matrix (one multiply per axis).
+template <bool kDiag>
+__device__ __forceinline__ Staged stage_atom(const StatesParams &p, double f0, double f1, double f2) {
     double cx, cy, cz;
-    if (p.is_diag) {
+    if (kDiag) {
         cx = __dmul_rn(f0, p.m[0]);
         cy = __dmul_rn(f1, p.m[4]);
         cz = __dmul_rn(f2, p.m[8]);
@@ -211,61 +221,104 @@ __device__ __forceinline__ void classify(const StatesParams &p, const GdGroupRec
         cy = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[1]), __dmul_rn(f1, p.m[4])), __dmul_rn(f2, p.m[7]));
         cz = __dadd_rn(__dadd_rn(__dmul_rn(f0, p.m[2]), __dmul_rn(f1, p.m[5])), __dmul_rn(f2, p.m[8]));
     }
-    float ax = __double2float_rn(cx), ay = __double2float_rn(cy), az = __double2float_rn(cz);
-    const float Lx = p.box[0], Ly = p.box[1], Lz = p.box[2];
-    if (!(ax >= 0.0f && ax < Lx)) ax = wrap_slow(ax, Lx, p.inv_box[0]);
-    if (!(ay >= 0.0f && ay < Ly)) ay = wrap_slow(ay, Ly, p.inv_box[1]);
-    if (!(az >= 0.0f && az < Lz)) az = wrap_slow(az, Lz, p.inv_box[2]);
-    const double a0x = (double)ax, a0y = (double)ay, a0z = (double)az;
+    Staged s;
+    s.ax = __double2float_rn(cx);
+    s.ay = __double2float_rn(cy);
+    s.az = __double2float_rn(cz);
+    // positions handed over by Trajectory.positions are in [0, 1): one test, wrap out of line
+    const bool inside = (s.ax >= 0.0f) & (s.ax < p.box[0]) & (s.ay >= 0.0f) & (s.ay < p.box[1]) &
+                        (s.az >= 0.0f) & (s.az < p.box[2]);
+    if (__builtin_expect(!inside, 0)) {
+        s.ax = wrap_slow(s.ax, p.box[0], p.inv_box[0]);
+        s.ay = wrap_slow(s.ay, p.box[1], p.inv_box[1]);
+        s.az = wrap_slow(s.az, p.box[2], p.inv_box[2]);
+    }
+    const unsigned ix = min((unsigned)cell_raw(s.ax, p.inv_cell[0]), (unsigned)(p.dims[0] - 1));
+    const unsigned iy = min((unsigned)cell_raw(s.ay, p.inv_cell[1]), (unsigned)(p.dims[1] - 1));
+    const unsigned iz = min((unsigned)cell_raw(s.az, p.inv_cell[2]), (unsigned)(p.dims[2] - 1));
+    s.cell = __ldg(p.cells + ((ix * (unsigned)p.dims[1] + iy) * (unsigned)p.dims[2] + iz));
+    return s;
+}
 
-    // ---- candidate sites of this cell
-    const unsigned ix = min((unsigned)cell_raw(ax, p.inv_cell[0]), (unsigned)(p.dims[0] - 1));
-    const unsigned iy = min((unsigned)cell_raw(ay, p.inv_cell[1]), (unsigned)(p.dims[1] - 1));
-    const unsigned iz = min((unsigned)cell_raw(az, p.inv_cell[2]), (unsigned)(p.dims[2] - 1));
-    const uint32_t cell = __ldg(p.cells + ((ix * (unsigned)p.dims[1] + iy) * (unsigned)p.dims[2] + iz));
-    const uint32_t count = cell >> 24, payload = cell & 0xFFFFFFu;
-
-    best_o = GD_NOSITE;
-    best_i = GD_NOSITE;
+// Rare path (overlapping spheres): more than one site of the cell contains the atom, so sites
+// other than the winner were "visited" too.  Re-walks the cell and flags every hit.
+template <bool kOneGroup>
+__device__ __noinline__ void mark_all_hits(const StatesParams &p, const GdGroupRec *s_groups,
+                                           uint8_t *vis, Staged st) {
+    const uint32_t count = st.cell >> 24, payload = st.cell & 0xFFFFFFu;
+    const double a0x = (double)st.ax, a0y = (double)st.ay, a0z = (double)st.az;
     for (uint32_t k = 0; k < count; ++k) {
         const uint32_t word = (count == 1) ? payload : __ldg(p.entries + payload + k);
-        const float4 rec = __ldg(p.sites + (word & kRankMask));
-        const int natgrp = __float_as_int(rec.w);
+        const GdSiteRec *rec = p.sites + (word & kRankMask);
+        const double sx = rec->x, sy = rec->y, sz = rec->z;
+        const int natgrp = rec->natgrp;
         const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[natgrp >> 24];
-        const double sx = (double)rec.x, sy = (double)rec.y, sz = (double)rec.z;
         double dx = __dsub_rn(sx, a0x), dy = __dsub_rn(sy, a0y), dz = __dsub_rn(sz, a0z);
-        if (word >> 20) {  // a periodic image of the atom can be the closer one (rare)
-            if (word & (1u << 20)) dx = axis_delta_image(dx, sx, ax, Lx, p.cutoff32);
-            if (word & (1u << 21)) dy = axis_delta_image(dy, sy, ay, Ly, p.cutoff32);
-            if (word & (1u << 22)) dz = axis_delta_image(dz, sz, az, Lz, p.cutoff32);
+        if (word & (1u << 20)) dx = axis_delta_image(dx, sx, st.ax, p.box[0], p.cutoff32);
+        if (word & (1u << 21)) dy = axis_delta_image(dy, sy, st.ay, p.box[1], p.cutoff32);
+        if (word & (1u << 22)) dz = axis_delta_image(dz, sz, st.az, p.box[2], p.cutoff32);
+        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+        const int natural = natgrp & 0x00FFFFFF;
+        if (d2 <= g.r2_outer) vis[natural] = 1;
+        if (d2 <= g.r2_inner) vis[p.n_sites_total + natural] = 1;
+    }
+}
+
+// Site states of one staged atom-frame: walk the candidate sites of its cell in overwrite
+// order, exact float64 test on the float32-staged coordinates, last match wins.
+// `multi` is set when a second site contains the atom (then mark_all_hits runs).
+template <bool kOneGroup, bool kBand>
+__device__ __forceinline__ void classify(const StatesParams &p, const GdGroupRec *s_groups,
+                                         const Staged &st, bool count_band, int32_t &best_o,
+                                         int32_t &best_i, bool &multi, BandCounters &bc) {
+    best_o = GD_NOSITE;
+    best_i = GD_NOSITE;
+    multi = false;
+    uint32_t n = st.cell >> 24;
+    if (n == 0) return;
+    const uint32_t payload = st.cell & 0xFFFFFFu;
+    const double a0x = (double)st.ax, a0y = (double)st.ay, a0z = (double)st.az;
+    const uint32_t *ep = p.entries + payload;
+    uint32_t word = (n == 1) ? payload : __ldg(ep);
+    for (;;) {
+        const GdSiteRec *rec = p.sites + (word & kRankMask);
+        const double2 sxy = __ldg(reinterpret_cast<const double2 *>(rec));
+        const double sz = __ldg(&rec->z);
+        const int natgrp = __ldg(&rec->natgrp);
+        const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[natgrp >> 24];
+        double dx = __dsub_rn(sxy.x, a0x), dy = __dsub_rn(sxy.y, a0y), dz = __dsub_rn(sz, a0z);
+        if (word >> 20) {  // a periodic image of the atom can be the closer one
+            float ax = st.ax, ay = st.ay, az = st.az;
+            asm volatile("" : "+f"(ax), "+f"(ay), "+f"(az));  // keep the image arithmetic in here
+            if (word & (1u << 20)) dx = axis_delta_image(dx, sxy.x, ax, p.box[0], p.cutoff32);
+            if (word & (1u << 21)) dy = axis_delta_image(dy, sxy.y, ay, p.box[1], p.cutoff32);
+            if (word & (1u << 22)) dz = axis_delta_image(dz, sz, az, p.box[2], p.cutoff32);
         }
         const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
         const int natural = natgrp & 0x00FFFFFF;
         const bool hit_o = d2 <= g.r2_outer, hit_i = d2 <= g.r2_inner;
+        multi |= (hit_o & (best_o >= 0)) | (hit_i & (best_i >= 0));
         if (hit_o) best_o = natural;  // entries ascend in overwrite order: last match wins
         if (hit_i) best_i = natural;
-        if (p.vis_mode == 1) {
-            if (hit_o) s_vis[natural] = 1;
-            if (hit_i) s_vis[p.n_sites_total + natural] = 1;
-        } else if (p.vis_mode == 2) {
-            if (hit_o) p.visited[natural] = 1;
-            if (hit_i) p.visited[p.n_sites_total + natural] = 1;
+        if (kBand) {
+            // boundary-band diagnostics: integer pre-filter on the high word of d2, exact test
+            // on the rare path
+            const int hi = __double2hiint(d2);
+            if ((unsigned)(hi - g.band_lo_o) <= (unsigned)g.band_span_o ||
+                (unsigned)(hi - g.band_lo_i) <= (unsigned)g.band_span_i) {
+                const unsigned b = count_band ? band_diag(d2, &g) : 0u;
+                bc.o12 += b & 1u;
+                bc.of += (b >> 1) & 1u;
+                bc.i12 += (b >> 2) & 1u;
+                bc.fi += (b >> 3) & 1u;
+            }
         }
-        // boundary-band diagnostics: integer pre-filter on the high word, exact test on the
-        // rare path
-        const int hi = __double2hiint(d2);
-        if ((unsigned)(hi - g.band_lo_o) <= (unsigned)g.band_span_o ||
-            (unsigned)(hi - g.band_lo_i) <= (unsigned)g.band_span_i) {
-            const unsigned b = band_diag(d2, &g);
-            bc.o12 += b & 1u;
-            bc.of += (b >> 1) & 1u;
-            bc.i12 += (b >> 2) & 1u;
-            bc.fi += (b >> 3) & 1u;
-        }
+        if (--n == 0) break;
+        word = __ldg(++ep);
     }
 }
 
-template <bool kTma, bool kOneGroup>
+template <bool kTma, bool kOneGroup, bool kDiag, bool kBand>
 __global__ void __launch_bounds__(kThreads, 4)
     k_site_states(const __grid_constant__ StatesParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -274,9 +327,13 @@ __global__ void __launch_bounds__(kThreads, 4)
     GdGroupRec *s_groups = reinterpret_cast<GdGroupRec *>(full + kWarps * kStages);
     uint8_t *s_vis = reinterpret_cast<uint8_t *>(s_groups + kMaxGroups);
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // warp index through a shuffle: tells the compiler it is warp-uniform, so the strip / chunk /
+    // row-pointer arithmetic below stays on the uniform datapath
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
 
-    for (int g = tid; g < p.n_groups; g += kThreads) s_groups[g] = p.groups[g];
+    if (!kOneGroup)
+        for (int g = tid; g < p.n_groups; g += kThreads) s_groups[g] = p.groups[g];
     const int n_vis = 2 * p.n_sites_total;
     if (p.vis_mode == 1)
         for (int i = tid; i < (n_vis + 3) / 4; i += kThreads) reinterpret_cast<uint32_t *>(s_vis)[i] = 0;
@@ -296,115 +353,132 @@ __global__ void __launch_bounds__(kThreads, 4)
 
     if (strip < p.n_strips && chunk < p.n_chunks) {
         const int32_t a0 = strip * 32;
-        const int32_t a = a0 + lane;
-        const bool lane_on = a < p.n_atoms;
         const int r = min(32, p.n_atoms - a0);  // atoms in this strip
+        const bool lane_on = lane < r;
+        // lanes past the end of a partial strip shadow its last atom (no divergence in the
+        // walk); they never store and never count
+        const int lsrc = min(lane, r - 1);
+        const int32_t a = a0 + lsrc;
         const int64_t t0 = chunk * p.f;
         const int64_t t1 = min(p.n_frames, t0 + (int64_t)p.f);
         const int n_own = (int)(t1 - t0);
-        // halo row for the event at the chunk's last frame
-        const bool halo = p.work != nullptr && (t1 < p.n_frames || p.next_row != nullptr);
-        const int n_rows = n_own + (halo ? 1 : 0);
         const int64_t A3 = (int64_t)p.n_atoms * 3;
         const double *row0 = p.pos + t0 * A3 + (int64_t)a0 * 3;
-        const double *halo_row = (t1 < p.n_frames) ? p.pos + t1 * A3 + (int64_t)a0 * 3
-                                                   : (p.next_row ? p.next_row + (int64_t)a0 * 3 : nullptr);
-        auto row_ptr = [&](int k) { return k < n_own ? row0 + (int64_t)k * A3 : halo_row; };
-
-        // bytes of a row that the bulk copy moves (multiple of 16); an odd strip leaves the
-        // last atom's z to a plain load
-        const uint32_t row_bytes = (uint32_t)(r * 24) & ~15u;
-        const int covered = (int)(row_bytes >> 3);  // doubles in shared memory
-        double *my_ring = ring + (size_t)warp * kStages * kRowDoubles;
-        uint64_t *my_full = full + warp * kStages;
-
-        if (kTma && lane == 0) {
-            for (int s = 0; s < kStages && s < n_rows; ++s) {
-                gd_mbar_arrive_expect_tx(&my_full[s], row_bytes);
-                gd_tma_load_1d(my_ring + s * kRowDoubles, row_ptr(s), row_bytes, &my_full[s]);
-            }
-        }
-        // register prefetch of the non-TMA variant (odd n_atoms: rows are only 8-byte aligned)
-        double n0 = 0.0, n1 = 0.0, n2 = 0.0;
-        if (!kTma && lane_on) {
-            const double *q = row_ptr(0) + 3 * lane;
-            n0 = __ldg(q);
-            n1 = __ldg(q + 1);
-            n2 = __ldg(q + 2);
+        // halo row for the event at the chunk's last frame
+        const double *halo_row = nullptr;
+        if (p.work != nullptr) {
+            if (t1 < p.n_frames)
+                halo_row = p.pos + t1 * A3 + (int64_t)a0 * 3;
+            else if (p.next_row != nullptr)
+                halo_row = p.next_row + (int64_t)a0 * 3;
         }
 
-        int32_t prev_o = GD_NOSITE, prev_i = GD_NOSITE;
-        int cnt = 0;
-        int chg = 0;  // bit 0: outer state changed somewhere, bit 1: inner
-        const bool tail_lane = 3 * lane + 2 >= covered;  // z of an odd strip's last atom
-        const double *my_row = my_ring + 3 * lane;
-        int slot = 0;
-        uint32_t phase = 0;
+        // -2 never equals a state: row 0 counts as a change of both (subtracted at the end),
+        // which also flags the first state as visited
+        int32_t prev_o = -2, prev_i = -2;
+        int cnt = 0, n_do = 0, n_di = 0;
         int32_t *po = p.out_o + t0 * p.n_atoms + a;
         int32_t *pi = p.out_i + t0 * p.n_atoms + a;
+        uint8_t *vis_g = p.visited;
+        const int nst = p.n_sites_total;
+        const int vis_mode = p.vis_mode;
 
-        for (int k = 0; k < n_rows; ++k) {
-            double f0 = 0.0, f1 = 0.0, f2 = 0.0;
-            if (kTma) {
-                gd_mbar_wait(&my_full[slot], phase);
+        auto process = [&](double f0, double f1, double f2, bool own) {
+            const Staged st = stage_atom<kDiag>(p, f0, f1, f2);
+            int32_t so, si;
+            bool multi;
+            classify<kOneGroup, kBand>(p, s_groups, st, lane_on, so, si, multi, bc);
+            const bool d_o = so != prev_o, d_i = si != prev_i;
+            if (d_o) ++n_do;
+            if (d_i) ++n_di;
+            if (d_o | d_i) ++cnt;
+            // a site is visited when a state switches to it (or in mark_all_hits when several
+            // sites contain the atom at once)
+            if (vis_mode == 1) {
+                if (d_o & (so >= 0)) s_vis[so] = 1;
+                if (d_i & (si >= 0)) s_vis[nst + si] = 1;
+            } else if (vis_mode == 2) {
+                if (d_o & (so >= 0)) vis_g[so] = 1;
+                if (d_i & (si >= 0)) vis_g[nst + si] = 1;
+            }
+            if (__builtin_expect(multi && vis_mode != 0, 0))
+                mark_all_hits<kOneGroup>(p, s_groups, vis_mode == 1 ? s_vis : vis_g, st);
+            prev_o = so;
+            prev_i = si;
+            if (own) {
                 if (lane_on) {
-                    const double *sp = my_row + slot * kRowDoubles;
-                    f0 = sp[0];
-                    f1 = sp[1];
-                    f2 = tail_lane ? __ldg(row_ptr(k) + 3 * lane + 2) : sp[2];
+                    *po = so;
+                    *pi = si;
                 }
-                // The slot is refilled by the async proxy (TMA); the reads above are
-                // generic-proxy LDS.  Order them before the refill (observed on B200
-                // without the fence: whole warps read the data of a later row).
-                gd_fence_proxy_async();
-                __syncwarp();
-                if (lane == 0 && k + kStages < n_rows) {
-                    gd_mbar_arrive_expect_tx(&my_full[slot], row_bytes);
-                    gd_tma_load_1d(my_ring + slot * kRowDoubles, row_ptr(k + kStages), row_bytes,
-                                   &my_full[slot]);
+                po += p.n_atoms;
+                pi += p.n_atoms;
+            }
+        };
+
+        if (kTma) {
+            // rows of an even atom count are 16-byte aligned and r is even: the whole strip row
+            // moves as one bulk copy
+            const uint32_t row_bytes = (uint32_t)(r * 24);
+            double *my_ring = ring + (size_t)warp * kStages * kRowDoubles;
+            uint64_t *my_full = full + warp * kStages;
+            if (lane == 0) {
+                for (int s = 0; s < kStages && s < n_own; ++s) {
+                    gd_mbar_arrive_expect_tx(&my_full[s], row_bytes);
+                    gd_tma_load_1d(my_ring + s * kRowDoubles, row0 + (int64_t)s * A3, row_bytes, &my_full[s]);
                 }
-                if (++slot == kStages) {
-                    slot = 0;
-                    phase ^= 1u;
+            }
+            const double *next_src = row0 + (int64_t)kStages * A3;  // row k + kStages
+            const double *my_row = my_ring + 3 * lsrc;
+            uint32_t phase = 0;
+            for (int k = 0; k < n_own; k += kStages) {
+#pragma unroll
+                for (int s = 0; s < kStages; ++s) {
+                    if (k + s < n_own) {  // warp-uniform
+                        gd_mbar_wait(&my_full[s], phase);
+                        const double *sp = my_row + s * kRowDoubles;
+                        const double f0 = sp[0], f1 = sp[1], f2 = sp[2];
+                        // The slot is refilled by the async proxy (TMA); the reads above are
+                        // generic-proxy LDS.  Order them before the refill (observed on B200
+                        // without the fence: whole warps read the data of a later row).
+                        gd_fence_proxy_async();
+                        __syncwarp();
+                        if (k + s + kStages < n_own && lane == 0) {
+                            gd_mbar_arrive_expect_tx(&my_full[s], row_bytes);
+                            gd_tma_load_1d(my_ring + s * kRowDoubles, next_src, row_bytes, &my_full[s]);
+                        }
+                        next_src += A3;
+                        process(f0, f1, f2, true);
+                    }
                 }
-            } else {
-                f0 = n0;
-                f1 = n1;
-                f2 = n2;
-                if (lane_on && k + 1 < n_rows) {
-                    const double *q = row_ptr(k + 1) + 3 * lane;
+                phase ^= 1u;
+            }
+        } else {
+            // odd n_atoms: rows are only 8-byte aligned, no bulk copies; register prefetch
+            const double *q = row0 + 3 * lsrc;
+            double n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2);
+            for (int k = 0; k < n_own; ++k) {
+                const double f0 = n0, f1 = n1, f2 = n2;
+                if (k + 1 < n_own) {
+                    q += A3;
                     n0 = __ldg(q);
                     n1 = __ldg(q + 1);
                     n2 = __ldg(q + 2);
                 }
-            }
-            if (!lane_on) continue;
-
-            int32_t so, si;
-            classify<kOneGroup>(p, s_groups, s_vis, f0, f1, f2, so, si, bc);
-
-            if (k > 0) {
-                const int d_o = so != prev_o, d_i = si != prev_i;
-                cnt += d_o | d_i;
-                chg |= d_o | (d_i << 1);
-            }
-            prev_o = so;
-            prev_i = si;
-            if (k < n_own) {
-                *po = so;
-                *pi = si;
-                po += p.n_atoms;
-                pi += p.n_atoms;
+                process(f0, f1, f2, true);
             }
         }
+        if (halo_row != nullptr) {
+            const double *q = halo_row + 3 * lsrc;
+            process(__ldg(q), __ldg(q + 1), __ldg(q + 2), false);
+        }
         if (p.work && lane_on) {
-            p.work[(int64_t)a * p.n_chunks + chunk] = cnt;
-            if (chg & 1) p.changed[a] = 1;
-            if (chg & 2) p.changed[p.n_atoms + a] = 1;
+            p.work[(int64_t)a * p.n_chunks + chunk] = cnt - 1;
+            if (n_do > 1) p.changed[a] = 1;
+            if (n_di > 1) p.changed[p.n_atoms + a] = 1;
         }
     }
 
-    if (p.band) {
+    if (kBand && p.band) {
         const int o12 = gd_warp_sum((int)bc.o12), i12 = gd_warp_sum((int)bc.i12);
         const int of = gd_warp_sum((int)bc.of), fi = gd_warp_sum((int)bc.fi);
         if (lane == 0) {
@@ -629,7 +703,7 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
                "gd_sitegrid_build: %u candidate sites in one cell exceed the limit of 255", maxc);
 
     const size_t off_sites = sizeof(GdGridHeader);
-    const size_t off_groups = align256(off_sites + (size_t)n_ranked * 16);
+    const size_t off_groups = align256(off_sites + (size_t)n_ranked * sizeof(GdSiteRec));
     const size_t off_cells = align256(off_groups + (size_t)n_groups * sizeof(GdGroupRec));
     const size_t off_entries = align256(off_cells + (size_t)ncell * 4);
     const size_t total = align256(off_entries + std::max<size_t>(n_entries, 1) * 4);
@@ -663,13 +737,13 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     h->off_entries = off_entries;
     h->total_bytes = total;
 
-    float *srec = reinterpret_cast<float *>(base + off_sites);
+    GdSiteRec *srec = reinterpret_cast<GdSiteRec *>(base + off_sites);
     for (int32_t e = 0; e < n_ranked; ++e) {
-        srec[4 * e + 0] = sx[3 * e + 0];
-        srec[4 * e + 1] = sx[3 * e + 1];
-        srec[4 * e + 2] = sx[3 * e + 2];
-        const int32_t packed = order[e] | (h_site_group[order[e]] << 24);
-        memcpy(&srec[4 * e + 3], &packed, 4);
+        srec[e].x = (double)sx[3 * e + 0];
+        srec[e].y = (double)sx[3 * e + 1];
+        srec[e].z = (double)sx[3 * e + 2];
+        srec[e].natgrp = order[e] | (h_site_group[order[e]] << 24);
+        srec[e].pad = 0;
     }
     memcpy(base + off_groups, groups.data(), (size_t)n_groups * sizeof(GdGroupRec));
 
@@ -721,14 +795,19 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames
     p.n_chunks = geo.n_chunks;
     p.n_strips = (n_atoms + 31) / 32;
     int spg_shift = 0;
-    while ((1 << spg_shift) < kWarps && (1 << spg_shift) < p.n_strips) ++spg_shift;
+    int spg_max = kWarps;  // strips per CTA (GD_K1_SPG overrides for tuning: 1, 2, 4, 8)
+    if (const char *env = getenv("GD_K1_SPG")) {
+        const int v = atoi(env);
+        if (v == 1 || v == 2 || v == 4 || v == 8) spg_max = v;
+    }
+    while ((1 << spg_shift) < spg_max && (1 << spg_shift) < p.n_strips) ++spg_shift;
     p.spg_shift = spg_shift;
     const int cpg = kWarps >> spg_shift;
     p.n_cblocks = gd_ceil_div(geo.n_chunks, cpg);
     const int64_t n_groups_of_strips = gd_ceil_div(p.n_strips, 1 << spg_shift);
     const int64_t grid = n_groups_of_strips * p.n_cblocks;
     GD_REQUIRE(grid < (int64_t(1) << 31), GD_ERR_INVALID, "gd_site_states: shard too large");
-    p.sites = reinterpret_cast<const float4 *>(base + h->off_sites);
+    p.sites = reinterpret_cast<const GdSiteRec *>(base + h->off_sites);
     p.cells = reinterpret_cast<const uint32_t *>(base + h->off_cells);
     p.entries = reinterpret_cast<const uint32_t *>(base + h->off_entries);
     p.groups = reinterpret_cast<const GdGroupRec *>(base + h->off_groups);
@@ -740,7 +819,6 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames
     p.changed = d_changed;
     p.n_sites_total = h->n_sites_total;
     p.n_groups = h->n_groups;
-    p.is_diag = h->is_diag;
     p.cutoff32 = h->cutoff32;
     for (int j = 0; j < 3; ++j) {
         p.dims[j] = h->dims[j];
@@ -759,9 +837,20 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames
     // rows of an odd-sized atom axis start on 8-byte boundaries only: no bulk copies then
     const bool tma = (n_atoms % 2) == 0;
     const bool one = h->n_groups == 1;
-    void (*kern)(StatesParams) =
-        tma ? (one ? k_site_states<true, true> : k_site_states<true, false>)
-            : (one ? k_site_states<false, true> : k_site_states<false, false>);
+    // variant: 0 = diagonal lattice + band counters, 1 = diagonal, no band counters,
+    //          2 = general orthorhombic matrix (band code kept)
+    const int variant = h->is_diag ? (d_band_counts ? 0 : 1) : 2;
+    typedef void (*Kern)(StatesParams);
+    static const Kern table[2][2][3] = {
+        {{k_site_states<false, false, true, true>, k_site_states<false, false, true, false>,
+          k_site_states<false, false, false, true>},
+         {k_site_states<false, true, true, true>, k_site_states<false, true, true, false>,
+          k_site_states<false, true, false, true>}},
+        {{k_site_states<true, false, true, true>, k_site_states<true, false, true, false>,
+          k_site_states<true, false, false, true>},
+         {k_site_states<true, true, true, true>, k_site_states<true, true, true, false>,
+          k_site_states<true, true, false, true>}}};
+    const Kern kern = table[tma ? 1 : 0][one ? 1 : 0][variant];
     GD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)grid, kThreads, smem, (cudaStream_t)stream>>>(p);
     GD_LAUNCH_CHECK();

@@ -39,6 +39,47 @@ def merge_plan(counts: np.ndarray) -> tuple[np.ndarray, np.ndarray]:
     return atom_offsets, atom_offsets[:-1][None, :] + before
 
 
+class Comm:
+    """The two collectives the path needs, over ``torch.distributed``.
+
+    NCCL (one rank per GPU, NVLink) takes device tensors directly.  Any other backend (gloo:
+    the CPU tests of the host logic, and several ranks sharing one GPU in the GPU tests) is
+    staged through host memory -- every exchange on this path is O(n_atoms) or O(n_events).
+    """
+
+    def __init__(self, world: int = 1, group=None):
+        self.world, self.group = world, group
+        self.direct = True
+        if world > 1:
+            import torch.distributed as dist
+
+            self.dist = dist
+            self.direct = dist.get_backend(group) == 'nccl'
+
+    def all_gather(self, t: torch.Tensor) -> torch.Tensor:
+        """[world, *t.shape] on the device of ``t`` (every rank contributes the same shape)."""
+        if self.world == 1:
+            return t.unsqueeze(0)
+        src = t.contiguous() if self.direct else t.detach().cpu().contiguous()
+        # flat in / flat out: the one layout every backend accepts
+        out = torch.empty((self.world * src.numel(),), dtype=src.dtype, device=src.device)
+        self.dist.all_gather_into_tensor(out, src.reshape(-1), group=self.group)
+        out = out.reshape((self.world,) + tuple(src.shape))
+        return out if self.direct else out.to(t.device)
+
+    def all_reduce_max(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place elementwise maximum over the ranks."""
+        if self.world == 1:
+            return t
+        if self.direct:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        else:
+            h = t.detach().cpu()
+            self.dist.all_reduce(h, op=self.dist.ReduceOp.MAX, group=self.group)
+            t.copy_(h)
+        return t
+
+
 class HotPath:
     def __init__(self, *, sites, lattice, n_atoms: int, site_radius, site_inner_fraction=1.0,
                  minimal_residence: int = 0, n_frames_total: int, frame0: int = 0,
@@ -54,16 +95,12 @@ class HotPath:
         self.n_frames_total = int(n_frames_total)
         self.frame0 = int(frame0)
         self.world, self.rank, self.group = world, rank, group
+        self.comm = Comm(world, group)
         self.launches_per_run = 0
         self.last_k1_events = None
         self._buf = {}
 
     # ------------------------------------------------------------------ helpers
-    def _dist(self):
-        import torch.distributed as dist
-
-        return dist
-
     def _tensor(self, name, shape, dtype):
         t = self._buf.get(name)
         if t is None or tuple(t.shape) != tuple(shape) or t.dtype != dtype:
@@ -72,9 +109,7 @@ class HotPath:
         return t
 
     def _all_gather(self, t: torch.Tensor) -> torch.Tensor:
-        out = dv.empty((self.world,) + tuple(t.shape), t.dtype)
-        self._dist().all_gather_into_tensor(out, t.contiguous(), group=self.group)
-        return out
+        return self.comm.all_gather(t)
 
     # ------------------------------------------------------------------ the pass
     def run(self, pos: torch.Tensor) -> dict:
@@ -113,7 +148,7 @@ class HotPath:
         launches += 1
 
         if self.world > 1:
-            self._dist().all_reduce(visited, op=self._dist().ReduceOp.MAX, group=self.group)
+            self.comm.all_reduce_max(visited)
         vis = dv.to_host(visited).astype(bool).reshape(2, self.n_sites)
         for arr, v in ((outer, vis[0]), (inner, vis[1])):
             for label, key in zip(self.grid.group_labels, self.grid.group_keys):
@@ -132,7 +167,7 @@ class HotPath:
             rows = self._all_gather(torch.stack([outer[0], inner[0]]))  # [W, 2, A]
             if self.rank + 1 < self.world:
                 next_o, next_i = rows[self.rank + 1, 0].contiguous(), rows[self.rank + 1, 1].contiguous()
-            self._dist().all_reduce(changed, op=self._dist().ReduceOp.MAX, group=self.group)
+            self.comm.all_reduce_max(changed)
         offsets = self._tensor('offsets', (n_atoms + 1,), torch.int64)
         n_events = C.c_int64(0)
         st = lib.gd_events_scan(dv.ptr(work), n_frames, n_atoms, dv.ptr(changed), dv.ptr(offsets),

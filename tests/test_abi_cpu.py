@@ -49,9 +49,11 @@ def parse_blob(blob: np.ndarray):
     inv_box = np.frombuffer(raw, dtype=np.float64, count=3, offset=off)
     matrix = np.frombuffer(raw, dtype=np.float64, count=9, offset=off + 24)
     o_sites, o_cells, o_entries, o_groups, total = struct.unpack_from('<5Q', raw, off + 24 + 72)
-    assert magic == 0x47534447 and version == 2 and total == len(raw)
-    sites = np.frombuffer(raw, dtype=np.float32, count=4 * n_sites, offset=o_sites).reshape(-1, 4)
-    natgrp = sites[:, 3].copy().view(np.int32)
+    assert magic == 0x47534447 and version == 3 and total == len(raw)
+    # 32-byte site records: float64 x, y, z (the float32-staged centre, widened), int32 natgrp, pad
+    sites = np.frombuffer(raw, dtype=np.float64, count=4 * n_sites, offset=o_sites).reshape(-1, 4)
+    natgrp = sites[:, 3].copy().view(np.int32)[::2]
+    assert np.array_equal(sites[:, :3], sites[:, :3].astype(np.float32).astype(np.float64))
     ncell = dims[0] * dims[1] * dims[2]
     cells = np.frombuffer(raw, dtype=np.uint32, count=ncell, offset=o_cells)
     entries = np.frombuffer(raw, dtype=np.uint32, count=max(n_entries, 1), offset=o_entries)
@@ -59,7 +61,7 @@ def parse_blob(blob: np.ndarray):
     r2 = grp[:, :16].copy().view(np.float64).reshape(-1, 2)  # r2_outer, r2_inner
     band = grp[:, 16:32].copy().view(np.int32).reshape(-1, 4)  # lo_o, span_o, lo_i, span_i
     return dict(n_sites=n_sites, n_total=n_total, dims=dims, box=box, cutoff32=cutoff32,
-                inv_cell=inv_cell, matrix=matrix.reshape(3, 3), xyz=sites[:, :3],
+                inv_cell=inv_cell, matrix=matrix.reshape(3, 3), xyz=sites[:, :3].astype(np.float32),
                 natural=natgrp & 0xFFFFFF, group=natgrp >> 24, cells=cells, entries=entries,
                 r2=r2, band=band, is_diag=is_diag, max_count=max_count, n_entries=n_entries)
 

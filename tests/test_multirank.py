@@ -1,0 +1,180 @@
+"""Frame-sharded path: world_size-2 runs over ``torch.distributed``.
+
+* CPU (gloo, no GPU): the host-side plan -- ``Comm`` collectives, the halo rule for the event
+  at a shard's last frame, the global OR of the "state ever changes" flags and ``merge_plan``
+  -- with the oracle standing in for the kernels, against the oracle on the whole trajectory.
+* GPU (``-m gpu``): two ranks sharing ``cuda:0`` (gloo transport; NCCL needs one GPU per
+  rank) run the real ``HotPath`` kernels on their shards and must reproduce the single-rank
+  tables bit for bit.
+"""
+
+from __future__ import annotations
+
+import os
+import socket
+import sys
+import warnings
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _init(rank: int, world: int, port: int):
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+
+
+def _small_case(n_frames=1200):
+    from gemdat_b200 import synth
+
+    rec = synth.config_c2(n_frames=n_frames, seed=11)
+    return rec, rec.host_positions(0, n_frames)
+
+
+def _oracle_states(rec, pos):
+    from oracle import cstates
+
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        return cstates.calculate_atom_states_pair(
+            site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels, positions=pos,
+            lattice_matrix=rec.lattice, site_radius={'': 0.9}, site_inner_fraction={'': 0.5})
+
+
+def _shard_events(so, si, next_o, next_i, changed_outer, frame0):
+    """What gd_events_fill produces for one shard: rows sorted by (atom, time); the event at the
+    last frame uses the following shard's first states; atoms whose outer state never changes
+    anywhere are skipped (transitions.py:442-443)."""
+    if next_o is not None:
+        so = np.vstack([so, next_o[None]])
+        si = np.vstack([si, next_i[None]])
+    rows = []
+    for a in range(so.shape[1]):
+        if not changed_outer[a]:
+            continue
+        t = np.nonzero((so[:-1, a] != so[1:, a]) | (si[:-1, a] != si[1:, a]))[0]
+        for k in t:
+            rows.append((a, so[k, a], so[k + 1, a], si[k, a], si[k + 1, a], frame0 + k))
+    return np.array(rows, dtype=np.int64).reshape(-1, 6)
+
+
+def _cpu_worker(rank: int, world: int, port: int, out_path: str):
+    _init(rank, world, port)
+    try:
+        from gemdat_b200.pipeline import Comm, merge_plan
+        from oracle import events as oevents
+
+        rec, pos = _small_case()
+        n_frames, n_atoms = pos.shape[:2]
+        f0, f1 = n_frames * rank // world, n_frames * (rank + 1) // world
+        so, si = _oracle_states(rec, pos[f0:f1])
+        comm = Comm(world)
+
+        # halo: first state rows of every shard; rank r uses those of rank r + 1
+        first = comm.all_gather(torch.from_numpy(np.stack([so[0], si[0]])))
+        assert first.shape == (world, 2, n_atoms)
+        nxt = first[rank + 1].numpy() if rank + 1 < world else None
+        # "outer state ever changes" is a property of the whole trajectory
+        ext = so if nxt is None else np.vstack([so, nxt[0][None]])
+        changed = torch.from_numpy((ext[1:] != ext[:-1]).any(axis=0).astype(np.uint8))
+        comm.all_reduce_max(changed)
+        rows = _shard_events(so, si, None if nxt is None else nxt[0], None if nxt is None else nxt[1],
+                             changed.numpy().astype(bool), f0)
+
+        counts = np.bincount(rows[:, 0], minlength=n_atoms) if len(rows) else np.zeros(n_atoms, np.int64)
+        all_counts = comm.all_gather(torch.from_numpy(counts.astype(np.int64))).numpy()
+        cap = int(all_counts.sum(axis=1).max())
+        padded = np.zeros((max(cap, 1), 6), dtype=np.int64)
+        padded[: len(rows)] = rows
+        gathered = comm.all_gather(torch.from_numpy(padded)).numpy()
+        atom_offsets, dst_start = merge_plan(all_counts)
+        merged = np.zeros((int(atom_offsets[-1]), 6), dtype=np.int64)
+        for r in range(world):
+            src_off = np.concatenate([[0], np.cumsum(all_counts[r])])
+            for a in range(n_atoms):
+                n = all_counts[r, a]
+                merged[dst_start[r, a]: dst_start[r, a] + n] = gathered[r, src_off[a]: src_off[a] + n]
+
+        if rank == 0:
+            full_o, full_i = _oracle_states(rec, pos)
+            expected = oevents.calculate_transition_events(full_o, full_i)
+            np.testing.assert_array_equal(merged, expected)
+            Path(out_path).write_text(f'ok {len(expected)}')
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_plan_world2_gloo_cpu(tmp_path):
+    out = tmp_path / 'result.txt'
+    mp.spawn(_cpu_worker, args=(2, _free_port(), str(out)), nprocs=2, join=True)
+    assert out.read_text().startswith('ok ')
+    assert int(out.read_text().split()[1]) > 50
+
+
+def test_merge_plan_places_rows_by_atom_then_shard():
+    from gemdat_b200.pipeline import merge_plan
+
+    counts = np.array([[2, 0, 3], [1, 4, 0]])
+    atom_offsets, dst = merge_plan(counts)
+    np.testing.assert_array_equal(atom_offsets, [0, 3, 7, 10])
+    np.testing.assert_array_equal(dst, [[0, 3, 7], [2, 3, 10]])
+
+
+# ------------------------------------------------------------------------------------ GPU
+
+
+def _gpu_worker(rank: int, world: int, port: int, out_path: str):
+    _init(rank, world, port)
+    try:
+        torch.cuda.set_device(0)
+        from gemdat_b200.pipeline import HotPath
+
+        rec, pos = _small_case(n_frames=3000)
+        n_frames, n_atoms = pos.shape[:2]
+        f0, f1 = n_frames * rank // world, n_frames * (rank + 1) // world
+        hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=n_atoms, site_radius=0.9,
+                     site_inner_fraction=0.5, minimal_residence=3, n_frames_total=n_frames,
+                     frame0=f0, world=world, rank=rank)
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            res = hp.run(torch.from_numpy(pos[f0:f1]).cuda())
+        np.savez(f'{out_path}.{rank}.npz', outer=res['outer'].cpu().numpy(), inner=res['inner'].cpu().numpy(),
+                 events=res['events'].cpu().numpy(), jumps=res['jumps'].cpu().numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_hotpath_two_frame_shards_equal_one(tmp_path):
+    from gemdat_b200.pipeline import HotPath
+
+    out = str(tmp_path / 'rank')
+    mp.spawn(_gpu_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    rec, pos = _small_case(n_frames=3000)
+    hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=pos.shape[1], site_radius=0.9,
+                 site_inner_fraction=0.5, minimal_residence=3, n_frames_total=len(pos))
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        one = hp.run(torch.from_numpy(pos).cuda())
+    r0, r1 = np.load(f'{out}.0.npz'), np.load(f'{out}.1.npz')
+    np.testing.assert_array_equal(np.vstack([r0['outer'], r1['outer']]), one['outer'].cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r0['inner'], r1['inner']]), one['inner'].cpu().numpy())
+    for r in (r0, r1):  # every rank holds the whole merged tables
+        np.testing.assert_array_equal(r['events'], one['events'].cpu().numpy())
+        np.testing.assert_array_equal(r['jumps'], one['jumps'].cpu().numpy())
+    assert len(one['events']) > 100 and len(one['jumps']) > 0
