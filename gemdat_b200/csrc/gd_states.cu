@@ -44,7 +44,7 @@
 namespace {
 
 constexpr uint32_t kMagic = 0x47534447u;  // "GDSG"
-constexpr uint32_t kBlobVersion = 3;
+constexpr uint32_t kBlobVersion = 4;
 constexpr int kMaxGroups = 64;
 constexpr int kWarps = 8;  // strips per CTA
 constexpr int kThreads = kWarps * 32;
@@ -74,7 +74,8 @@ struct GdGridHeader {  // 256 bytes, little endian, position independent
     uint64_t off_entries;
     uint64_t off_groups;
     uint64_t total_bytes;
-    unsigned char pad[256 - 216];
+    uint64_t off_excl;
+    unsigned char pad[256 - 224];
 };
 static_assert(sizeof(GdGridHeader) == 256, "header layout");
 
@@ -129,12 +130,7 @@ __host__ __device__ inline float wrap_ortho(float c, float L, double invL) {
 // device cell index along one axis: float32 multiply, truncate (clamped by the caller)
 __host__ __device__ inline int cell_raw(float x, float inv_cell) { return (int)GD_FMUL(x, inv_cell); }
 
-struct GdSiteRec {  // 32 bytes: the float32-staged centre widened (exactly) to float64
-    double x, y, z;
-    int32_t natgrp;  // natural index | group << 24
-    int32_t pad;
-};
-static_assert(sizeof(GdSiteRec) == 32, "site record layout");
+constexpr uint32_t kSiteImgShift = 20;  // site record w: natural (20 bits) | image axes << 20 | group << 24
 
 struct StatesParams {
     const double *pos;
@@ -146,7 +142,8 @@ struct StatesParams {
     int32_t f;               // frames per chunk
     int32_t n_strips;
     int32_t spg_shift;       // log2(strips per CTA)
-    const GdSiteRec *sites;  // [n_sites] in rank (overwrite) order
+    const float4 *sites;     // [n_sites] in rank (overwrite) order: x, y, z, bits(natural | img << 20 | group << 24)
+    const float *excl2;      // [n_sites] squared exclusive radius of the site (< 0: none)
     const uint32_t *cells;   // [ncell] count << 24 | payload
     const uint32_t *entries; // rank | flags << 20, ranks ascending inside a cell
     const GdGroupRec *groups;
@@ -204,11 +201,11 @@ __device__ __noinline__ float wrap_slow(float c, float L, double invL) { return 
 // What the walk knows about one atom-frame besides its two states.
 struct Staged {
     float ax, ay, az;  // float32-staged, wrapped Cartesian position
-    uint32_t cell;     // its cell word
+    uint32_t cell;     // its cell word (filled by lookup_cell)
 };
 
-// float64 frac -> float64 Cartesian -> float32 -> wrap (the reference's staging), then the
-// cell word.  kDiag: orthorhombic cell given as a diagonal matrix (one multiply per axis).
+// float64 frac -> float64 Cartesian -> float32 -> wrap (the reference's staging).
+// kDiag: orthorhombic cell given as a diagonal matrix (one multiply per axis).
 template <bool kDiag>
 __device__ __forceinline__ Staged stage_atom(const StatesParams &p, double f0, double f1, double f2) {
     double cx, cy, cz;
@@ -225,6 +222,7 @@ __device__ __forceinline__ Staged stage_atom(const StatesParams &p, double f0, d
     s.ax = __double2float_rn(cx);
     s.ay = __double2float_rn(cy);
     s.az = __double2float_rn(cz);
+    s.cell = 0;
     // positions handed over by Trajectory.positions are in [0, 1): one test, wrap out of line
     const bool inside = (s.ax >= 0.0f) & (s.ax < p.box[0]) & (s.ay >= 0.0f) & (s.ay < p.box[1]) &
                         (s.az >= 0.0f) & (s.az < p.box[2]);
@@ -233,11 +231,57 @@ __device__ __forceinline__ Staged stage_atom(const StatesParams &p, double f0, d
         s.ay = wrap_slow(s.ay, p.box[1], p.inv_box[1]);
         s.az = wrap_slow(s.az, p.box[2], p.inv_box[2]);
     }
+    return s;
+}
+
+__device__ __forceinline__ void lookup_cell(const StatesParams &p, Staged &s) {
     const unsigned ix = min((unsigned)cell_raw(s.ax, p.inv_cell[0]), (unsigned)(p.dims[0] - 1));
     const unsigned iy = min((unsigned)cell_raw(s.ay, p.inv_cell[1]), (unsigned)(p.dims[1] - 1));
     const unsigned iz = min((unsigned)cell_raw(s.az, p.inv_cell[2]), (unsigned)(p.dims[2] - 1));
     s.cell = __ldg(p.cells + ((ix * (unsigned)p.dims[1] + iy) * (unsigned)p.dims[2] + iz));
-    return s;
+}
+
+// The last site an atom was found in, kept in registers by the lane that owns the atom.
+// While the atom stays inside the site's exclusive ball (squared radius excl2: no other
+// site's sphere, nor any periodic image of one, reaches into it) the states follow from this
+// one record and no table is read at all.
+struct SiteCache {
+    double x, y, z;  // float32-staged centre, widened
+    double excl2;    // < 0: nothing cached
+    int natgrp;      // natural | image axes << 20 | group << 24
+};
+
+template <bool kBand>
+__device__ __forceinline__ void band_check(const GdGroupRec &g, double d2, bool count_band,
+                                           BandCounters &bc) {
+    if (kBand) {
+        // boundary-band diagnostics: integer pre-filter on the high word of d2, exact test on
+        // the rare path
+        const int hi = __double2hiint(d2);
+        if ((unsigned)(hi - g.band_lo_o) <= (unsigned)g.band_span_o ||
+            (unsigned)(hi - g.band_lo_i) <= (unsigned)g.band_span_i) {
+            const unsigned b = count_band ? band_diag(d2, &g) : 0u;
+            bc.o12 += b & 1u;
+            bc.of += (b >> 1) & 1u;
+            bc.i12 += (b >> 2) & 1u;
+            bc.fi += (b >> 3) & 1u;
+        }
+    }
+}
+
+// Squared distance site -> atom with the reference's arithmetic: float64 differences of the
+// float32-staged coordinates, on the axes in `img` the atom's periodic image if it is closer,
+// every operation individually rounded, summed x, y, z.
+__device__ __forceinline__ double staged_d2(const StatesParams &p, double sx, double sy, double sz,
+                                            float ax, float ay, float az, uint32_t img) {
+    double dx = __dsub_rn(sx, (double)ax), dy = __dsub_rn(sy, (double)ay), dz = __dsub_rn(sz, (double)az);
+    if (img) {  // a periodic image of the atom can be the closer one
+        asm volatile("" : "+f"(ax), "+f"(ay), "+f"(az));  // keep the image arithmetic in here
+        if (img & 1u) dx = axis_delta_image(dx, sx, ax, p.box[0], p.cutoff32);
+        if (img & 2u) dy = axis_delta_image(dy, sy, ay, p.box[1], p.cutoff32);
+        if (img & 4u) dz = axis_delta_image(dz, sz, az, p.box[2], p.cutoff32);
+    }
+    return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
 
 // Rare path (overlapping spheres): more than one site of the cell contains the atom, so sites
@@ -246,80 +290,63 @@ template <bool kOneGroup>
 __device__ __noinline__ void mark_all_hits(const StatesParams &p, const GdGroupRec *s_groups,
                                            uint8_t *vis, Staged st) {
     const uint32_t count = st.cell >> 24, payload = st.cell & 0xFFFFFFu;
-    const double a0x = (double)st.ax, a0y = (double)st.ay, a0z = (double)st.az;
     for (uint32_t k = 0; k < count; ++k) {
         const uint32_t word = (count == 1) ? payload : __ldg(p.entries + payload + k);
-        const GdSiteRec *rec = p.sites + (word & kRankMask);
-        const double sx = rec->x, sy = rec->y, sz = rec->z;
-        const int natgrp = rec->natgrp;
+        const float4 rec = __ldg(p.sites + (word & kRankMask));
+        const int natgrp = __float_as_int(rec.w);
         const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[natgrp >> 24];
-        double dx = __dsub_rn(sx, a0x), dy = __dsub_rn(sy, a0y), dz = __dsub_rn(sz, a0z);
-        if (word & (1u << 20)) dx = axis_delta_image(dx, sx, st.ax, p.box[0], p.cutoff32);
-        if (word & (1u << 21)) dy = axis_delta_image(dy, sy, st.ay, p.box[1], p.cutoff32);
-        if (word & (1u << 22)) dz = axis_delta_image(dz, sz, st.az, p.box[2], p.cutoff32);
-        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-        const int natural = natgrp & 0x00FFFFFF;
+        const double d2 = staged_d2(p, (double)rec.x, (double)rec.y, (double)rec.z, st.ax, st.ay, st.az,
+                                    word >> 20);
+        const int natural = natgrp & (int)kRankMask;
         if (d2 <= g.r2_outer) vis[natural] = 1;
         if (d2 <= g.r2_inner) vis[p.n_sites_total + natural] = 1;
     }
 }
 
-// Site states of one staged atom-frame: walk the candidate sites of its cell in overwrite
-// order, exact float64 test on the float32-staged coordinates, last match wins.
-// `multi` is set when a second site contains the atom (then mark_all_hits runs).
+// Site states of one staged atom-frame from the tables: walk the candidate sites of its cell
+// in overwrite order, exact float64 test on the float32-staged coordinates, last match wins.
+// `multi` is set when a second site contains the atom (then mark_all_hits runs).  The last
+// site hit is left in the lane's cache.
 template <bool kOneGroup, bool kBand>
 __device__ __forceinline__ void classify(const StatesParams &p, const GdGroupRec *s_groups,
                                          const Staged &st, bool count_band, int32_t &best_o,
-                                         int32_t &best_i, bool &multi, BandCounters &bc) {
+                                         int32_t &best_i, bool &multi, SiteCache &cache,
+                                         BandCounters &bc) {
     best_o = GD_NOSITE;
     best_i = GD_NOSITE;
     multi = false;
     uint32_t n = st.cell >> 24;
     if (n == 0) return;
     const uint32_t payload = st.cell & 0xFFFFFFu;
-    const double a0x = (double)st.ax, a0y = (double)st.ay, a0z = (double)st.az;
     const uint32_t *ep = p.entries + payload;
     uint32_t word = (n == 1) ? payload : __ldg(ep);
     for (;;) {
-        const GdSiteRec *rec = p.sites + (word & kRankMask);
-        const double2 sxy = __ldg(reinterpret_cast<const double2 *>(rec));
-        const double sz = __ldg(&rec->z);
-        const int natgrp = __ldg(&rec->natgrp);
+        const uint32_t rank = word & kRankMask;
+        const float4 rec = __ldg(p.sites + rank);
+        const int natgrp = __float_as_int(rec.w);
         const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[natgrp >> 24];
-        double dx = __dsub_rn(sxy.x, a0x), dy = __dsub_rn(sxy.y, a0y), dz = __dsub_rn(sz, a0z);
-        if (word >> 20) {  // a periodic image of the atom can be the closer one
-            float ax = st.ax, ay = st.ay, az = st.az;
-            asm volatile("" : "+f"(ax), "+f"(ay), "+f"(az));  // keep the image arithmetic in here
-            if (word & (1u << 20)) dx = axis_delta_image(dx, sxy.x, ax, p.box[0], p.cutoff32);
-            if (word & (1u << 21)) dy = axis_delta_image(dy, sxy.y, ay, p.box[1], p.cutoff32);
-            if (word & (1u << 22)) dz = axis_delta_image(dz, sz, az, p.box[2], p.cutoff32);
-        }
-        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
-        const int natural = natgrp & 0x00FFFFFF;
+        const double sx = (double)rec.x, sy = (double)rec.y, sz = (double)rec.z;
+        const double d2 = staged_d2(p, sx, sy, sz, st.ax, st.ay, st.az, word >> 20);
+        const int natural = natgrp & (int)kRankMask;
         const bool hit_o = d2 <= g.r2_outer, hit_i = d2 <= g.r2_inner;
         multi |= (hit_o & (best_o >= 0)) | (hit_i & (best_i >= 0));
         if (hit_o) best_o = natural;  // entries ascend in overwrite order: last match wins
         if (hit_i) best_i = natural;
-        if (kBand) {
-            // boundary-band diagnostics: integer pre-filter on the high word of d2, exact test
-            // on the rare path
-            const int hi = __double2hiint(d2);
-            if ((unsigned)(hi - g.band_lo_o) <= (unsigned)g.band_span_o ||
-                (unsigned)(hi - g.band_lo_i) <= (unsigned)g.band_span_i) {
-                const unsigned b = count_band ? band_diag(d2, &g) : 0u;
-                bc.o12 += b & 1u;
-                bc.of += (b >> 1) & 1u;
-                bc.i12 += (b >> 2) & 1u;
-                bc.fi += (b >> 3) & 1u;
-            }
+        if (hit_o | hit_i) {
+            cache.x = sx;
+            cache.y = sy;
+            cache.z = sz;
+            cache.natgrp = natgrp;
+            cache.excl2 = (double)__ldg(p.excl2 + rank);
         }
+        band_check<kBand>(g, d2, count_band, bc);
         if (--n == 0) break;
         word = __ldg(++ep);
     }
 }
 
 template <bool kTma, bool kOneGroup, bool kDiag, bool kBand>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 3)
     k_site_states(const __grid_constant__ StatesParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     double *ring = reinterpret_cast<double *>(smem);  // [kWarps][kStages][96]
@@ -383,11 +410,29 @@ __global__ void __launch_bounds__(kThreads, 4)
         const int nst = p.n_sites_total;
         const int vis_mode = p.vis_mode;
 
+        SiteCache cache;
+        cache.x = cache.y = cache.z = 0.0;
+        cache.excl2 = -1.0;
+        cache.natgrp = 0;
+
         auto process = [&](double f0, double f1, double f2, bool own) {
-            const Staged st = stage_atom<kDiag>(p, f0, f1, f2);
+            Staged st = stage_atom<kDiag>(p, f0, f1, f2);
             int32_t so, si;
-            bool multi;
-            classify<kOneGroup, kBand>(p, s_groups, st, lane_on, so, si, multi, bc);
+            bool multi = false;
+            // fast path: still inside the exclusive ball of the cached site -> its record
+            // alone decides both states (no table reads)
+            const uint32_t c_img = ((uint32_t)cache.natgrp >> kSiteImgShift) & 7u;
+            const double d2c = staged_d2(p, cache.x, cache.y, cache.z, st.ax, st.ay, st.az, c_img);
+            if (d2c <= cache.excl2) {
+                const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[cache.natgrp >> 24];
+                const int natural = cache.natgrp & (int)kRankMask;
+                so = d2c <= g.r2_outer ? natural : GD_NOSITE;
+                si = d2c <= g.r2_inner ? natural : GD_NOSITE;
+                band_check<kBand>(g, d2c, lane_on, bc);
+            } else {
+                lookup_cell(p, st);
+                classify<kOneGroup, kBand>(p, s_groups, st, lane_on, so, si, multi, cache, bc);
+            }
             const bool d_o = so != prev_o, d_i = si != prev_i;
             if (d_o) ++n_do;
             if (d_i) ++n_di;
@@ -498,6 +543,80 @@ __global__ void __launch_bounds__(kThreads, 4)
 }  // namespace
 
 // ------------------------------------------------------------------------------------ host build
+
+// Squared "exclusive radius" of every ranked site: inside that ball around the (staged) site
+// centre, measured with the minimum-image metric, no OTHER site's outer or inner sphere -- nor a
+// periodic image of one, nor an image of the site itself -- can contain an atom.  There the
+// site's own record decides both states, which is what the kernel's register cache relies on.
+//   R(X) = min_Y ( dist(X, Y) - reach(Y) ) - margin,  capped at 4 * the largest reach,
+// float32 rounded towards zero; -1 when there is no such ball (duplicate / touching sites).
+// GD_K1_NOCACHE=1 disables the cache (every entry -1) for A/B measurements.
+static std::vector<float> exclusive_radii2(const std::vector<float> &sx, int32_t n,
+                                           const std::vector<int32_t> &order,
+                                           const int32_t *h_site_group,
+                                           const std::vector<GdGroupRec> &groups, const float *box,
+                                           double margin) {
+    std::vector<float> out((size_t)std::max(n, 1), -1.0f);
+    if (const char *env = getenv("GD_K1_NOCACHE"))
+        if (atoi(env) != 0) return out;
+    std::vector<double> reach(n);
+    double reach_max = 0.0;
+    for (int32_t e = 0; e < n; ++e) {
+        const GdGroupRec &g = groups[h_site_group[order[e]]];
+        reach[e] = std::max(g.r_outer, g.r_inner);
+        reach_max = std::max(reach_max, reach[e]);
+    }
+    const double cap = 4.0 * reach_max;
+    const double width = cap + reach_max + margin;  // sites farther than this cannot matter
+    int nb[3];
+    for (int j = 0; j < 3; ++j) nb[j] = std::min(64, std::max(1, (int)floor((double)box[j] / width)));
+    auto bin_of = [&](int32_t e, int j) {
+        int b = (int)((double)sx[3 * e + j] / (double)box[j] * nb[j]);
+        return std::min(std::max(b, 0), nb[j] - 1);
+    };
+    std::vector<std::vector<int32_t>> bins((size_t)nb[0] * nb[1] * nb[2]);
+    for (int32_t e = 0; e < n; ++e)
+        bins[((size_t)bin_of(e, 0) * nb[1] + bin_of(e, 1)) * nb[2] + bin_of(e, 2)].push_back(e);
+    for (int32_t e = 0; e < n; ++e) {
+        double r = cap;
+        for (int j = 0; j < 3; ++j) r = std::min(r, (double)box[j] - reach[e] - margin);  // own images
+        int lo[3], cnt[3];
+        for (int j = 0; j < 3; ++j) {
+            if (nb[j] <= 3) {
+                lo[j] = 0;
+                cnt[j] = nb[j];
+            } else {
+                lo[j] = bin_of(e, j) - 1;
+                cnt[j] = 3;
+            }
+        }
+        for (int ix = 0; ix < cnt[0]; ++ix)
+            for (int iy = 0; iy < cnt[1]; ++iy)
+                for (int iz = 0; iz < cnt[2]; ++iz) {
+                    const int bx = ((lo[0] + ix) % nb[0] + nb[0]) % nb[0];
+                    const int by = ((lo[1] + iy) % nb[1] + nb[1]) % nb[1];
+                    const int bz = ((lo[2] + iz) % nb[2] + nb[2]) % nb[2];
+                    for (int32_t y : bins[((size_t)bx * nb[1] + by) * nb[2] + bz]) {
+                        if (y == e) continue;
+                        double d2 = 0.0;
+                        for (int j = 0; j < 3; ++j) {
+                            const double L = (double)box[j];
+                            double d = (double)sx[3 * y + j] - (double)sx[3 * e + j];
+                            d -= L * nearbyint(d / L);
+                            d2 += d * d;
+                        }
+                        r = std::min(r, sqrt(d2) - reach[y] - margin);
+                    }
+                }
+        if (r > 0.0) {
+            float f = (float)(r * r);
+            if ((double)f > r * r) f = nextafterf(f, 0.0f);
+            out[e] = f;
+        }
+    }
+    return out;
+}
+
 
 extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *h_sites_frac,
                                          const int32_t *h_site_group, int32_t n_sites,
@@ -644,6 +763,7 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     };
     std::vector<AxisHit> hits[3];
     std::vector<uint32_t> e_cell, e_word;
+    std::vector<uint32_t> site_img((size_t)std::max(n_ranked, 1), 0u);  // axes flagged in any entry
     e_cell.reserve((size_t)n_ranked * 32);
     e_word.reserve((size_t)n_ranked * 32);
     for (int32_t e = 0; e < n_ranked; ++e) {
@@ -684,6 +804,7 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
                     const uint32_t flags = (hx.flag ? 1u : 0u) | (hy.flag ? 2u : 0u) | (hz.flag ? 4u : 0u);
                     e_cell.push_back((uint32_t)(((int64_t)hx.cell * dims[1] + hy.cell) * dims[2] + hz.cell));
                     e_word.push_back((uint32_t)e | (flags << 20));
+                    site_img[e] |= flags;
                 }
             }
     }
@@ -703,7 +824,8 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
                "gd_sitegrid_build: %u candidate sites in one cell exceed the limit of 255", maxc);
 
     const size_t off_sites = sizeof(GdGridHeader);
-    const size_t off_groups = align256(off_sites + (size_t)n_ranked * sizeof(GdSiteRec));
+    const size_t off_excl = align256(off_sites + (size_t)n_ranked * 16);
+    const size_t off_groups = align256(off_excl + (size_t)n_ranked * 4);
     const size_t off_cells = align256(off_groups + (size_t)n_groups * sizeof(GdGroupRec));
     const size_t off_entries = align256(off_cells + (size_t)ncell * 4);
     const size_t total = align256(off_entries + std::max<size_t>(n_entries, 1) * 4);
@@ -737,14 +859,17 @@ extern "C" gd_status_t gd_sitegrid_build(const double *h_lattice, const double *
     h->off_entries = off_entries;
     h->total_bytes = total;
 
-    GdSiteRec *srec = reinterpret_cast<GdSiteRec *>(base + off_sites);
+    float *srec = reinterpret_cast<float *>(base + off_sites);
     for (int32_t e = 0; e < n_ranked; ++e) {
-        srec[e].x = (double)sx[3 * e + 0];
-        srec[e].y = (double)sx[3 * e + 1];
-        srec[e].z = (double)sx[3 * e + 2];
-        srec[e].natgrp = order[e] | (h_site_group[order[e]] << 24);
-        srec[e].pad = 0;
+        srec[4 * e + 0] = sx[3 * e + 0];
+        srec[4 * e + 1] = sx[3 * e + 1];
+        srec[4 * e + 2] = sx[3 * e + 2];
+        const int32_t packed = order[e] | (int32_t)(site_img[e] << kSiteImgShift) | (h_site_group[order[e]] << 24);
+        memcpy(&srec[4 * e + 3], &packed, 4);
     }
+    const std::vector<float> excl2 = exclusive_radii2(sx, n_ranked, order, h_site_group, groups, box, margin);
+    memcpy(base + off_excl, excl2.data(), (size_t)n_ranked * 4);
+    h->off_excl = off_excl;
     memcpy(base + off_groups, groups.data(), (size_t)n_groups * sizeof(GdGroupRec));
 
     // counting sort by cell; sites were visited in ascending rank so every list ascends
@@ -807,7 +932,8 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames
     const int64_t n_groups_of_strips = gd_ceil_div(p.n_strips, 1 << spg_shift);
     const int64_t grid = n_groups_of_strips * p.n_cblocks;
     GD_REQUIRE(grid < (int64_t(1) << 31), GD_ERR_INVALID, "gd_site_states: shard too large");
-    p.sites = reinterpret_cast<const GdSiteRec *>(base + h->off_sites);
+    p.sites = reinterpret_cast<const float4 *>(base + h->off_sites);
+    p.excl2 = reinterpret_cast<const float *>(base + h->off_excl);
     p.cells = reinterpret_cast<const uint32_t *>(base + h->off_cells);
     p.entries = reinterpret_cast<const uint32_t *>(base + h->off_entries);
     p.groups = reinterpret_cast<const GdGroupRec *>(base + h->off_groups);

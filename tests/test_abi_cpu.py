@@ -48,12 +48,12 @@ def parse_blob(blob: np.ndarray):
     off = 76 + 4  # pad0 -> 80
     inv_box = np.frombuffer(raw, dtype=np.float64, count=3, offset=off)
     matrix = np.frombuffer(raw, dtype=np.float64, count=9, offset=off + 24)
-    o_sites, o_cells, o_entries, o_groups, total = struct.unpack_from('<5Q', raw, off + 24 + 72)
-    assert magic == 0x47534447 and version == 3 and total == len(raw)
-    # 32-byte site records: float64 x, y, z (the float32-staged centre, widened), int32 natgrp, pad
-    sites = np.frombuffer(raw, dtype=np.float64, count=4 * n_sites, offset=o_sites).reshape(-1, 4)
-    natgrp = sites[:, 3].copy().view(np.int32)[::2]
-    assert np.array_equal(sites[:, :3], sites[:, :3].astype(np.float32).astype(np.float64))
+    o_sites, o_cells, o_entries, o_groups, total, o_excl = struct.unpack_from('<6Q', raw, off + 24 + 72)
+    assert magic == 0x47534447 and version == 4 and total == len(raw)
+    # 16-byte site records: float32 x, y, z (staged like the reference) + packed int32
+    sites = np.frombuffer(raw, dtype=np.float32, count=4 * n_sites, offset=o_sites).reshape(-1, 4)
+    natgrp = sites[:, 3].copy().view(np.int32)
+    excl2 = np.frombuffer(raw, dtype=np.float32, count=n_sites, offset=o_excl)
     ncell = dims[0] * dims[1] * dims[2]
     cells = np.frombuffer(raw, dtype=np.uint32, count=ncell, offset=o_cells)
     entries = np.frombuffer(raw, dtype=np.uint32, count=max(n_entries, 1), offset=o_entries)
@@ -61,8 +61,9 @@ def parse_blob(blob: np.ndarray):
     r2 = grp[:, :16].copy().view(np.float64).reshape(-1, 2)  # r2_outer, r2_inner
     band = grp[:, 16:32].copy().view(np.int32).reshape(-1, 4)  # lo_o, span_o, lo_i, span_i
     return dict(n_sites=n_sites, n_total=n_total, dims=dims, box=box, cutoff32=cutoff32,
-                inv_cell=inv_cell, matrix=matrix.reshape(3, 3), xyz=sites[:, :3].astype(np.float32),
-                natural=natgrp & 0xFFFFFF, group=natgrp >> 24, cells=cells, entries=entries,
+                inv_cell=inv_cell, matrix=matrix.reshape(3, 3), xyz=sites[:, :3], excl2=excl2,
+                site_img=(natgrp >> 20) & 7,
+                natural=natgrp & 0xFFFFF, group=natgrp >> 24, cells=cells, entries=entries,
                 r2=r2, band=band, is_diag=is_diag, max_count=max_count, n_entries=n_entries)
 
 
@@ -208,3 +209,63 @@ def test_compute_entry_points_fail_loudly_without_gpu():
     t = Trajectory(species=['Li'], coords=np.zeros((4, 1, 3)), lattice=np.eye(3), time_step=1.0)
     with pytest.raises(RuntimeError, match='no CPU fallback'):
         t.distances_from_base_position()
+
+
+@pytest.mark.parametrize('lengths,n_sites,radius,inner,pattern', CASES + [
+    ((25.94, 25.94, 12.97), 160, {'': 0.6}, {'': 0.5}, None),  # well separated sites: big balls
+])
+def test_exclusive_ball_decides_alone(lengths, n_sites, radius, inner, pattern):
+    """K1's register cache: inside the exclusive ball of a site (periodic metric) the site's own
+    record, evaluated with its SITE-level image flags, gives the brute-force oracle's states."""
+    rng = np.random.default_rng(7 * n_sites + 1)
+    lattice = np.diag(lengths)
+    if n_sites == 160:  # jittered lattice, >= 2.2 A apart
+        g = np.stack(np.meshgrid(np.arange(8), np.arange(5), np.arange(4), indexing='ij'), -1).reshape(-1, 3)
+        site_frac = (g + 0.5 + rng.uniform(-0.12, 0.12, g.shape)) / np.array([8, 5, 4])
+    else:
+        site_frac = rng.random((n_sites, 3)) * 1.2 - 0.1
+    labels = ['X'] * n_sites if pattern is None else [pattern[i % len(pattern)] for i in range(n_sites)]
+    grid = SiteGrid(lattice_matrix=lattice, site_frac=site_frac, site_labels=labels,
+                    site_radius=radius, site_inner_fraction=inner)
+    b = parse_blob(grid.h_blob)
+    has_ball = np.nonzero(b['excl2'] > 0)[0]
+    if n_sites == 160:
+        assert len(has_ball) == n_sites and b['excl2'].min() > 0.6**2
+    if len(has_ball) == 0:
+        return
+    # points in the balls: uniform directions, radii up to (just inside) the exclusive radius
+    pick = has_ball[rng.integers(len(has_ball), size=6000)]
+    u = rng.normal(size=(6000, 3))
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    rad = np.sqrt(b['excl2'][pick].astype(np.float64)) * np.minimum(1.0, rng.random(6000) * 1.05) * (1 - 1e-6)
+    centre = b['xyz'][pick].astype(np.float64)
+    pos = np.mod((centre + u * rad[:, None]) / np.array(lengths), 1.0).reshape(-1, 1, 3)
+    cutoff = max(radius.values())
+    c0, c1, _ = ostates.staged_atoms(pos, lattice, cutoff)
+    # the fast path's arithmetic: per-axis image on the site-level flagged axes
+    s64 = b['xyz'][pick].astype(np.float64)
+    d = s64 - c0.astype(np.float64)
+    alt = s64 - c1.astype(np.float64)
+    use = ((b['site_img'][pick][:, None] >> np.arange(3)) & 1).astype(bool) & ~np.isnan(c1) & (np.abs(alt) < np.abs(d))
+    d = np.where(use, alt, d)
+    d2 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+    inside = d2 <= b['excl2'][pick].astype(np.float64)
+    assert inside.mean() > 0.9
+    r2o, r2i = b['r2'][b['group'][pick]].T
+    got_o = np.where(d2 <= r2o, b['natural'][pick], -1)
+    got_i = np.where(d2 <= r2i, b['natural'][pick], -1)
+    kw = dict(site_frac=site_frac, site_labels=labels, positions=pos, lattice_matrix=lattice, site_radius=radius)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        exp_o, vis_o = ostates.calculate_atom_states_bruteforce(
+            **kw, site_inner_fraction={k: 1.0 for k in radius}, return_visited=True)
+        exp_i, vis_i = ostates.calculate_atom_states_bruteforce(
+            **kw, site_inner_fraction=inner, return_visited=True)
+    lut_o, lut_i = grid.remap_lut(vis_o), grid.remap_lut(vis_i)
+    if lut_o is not None:
+        got_o = np.where(got_o >= 0, lut_o[np.clip(got_o, 0, None)], -1)
+    if lut_i is not None:
+        got_i = np.where(got_i >= 0, lut_i[np.clip(got_i, 0, None)], -1)
+    np.testing.assert_array_equal(got_o[inside], exp_o[inside, 0])
+    np.testing.assert_array_equal(got_i[inside], exp_i[inside, 0])
