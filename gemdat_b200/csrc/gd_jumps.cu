@@ -9,6 +9,8 @@
 // do segments of 512 events of the same atom (speculate / chain / fill, see below).
 // Two phases (count, fill) give the exact output size without any allocation in the
 // library.
+#include <stdlib.h>
+
 #include "gd_common.cuh"
 
 namespace {
@@ -278,6 +280,57 @@ __global__ void __launch_bounds__(64)
     }
 }
 
+// Parallel form of the chain (thread per segment).  After its first departure row a
+// segment's state no longer depends on how it was entered, so the true entry state of segment
+// s is the speculative exit state of segment s-1 -- PROVIDED the true run of s-1 merged with
+// its speculative run.  Every thread therefore assumes that entry, replays its own prefix in
+// lockstep with the speculative run and reports whether the two merged; by induction from the
+// (exactly known, empty) entry of an atom's first segment all assumptions hold iff every
+// segment merged.  If one does not (event streams that are not state-consistent), *flag is
+// set and the caller falls back to the sequential k_jumps_chain: never wrong, rarely slow.
+__global__ void __launch_bounds__(128)
+    k_jumps_chain_par(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
+                      const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
+                      int64_t minimal_residence, const SegSpec *__restrict__ spec,
+                      PackedState *__restrict__ entry, int64_t *__restrict__ counts,
+                      int32_t *__restrict__ flag) {
+    const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int32_t a;
+    int64_t r0;
+    int n;
+    if (!locate_segment(seg, seg_off, atom_offsets, n_atoms, a, r0, n)) return;
+    const bool first = seg == seg_off[a], last = seg + 1 == seg_off[a + 1];
+    JumpMachine truth(minimal_residence);
+    truth.c_atom = a;
+    if (!first) unpack(truth, spec[seg - 1].exit, a);
+    entry[seg] = pack(truth);
+    const SegSpec sp = spec[seg];
+    JumpMachine guess(minimal_residence);
+    int64_t n_true = 0;
+    int n_guess_after = 0;  // jumps of the speculative run in rows [sync, k)
+    bool merged = false;
+    auto emit_true = [&](const Jump &) { ++n_true; };
+    for (int k = 0; k < n; ++k) {
+        if (k >= sp.sync && same_state(truth, guess)) {
+            merged = true;
+            break;
+        }
+        const bool after = k >= sp.sync;
+        auto emit_guess = [&](const Jump &) { n_guess_after += after ? 1 : 0; };
+        const Row e = load_row(events, r0 + k);
+        truth.step(e.atom, e.s0, e.s1, e.i1, e.t, emit_true);
+        guess.step(e.atom, e.s0, e.s1, e.i1, e.t, emit_guess);
+    }
+    if (merged || same_state(truth, guess)) {
+        n_true += sp.n_after - n_guess_after;
+        unpack(truth, sp.exit, a);
+    } else if (!last) {
+        atomicExch(flag, 1);  // the next segment's assumed entry state is not proven
+    }
+    if (last && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
+    counts[seg] = n_true;
+}
+
 __global__ void __launch_bounds__(128)
     k_jumps_fill(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
                  const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
@@ -344,6 +397,7 @@ struct JumpWork {
     int64_t *counts;     // [max_segs + 1]
     SegSpec *spec;       // [max_segs]
     PackedState *entry;  // [max_segs]
+    int32_t *flag;       // [4]: set when the parallel chain could not prove a segment's entry state
     size_t bytes;
 };
 inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
@@ -360,6 +414,8 @@ inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
     off += up((size_t)w.max_segs * sizeof(SegSpec));
     w.entry = reinterpret_cast<PackedState *>(p + off);
     off += up((size_t)w.max_segs * sizeof(PackedState));
+    w.flag = reinterpret_cast<int32_t *>(p + off);
+    off += 16;
     w.bytes = off;
     return w;
 }
@@ -421,15 +477,33 @@ extern "C" gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_
         d_events, d_atom_offsets, w.seg_off, n_atoms, minimal_residence, w.spec);
     GD_LAUNCH_CHECK();
     GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
-    k_jumps_chain<<<(unsigned)gd_ceil_div(n_atoms, 64), 64, 0, st>>>(
-        d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence, w.spec,
-        w.entry, w.counts);
-    GD_LAUNCH_CHECK();
-    k_scan_counts<<<1, 1024, 0, st>>>(w.counts, w.max_segs);
-    GD_LAUNCH_CHECK();
-    GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
-                                  cudaMemcpyDeviceToHost, st));
-    GD_CUDA_CHECK(cudaStreamSynchronize(st));
+    GD_CUDA_CHECK(cudaMemsetAsync(w.flag, 0, 16, st));
+    // GD_JUMPS_SEQUENTIAL=1 forces the sequential chain (tests / A-B timing)
+    const char *env = getenv("GD_JUMPS_SEQUENTIAL");
+    bool sequential = env && atoi(env) != 0;
+    int32_t h_flag = 0;
+    for (;;) {
+        if (sequential) {
+            k_jumps_chain<<<(unsigned)gd_ceil_div(n_atoms, 64), 64, 0, st>>>(
+                d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
+                w.spec, w.entry, w.counts);
+        } else {
+            k_jumps_chain_par<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
+                d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
+                w.spec, w.entry, w.counts, w.flag);
+        }
+        GD_LAUNCH_CHECK();
+        k_scan_counts<<<1, 1024, 0, st>>>(w.counts, w.max_segs);
+        GD_LAUNCH_CHECK();
+        GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
+                                      cudaMemcpyDeviceToHost, st));
+        GD_CUDA_CHECK(cudaMemcpyAsync(&h_flag, w.flag, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        GD_CUDA_CHECK(cudaStreamSynchronize(st));
+        if (sequential || h_flag == 0) break;
+        // some segment's entry state could not be proven: redo with the sequential chain
+        sequential = true;
+        GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
+    }
     return GD_OK;
 }
 
