@@ -133,22 +133,31 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
         site_radius=site_radius,
         site_inner_fraction=site_inner_fraction,
     )
-    pos = trajectory._device_positions()
-    n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
-    outer = dv.empty((n_frames, n_atoms), torch.int32)
-    inner = dv.empty((n_frames, n_atoms), torch.int32)
-    visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
-    band = dv.zeros((4,), torch.int64)
-    work = changed = None
-    if count_events and n_frames > 0:
-        work = dv.empty((int(_lib.lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
-        changed = dv.zeros((2 * n_atoms,), torch.uint8)
-    st = _lib.lib.gd_site_states(
-        dv.ptr(pos), n_frames, n_atoms, None, dv.ptr(grid.d_blob), grid.h_blob.ctypes.data,
-        dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band), dv.ptr(work), dv.ptr(changed),
-        dv.stream_ptr(),
-    )
-    _lib.check(st)
+    host_future = None
+    if _wants_pipeline(trajectory, count_events):
+        # host-resident input: upload, K1 and the download of the int64 states run as a
+        # three-stage pipeline over frame parts (PCIe is full duplex); events are counted by the
+        # stand-alone pass afterwards (it re-reads 8 B/atom-frame from HBM, noise next to PCIe)
+        pos, outer, inner, visited, band, host_future = _pipelined_states(trajectory, grid)
+        n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+        work = changed = None
+    else:
+        pos = trajectory._device_positions()
+        n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+        outer = dv.empty((n_frames, n_atoms), torch.int32)
+        inner = dv.empty((n_frames, n_atoms), torch.int32)
+        visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
+        band = dv.zeros((4,), torch.int64)
+        work = changed = None
+        if count_events and n_frames > 0:
+            work = dv.empty((int(_lib.lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
+            changed = dv.zeros((2 * n_atoms,), torch.uint8)
+        st = _lib.lib.gd_site_states(
+            dv.ptr(pos), n_frames, n_atoms, None, dv.ptr(grid.d_blob), grid.h_blob.ctypes.data,
+            dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band), dv.ptr(work), dv.ptr(changed),
+            dv.stream_ptr(),
+        )
+        _lib.check(st)
     visited_h = dv.to_host(visited).astype(bool).reshape(2, grid.n_sites)
     band_h = dv.to_host(band)
     for which_i, (arr, vis) in enumerate(((outer, visited_h[0]), (inner, visited_h[1]))):
@@ -165,6 +174,7 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
             d_lut = dv.to_device(lut)
             _lib.check(_lib.lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut),
                                                 grid.n_sites, dv.stream_ptr()))
+            host_future = None  # the prefetched host copy predates the remap: fetch again lazily
     info = {
         'visited_outer': visited_h[0],
         'visited_inner': visited_h[1],
@@ -172,8 +182,112 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
         'band_4e-6': (int(band_h[2]), int(band_h[3])),
         'event_work': work,
         'changed': changed,
+        'host_future': host_future,
     }
     return outer, inner, info
+
+
+PIPELINE_MIN_BYTES = 64 << 20
+PIPELINE_PARTS = 16
+
+
+def _wants_pipeline(trajectory, count_events: bool) -> bool:
+    coords = trajectory.coords
+    if dv.is_device(coords) or not count_events or trajectory.coords_are_displacement:
+        return False
+    holder = trajectory.__dict__.get('_dev_holder') or {}
+    cached = holder.get('pos')
+    if cached is not None and cached[0] is coords:
+        return False  # already on the device
+    return coords.nbytes >= PIPELINE_MIN_BYTES and coords.flags.c_contiguous
+
+
+class HostStates:
+    """int64 host copies of the two state arrays, arriving through a side stream."""
+
+    def __init__(self, outer: torch.Tensor, inner: torch.Tensor, done: torch.cuda.Event):
+        self._outer, self._inner, self._done = outer, inner, done
+
+    def outer(self) -> np.ndarray:
+        self._done.synchronize()
+        return self._outer.numpy()
+
+    def inner(self) -> np.ndarray:
+        self._done.synchronize()
+        return self._inner.numpy()
+
+
+def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
+    """K1 over frame parts with upload (copy stream), compute (current stream) and the
+    download of the widened states (second copy stream) overlapped."""
+    lib = _lib.lib
+    dev = dv.require_cuda()
+    coords = trajectory.coords
+    n_frames, n_atoms = int(coords.shape[0]), int(coords.shape[1])
+    d_blob = grid.d_blob  # small table upload first: it shares the H2D engine with the parts below
+    src = torch.from_numpy(coords)
+    pos = dv.empty((n_frames, n_atoms, 3), torch.float64)
+    outer = dv.empty((n_frames, n_atoms), torch.int32)
+    inner = dv.empty((n_frames, n_atoms), torch.int32)
+    visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
+    band = dv.zeros((4,), torch.int64)
+    host_o = torch.empty((n_frames, n_atoms), dtype=torch.int64, pin_memory=True)
+    host_i = torch.empty((n_frames, n_atoms), dtype=torch.int64, pin_memory=True)
+    n_parts = min(PIPELINE_PARTS, n_frames)
+    # frame boundaries in multiples of 4 keep every part 16-byte aligned whatever n_atoms is
+    bounds = sorted({min(n_frames, (n_frames * k // n_parts + 3) & ~3) for k in range(n_parts)} | {0, n_frames})
+    n_parts = len(bounds) - 1
+    part_max = max(b - a for a, b in zip(bounds[:-1], bounds[1:]))
+    stage = [(dv.empty((part_max, n_atoms), torch.int64), dv.empty((part_max, n_atoms), torch.int64))
+             for _ in range(2)]
+    main = torch.cuda.current_stream()
+    up, down = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    up.wait_stream(main)
+    down.wait_stream(main)
+    uploaded = [torch.cuda.Event(enable_timing=trace is not None) for _ in range(n_parts)]
+    staged_free = [None, None]
+
+    def upload(k):
+        with torch.cuda.stream(up):
+            pos[bounds[k]:bounds[k + 1]].copy_(src[bounds[k]:bounds[k + 1]], non_blocking=True)
+            uploaded[k].record(up)
+
+    upload(0)
+    done = torch.cuda.Event()
+    for k in range(n_parts):
+        if k + 1 < n_parts:
+            upload(k + 1)
+        f0, f1 = bounds[k], bounds[k + 1]
+        main.wait_event(uploaded[k])
+        _lib.check(lib.gd_site_states(
+            dv.ptr(pos[f0:f1]), f1 - f0, n_atoms, None, dv.ptr(d_blob), grid.h_blob.ctypes.data,
+            dv.ptr(outer[f0:f1]), dv.ptr(inner[f0:f1]), dv.ptr(visited), dv.ptr(band), None, None,
+            main.cuda_stream))
+        buf = stage[k % 2]
+        if staged_free[k % 2] is not None:
+            main.wait_event(staged_free[k % 2])
+        n = (f1 - f0) * n_atoms
+        _lib.check(lib.gd_widen_i32_i64(dv.ptr(outer[f0:f1]), dv.ptr(buf[0]), n, main.cuda_stream))
+        _lib.check(lib.gd_widen_i32_i64(dv.ptr(inner[f0:f1]), dv.ptr(buf[1]), n, main.cuda_stream))
+        ready = torch.cuda.Event(enable_timing=trace is not None)
+        ready.record(main)
+        with torch.cuda.stream(down):
+            down.wait_event(ready)
+            host_o[f0:f1].copy_(buf[0][: f1 - f0], non_blocking=True)
+            host_i[f0:f1].copy_(buf[1][: f1 - f0], non_blocking=True)
+            free = torch.cuda.Event(enable_timing=trace is not None)
+            free.record(down)
+            staged_free[k % 2] = free
+        if trace is not None:
+            trace.append((uploaded[k], ready, free))
+    done.record(down)
+    # later work on the current stream (and the allocator's reuse of the staging buffers) is
+    # ordered after both side streams
+    main.wait_stream(up)
+    main.wait_stream(down)
+    holder = trajectory.__dict__.setdefault('_dev_holder', {})
+    holder['pos'] = (coords, pos)
+    return pos, outer, inner, visited, band, HostStates(host_o, host_i, done)
 
 
 def widen_to_host(t: torch.Tensor) -> np.ndarray:
@@ -349,13 +463,15 @@ class Transitions:
     @property
     def states(self) -> np.ndarray:
         if self._states is None:
-            self._states = widen_to_host(self._dev['outer'])
+            fut = self.info.get('host_future')
+            self._states = fut.outer() if fut is not None else widen_to_host(self._dev['outer'])
         return self._states
 
     @property
     def inner_states(self) -> np.ndarray:
         if self._inner_states is None:
-            self._inner_states = widen_to_host(self._dev['inner'])
+            fut = self.info.get('host_future')
+            self._inner_states = fut.inner() if fut is not None else widen_to_host(self._dev['inner'])
         return self._inner_states
 
     @property

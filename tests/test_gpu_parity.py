@@ -470,3 +470,27 @@ def test_k1_strip_walker_shapes(n_frames, n_atoms):
 
     ev2 = _calculate_transition_events(atom_sites=eo, atom_inner_sites=ei)
     assert_array_equal(ev2.to_numpy(), tr.events.to_numpy())
+
+
+@pytest.mark.parametrize('n_atoms', [48, 33])
+def test_pipelined_host_path_equals_resident_path(monkeypatch, n_atoms):
+    """Host numpy input large enough for the upload / K1 / download pipeline (forced here) gives
+    the same states, events and jumps as the single-launch path on a device-resident copy."""
+    import gemdat_b200.transitions as gt
+    from gemdat_b200 import Sites, Trajectory, synth
+
+    rec = synth.config_c2(n_frames=4001, seed=5)
+    pos = rec.host_positions(0, 4001)[:, :n_atoms].copy()
+    kw = dict(site_radius=0.9, site_inner_fraction=0.5)
+    ref = Trajectory(species=['Li'] * n_atoms, coords=torch.from_numpy(pos).cuda(), lattice=rec.lattice,
+                     time_step=2e-15).transitions_between_sites(rec.sites, 'Li', **kw)
+    monkeypatch.setattr(gt, 'PIPELINE_MIN_BYTES', 0)
+    tr = Trajectory(species=['Li'] * n_atoms, coords=pos, lattice=rec.lattice,
+                    time_step=2e-15).transitions_between_sites(rec.sites, 'Li', **kw)
+    assert tr.info['host_future'] is not None and ref.info['host_future'] is None
+    assert_array_equal(tr.states, ref.states)
+    assert_array_equal(tr.inner_states, ref.inner_states)
+    assert tr.states.dtype == np.int64
+    assert_array_equal(tr.events.to_numpy(), ref.events.to_numpy())
+    assert_array_equal(tr.jumps(minimal_residence=3).data.to_numpy(), ref.jumps(minimal_residence=3).data.to_numpy())
+    assert tr.info['band_4e-6'] == ref.info['band_4e-6']
