@@ -67,6 +67,45 @@ class Comm:
         out = out.reshape((self.world,) + tuple(src.shape))
         return out if self.direct else out.to(t.device)
 
+    def all_gather_rows(self, rows: torch.Tensor) -> torch.Tensor:
+        """Concatenation over the ranks (in rank order) of row tables with different lengths."""
+        if self.world == 1:
+            return rows
+        n = torch.tensor([rows.shape[0]], dtype=torch.int64, device=rows.device)
+        counts = self.all_gather(n).flatten().tolist()
+        cap = max(1, max(counts))
+        padded = torch.zeros((cap,) + tuple(rows.shape[1:]), dtype=rows.dtype, device=rows.device)
+        padded[: rows.shape[0]] = rows
+        allp = self.all_gather(padded)
+        return torch.cat([allp[r, : counts[r]] for r in range(self.world)], dim=0)
+
+    def all_to_all_rows(self, rows: torch.Tensor, send: list[int], recv: list[int]) -> list[torch.Tensor]:
+        """Rank r receives, from every rank q, the slice of q's ``rows`` meant for r.
+
+        ``rows`` holds the slices for ranks 0..W-1 back to back (``send[r]`` rows each);
+        ``recv[q]`` is the number of rows coming from rank q.  NCCL: one grouped send/recv
+        (``all_to_all_single``), every row crosses the link once.  Other backends (CPU tests,
+        ranks sharing a GPU) emulate it with a padded all-gather.
+        """
+        width = int(rows.shape[1])
+        if self.direct:
+            out = torch.empty((sum(recv), width), dtype=rows.dtype, device=rows.device)
+            self.dist.all_to_all_single(out, rows.contiguous(), output_split_sizes=recv,
+                                        input_split_sizes=send, group=self.group)
+            return list(torch.split(out, recv, dim=0))
+        me = self.dist.get_rank(self.group)
+        sends = self.all_gather(torch.tensor(send, dtype=torch.int64, device=rows.device))  # [W, W]
+        sends_h = sends.cpu().numpy()
+        cap = max(1, int(sends_h.sum(axis=1).max()))
+        padded = torch.zeros((cap, width), dtype=rows.dtype, device=rows.device)
+        padded[: rows.shape[0]] = rows
+        allp = self.all_gather(padded)
+        out = []
+        for q in range(self.world):
+            start = int(sends_h[q, :me].sum())
+            out.append(allp[q, start: start + int(sends_h[q, me])].contiguous())
+        return out
+
     def all_reduce_max(self, t: torch.Tensor) -> torch.Tensor:
         """In-place elementwise maximum over the ranks."""
         if self.world == 1:
@@ -187,45 +226,75 @@ class HotPath:
             launches += 1
         rows = rows[: n_events.value]
 
+        # ---- K3.  Frame shards hold time slices of every atom; the jump machine needs an atom's
+        # whole history.  So the event rows change hands ONCE, by atom block (all-to-all: each row
+        # crosses NVLink at most once), every rank runs K3 on its atoms only, and the small jump
+        # tables are gathered.  The event table stays sharded by atom block (`gather_events`
+        # assembles it on demand).
+        a_lo, a_hi = 0, n_atoms
+        n_events_global = n_events.value
         if self.world > 1:
-            rows, offsets, n_total = self._merge_events(rows, offsets, n_atoms)
+            rows, offsets, a_lo, a_hi, n_events_global = self._exchange_events(rows, offsets, n_atoms)
             launches += self.world
-        else:
-            n_total = n_events.value
+        n_local = int(rows.shape[0])
+        n_block = a_hi - a_lo
 
-        # ---- K3 (time-parallel state machine: 5 launches to count, 1 to fill)
-        jwork = self._tensor('jwork', (int(lib.gd_jumps_work_bytes(n_total, n_atoms)),), torch.uint8)
+        jwork = self._tensor('jwork', (int(lib.gd_jumps_work_bytes(n_local, max(n_block, 1))),), torch.uint8)
         n_jumps = C.c_int64(0)
-        _lib.check(lib.gd_jumps_count(dv.ptr(rows), dv.ptr(offsets), n_total, n_atoms, self.n_frames_total,
-                                      self.minimal_residence, dv.ptr(jwork), C.byref(n_jumps), s))
-        launches += 4
+        if n_block > 0:
+            _lib.check(lib.gd_jumps_count(dv.ptr(rows), dv.ptr(offsets), n_local, n_block, self.n_frames_total,
+                                          self.minimal_residence, dv.ptr(jwork), C.byref(n_jumps), s))
+            launches += 4
         jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
         if n_jumps.value:
-            _lib.check(lib.gd_jumps_fill(dv.ptr(rows), dv.ptr(offsets), n_total, n_atoms, self.n_frames_total,
+            _lib.check(lib.gd_jumps_fill(dv.ptr(rows), dv.ptr(offsets), n_local, n_block, self.n_frames_total,
                                          self.minimal_residence, dv.ptr(jwork), dv.ptr(jumps), s))
             launches += 1
+        jumps = jumps[: n_jumps.value]
+        if self.world > 1:
+            jumps = self.comm.all_gather_rows(jumps)  # rank order = atom-block order = (atom, time) order
         self.launches_per_run = launches
         return {'outer': outer, 'inner': inner, 'events': rows, 'atom_offsets': offsets,
-                'jumps': jumps[: n_jumps.value], 'n_events': n_total, 'n_jumps': n_jumps.value,
-                'visited': vis, 'band': band}
+                'atom_block': (a_lo, a_hi), 'jumps': jumps, 'n_events': n_events_global,
+                'n_jumps': int(jumps.shape[0]), 'visited': vis, 'band': band}
 
-    def _merge_events(self, rows, offsets, n_atoms):
-        """All-gather the per-shard tables and merge them per atom (every rank gets the whole table)."""
+    def atom_block(self, rank: int, n_atoms: int) -> tuple[int, int]:
+        return n_atoms * rank // self.world, n_atoms * (rank + 1) // self.world
+
+    def _exchange_events(self, rows, offsets, n_atoms):
+        """All-to-all by atom block + per-atom merge of the pieces.
+
+        Every shard's rows are sorted by (atom, time), so the rows for one atom block are one
+        contiguous slice.  Returns this rank's block: rows sorted by (atom, time) over ALL frames,
+        block-local offsets [n_block + 1], the block bounds and the global event count.
+        """
         lib = _lib.lib
         s = dv.stream_ptr()
-        all_off = self._all_gather(offsets)  # [W, A+1]
-        off_h = dv.to_host(all_off)
-        counts = np.diff(off_h, axis=1)
-        n_per = off_h[:, -1]
-        cap = int(max(1, n_per.max()))
-        padded = dv.zeros((cap, 6), torch.int32)
-        padded[: rows.shape[0]] = rows
-        gathered = self._all_gather(padded)  # [W, cap, 6]
-        atom_offsets, dst_start = merge_plan(counts)
-        merged = dv.empty((max(int(atom_offsets[-1]), 1), 6), torch.int32)
+        W, me = self.world, self.rank
+        all_off = dv.to_host(self.comm.all_gather(offsets))  # [W, A + 1] row offsets of every shard
+        counts = np.diff(all_off, axis=1)                     # [W, A]
+        bounds = [self.atom_block(r, n_atoms) for r in range(W)]
+        a_lo, a_hi = bounds[me]
+        send = [int(all_off[me, hi] - all_off[me, lo]) for lo, hi in bounds]
+        recv = [int(all_off[r, a_hi] - all_off[r, a_lo]) for r in range(W)]
+        pieces = self.comm.all_to_all_rows(rows, send, recv)  # list of [recv[r], 6], piece r from shard r
+        # place piece r's rows of atom a after the rows of earlier shards of a
+        block_counts = counts[:, a_lo:a_hi]
+        atom_offsets, dst_start = merge_plan(block_counts)
+        n_local = int(atom_offsets[-1])
+        merged = dv.empty((max(n_local, 1), 6), torch.int32)
         d_dst = dv.to_device(np.ascontiguousarray(dst_start))
-        for r in range(self.world):
-            if n_per[r]:
-                _lib.check(lib.gd_events_merge(dv.ptr(gathered[r]), dv.ptr(all_off[r]), dv.ptr(d_dst[r]),
-                                               n_atoms, dv.ptr(merged), s))
-        return merged[: int(atom_offsets[-1])], dv.to_device(atom_offsets.astype(np.int64)), int(atom_offsets[-1])
+        for r in range(W):
+            if recv[r] and a_hi > a_lo:
+                src_off = all_off[r, a_lo:a_hi + 1] - all_off[r, a_lo]
+                d_src_off = dv.to_device(np.ascontiguousarray(src_off.astype(np.int64)))
+                _lib.check(lib.gd_events_merge(dv.ptr(pieces[r]), dv.ptr(d_src_off), dv.ptr(d_dst[r]),
+                                               a_hi - a_lo, dv.ptr(merged), s))
+        return (merged[:n_local], dv.to_device(atom_offsets.astype(np.int64)), a_lo, a_hi,
+                int(all_off[:, -1].sum()))
+
+    def gather_events(self, res: dict) -> torch.Tensor:
+        """The whole event table [E, 6] (sorted by atom, time) from the atom-block shards."""
+        if self.world == 1:
+            return res['events']
+        return self.comm.all_gather_rows(res['events'])

@@ -110,10 +110,29 @@ def _cpu_worker(rank: int, world: int, port: int, out_path: str):
                 n = all_counts[r, a]
                 merged[dst_start[r, a]: dst_start[r, a] + n] = gathered[r, src_off[a]: src_off[a] + n]
 
+        full_o, full_i = _oracle_states(rec, pos)
+        expected = oevents.calculate_transition_events(full_o, full_i)
+        np.testing.assert_array_equal(merged, expected)
+
+        # the product's route: all-to-all by atom block, per-atom merge of the pieces, and the
+        # ragged gather that reassembles the table
+        lo, hi = n_atoms * rank // world, n_atoms * (rank + 1) // world
+        off = np.concatenate([[0], np.cumsum(all_counts, axis=1)[rank]])
+        blocks = [(n_atoms * r // world, n_atoms * (r + 1) // world) for r in range(world)]
+        send = [int(off[b] - off[a]) for a, b in blocks]
+        recv = [int(all_counts[r, lo:hi].sum()) for r in range(world)]
+        pieces = comm.all_to_all_rows(torch.from_numpy(rows), send, recv)
+        b_off, b_dst = merge_plan(all_counts[:, lo:hi])
+        mine = np.zeros((int(b_off[-1]), 6), dtype=np.int64)
+        for r in range(world):
+            piece = pieces[r].numpy()
+            src_off = np.concatenate([[0], np.cumsum(all_counts[r, lo:hi])])
+            for a in range(hi - lo):
+                n = all_counts[r, lo + a]
+                mine[b_dst[r, a]: b_dst[r, a] + n] = piece[src_off[a]: src_off[a] + n]
+        np.testing.assert_array_equal(mine, expected[(expected[:, 0] >= lo) & (expected[:, 0] < hi)])
+        np.testing.assert_array_equal(comm.all_gather_rows(torch.from_numpy(mine)).numpy(), expected)
         if rank == 0:
-            full_o, full_i = _oracle_states(rec, pos)
-            expected = oevents.calculate_transition_events(full_o, full_i)
-            np.testing.assert_array_equal(merged, expected)
             Path(out_path).write_text(f'ok {len(expected)}')
     finally:
         dist.destroy_process_group()
@@ -154,7 +173,8 @@ def _gpu_worker(rank: int, world: int, port: int, out_path: str):
             warnings.simplefilter('ignore')
             res = hp.run(torch.from_numpy(pos[f0:f1]).cuda())
         np.savez(f'{out_path}.{rank}.npz', outer=res['outer'].cpu().numpy(), inner=res['inner'].cpu().numpy(),
-                 events=res['events'].cpu().numpy(), jumps=res['jumps'].cpu().numpy())
+                 events=hp.gather_events(res).cpu().numpy(), jumps=res['jumps'].cpu().numpy(),
+                 block=np.array(res['atom_block']), local_events=res['events'].cpu().numpy())
     finally:
         dist.destroy_process_group()
 
@@ -178,3 +198,7 @@ def test_hotpath_two_frame_shards_equal_one(tmp_path):
         np.testing.assert_array_equal(r['events'], one['events'].cpu().numpy())
         np.testing.assert_array_equal(r['jumps'], one['jumps'].cpu().numpy())
     assert len(one['events']) > 100 and len(one['jumps']) > 0
+    ev = one['events'].cpu().numpy()
+    for r in (r0, r1):  # each rank keeps the rows of its atom block
+        lo, hi = r['block']
+        np.testing.assert_array_equal(r['local_events'], ev[(ev[:, 0] >= lo) & (ev[:, 0] < hi)])
