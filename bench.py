@@ -42,6 +42,8 @@ def parse_args():
     ap.add_argument('--e2e-frames', type=int, default=100_000, help='frames per e2e step (host buffers)')
     ap.add_argument('--cpu-frames', type=int, default=2_000, help='frames of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-extras', action='store_true', help='skip the MSD / unwrap / density section')
+    ap.add_argument('--msd-lags', type=int, default=2048, help='lags of the MSD section (whole job)')
     return ap.parse_args()
 
 
@@ -190,6 +192,118 @@ def workload_config(rec, args):
     }
 
 
+# ------------------------------------------------------------------------------ MSD / K0 / K5
+
+
+def run_extras(args, rec, world, rank, peaks):
+    """The other kernels of the path on the same C3 trajectory, timed with CUDA events:
+    K0 unwrap (HBM bound), K4 direct MSD over a bounded lag range (fp64 pipe bound; the lag axis
+    is sharded over the ranks, positions replicated), K5 density histogram at 0.1 A."""
+    import ctypes as C
+
+    import torch
+    import torch.distributed as dist
+
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from gemdat_b200.lattice import Lattice
+    from gemdat_b200.volume import density_device, grid_edges
+
+    lib = _lib.lib
+    s = dv.stream_ptr()
+    T, A = args.frames, rec.n_atoms
+    out = {}
+
+    def timed(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        best = 1e30
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b))
+        return best
+
+    def reduce_max(ms):
+        if world > 1:
+            t = torch.tensor([ms], device='cuda', dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    hbm = float(peaks.get('hbm_gbs', 6650.0))
+    pos = rec.device_positions(0, T)  # replicated: MSD pairs distant frames (SURVEY 8e)
+    lat = np.ascontiguousarray(rec.lattice, dtype=np.float64)
+
+    # ---- K0: wrapped positions -> cumulative Cartesian displacement (+ winding scan)
+    n_chunks = int(lib.gd_unwrap_chunks(T, A))
+    work = dv.empty((n_chunks * A * 3,), torch.int32)
+    cart = dv.empty((T, A, 3), torch.float64)
+    wind = dv.empty((A, 3), torch.int32)
+
+    def k0():
+        _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None, dv.ptr(work),
+                                 None, dv.ptr(cart), None, dv.ptr(wind), s))
+
+    ms = reduce_max(timed(k0))
+    gbs = 72.0 * T * A / (ms * 1e-3) / 1e9  # 24 B read twice (winding pass + apply) + 24 B written
+    out['unwrap'] = {'ms': ms, 'atom_frames_per_s': T * A / (ms * 1e-3), 'algorithmic_GBps': gbs,
+                     'frac_of_hbm': gbs / hbm, 'bytes_per_atom_frame': 72, 'replicas': world}
+
+    # ---- K5: density histogram at 0.1 A (uint32 grid, one RED per atom-frame)
+    nedges = grid_edges(Lattice(rec.lattice), 0.1)
+    grid, flag = density_device(pos, nedges)
+
+    def k5():
+        grid.zero_()
+        density_device(pos, nedges, grid)
+
+    ms = reduce_max(timed(k5))
+    gbs = 28.0 * T * A / (ms * 1e-3) / 1e9
+    out['density'] = {'ms': ms, 'atom_frames_per_s': T * A / (ms * 1e-3), 'algorithmic_GBps': gbs,
+                      'frac_of_hbm': gbs / hbm, 'grid': [int(n) - 1 for n in nedges], 'resolution_A': 0.1,
+                      'count_ok': bool(int(grid.view(torch.int32).to(torch.int64).sum().item()) == T * A),
+                      'replicas': world}
+    del grid
+
+    # ---- K4: direct MSD, lags 1 .. msd_lags split over the ranks
+    soa = dv.empty((A, 3, T), torch.float64)
+    _lib.check(lib.gd_transpose_soa(dv.ptr(cart), T, A, dv.ptr(soa), s))
+    torch.cuda.synchronize()
+    del cart
+    lo = 1 + args.msd_lags * rank // world
+    hi = 1 + args.msd_lags * (rank + 1) // world
+    msd = dv.empty((A, hi - lo), torch.float64)
+
+    def k4():
+        _lib.check(lib.gd_msd_direct(dv.ptr(soa), T, A, lo, hi - lo, dv.ptr(msd), s))
+
+    ms = reduce_max(timed(k4, reps=2))
+    peak = C.c_double(0.0)
+    _lib.check(lib.gd_fp64_peak(1 << 14, C.byref(peak), s))
+    pairs = float(sum(T - k for k in range(1, args.msd_lags + 1))) * A
+    # atom-averaged curve: every rank holds its lag range -> all-gather of the partial results
+    curve = msd.mean(dim=0)
+    if world > 1:
+        parts = [torch.empty(((1 + args.msd_lags * (r + 1) // world) - (1 + args.msd_lags * r // world),),
+                             dtype=torch.float64, device='cuda') for r in range(world)]
+        dist.all_gather(parts, curve)
+        curve = torch.cat(parts)
+    out['msd'] = {
+        'ms': ms, 'lags': args.msd_lags, 'lags_per_s': args.msd_lags / (ms * 1e-3),
+        'pair_terms_per_s': pairs / (ms * 1e-3),
+        'fp64_inst_per_pair': 6,
+        'fp64_peak_dfma_per_s_measured': peak.value * world,
+        'frac_of_fp64_pipe': (6.0 * pairs / (ms * 1e-3)) / (peak.value * world),
+        'lag_axis_sharded_over': world, 'msd_at_last_lag_A2': float(curve[-1].item()),
+        'note': 'unit lag = one lag over all atoms and all frame pairs of the 1e6-frame trajectory',
+    }
+    return out
+
+
 # ------------------------------------------------------------------------------ GPU arm
 
 
@@ -247,12 +361,12 @@ def run_ours(args):
     value = n_af_total / (ms_per_step * 1e-3)
 
     line = None
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / 'MEASURED_PEAKS.json').read_text())
+    except Exception:
+        pass
     if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.loads((ROOT / 'MEASURED_PEAKS.json').read_text())
-        except Exception:
-            pass
         peak = float(peaks.get('hbm_gbs', 6650.0))
         k1_bytes = 32.0 * (f1 - f0) * n_atoms
         achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
@@ -269,6 +383,12 @@ def run_ours(args):
             'clocks': sampler.summary(),
             'results': {'n_events': int(res['n_events']), 'n_jumps': int(res['n_jumps'])},
         }
+
+    extras = None
+    if not args.no_extras:
+        del res
+        hp._buf.clear()
+        extras = run_extras(args, rec, world, rank, peaks)
 
     # ---- e2e through the public API with pinned host buffers (rank-local window)
     from gemdat_b200 import Trajectory
@@ -304,6 +424,8 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_dt = float(t.item())
     if rank == 0:
+        if extras is not None:
+            line['extras'] = extras
         line['e2e'] = {
             'value': world * e2e_frames * n_atoms / e2e_dt, 'unit': UNIT,
             'h2d_bytes_per_step': int(host_np.nbytes),
