@@ -25,6 +25,7 @@ GD_ERR_INNER_CONSTANT = 7
 GD_ERR_NO_EVENTS = 8
 GD_ERR_NO_JUMPS = 9
 GD_ERR_RANGE = 10
+GD_JUMP_STATE_BYTES = 40
 
 
 class GemdatB200Error(RuntimeError):
@@ -69,6 +70,9 @@ SIGNATURES = {
     'gd_jumps_work_bytes': (_i64, [_i64, _i32]),
     'gd_jumps_count': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
     'gd_jumps_fill': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _p]),
+    'gd_jumps_count_shard': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.c_int, _p, _p, _p, _p,
+                                       C.POINTER(_i64), C.POINTER(_i32), _p]),
+    'gd_jumps_resolve': (C.c_int, [_p, _i32, _i32, _i32, _p, _p, C.POINTER(_i32), _p]),
     'gd_pair_matrix': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),
     'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -96,12 +96,18 @@ struct JumpMachine {
 
 constexpr int kSeg = 512;  // event rows per segment
 
-struct PackedState {  // 40 bytes
+struct PackedState {  // 40 bytes == GD_JUMP_STATE_BYTES
     int32_t have;  // bit 0: from pending, bit 1: candidate pending
     int32_t f_start, f_dest, f_time;
     int32_t c_start, c_dest, c_inner, c_start_time, c_stop_time;
-    int32_t pad;
+    int32_t flags;  // per-atom shard records only (kHasEvents | kSynced | kKnown), else 0
 };
+static_assert(sizeof(PackedState) == GD_JUMP_STATE_BYTES, "jump state record size is part of the ABI");
+
+// flags of a per-atom record of a frame shard
+constexpr int32_t kHasEvents = 1;  // the shard holds events of this atom
+constexpr int32_t kSynced = 2;     // ... one of them a departure: the exit state does not depend on the entry
+constexpr int32_t kKnown = 4;      // the state in the record is the true one
 
 __device__ __forceinline__ PackedState pack(const JumpMachine &m) {
     PackedState s;
@@ -114,7 +120,7 @@ __device__ __forceinline__ PackedState pack(const JumpMachine &m) {
     s.c_inner = m.c_dest_inner;
     s.c_start_time = m.c_start_time;
     s.c_stop_time = m.c_stop_time;
-    s.pad = 0;
+    s.flags = 0;
     return s;
 }
 
@@ -170,7 +176,11 @@ __global__ void __launch_bounds__(1024)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int base = 0; base < n_atoms; base += 1024) {
         const int idx = base + threadIdx.x;
-        const int64_t v = idx < n_atoms ? (atom_offsets[idx + 1] - atom_offsets[idx] + kSeg - 1) / kSeg : 0;
+        int64_t v = 0;  // every atom owns at least one (possibly empty) segment: its last segment
+        if (idx < n_atoms) {  // carries the atom's exit state and the end-of-trajectory close
+            v = (atom_offsets[idx + 1] - atom_offsets[idx] + kSeg - 1) / kSeg;
+            if (v < 1) v = 1;
+        }
         int64_t incl = v;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -211,7 +221,7 @@ __device__ __forceinline__ bool locate_segment(int64_t seg, const int64_t *__res
 __global__ void __launch_bounds__(128)
     k_jumps_spec(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
                  const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t minimal_residence,
-                 SegSpec *__restrict__ spec) {
+                 SegSpec *__restrict__ spec, int32_t *__restrict__ atom_flags) {
     const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int32_t atom;
     int64_t r0;
@@ -234,19 +244,43 @@ __global__ void __launch_bounds__(128)
     out.sync = sync;
     out.n_after = n_after;
     spec[seg] = out;
+    const int32_t fl = (n > 0 ? kHasEvents : 0) | (synced ? kSynced : 0);
+    if (fl) atomicOr(atom_flags + atom, fl);
+}
+
+// first-segment entry state of an atom: the caller's record (frame shards) or the empty state
+__device__ __forceinline__ bool atom_entry_state(JumpMachine &m, const PackedState *__restrict__ atom_entry,
+                                                 int32_t a) {
+    m.c_atom = a;
+    if (!atom_entry) return true;
+    const PackedState e = atom_entry[a];
+    unpack(m, e, a);
+    return (e.flags & kKnown) != 0;
+}
+
+// record of the atom's state when it leaves this shard (before any end-of-trajectory close)
+__device__ __forceinline__ void write_atom_exit(PackedState *__restrict__ atom_exit, int32_t a,
+                                                const JumpMachine &m, int32_t shard_flags,
+                                                bool entry_known) {
+    if (!atom_exit) return;
+    PackedState e = pack(m);
+    e.flags = shard_flags | ((entry_known || (shard_flags & kSynced)) ? kKnown : 0);
+    atom_exit[a] = e;
 }
 
 __global__ void __launch_bounds__(64)
     k_jumps_chain(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
                   const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
                   int64_t minimal_residence, const SegSpec *__restrict__ spec,
-                  PackedState *__restrict__ entry, int64_t *__restrict__ counts) {
+                  PackedState *__restrict__ entry, int64_t *__restrict__ counts,
+                  const PackedState *__restrict__ atom_entry, PackedState *__restrict__ atom_exit,
+                  const int32_t *__restrict__ atom_flags, int is_last_shard) {
     const int32_t a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= n_atoms) return;
     const int64_t s0 = seg_off[a], s1 = seg_off[a + 1];
     const int64_t row_end = atom_offsets[a + 1];
     JumpMachine truth(minimal_residence);
-    truth.c_atom = a;
+    const bool entry_known = atom_entry_state(truth, atom_entry, a);
     for (int64_t seg = s0; seg < s1; ++seg) {
         entry[seg] = pack(truth);
         const int64_t r0 = atom_offsets[a] + (seg - s0) * kSeg;
@@ -275,7 +309,10 @@ __global__ void __launch_bounds__(64)
             unpack(truth, sp.exit, a);
         }
         // (otherwise the whole segment was replayed and `truth` already is its exit state)
-        if (seg + 1 == s1 && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
+        if (seg + 1 == s1) {
+            write_atom_exit(atom_exit, a, truth, atom_flags[a], entry_known);
+            if (is_last_shard && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
+        }
         counts[seg] = n_true;
     }
 }
@@ -293,7 +330,9 @@ __global__ void __launch_bounds__(128)
                       const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
                       int64_t minimal_residence, const SegSpec *__restrict__ spec,
                       PackedState *__restrict__ entry, int64_t *__restrict__ counts,
-                      int32_t *__restrict__ flag) {
+                      int32_t *__restrict__ flag, const PackedState *__restrict__ atom_entry,
+                      PackedState *__restrict__ atom_exit, const int32_t *__restrict__ atom_flags,
+                      int is_last_shard) {
     const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int32_t a;
     int64_t r0;
@@ -301,8 +340,9 @@ __global__ void __launch_bounds__(128)
     if (!locate_segment(seg, seg_off, atom_offsets, n_atoms, a, r0, n)) return;
     const bool first = seg == seg_off[a], last = seg + 1 == seg_off[a + 1];
     JumpMachine truth(minimal_residence);
-    truth.c_atom = a;
-    if (!first) unpack(truth, spec[seg - 1].exit, a);
+    bool entry_known = true;
+    if (first) entry_known = atom_entry_state(truth, atom_entry, a);
+    else unpack(truth, spec[seg - 1].exit, a);
     entry[seg] = pack(truth);
     const SegSpec sp = spec[seg];
     JumpMachine guess(minimal_residence);
@@ -327,7 +367,14 @@ __global__ void __launch_bounds__(128)
     } else if (!last) {
         atomicExch(flag, 1);  // the next segment's assumed entry state is not proven
     }
-    if (last && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
+    if (last) {
+        // entry_known of a later segment: proven by the merge checks of the segments before it
+        // (else *flag is set and the sequential chain redoes this); the record's kKnown then
+        // follows from the atom's own entry record
+        const bool known = first ? entry_known : (!atom_entry || (atom_entry[a].flags & kKnown) != 0);
+        write_atom_exit(atom_exit, a, truth, atom_flags[a], known);
+        if (is_last_shard && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
+    }
     counts[seg] = n_true;
 }
 
@@ -335,7 +382,8 @@ __global__ void __launch_bounds__(128)
     k_jumps_fill(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
                  const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
                  int64_t minimal_residence, const PackedState *__restrict__ entry,
-                 const int64_t *__restrict__ counts, int32_t *__restrict__ jumps) {
+                 const int64_t *__restrict__ counts, int32_t *__restrict__ jumps,
+                 const int32_t *__restrict__ shard_flag) {
     const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int32_t atom;
     int64_t r0;
@@ -358,7 +406,8 @@ __global__ void __launch_bounds__(128)
         m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
     }
     const bool last_of_atom = r0 + n == atom_offsets[atom + 1];
-    if (last_of_atom && m.have_cand && out < out1) m.close_candidate(n_frames_total, emit);
+    // shard_flag[2]: this is the trajectory's last frame shard (left by the count call)
+    if (last_of_atom && shard_flag[2] != 0 && m.have_cand && out < out1) m.close_candidate(n_frames_total, emit);
 }
 
 // single block exclusive scan, c[0..n) -> offsets, c[n] = total
@@ -397,7 +446,9 @@ struct JumpWork {
     int64_t *counts;     // [max_segs + 1]
     SegSpec *spec;       // [max_segs]
     PackedState *entry;  // [max_segs]
-    int32_t *flag;       // [4]: set when the parallel chain could not prove a segment's entry state
+    int32_t *flag;       // [4]: [0] parallel chain could not prove a segment's entry state,
+                         //      [1] a published shard record differs from the true exit, [2] is_last_shard
+    int32_t *atom_flags; // [n_atoms]: kHasEvents | kSynced of this shard's events per atom
     size_t bytes;
 };
 inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
@@ -416,6 +467,8 @@ inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
     off += up((size_t)w.max_segs * sizeof(PackedState));
     w.flag = reinterpret_cast<int32_t *>(p + off);
     off += 16;
+    w.atom_flags = reinterpret_cast<int32_t *>(p + off);
+    off += up((size_t)n_atoms * 4);
     w.bytes = off;
     return w;
 }
@@ -459,51 +512,153 @@ extern "C" int64_t gd_jumps_work_bytes(int64_t n_events, int32_t n_atoms) {
     return (int64_t)jump_work(nullptr, n_events, n_atoms).bytes;
 }
 
-extern "C" gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_atom_offsets,
-                                      int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
-                                      int64_t minimal_residence, void *d_work, int64_t *h_n_jumps,
-                                      void *stream) {
-    GD_REQUIRE(d_atom_offsets && d_work && h_n_jumps, GD_ERR_INVALID, "gd_jumps_count: null argument");
+namespace {
+
+// per-atom exclusive jump offsets from the scanned per-segment counts
+__global__ void __launch_bounds__(256)
+    k_atom_jump_offsets(const int64_t *__restrict__ counts, const int64_t *__restrict__ seg_off,
+                        int32_t n_atoms, int64_t *__restrict__ out) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a <= n_atoms) out[a] = counts[seg_off[a]];
+}
+
+// a record published as known (entry independent, or run from a known entry) must equal the
+// true exit state of the final pass
+__global__ void __launch_bounds__(256)
+    k_check_published(const PackedState *__restrict__ exit_now, const PackedState *__restrict__ published,
+                      int32_t n_atoms, int32_t *__restrict__ flag) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n_atoms) return;
+    const PackedState pub = published[a];
+    if (!(pub.flags & kKnown)) return;
+    JumpMachine x(0), y(0);
+    unpack(x, exit_now[a], a);
+    unpack(y, pub, a);
+    if (!same_state(x, y)) atomicExch(flag + 1, 1);
+}
+
+// Entry state of every atom for shard `rank` from the records of all shards (thread per
+// (shard, atom): every rank evaluates all shards so that all ranks agree on `unresolved`).
+__global__ void __launch_bounds__(256)
+    k_jumps_resolve(const PackedState *__restrict__ all, int32_t world, int32_t rank, int32_t n_atoms,
+                    PackedState *__restrict__ entry, int32_t *__restrict__ unresolved) {
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (int64_t)world * n_atoms) return;
+    const int32_t q = (int32_t)(idx / n_atoms), a = (int32_t)(idx - (int64_t)q * n_atoms);
+    PackedState e;
+    e.have = 0;
+    e.f_start = e.f_dest = e.f_time = 0;
+    e.c_start = e.c_dest = e.c_inner = e.c_start_time = e.c_stop_time = 0;
+    e.flags = kKnown;  // no earlier shard has events of this atom: the empty state
+    for (int32_t p = q - 1; p >= 0; --p) {
+        const PackedState r = all[(int64_t)p * n_atoms + a];
+        if (!(r.flags & kHasEvents)) continue;  // the atom's state passes through shard p unchanged
+        e = r;
+        e.flags = r.flags & kKnown;
+        break;
+    }
+    if (!(e.flags & kKnown)) atomicAdd(unresolved, 1);
+    if (q == rank) entry[a] = e;
+}
+
+}  // namespace
+
+extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_offsets,
+                                            int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                            int64_t minimal_residence, const void *d_entry,
+                                            int is_last_shard, const void *d_published, void *d_work,
+                                            void *d_exit, int64_t *d_atom_jump_offsets,
+                                            int64_t *h_n_jumps, int32_t *h_flags, void *stream) {
+    GD_REQUIRE(d_atom_offsets && d_work, GD_ERR_INVALID, "gd_jumps_count: null argument");
     GD_REQUIRE(n_events >= 0 && (n_events == 0 || d_events), GD_ERR_INVALID,
                "gd_jumps_count: bad event table");
     GD_REQUIRE(n_atoms > 0, GD_ERR_INVALID, "gd_jumps_count: n_atoms must be positive");
     GD_REQUIRE((reinterpret_cast<uintptr_t>(d_work) & 15) == 0, GD_ERR_ALIGNMENT,
                "gd_jumps_count: d_work must be 16-byte aligned");
+    GD_REQUIRE(!d_published || d_exit, GD_ERR_INVALID, "gd_jumps_count_shard: d_published needs d_exit");
     cudaStream_t st = (cudaStream_t)stream;
     const JumpWork w = jump_work(d_work, n_events, n_atoms);
+    const PackedState *entry = static_cast<const PackedState *>(d_entry);
+    PackedState *exit_rec = static_cast<PackedState *>(d_exit);
     k_seg_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms, w.seg_off);
     GD_LAUNCH_CHECK();
+    GD_CUDA_CHECK(cudaMemsetAsync(w.atom_flags, 0, (size_t)n_atoms * 4, st));
     k_jumps_spec<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
-        d_events, d_atom_offsets, w.seg_off, n_atoms, minimal_residence, w.spec);
+        d_events, d_atom_offsets, w.seg_off, n_atoms, minimal_residence, w.spec, w.atom_flags);
     GD_LAUNCH_CHECK();
     GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
-    GD_CUDA_CHECK(cudaMemsetAsync(w.flag, 0, 16, st));
+    const int32_t flags0[4] = {0, 0, is_last_shard ? 1 : 0, 0};
+    GD_CUDA_CHECK(cudaMemcpyAsync(w.flag, flags0, 16, cudaMemcpyHostToDevice, st));
     // GD_JUMPS_SEQUENTIAL=1 forces the sequential chain (tests / A-B timing)
     const char *env = getenv("GD_JUMPS_SEQUENTIAL");
     bool sequential = env && atoi(env) != 0;
-    int32_t h_flag = 0;
+    int32_t h_flag[2] = {0, 0};
     for (;;) {
         if (sequential) {
             k_jumps_chain<<<(unsigned)gd_ceil_div(n_atoms, 64), 64, 0, st>>>(
                 d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
-                w.spec, w.entry, w.counts);
+                w.spec, w.entry, w.counts, entry, exit_rec, w.atom_flags, is_last_shard);
         } else {
             k_jumps_chain_par<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
                 d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
-                w.spec, w.entry, w.counts, w.flag);
+                w.spec, w.entry, w.counts, w.flag, entry, exit_rec, w.atom_flags, is_last_shard);
         }
         GD_LAUNCH_CHECK();
         k_scan_counts<<<1, 1024, 0, st>>>(w.counts, w.max_segs);
         GD_LAUNCH_CHECK();
-        GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
-                                      cudaMemcpyDeviceToHost, st));
-        GD_CUDA_CHECK(cudaMemcpyAsync(&h_flag, w.flag, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        if (h_n_jumps)
+            GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
+                                          cudaMemcpyDeviceToHost, st));
+        GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         GD_CUDA_CHECK(cudaStreamSynchronize(st));
-        if (sequential || h_flag == 0) break;
+        if (sequential || h_flag[0] == 0) break;
         // some segment's entry state could not be proven: redo with the sequential chain
         sequential = true;
         GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
     }
+    if (d_atom_jump_offsets) {
+        k_atom_jump_offsets<<<(unsigned)gd_ceil_div(n_atoms + 1, 256), 256, 0, st>>>(
+            w.counts, w.seg_off, n_atoms, d_atom_jump_offsets);
+        GD_LAUNCH_CHECK();
+    }
+    if (d_published) {
+        k_check_published<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(
+            exit_rec, static_cast<const PackedState *>(d_published), n_atoms, w.flag);
+        GD_LAUNCH_CHECK();
+        if (h_flags) {
+            GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            GD_CUDA_CHECK(cudaStreamSynchronize(st));
+        }
+    }
+    if (h_flags) *h_flags = (sequential ? 1 : 0) | (h_flag[1] ? 2 : 0);
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_atom_offsets,
+                                      int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                      int64_t minimal_residence, void *d_work, int64_t *h_n_jumps,
+                                      void *stream) {
+    GD_REQUIRE(h_n_jumps, GD_ERR_INVALID, "gd_jumps_count: null argument");
+    return gd_jumps_count_shard(d_events, d_atom_offsets, n_events, n_atoms, n_frames_total,
+                                minimal_residence, nullptr, 1, nullptr, d_work, nullptr, nullptr,
+                                h_n_jumps, nullptr, stream);
+}
+
+extern "C" gd_status_t gd_jumps_resolve(const void *d_all_records, int32_t world, int32_t rank,
+                                        int32_t n_atoms, void *d_entry, int32_t *d_unresolved,
+                                        int32_t *h_unresolved, void *stream) {
+    GD_REQUIRE(d_all_records && d_entry && d_unresolved && h_unresolved, GD_ERR_INVALID,
+               "gd_jumps_resolve: null argument");
+    GD_REQUIRE(world > 0 && rank >= 0 && rank < world && n_atoms > 0, GD_ERR_INVALID,
+               "gd_jumps_resolve: bad shard geometry");
+    cudaStream_t st = (cudaStream_t)stream;
+    GD_CUDA_CHECK(cudaMemsetAsync(d_unresolved, 0, sizeof(int32_t), st));
+    k_jumps_resolve<<<(unsigned)gd_ceil_div((int64_t)world * n_atoms, 256), 256, 0, st>>>(
+        static_cast<const PackedState *>(d_all_records), world, rank, n_atoms,
+        static_cast<PackedState *>(d_entry), d_unresolved);
+    GD_LAUNCH_CHECK();
+    GD_CUDA_CHECK(cudaMemcpyAsync(h_unresolved, d_unresolved, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    GD_CUDA_CHECK(cudaStreamSynchronize(st));
     return GD_OK;
 }
 
@@ -511,13 +666,13 @@ extern "C" gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_a
                                      int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
                                      int64_t minimal_residence, const void *d_work,
                                      int32_t *d_jumps, void *stream) {
-    GD_REQUIRE(d_events && d_atom_offsets && d_work && d_jumps, GD_ERR_INVALID,
-               "gd_jumps_fill: null argument");
-    GD_REQUIRE(n_atoms > 0 && n_events >= 0, GD_ERR_INVALID, "gd_jumps_fill: bad size");
+    GD_REQUIRE(d_atom_offsets && d_work && d_jumps, GD_ERR_INVALID, "gd_jumps_fill: null argument");
+    GD_REQUIRE(n_atoms > 0 && n_events >= 0 && (n_events == 0 || d_events), GD_ERR_INVALID,
+               "gd_jumps_fill: bad size");
     const JumpWork w = jump_work(const_cast<void *>(d_work), n_events, n_atoms);
     k_jumps_fill<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, (cudaStream_t)stream>>>(
         d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence, w.entry,
-        w.counts, d_jumps);
+        w.counts, d_jumps, w.flag);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

@@ -14,6 +14,7 @@ the same kernels through ``gemdat_b200.transitions``.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import warnings
 
 import numpy as np
@@ -137,6 +138,8 @@ class HotPath:
         self.comm = Comm(world, group)
         self.launches_per_run = 0
         self.last_k1_events = None
+        # GD_K3_EXCHANGE=1: always exchange the event rows by atom block (the fallback route; A/B)
+        self.k3_exchange = os.environ.get('GD_K3_EXCHANGE', '0') not in ('', '0')
         self._buf = {}
 
     # ------------------------------------------------------------------ helpers
@@ -186,9 +189,17 @@ class HotPath:
         self.last_k1_events = (e0, e1)
         launches += 1
 
+        # ---- what K2 needs from the other shards, in ONE exchange: the OR of the visited flags
+        # (warning + Q2 LUT are global), the OR of the "state ever changes" flags (Q4 "atom is
+        # skipped" is a whole-trajectory property) and the following shard's first state rows
+        # (destination states of the halo event).
+        next_o = next_i = None
         if self.world > 1:
-            self.comm.all_reduce_max(visited)
-        vis = dv.to_host(visited).astype(bool).reshape(2, self.n_sites)
+            next_o, next_i = self._exchange_after_k1(visited, changed, outer, inner)
+        host = dv.to_host(torch.cat([visited, changed[:n_atoms].amax().reshape(1)]))
+        vis = host[:-1].astype(bool).reshape(2, self.n_sites)
+        any_outer_change = bool(host[-1])
+        remapped = False
         for arr, v in ((outer, vis[0]), (inner, vis[1])):
             for label, key in zip(self.grid.group_labels, self.grid.group_keys):
                 if not (v.any() if key is None else v[key].any()):
@@ -199,14 +210,13 @@ class HotPath:
                 d_lut = dv.to_device(lut)
                 _lib.check(lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut), self.n_sites, s))
                 launches += 1
-
-        # ---- K2: scan + fill (the fill writes the halo event with the neighbour's first states)
-        next_o = next_i = None
-        if self.world > 1:
+                remapped = True
+        if remapped and self.world > 1:  # rare (Q2): the halo rows must carry the remapped indices
             rows = self._all_gather(torch.stack([outer[0], inner[0]]))  # [W, 2, A]
             if self.rank + 1 < self.world:
                 next_o, next_i = rows[self.rank + 1, 0].contiguous(), rows[self.rank + 1, 1].contiguous()
-            self.comm.all_reduce_max(changed)
+
+        # ---- K2: scan + fill (the fill writes the halo event with the neighbour's first states)
         offsets = self._tensor('offsets', (n_atoms + 1,), torch.int64)
         n_events = C.c_int64(0)
         st = lib.gd_events_scan(dv.ptr(work), n_frames, n_atoms, dv.ptr(changed), dv.ptr(offsets),
@@ -216,7 +226,7 @@ class HotPath:
         _lib.check(st)
         launches += 2
         self.last_n_local_events = n_events.value
-        if not bool(changed[:n_atoms].any()):
+        if not any_outer_change:
             raise ValueError('need at least one array to concatenate')
         rows = dv.empty((max(n_events.value, 1), 6), torch.int32)
         if n_events.value:
@@ -226,19 +236,62 @@ class HotPath:
             launches += 1
         rows = rows[: n_events.value]
 
-        # ---- K3.  Frame shards hold time slices of every atom; the jump machine needs an atom's
-        # whole history.  So the event rows change hands ONCE, by atom block (all-to-all: each row
-        # crosses NVLink at most once), every rank runs K3 on its atoms only, and the small jump
-        # tables are gathered.  The event table stays sharded by atom block (`gather_events`
-        # assembles it on demand).
-        a_lo, a_hi = 0, n_atoms
-        n_events_global = n_events.value
-        if self.world > 1:
-            rows, offsets, a_lo, a_hi, n_events_global = self._exchange_events(rows, offsets, n_atoms)
-            launches += self.world
-        n_local = int(rows.shape[0])
-        n_block = a_hi - a_lo
+        # ---- K3.  Frame shards hold time slices of every atom while the jump machine is
+        # sequential along an atom's history.  Its state forgets the past at every departure
+        # event, so each shard runs its own slice and only the per-atom machine STATE crosses the
+        # shard boundary (40 B per atom, `_jumps_frame_sharded`); the events never move.  Event
+        # tables that are not state-consistent fall back to exchanging the rows by atom block.
+        res = {'outer': outer, 'inner': inner, 'visited': vis, 'band': band}
+        if self.world == 1:
+            jumps, k3_launches = self._jumps_local(rows, offsets, n_atoms)
+            res.update(events=rows, atom_offsets=offsets, events_layout='whole', jumps=jumps,
+                       n_events=n_events.value)
+        else:
+            out = None if self.k3_exchange else self._jumps_frame_sharded(rows, offsets, n_atoms)
+            if out is not None:
+                jumps, n_events_global, k3_launches = out
+                res.update(events=rows, atom_offsets=offsets, events_layout='frame_shard', jumps=jumps,
+                           n_events=n_events_global)
+            else:
+                rows, offsets, a_lo, a_hi, n_events_global = self._exchange_events(rows, offsets, n_atoms)
+                jumps, k3_launches = self._jumps_local(rows, offsets, a_hi - a_lo)
+                jumps = self.comm.all_gather_rows(jumps)  # rank order = atom-block order = (atom, time)
+                k3_launches += self.world
+                res.update(events=rows, atom_offsets=offsets, events_layout='atom_block',
+                           atom_block=(a_lo, a_hi), jumps=jumps, n_events=n_events_global)
+        launches += k3_launches
+        res['n_jumps'] = int(res['jumps'].shape[0])
+        self.launches_per_run = launches
+        return res
 
+    # ------------------------------------------------------------------ pieces of the pass
+    def _exchange_after_k1(self, visited, changed, outer, inner):
+        """One all-gather of [visited | changed | first outer row | first inner row] per rank;
+        ORs the flags in place and returns the following shard's first state rows."""
+        n_atoms = int(outer.shape[1])
+        parts = [visited, changed, outer[0].contiguous().view(torch.uint8), inner[0].contiguous().view(torch.uint8)]
+        offs, total = [], 0
+        for p in parts:
+            offs.append(total)
+            total += (p.numel() + 15) // 16 * 16  # int32 sections stay aligned
+        pack = self._tensor('pack_k1', (total,), torch.uint8)
+        for o, p in zip(offs, parts):
+            pack[o: o + p.numel()] = p
+        allp = self.comm.all_gather(pack)  # [W, total]
+        visited.copy_(allp[:, offs[0]: offs[0] + visited.numel()].amax(dim=0))
+        changed.copy_(allp[:, offs[1]: offs[1] + changed.numel()].amax(dim=0))
+        if self.rank + 1 == self.world:
+            return None, None
+        nxt = allp[self.rank + 1]
+        return (nxt[offs[2]: offs[2] + 4 * n_atoms].contiguous().view(torch.int32),
+                nxt[offs[3]: offs[3] + 4 * n_atoms].contiguous().view(torch.int32))
+
+    def _jumps_local(self, rows, offsets, n_block):
+        """K3 on a table holding the whole history of ``n_block`` atoms (count -> allocate -> fill)."""
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        n_local = int(rows.shape[0])
+        launches = 0
         jwork = self._tensor('jwork', (int(lib.gd_jumps_work_bytes(n_local, max(n_block, 1))),), torch.uint8)
         n_jumps = C.c_int64(0)
         if n_block > 0:
@@ -250,13 +303,84 @@ class HotPath:
             _lib.check(lib.gd_jumps_fill(dv.ptr(rows), dv.ptr(offsets), n_local, n_block, self.n_frames_total,
                                          self.minimal_residence, dv.ptr(jwork), dv.ptr(jumps), s))
             launches += 1
+        return jumps[: n_jumps.value], launches
+
+    def _jumps_frame_sharded(self, rows, offsets, n_atoms):
+        """K3 on this rank's time slice of every atom; only machine states cross the boundary.
+
+        Returns ``(jumps [J, 6] whole table on every rank, global event count, launches)`` or
+        ``None`` when a published record turned out not to be the true one (caller falls back to
+        the event exchange; all ranks take the same decision)."""
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        W, me = self.world, self.rank
+        n_local = int(rows.shape[0])
+        last = 1 if me + 1 == W else 0
+        nbytes = _lib.GD_JUMP_STATE_BYTES
+        jwork = self._tensor('jwork', (int(lib.gd_jumps_work_bytes(n_local, n_atoms)),), torch.uint8)
+        exit_rec = self._tensor('jexit', (n_atoms, nbytes), torch.uint8)
+        entry = self._tensor('jentry', (n_atoms, nbytes), torch.uint8)
+        scratch = self._tensor('jscratch', (4,), torch.int32)
+        args = (dv.ptr(rows), dv.ptr(offsets), n_local, n_atoms, self.n_frames_total, self.minimal_residence)
+        launches = 0
+        # pass 1: every atom's exit record when the slice is run from the empty state
+        # (rank 0 really starts from the empty state; for the others all-zero records say "empty, not known")
+        entry.zero_()
+        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if me else None, last, None, dv.ptr(jwork),
+                                            dv.ptr(exit_rec), None, None, None, s))
+        launches += 4
+        published = None
+        for _ in range(W):
+            allrec = self.comm.all_gather(exit_rec)  # [W, A, 40]
+            if published is None:
+                published = allrec[me].contiguous()
+            unresolved = C.c_int32(0)
+            _lib.check(lib.gd_jumps_resolve(dv.ptr(allrec), W, me, n_atoms, dv.ptr(entry), dv.ptr(scratch),
+                                            C.byref(unresolved), s))
+            launches += 1
+            if unresolved.value == 0:
+                break
+            # some shard has events of an atom but no departure among them: its exit depends on
+            # its entry.  Run again from what is known so far; every round settles one more shard.
+            _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, None, dv.ptr(jwork),
+                                                dv.ptr(exit_rec), None, None, None, s))
+            launches += 4
+        else:
+            raise RuntimeError('jump machine states did not resolve in world rounds')
+        # final pass from the true entry states
+        atom_off = self._tensor('jatom_off', (n_atoms + 2,), torch.int64)
+        n_jumps, flags = C.c_int64(0), C.c_int32(0)
+        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, dv.ptr(published), dv.ptr(jwork),
+                                            dv.ptr(exit_rec), dv.ptr(atom_off), C.byref(n_jumps),
+                                            C.byref(flags), s))
+        launches += 6
+        jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
+        if n_jumps.value:
+            _lib.check(lib.gd_jumps_fill(*args, dv.ptr(jwork), dv.ptr(jumps), s))
+            launches += 1
         jumps = jumps[: n_jumps.value]
-        if self.world > 1:
-            jumps = self.comm.all_gather_rows(jumps)  # rank order = atom-block order = (atom, time) order
-        self.launches_per_run = launches
-        return {'outer': outer, 'inner': inner, 'events': rows, 'atom_offsets': offsets,
-                'atom_block': (a_lo, a_hi), 'jumps': jumps, 'n_events': n_events_global,
-                'n_jumps': int(jumps.shape[0]), 'visited': vis, 'band': band}
+        # gather: per-atom jump offsets + (mismatch flag, local event count) of every shard, then the rows
+        atom_off[n_atoms + 1] = (n_local << 1) | (1 if flags.value & 2 else 0)
+        all_off = dv.to_host(self.comm.all_gather(atom_off))  # [W, A + 2]
+        tail = all_off[:, -1]
+        if (tail & 1).any():
+            return None
+        n_events_global = int((tail >> 1).sum())
+        all_off = all_off[:, : n_atoms + 1]
+        counts = np.diff(all_off, axis=1)
+        cap = max(1, int(all_off[:, -1].max()))
+        padded = self._tensor('jpad', (cap, 6), torch.int32)
+        padded[: jumps.shape[0]] = jumps
+        allj = self.comm.all_gather(padded)  # [W, cap, 6]
+        total_off, dst_start = merge_plan(counts)
+        merged = dv.empty((max(int(total_off[-1]), 1), 6), torch.int32)
+        d_plan = dv.to_device(np.ascontiguousarray(np.concatenate([all_off, dst_start], axis=1)))  # [W, 2A+1]
+        for r in range(W):
+            if all_off[r, -1]:
+                _lib.check(lib.gd_events_merge(dv.ptr(allj[r]), dv.ptr(d_plan[r]),
+                                               dv.ptr(d_plan[r, n_atoms + 1:]), n_atoms, dv.ptr(merged), s))
+                launches += 1
+        return merged[: int(total_off[-1])], n_events_global, launches
 
     def atom_block(self, rank: int, n_atoms: int) -> tuple[int, int]:
         return n_atoms * rank // self.world, n_atoms * (rank + 1) // self.world
@@ -294,7 +418,27 @@ class HotPath:
                 int(all_off[:, -1].sum()))
 
     def gather_events(self, res: dict) -> torch.Tensor:
-        """The whole event table [E, 6] (sorted by atom, time) from the atom-block shards."""
-        if self.world == 1:
+        """The whole event table [E, 6] (sorted by atom, time) on every rank."""
+        layout = res.get('events_layout', 'whole')
+        if self.world == 1 or layout == 'whole':
             return res['events']
-        return self.comm.all_gather_rows(res['events'])
+        if layout == 'atom_block':
+            return self.comm.all_gather_rows(res['events'])
+        # frame shards: every shard's rows are sorted by (atom, time); place shard r's rows of atom
+        # a after the rows of atoms < a and of earlier shards of a
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        rows, n_atoms = res['events'], self.n_atoms
+        all_off = dv.to_host(self.comm.all_gather(res['atom_offsets']))  # [W, A + 1]
+        cap = max(1, int(all_off[:, -1].max()))
+        padded = torch.zeros((cap, 6), dtype=torch.int32, device=rows.device)
+        padded[: rows.shape[0]] = rows
+        allr = self.comm.all_gather(padded)
+        total_off, dst_start = merge_plan(np.diff(all_off, axis=1))
+        merged = dv.empty((max(int(total_off[-1]), 1), 6), torch.int32)
+        d_plan = dv.to_device(np.ascontiguousarray(np.concatenate([all_off, dst_start], axis=1)))
+        for r in range(self.world):
+            if all_off[r, -1]:
+                _lib.check(lib.gd_events_merge(dv.ptr(allr[r]), dv.ptr(d_plan[r]),
+                                               dv.ptr(d_plan[r, n_atoms + 1:]), n_atoms, dv.ptr(merged), s))
+        return merged[: int(total_off[-1])]

@@ -203,6 +203,44 @@ gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets
                           int32_t n_atoms, int64_t n_frames_total, int64_t minimal_residence,
                           const void *d_work, int32_t *d_jumps, void *stream);
 
+/* --- K3 over frame shards (no event exchange) ------------------------------------
+ * The reference runs the machine of jumps.py:45-105 over an atom's whole event list.
+ * With the frame axis sharded, every shard runs it over its own time slice of every
+ * atom; what crosses a shard boundary is the machine's state per atom, one opaque
+ * record of GD_JUMP_STATE_BYTES (pending `fromevent`, pending `candidate_jump`, and
+ * flags: shard has events of the atom / one of them is a departure, after which the
+ * state no longer depends on how the shard was entered / the state is the true one).
+ *
+ *   1. gd_jumps_count_shard(h_n_jumps = NULL) leaves in d_exit [n_atoms] every atom's record
+ *      when run from the empty state: d_entry = NULL on the shard that starts the trajectory
+ *      (empty IS its true entry), all-zero records on the others ("empty, not known");
+ *   2. the caller all-gathers the records of all shards ([world, n_atoms]);
+ *   3. gd_jumps_resolve gives this shard's true entry records and the number of
+ *      (shard, atom) pairs over ALL shards whose entry is not yet known (the same number on
+ *      every rank).  While it is > 0 (an atom with events but no departure in a shard --
+ *      rare): call gd_jumps_count_shard with the current d_entry, gather, resolve again;
+ *      at most world-1 rounds;
+ *   4. gd_jumps_count_shard(d_entry, d_published = this shard's gathered records) counts,
+ *      gd_jumps_fill writes this shard's jumps; d_atom_jump_offsets [n_atoms+1] places them
+ *      per atom when the shards' tables are merged (gd_events_merge takes any 6-int32 rows).
+ * is_last_shard: close pending candidates at n_frames_total (jumps.py:97-105) -- only the
+ * shard holding the trajectory's last frame does.  *h_flags: bit 0 the sequential chain
+ * ran, bit 1 a record published as known differs from the true exit state
+ * (event tables that are not state-consistent: fall back to exchanging the events).
+ * Every call synchronises (the time-parallel chain's proof flag is read back). */
+#define GD_JUMP_STATE_BYTES 40
+gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_offsets,
+                                 int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                 int64_t minimal_residence, const void *d_entry, int is_last_shard,
+                                 const void *d_published, void *d_work, void *d_exit,
+                                 int64_t *d_atom_jump_offsets, int64_t *h_n_jumps, int32_t *h_flags,
+                                 void *stream);
+/* d_all_records [world, n_atoms] records; d_entry [n_atoms] records out; d_unresolved one
+ * int32 of device scratch.  Synchronises. */
+gd_status_t gd_jumps_resolve(const void *d_all_records, int32_t world, int32_t rank, int32_t n_atoms,
+                             void *d_entry, int32_t *d_unresolved, int32_t *h_unresolved,
+                             void *stream);
+
 /* (start, destination) count matrix: _calculate_transitions_matrix,
  * src/gemdat/transitions.py:812-834.  d_rows [n_rows,row_stride] int32 with the
  * start site in column col_start and the destination in col_dest; d_scratch

@@ -425,6 +425,144 @@ def test_jump_machine_time_parallel_segments(mr):
     assert_array_equal(got, exp)
 
 
+def _jumps_frame_shards_via_abi(events, n_atoms, n_frames, minimal_residence, cuts):
+    """The frame-sharded K3 protocol of include/gemdat_b200.h on ONE device: the event table is
+    cut at the frame numbers ``cuts`` into time slices (each sorted by atom, time), every slice
+    runs gd_jumps_count_shard from the empty state, the per-atom records are "gathered" (stacked),
+    gd_jumps_resolve gives each slice its entry records (repeating while some are unknown), the
+    final pass counts and fills, and the slices' jumps are merged per atom.  Returns
+    (jumps, resolve rounds, OR of the mismatch flags)."""
+    import ctypes as C
+
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from gemdat_b200.pipeline import merge_plan
+
+    lib, s = _lib.lib, dv.stream_ptr()
+    nb = _lib.GD_JUMP_STATE_BYTES
+    edges = [-(1 << 40)] + list(cuts) + [1 << 40]
+    W = len(edges) - 1
+    shards = []
+    for r in range(W):
+        ev = events[(events[:, 5] >= edges[r]) & (events[:, 5] < edges[r + 1])]
+        d_ev = torch.from_numpy(np.ascontiguousarray(ev, dtype=np.int32)).cuda()
+        off = np.concatenate([[0], np.cumsum(np.bincount(ev[:, 0], minlength=n_atoms))]).astype(np.int64)
+        work = torch.empty(int(lib.gd_jumps_work_bytes(len(ev), n_atoms)), dtype=torch.uint8, device='cuda')
+        shards.append(dict(ev=d_ev, n=len(ev), off=torch.from_numpy(off).cuda(), work=work,
+                           exit=torch.zeros((n_atoms, nb), dtype=torch.uint8, device='cuda'),
+                           entry=torch.zeros((n_atoms, nb), dtype=torch.uint8, device='cuda')))
+
+    def count(r, entry, published=None, final=False):
+        sh = shards[r]
+        n, fl = C.c_int64(0), C.c_int32(0)
+        atom_off = torch.zeros(n_atoms + 1, dtype=torch.int64, device='cuda') if final else None
+        _lib.check(lib.gd_jumps_count_shard(
+            dv.ptr(sh['ev']) if sh['n'] else None, dv.ptr(sh['off']), sh['n'], n_atoms, n_frames,
+            minimal_residence, dv.ptr(entry), 1 if r == W - 1 else 0, dv.ptr(published), dv.ptr(sh['work']),
+            dv.ptr(sh['exit']), dv.ptr(atom_off), C.byref(n) if final else None,
+            C.byref(fl) if final else None, s))
+        return n.value, fl.value, atom_off
+
+    for r in range(W):  # shard 0 truly starts empty; zeroed records = "empty, not known"
+        count(r, shards[r]['entry'] if r else None)
+    scratch = torch.zeros(4, dtype=torch.int32, device='cuda')
+    published = None
+    rounds = 0
+    while True:
+        allrec = torch.stack([sh['exit'] for sh in shards]).contiguous()
+        if published is None:
+            published = allrec.clone()
+        unresolved = []
+        for r in range(W):
+            u = C.c_int32(0)
+            _lib.check(lib.gd_jumps_resolve(dv.ptr(allrec), W, r, n_atoms, dv.ptr(shards[r]['entry']),
+                                            dv.ptr(scratch), C.byref(u), s))
+            unresolved.append(u.value)
+        assert len(set(unresolved)) == 1, 'every rank must see the same number of unresolved entries'
+        rounds += 1
+        if unresolved[0] == 0:
+            break
+        assert rounds < W, 'states must resolve in at most world - 1 extra rounds'
+        for r in range(W):
+            count(r, shards[r]['entry'])
+    tables, offs, mismatch = [], [], 0
+    for r in range(W):
+        sh = shards[r]
+        n, fl, atom_off = count(r, sh['entry'], published[r].contiguous(), final=True)
+        mismatch |= fl & 2
+        out = torch.empty((max(n, 1), 6), dtype=torch.int32, device='cuda')
+        if n:
+            _lib.check(lib.gd_jumps_fill(dv.ptr(sh['ev']) if sh['n'] else None, dv.ptr(sh['off']), sh['n'],
+                                         n_atoms, n_frames, minimal_residence, dv.ptr(sh['work']),
+                                         dv.ptr(out), s))
+        tables.append(out[:n].cpu().numpy().astype(np.int64))
+        offs.append(atom_off.cpu().numpy())
+    offs = np.array(offs)
+    assert [len(t) for t in tables] == offs[:, -1].tolist()
+    total_off, dst = merge_plan(np.diff(offs, axis=1))
+    merged = np.zeros((int(total_off[-1]), 6), dtype=np.int64)
+    for r in range(W):
+        for a in range(n_atoms):
+            k = offs[r, a + 1] - offs[r, a]
+            merged[dst[r, a]: dst[r, a] + k] = tables[r][offs[r, a]: offs[r, a + 1]]
+    return merged, rounds, mismatch
+
+
+@pytest.mark.parametrize('mr', [0, 3])
+@pytest.mark.parametrize('n_shards', [2, 3, 8])
+def test_jump_machine_frame_shards(mr, n_shards):
+    """K3 over frame shards: only the machine's per-atom state crosses a shard boundary.  Atoms
+    with thousands of events per shard (one round), atoms whose shard holds events but no
+    departure (extra rounds), atoms without events in some or all shards, and candidates that
+    stay open across several shards must all give the sequential oracle's table."""
+    from oracle import jumps as ojumps
+
+    rng = np.random.default_rng(5 + 17 * mr + n_shards)
+    streams = [
+        _random_event_stream(rng, 6000, 6, 0.5),
+        _random_event_stream(rng, 4000, 3, 0.97),    # long stretches without a departure
+        _random_event_stream(rng, 40, 4, 0.9),       # a few events per shard, mostly inner-only
+        _random_event_stream(rng, 9, 4, 0.3),
+        _random_event_stream(rng, 1, 4, 0.5),
+        _random_event_stream(rng, 2500, 5, 0.6),
+    ]
+    atom_ids = [0, 1, 3, 4, 5, 7]                    # atoms 2 and 6 have no events at all
+    rows, n_frames = [], 0
+    for k, (a, (r, t_end)) in enumerate(zip(atom_ids, streams)):
+        stretch = [1, 1, 150, 700, 1, 2][k]          # sparse atoms span the whole time axis
+        rows += [(a,) + x[1:5] + (x[5] * stretch,) for x in r]
+        n_frames = max(n_frames, t_end * stretch)
+    events = np.array(rows, dtype=np.int64)
+    cuts = [n_frames * (k + 1) // n_shards for k in range(n_shards - 1)]
+    got, rounds, mismatch = _jumps_frame_shards_via_abi(events, 8, n_frames, mr, cuts)
+    exp = ojumps.transitions_to_jumps(events, n_frames, mr)
+    assert len(exp) > 50 and mismatch == 0
+    assert_array_equal(got, exp)
+    assert_array_equal(_jumps_via_abi(events, 8, n_frames, mr), exp)
+    if n_shards == 8:
+        assert rounds > 1, 'the sparse atoms should have needed a second resolve round'
+
+
+def test_jump_machine_frame_shards_flag_inconsistent_stream():
+    """Rows whose start state is not the previous destination cannot come from K2; if such a
+    table is sharded the published records may be wrong -- the final pass must either flag it
+    or still be right."""
+    from oracle import jumps as ojumps
+
+    rng = np.random.default_rng(1234)
+    flagged = wrong_unflagged = 0
+    for trial in range(6):
+        r, t_end = _random_event_stream(rng, 3000, 4, 0.5, consistent=False)
+        events = np.array(r, dtype=np.int64)
+        got, _, mismatch = _jumps_frame_shards_via_abi(events, 1, t_end, 2, [t_end // 3, 2 * t_end // 3])
+        exp = ojumps.transitions_to_jumps(events, t_end, 2)
+        if mismatch:
+            flagged += 1
+        elif not np.array_equal(got, exp):
+            wrong_unflagged += 1
+    assert wrong_unflagged == 0
+
+
 @pytest.mark.parametrize('n_frames,n_atoms', [(300, 33), (400, 65), (1000, 31), (600, 2), (260, 97), (40, 5)])
 def test_k1_strip_walker_shapes(n_frames, n_atoms):
     """Odd atom counts take the non-TMA variant (rows only 8-byte aligned), partial strips and

@@ -157,7 +157,8 @@ def test_merge_plan_places_rows_by_atom_then_shard():
 # ------------------------------------------------------------------------------------ GPU
 
 
-def _gpu_worker(rank: int, world: int, port: int, out_path: str):
+def _gpu_worker(rank: int, world: int, port: int, out_path: str, exchange: bool):
+    os.environ['GD_K3_EXCHANGE'] = '1' if exchange else '0'
     _init(rank, world, port)
     try:
         torch.cuda.set_device(0)
@@ -174,31 +175,41 @@ def _gpu_worker(rank: int, world: int, port: int, out_path: str):
             res = hp.run(torch.from_numpy(pos[f0:f1]).cuda())
         np.savez(f'{out_path}.{rank}.npz', outer=res['outer'].cpu().numpy(), inner=res['inner'].cpu().numpy(),
                  events=hp.gather_events(res).cpu().numpy(), jumps=res['jumps'].cpu().numpy(),
-                 block=np.array(res['atom_block']), local_events=res['events'].cpu().numpy())
+                 n_events=res['n_events'], layout=res['events_layout'],
+                 block=np.array(res.get('atom_block', (f0, f1))), local_events=res['events'].cpu().numpy())
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.gpu
-def test_hotpath_two_frame_shards_equal_one(tmp_path):
+@pytest.mark.parametrize('world,exchange', [(2, False), (3, False), (2, True)])
+def test_hotpath_frame_shards_equal_one(tmp_path, world, exchange):
+    """Ranks sharing cuda:0 (gloo transport) run the real kernels on their frame shards.  Default
+    route: events stay on their frame shard, only jump-machine states cross the boundaries.
+    ``exchange``: the fallback route (event rows change hands by atom block)."""
     from gemdat_b200.pipeline import HotPath
 
     out = str(tmp_path / 'rank')
-    mp.spawn(_gpu_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    mp.spawn(_gpu_worker, args=(world, _free_port(), out, exchange), nprocs=world, join=True)
     rec, pos = _small_case(n_frames=3000)
     hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=pos.shape[1], site_radius=0.9,
                  site_inner_fraction=0.5, minimal_residence=3, n_frames_total=len(pos))
     with warnings.catch_warnings():
         warnings.simplefilter('ignore')
         one = hp.run(torch.from_numpy(pos).cuda())
-    r0, r1 = np.load(f'{out}.0.npz'), np.load(f'{out}.1.npz')
-    np.testing.assert_array_equal(np.vstack([r0['outer'], r1['outer']]), one['outer'].cpu().numpy())
-    np.testing.assert_array_equal(np.vstack([r0['inner'], r1['inner']]), one['inner'].cpu().numpy())
-    for r in (r0, r1):  # every rank holds the whole merged tables
-        np.testing.assert_array_equal(r['events'], one['events'].cpu().numpy())
-        np.testing.assert_array_equal(r['jumps'], one['jumps'].cpu().numpy())
-    assert len(one['events']) > 100 and len(one['jumps']) > 0
+    ranks = [np.load(f'{out}.{r}.npz') for r in range(world)]
+    np.testing.assert_array_equal(np.vstack([r['outer'] for r in ranks]), one['outer'].cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r['inner'] for r in ranks]), one['inner'].cpu().numpy())
     ev = one['events'].cpu().numpy()
-    for r in (r0, r1):  # each rank keeps the rows of its atom block
+    assert len(ev) > 100 and len(one['jumps']) > 0
+    for r in ranks:  # every rank holds the whole jump table and can assemble the whole event table
+        np.testing.assert_array_equal(r['events'], ev)
+        np.testing.assert_array_equal(r['jumps'], one['jumps'].cpu().numpy())
+        assert int(r['n_events']) == len(ev)
         lo, hi = r['block']
-        np.testing.assert_array_equal(r['local_events'], ev[(ev[:, 0] >= lo) & (ev[:, 0] < hi)])
+        if exchange:  # each rank keeps the rows of its atom block
+            assert str(r['layout']) == 'atom_block'
+            np.testing.assert_array_equal(r['local_events'], ev[(ev[:, 0] >= lo) & (ev[:, 0] < hi)])
+        else:         # each rank keeps the rows of its frames, sorted by (atom, time)
+            assert str(r['layout']) == 'frame_shard'
+            np.testing.assert_array_equal(r['local_events'], ev[(ev[:, 5] >= lo) & (ev[:, 5] < hi)])
