@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument('--cpu-frames', type=int, default=2_000, help='frames of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-extras', action='store_true', help='skip the MSD / unwrap / density section')
+    ap.add_argument('--phases', action='store_true',
+                    help='after the timed region, run 3 more steps synchronising at phase boundaries '
+                         'and report wall ms per phase (diagnostics)')
     ap.add_argument('--msd-lags', type=int, default=2048, help='lags of the MSD section (whole job)')
     return ap.parse_args()
 
@@ -51,30 +54,69 @@ def parse_args():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    """Samples SM clock and throttle reasons DURING the timed region: NVML in-process every
+    few ms (the timed region of a 13 ms step is too short for repeated nvidia-smi calls),
+    nvidia-smi as the fallback."""
 
     QUERY = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
              'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
              'clocks_event_reasons.sw_power_cap')
+    NAMES = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
 
     def __init__(self, index: int):
         self.index = index
-        self.samples = []
+        self.samples = []  # (sm_mhz, [active reason names])
+        self.sm_max = None
+        self.source = 'nvidia-smi'
         self._stop = threading.Event()
         self._thread = threading.Thread(target=self._run, daemon=True)
+        self._nvml = None
+        try:
+            import pynvml
+            import torch
+
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(index).uuid)
+            uuid = uuid if uuid.startswith('GPU-') else 'GPU-' + uuid
+            try:
+                h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self._bits = [(getattr(pynvml, 'nvmlClocksThrottleReasonHwSlowdown', 0x8), 'hw_slowdown'),
+                          (getattr(pynvml, 'nvmlClocksThrottleReasonHwThermalSlowdown', 0x40), 'hw_thermal_slowdown'),
+                          (getattr(pynvml, 'nvmlClocksThrottleReasonSwThermalSlowdown', 0x20), 'sw_thermal_slowdown'),
+                          (getattr(pynvml, 'nvmlClocksThrottleReasonSwPowerCap', 0x4), 'sw_power_cap')]
+            self._nvml, self._h, self.source = pynvml, h, 'nvml'
+        except Exception:
+            self._nvml = None
+
+    def _sample_nvml(self):
+        n = self._nvml
+        sm = int(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM))
+        mask = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h))
+        self.samples.append((sm, [name for bit, name in self._bits if mask & bit]))
+
+    def _sample_smi(self):
+        out = subprocess.run(['nvidia-smi', f'--id={self.index}', f'--query-gpu={self.QUERY}',
+                              '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+        parts = [p.strip() for p in out.strip().split(',')]
+        if len(parts) >= 6 and parts[0].isdigit():
+            if parts[1].isdigit():
+                self.sm_max = int(parts[1])
+            self.samples.append((int(parts[0]),
+                                 [n for k, n in enumerate(self.NAMES) if parts[2 + k].lower().startswith('active')]))
 
     def _run(self):
         while not self._stop.is_set():
             try:
-                out = subprocess.run(
-                    ['nvidia-smi', f'--id={self.index}', f'--query-gpu={self.QUERY}',
-                     '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(',')]
-                if len(parts) >= 6:
-                    self.samples.append(parts)
+                if self._nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.003 if self._nvml is not None else 0.2)
 
     def __enter__(self):
         self._thread.start()
@@ -86,13 +128,11 @@ class ClockSampler:
 
     def summary(self):
         if not self.samples:
-            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unavailable']}
-        sm = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = [n for k, n in enumerate(names) if any(s[2 + k].lower().startswith('active') for s in self.samples)]
-        return {'sm_mhz': sm[len(sm) // 2] if sm else None,
-                'sm_max_mhz': int(self.samples[0][1]) if self.samples[0][1].isdigit() else None,
-                'reasons': reasons, 'samples': len(self.samples)}
+            return {'sm_mhz': None, 'sm_max_mhz': self.sm_max, 'reasons': ['unavailable']}
+        sm = sorted(s[0] for s in self.samples)
+        reasons = [n for n in self.NAMES if any(n in s[1] for s in self.samples)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': self.sm_max, 'reasons': reasons,
+                'samples': len(self.samples), 'source': self.source}
 
 
 # ------------------------------------------------------------------------------ CPU arm
@@ -370,19 +410,40 @@ def run_ours(args):
         peak = float(peaks.get('hbm_gbs', 6650.0))
         k1_bytes = 32.0 * (f1 - f0) * n_atoms
         achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
+        traffic, traffic_src = None, None
+        try:  # DRAM bytes per launch from the committed ncu --set full capture of this kernel
+            tr = json.loads((ROOT / 'profiles' / 'k1_traffic.json').read_text())
+            traffic = float(tr['dram_bytes_per_atom_frame']) * (f1 - f0) * n_atoms
+            traffic_src = tr['source']
+        except Exception:
+            pass
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
             'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
             'config': workload_config(rec, args),
             'roofline': {'bound': 'hbm', 'kernel': 'k_site_states', 'achieved': achieved, 'peak': peak,
-                         'unit': 'GB/s', 'frac': achieved / peak, 'traffic': None,
+                         'unit': 'GB/s', 'frac': achieved / peak, 'traffic': traffic,
+                         'traffic_unit': 'bytes per launch (dram read + write)', 'traffic_source': traffic_src,
+                         'algorithmic_bytes_per_launch': k1_bytes,
                          'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback',
                          'algorithmic_bytes_per_atom_frame': 32, 'launch_ms': k1_avg_ms},
             'gpu_launches': hp.launches_per_run * args.steps,
             'clocks': sampler.summary(),
             'results': {'n_events': int(res['n_events']), 'n_jumps': int(res['n_jumps'])},
         }
+
+    if args.phases:
+        hp.profile_phases = True
+        acc = {}
+        for _ in range(3):
+            barrier()
+            hp.run(pos)
+            for k, v in hp.last_phases.items():
+                acc[k] = acc.get(k, 0.0) + v / 3
+        hp.profile_phases = False
+        if rank == 0:
+            line['phases_ms'] = {k: round(v, 3) for k, v in acc.items()}
 
     extras = None
     if not args.no_extras:

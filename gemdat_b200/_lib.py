@@ -59,6 +59,10 @@ SIGNATURES = {
     'gd_sm_count': (C.c_int, []),
     'gd_sitegrid_build': (C.c_int, [_p, _p, _p, _i32, _p, _p, _i32, _p, _sz, C.POINTER(_sz)]),
     'gd_site_states': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_events_stage_cap': (_i32, [_i64, _i32]),
+    'gd_events_stage_elems': (_i64, [_i64, _i32, _i32]),
+    'gd_site_states_staged': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p]),
+    'gd_events_compact': (C.c_int, [_p, _i32, _i64, _i32, _p, _p, _p, _i64, _p, _p]),
     'gd_remap_states': (C.c_int, [_p, _i64, _p, _i32, _p]),
     'gd_widen_i32_i64': (C.c_int, [_p, _p, _i64, _p]),
     'gd_events_work_elems': (_i64, [_i64, _i32]),
@@ -70,7 +74,7 @@ SIGNATURES = {
     'gd_jumps_work_bytes': (_i64, [_i64, _i32]),
     'gd_jumps_count': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
     'gd_jumps_fill': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _p]),
-    'gd_jumps_count_shard': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.c_int, _p, _p, _p, _p,
+    'gd_jumps_count_shard': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.c_int, C.c_int, _p, _p, _p, _p,
                                        C.POINTER(_i64), C.POINTER(_i32), _p]),
     'gd_jumps_resolve': (C.c_int, [_p, _i32, _i32, _i32, _p, _p, C.POINTER(_i32), _p]),
     'gd_pair_matrix': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p]),

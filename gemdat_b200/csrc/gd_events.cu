@@ -73,13 +73,11 @@ __global__ void __launch_bounds__(256)
     int32_t po = *qo, pi = *qi;
     int cnt = 0;
     bool ch_o = false, ch_i = false;
-    // transitions t -> t+1 with both frames inside this shard
+    // transitions t -> t+1 with both frames inside this shard.  The walk is latency bound (two
+    // 128-byte requests per warp and step), so kAhead rows are fetched before they are compared.
     const int64_t t_in = min(t1, g.n_frames - 1);
-#pragma unroll 8
-    for (int64_t t = t0; t < t_in; ++t) {
-        qo += A;
-        qi += A;
-        const int32_t no = *qo, ni = *qi;
+    constexpr int kAhead = 8;
+    auto step = [&](int32_t no, int32_t ni, int64_t t) {
         const bool d_o = no != po, d_i = ni != pi;
         if (d_o | d_i) {
             if (kFill) put_event(events, row++, a, po, no, pi, ni, (int32_t)(frame0 + t));
@@ -89,6 +87,24 @@ __global__ void __launch_bounds__(256)
         ch_i |= d_i;
         po = no;
         pi = ni;
+    };
+    int64_t t = t0;
+    for (; t + kAhead <= t_in; t += kAhead) {
+        int32_t vo[kAhead], vi[kAhead];
+#pragma unroll
+        for (int j = 0; j < kAhead; ++j) {
+            vo[j] = __ldcs(qo + (int64_t)(j + 1) * A);
+            vi[j] = __ldcs(qi + (int64_t)(j + 1) * A);
+        }
+        qo += kAhead * A;
+        qi += kAhead * A;
+#pragma unroll
+        for (int j = 0; j < kAhead; ++j) step(vo[j], vi[j], t + j);
+    }
+    for (; t < t_in; ++t) {
+        qo += A;
+        qi += A;
+        step(__ldcs(qo), __ldcs(qi), t);
     }
     // last frame of the shard: needs the first row of the following shard; without one the
     // np.roll wrap-around pseudo event of the reference is dropped (transitions.py:439-452)
@@ -106,6 +122,35 @@ __global__ void __launch_bounds__(256)
         work[(int64_t)a * g.n_chunks + c] = cnt;
         if (ch_o) changed[a] = 1;
         if (ch_i) changed[A + a] = 1;
+    }
+}
+
+// Staged event rows (written by K1 as it found them, [chunk, atom, cap] rows) -> the table.
+// kLanes lanes copy one (chunk, atom) segment: its rows are contiguous on both sides, so the copy
+// moves 8-byte words with coalesced pieces of kLanes * 8 bytes; the shard's first frame is added
+// to the time column on the way.
+constexpr int kCompactLanes = 16;
+__global__ void __launch_bounds__(256)
+    k_events_compact(const int2 *__restrict__ stage, int32_t cap, Geometry g,
+                     const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
+                     const int64_t *__restrict__ atom_offsets, int32_t frame0,
+                     int2 *__restrict__ events) {
+    const int64_t item = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / kCompactLanes;
+    const int sub = threadIdx.x % kCompactLanes;
+    if (item >= g.n_chunks * g.n_atoms) return;
+    const int64_t c = item / g.n_atoms;
+    const int32_t a = (int32_t)(item - c * g.n_atoms);
+    if (!changed_global[a]) return;  // outer state never changes: atom is skipped
+    const int32_t *w = work + (int64_t)a * g.n_chunks + c;
+    const int32_t first = w[0];
+    const int32_t last = (c + 1 < g.n_chunks) ? w[1] : (int32_t)(atom_offsets[a + 1] - atom_offsets[a]);
+    const int n_words = 3 * (last - first);
+    const int2 *src = stage + item * (int64_t)cap * 3;
+    int2 *dst = events + (atom_offsets[a] + first) * 3;
+    for (int k = sub; k < n_words; k += kCompactLanes) {
+        int2 v = __ldcs(src + k);
+        if (k % 3 == 2) v.y += frame0;  // (destination inner site, time)
+        dst[k] = v;
     }
 }
 
@@ -335,6 +380,28 @@ extern "C" gd_status_t gd_events_fill(const int32_t *d_states_outer, const int32
     k_events<true><<<blocks_for(items, 256), 256, 0, (cudaStream_t)stream>>>(
         d_states_outer, d_states_inner, g, d_next_outer, d_next_inner,
         const_cast<int32_t *>(d_work), nullptr, d_changed_global, d_atom_offsets, frame0, d_events);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_cap, int64_t n_frames,
+                                         int32_t n_atoms, const int32_t *d_work,
+                                         const uint8_t *d_changed_global,
+                                         const int64_t *d_atom_offsets, int64_t frame0,
+                                         int32_t *d_events, void *stream) {
+    GD_REQUIRE(d_stage && d_work && d_changed_global && d_atom_offsets && d_events, GD_ERR_INVALID,
+               "gd_events_compact: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0 && stage_cap > 0, GD_ERR_INVALID,
+               "gd_events_compact: empty input");
+    GD_REQUIRE(((reinterpret_cast<uintptr_t>(d_stage) | reinterpret_cast<uintptr_t>(d_events)) & 7) == 0,
+               GD_ERR_ALIGNMENT, "gd_events_compact: tables must be 8-byte aligned");
+    GD_REQUIRE(frame0 >= 0 && frame0 + n_frames < (int64_t(1) << 31), GD_ERR_INVALID,
+               "gd_events_compact: frame numbers must fit int32");
+    Geometry g = geometry(n_frames, n_atoms);
+    const int64_t threads = g.n_chunks * g.n_atoms * kCompactLanes;
+    k_events_compact<<<blocks_for(threads, 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const int2 *>(d_stage), stage_cap, g, d_work, d_changed_global,
+        d_atom_offsets, (int32_t)frame0, reinterpret_cast<int2 *>(d_events));
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

@@ -6,7 +6,7 @@
 //
 // The conversion is a per-atom sequential state machine over that atom's events
 // (already contiguous and time-ordered in the K2 table).  Atoms run in parallel, and so
-// do segments of 512 events of the same atom (speculate / chain / fill, see below).
+// do segments of 128 events of the same atom (speculate / chain / fill, see below).
 // Two phases (count, fill) give the exact output size without any allocation in the
 // library.
 #include <stdlib.h>
@@ -94,7 +94,8 @@ struct JumpMachine {
 //      each segment from its true entry state and writes its jumps in place.
 // Output order = segment order = (atom, time), exactly the reference's.
 
-constexpr int kSeg = 512;  // event rows per segment
+constexpr int kSeg = 128;  // event rows per segment
+constexpr int kBatch = 8;  // rows fetched ahead of the machine
 
 struct PackedState {  // 40 bytes == GD_JUMP_STATE_BYTES
     int32_t have;  // bit 0: from pending, bit 1: candidate pending
@@ -231,12 +232,23 @@ __global__ void __launch_bounds__(128)
     int sync = n, n_after = 0;
     bool synced = false;
     auto emit = [&](const Jump &) { n_after += synced ? 1 : 0; };
-    for (int k = 0; k < n; ++k) {
-        const Row e = load_row(events, r0 + k);
-        m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
-        if (!synced && e.s0 != GD_NOSITE && e.s0 != e.s1) {
-            synced = true;
-            sync = k + 1;
+    // rows do not depend on the machine: fetch kBatch of them before stepping (the walk is
+    // latency bound, one thread per segment)
+    for (int k0 = 0; k0 < n; k0 += kBatch) {
+        Row rows[kBatch];
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) rows[j] = load_row(events, r0 + min(k0 + j, n - 1));
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+            const int k = k0 + j;
+            if (k < n) {
+                const Row e = rows[j];
+                m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+                if (!synced && e.s0 != GD_NOSITE && e.s0 != e.s1) {
+                    synced = true;
+                    sync = k + 1;
+                }
+            }
         }
     }
     SegSpec out;
@@ -392,7 +404,9 @@ __global__ void __launch_bounds__(128)
     const int64_t out0 = counts[seg], out1 = counts[seg + 1];  // exclusive offsets after the scan
     if (out1 == out0) return;
     JumpMachine m(minimal_residence);
-    unpack(m, entry[seg], atom);
+    // `atom` is the index inside this table (an atom block after the event exchange); jump rows
+    // carry the atom index of the event rows, also for a candidate inherited from the entry state
+    unpack(m, entry[seg], n > 0 ? __ldg(events + r0 * 6) : atom);
     int64_t out = out0;
     auto emit = [&](const Jump &j) {
         int2 *o = reinterpret_cast<int2 *>(jumps + out * 6);
@@ -401,42 +415,82 @@ __global__ void __launch_bounds__(128)
         o[2] = make_int2(j.stop_time, j.residence);
         ++out;
     };
-    for (int k = 0; k < n && out < out1; ++k) {
-        const Row e = load_row(events, r0 + k);
-        m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+    for (int k0 = 0; k0 < n && out < out1; k0 += kBatch) {
+        Row rows[kBatch];
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) rows[j] = load_row(events, r0 + min(k0 + j, n - 1));
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+            const Row e = rows[j];
+            if (k0 + j < n && out < out1) m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+        }
     }
     const bool last_of_atom = r0 + n == atom_offsets[atom + 1];
     // shard_flag[2]: this is the trajectory's last frame shard (left by the count call)
     if (last_of_atom && shard_flag[2] != 0 && m.have_cand && out < out1) m.close_candidate(n_frames_total, emit);
 }
 
-// single block exclusive scan, c[0..n) -> offsets, c[n] = total
-__global__ void __launch_bounds__(1024) k_scan_counts(int64_t *__restrict__ c, int64_t n) {
-    __shared__ int64_t warp_tot[32];
-    __shared__ int64_t running_s;
-    if (threadIdx.x == 0) running_s = 0;
-    __syncthreads();
+// exclusive scan, c[0..n) -> offsets, c[n] = total.  Two launches: every block scans its tile of
+// kScanTile items in place and leaves the tile total; then every block adds the totals of the tiles
+// before it (a few hundred values at most, summed redundantly per block).
+constexpr int kScanItems = 4;
+constexpr int kScanTile = 1024 * kScanItems;
+
+__device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t *warp_tot, int64_t &total) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int64_t base = 0; base < n; base += 1024) {
-        const int64_t idx = base + threadIdx.x;
-        const int64_t v = idx < n ? c[idx] : 0;
-        int64_t incl = v;
+    int64_t incl = v;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            int64_t t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += t;
-        }
-        if (lane == 31) warp_tot[warp] = incl;
-        __syncthreads();
-        int64_t warp_base = 0;
-        for (int w = 0; w < warp; ++w) warp_base += warp_tot[w];
-        const int64_t running = running_s;
-        __syncthreads();
-        if (idx < n) c[idx] = running + warp_base + incl - v;
-        if (threadIdx.x == 1023) running_s = running + warp_base + incl;
-        __syncthreads();
+    for (int o = 1; o < 32; o <<= 1) {
+        int64_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
     }
-    if (threadIdx.x == 0) c[n] = running_s;
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    int64_t wv = lane < (int)(blockDim.x >> 5) ? warp_tot[lane] : 0;
+    int64_t wincl = wv;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int64_t t = __shfl_up_sync(0xffffffffu, wincl, o);
+        if (lane >= o) wincl += t;
+    }
+    total = __shfl_sync(0xffffffffu, wincl, 31);
+    const int64_t warp_base = __shfl_sync(0xffffffffu, wincl - wv, warp);
+    __syncthreads();
+    return warp_base + incl - v;
+}
+
+__global__ void __launch_bounds__(1024)
+    k_scan_tiles(int64_t *__restrict__ c, int64_t n, int64_t *__restrict__ tile_tot) {
+    __shared__ int64_t warp_tot[32];
+    const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+    int64_t v[kScanItems], sum = 0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; ++j) {
+        v[j] = base + j < n ? c[base + j] : 0;
+        sum += v[j];
+    }
+    int64_t total;
+    int64_t excl = block_exclusive_scan(sum, warp_tot, total);
+#pragma unroll
+    for (int j = 0; j < kScanItems; ++j) {
+        if (base + j < n) c[base + j] = excl;
+        excl += v[j];
+    }
+    if (threadIdx.x == 0) tile_tot[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024)
+    k_scan_add(int64_t *__restrict__ c, int64_t n, const int64_t *__restrict__ tile_tot) {
+    __shared__ int64_t warp_tot[32];
+    int64_t part = 0;  // totals of the tiles before this one
+    for (int64_t b = threadIdx.x; b < blockIdx.x; b += 1024) part += tile_tot[b];
+    int64_t before;
+    block_exclusive_scan(part, warp_tot, before);
+    const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanItems;
+#pragma unroll
+    for (int j = 0; j < kScanItems; ++j)
+        if (base + j < n) c[base + j] += before;
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) c[n] = before + tile_tot[blockIdx.x];
 }
 
 // scratch layout inside the caller's d_work (all 16-byte aligned)
@@ -449,6 +503,7 @@ struct JumpWork {
     int32_t *flag;       // [4]: [0] parallel chain could not prove a segment's entry state,
                          //      [1] a published shard record differs from the true exit, [2] is_last_shard
     int32_t *atom_flags; // [n_atoms]: kHasEvents | kSynced of this shard's events per atom
+    int64_t *tile_tot;   // [max_segs / kScanTile + 1] scan tile totals
     size_t bytes;
 };
 inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
@@ -469,6 +524,8 @@ inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
     off += 16;
     w.atom_flags = reinterpret_cast<int32_t *>(p + off);
     off += up((size_t)n_atoms * 4);
+    w.tile_tot = reinterpret_cast<int64_t *>(p + off);
+    off += up((size_t)(w.max_segs / kScanTile + 1) * 8);
     w.bytes = off;
     return w;
 }
@@ -566,7 +623,8 @@ __global__ void __launch_bounds__(256)
 extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_offsets,
                                             int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
                                             int64_t minimal_residence, const void *d_entry,
-                                            int is_last_shard, const void *d_published, void *d_work,
+                                            int is_last_shard, int reuse_work, const void *d_published,
+                                            void *d_work,
                                             void *d_exit, int64_t *d_atom_jump_offsets,
                                             int64_t *h_n_jumps, int32_t *h_flags, void *stream) {
     GD_REQUIRE(d_atom_offsets && d_work, GD_ERR_INVALID, "gd_jumps_count: null argument");
@@ -580,12 +638,14 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
     const JumpWork w = jump_work(d_work, n_events, n_atoms);
     const PackedState *entry = static_cast<const PackedState *>(d_entry);
     PackedState *exit_rec = static_cast<PackedState *>(d_exit);
-    k_seg_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms, w.seg_off);
-    GD_LAUNCH_CHECK();
-    GD_CUDA_CHECK(cudaMemsetAsync(w.atom_flags, 0, (size_t)n_atoms * 4, st));
-    k_jumps_spec<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
-        d_events, d_atom_offsets, w.seg_off, n_atoms, minimal_residence, w.spec, w.atom_flags);
-    GD_LAUNCH_CHECK();
+    if (!reuse_work) {  // segment bookkeeping + speculation: independent of the entry records
+        k_seg_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms, w.seg_off);
+        GD_LAUNCH_CHECK();
+        GD_CUDA_CHECK(cudaMemsetAsync(w.atom_flags, 0, (size_t)n_atoms * 4, st));
+        k_jumps_spec<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
+            d_events, d_atom_offsets, w.seg_off, n_atoms, minimal_residence, w.spec, w.atom_flags);
+        GD_LAUNCH_CHECK();
+    }
     GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
     const int32_t flags0[4] = {0, 0, is_last_shard ? 1 : 0, 0};
     GD_CUDA_CHECK(cudaMemcpyAsync(w.flag, flags0, 16, cudaMemcpyHostToDevice, st));
@@ -604,7 +664,10 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
                 w.spec, w.entry, w.counts, w.flag, entry, exit_rec, w.atom_flags, is_last_shard);
         }
         GD_LAUNCH_CHECK();
-        k_scan_counts<<<1, 1024, 0, st>>>(w.counts, w.max_segs);
+        const unsigned n_tiles = (unsigned)gd_ceil_div(w.max_segs, kScanTile);
+        k_scan_tiles<<<n_tiles, 1024, 0, st>>>(w.counts, w.max_segs, w.tile_tot);
+        GD_LAUNCH_CHECK();
+        k_scan_add<<<n_tiles, 1024, 0, st>>>(w.counts, w.max_segs, w.tile_tot);
         GD_LAUNCH_CHECK();
         if (h_n_jumps)
             GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
@@ -640,7 +703,7 @@ extern "C" gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_
                                       void *stream) {
     GD_REQUIRE(h_n_jumps, GD_ERR_INVALID, "gd_jumps_count: null argument");
     return gd_jumps_count_shard(d_events, d_atom_offsets, n_events, n_atoms, n_frames_total,
-                                minimal_residence, nullptr, 1, nullptr, d_work, nullptr, nullptr,
+                                minimal_residence, nullptr, 1, 0, nullptr, d_work, nullptr, nullptr,
                                 h_n_jumps, nullptr, stream);
 }
 

@@ -153,6 +153,9 @@ struct StatesParams {
     unsigned long long *band;
     int32_t *work;     // [n_atoms, n_chunks] event counts, or null
     uint8_t *changed;  // [2*n_atoms]
+    int32_t *stage;    // [n_chunks, n_atoms, stage_cap, 6] event rows as they are found, or null
+    int32_t *overflow; // set when a (chunk, atom) segment holds more than stage_cap events
+    int32_t stage_cap;
     int32_t n_sites_total;
     int32_t n_groups;
     int32_t dims[3];
@@ -415,6 +418,15 @@ __global__ void __launch_bounds__(kThreads, 3)
         cache.excl2 = -1.0;
         cache.natgrp = 0;
 
+        // event rows leave in the same pass (K2's fill then never re-reads the states): this
+        // lane's staging region for the chunk, and the frame of the row being processed
+        int2 *stage_row = nullptr;
+        if (p.stage != nullptr && lane_on)
+            stage_row = reinterpret_cast<int2 *>(p.stage) +
+                        (chunk * p.n_atoms + a) * (int64_t)p.stage_cap * 3;
+        const int stage_cap = p.stage_cap;
+        int32_t t_cur = (int32_t)t0;
+
         auto process = [&](double f0, double f1, double f2, bool own) {
             Staged st = stage_atom<kDiag>(p, f0, f1, f2);
             int32_t so, si;
@@ -436,7 +448,17 @@ __global__ void __launch_bounds__(kThreads, 3)
             const bool d_o = so != prev_o, d_i = si != prev_i;
             if (d_o) ++n_do;
             if (d_i) ++n_di;
-            if (d_o | d_i) ++cnt;
+            if (d_o | d_i) {
+                // cnt counts the chunk's first row as a pseudo event: real event k is cnt == k + 1
+                if (stage_row != nullptr && cnt >= 1 && cnt <= stage_cap) {
+                    int2 *e = stage_row + 3 * (cnt - 1);
+                    e[0] = make_int2(a, prev_o);
+                    e[1] = make_int2(so, prev_i);
+                    e[2] = make_int2(si, t_cur - 1);
+                }
+                ++cnt;
+            }
+            ++t_cur;
             // a site is visited when a state switches to it (or in mark_all_hits when several
             // sites contain the atom at once)
             if (vis_mode == 1) {
@@ -520,6 +542,7 @@ __global__ void __launch_bounds__(kThreads, 3)
             p.work[(int64_t)a * p.n_chunks + chunk] = cnt - 1;
             if (n_do > 1) p.changed[a] = 1;
             if (n_di > 1) p.changed[p.n_atoms + a] = 1;
+            if (stage_row != nullptr && cnt - 1 > stage_cap) *p.overflow = 1;
         }
     }
 
@@ -890,6 +913,34 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames
                                       int32_t *d_states_inner, uint8_t *d_visited,
                                       unsigned long long *d_band_counts, int32_t *d_event_work,
                                       uint8_t *d_changed, void *stream) {
+    return gd_site_states_staged(d_pos_frac, n_frames, n_atoms, d_next_pos_row, d_blob, h_blob,
+                                 d_states_outer, d_states_inner, d_visited, d_band_counts,
+                                 d_event_work, d_changed, nullptr, 0, nullptr, stream);
+}
+
+extern "C" int32_t gd_events_stage_cap(int64_t n_frames, int32_t n_atoms) {
+    if (n_frames <= 0 || n_atoms <= 0) return 0;
+    const int32_t f = gd_chunks(n_frames, n_atoms).f;
+    return f / 4 > 8 ? f / 4 : 8;  // room for one event every 4th frame of every atom
+}
+
+extern "C" int64_t gd_events_stage_elems(int64_t n_frames, int32_t n_atoms, int32_t stage_cap) {
+    if (n_frames <= 0 || n_atoms <= 0 || stage_cap <= 0) return 0;
+    return gd_chunks(n_frames, n_atoms).n_chunks * (int64_t)n_atoms * stage_cap * 6;
+}
+
+extern "C" gd_status_t gd_site_states_staged(const double *d_pos_frac, int64_t n_frames,
+                                             int32_t n_atoms, const double *d_next_pos_row,
+                                             const void *d_blob, const void *h_blob,
+                                             int32_t *d_states_outer, int32_t *d_states_inner,
+                                             uint8_t *d_visited, unsigned long long *d_band_counts,
+                                             int32_t *d_event_work, uint8_t *d_changed,
+                                             int32_t *d_stage, int32_t stage_cap,
+                                             int32_t *d_overflow, void *stream) {
+    GD_REQUIRE(d_stage == nullptr || (d_event_work && d_overflow && stage_cap > 0), GD_ERR_INVALID,
+               "gd_site_states_staged: staging needs d_event_work, d_overflow and a positive capacity");
+    GD_REQUIRE((reinterpret_cast<uintptr_t>(d_stage) & 7) == 0, GD_ERR_ALIGNMENT,
+               "gd_site_states_staged: d_stage must be 8-byte aligned");
     GD_REQUIRE(d_pos_frac && d_blob && h_blob && d_states_outer && d_states_inner, GD_ERR_INVALID,
                "gd_site_states: null argument");
     GD_REQUIRE(n_frames >= 0 && n_atoms > 0, GD_ERR_INVALID, "gd_site_states: bad size");
@@ -943,6 +994,9 @@ extern "C" gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames
     p.band = d_band_counts;
     p.work = d_event_work;
     p.changed = d_changed;
+    p.stage = d_stage;
+    p.stage_cap = stage_cap;
+    p.overflow = d_overflow;
     p.n_sites_total = h->n_sites_total;
     p.n_groups = h->n_groups;
     p.cutoff32 = h->cutoff32;

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import time
 import warnings
 
 import numpy as np
@@ -140,6 +141,14 @@ class HotPath:
         self.last_k1_events = None
         # GD_K3_EXCHANGE=1: always exchange the event rows by atom block (the fallback route; A/B)
         self.k3_exchange = os.environ.get('GD_K3_EXCHANGE', '0') not in ('', '0')
+        # profile_phases: synchronise at phase boundaries and keep wall-clock ms per phase in
+        # `last_phases` (diagnostics only; the timed runs leave it off)
+        # GD_EVENTS_STAGED=0: K2 re-reads the state arrays (gd_events_fill) instead of compacting
+        # rows staged by K1 (A/B; also the route taken when a staging segment overflows)
+        self.stage_events = os.environ.get('GD_EVENTS_STAGED', '1') not in ('', '0')
+        self.last_events_route = 'none'
+        self.profile_phases = False
+        self.last_phases = {}
         self._buf = {}
 
     # ------------------------------------------------------------------ helpers
@@ -152,6 +161,14 @@ class HotPath:
 
     def _all_gather(self, t: torch.Tensor) -> torch.Tensor:
         return self.comm.all_gather(t)
+
+    def _mark(self, name: str) -> None:
+        if not self.profile_phases:
+            return
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        self.last_phases[name] = self.last_phases.get(name, 0.0) + 1e3 * (now - self._t_mark)
+        self._t_mark = now
 
     # ------------------------------------------------------------------ the pass
     def run(self, pos: torch.Tensor) -> dict:
@@ -171,6 +188,9 @@ class HotPath:
         # state of the next shard's first frame: positions are known up front, so the halo ROW OF
         # POSITIONS is exchanged before K1 and its state recomputed locally -- K1 never waits for
         # a neighbour's kernel.
+        if self.profile_phases:
+            torch.cuda.synchronize()
+            self.last_phases, self._t_mark = {}, time.perf_counter()
         next_pos = None
         if self.world > 1:
             first_rows = self._all_gather(pos[0].contiguous())  # [W, A, 3]
@@ -179,15 +199,28 @@ class HotPath:
         work = self._tensor('work', (int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
         changed = self._tensor('changed', (2 * n_atoms,), torch.uint8)
         changed.zero_()
+        self._mark('halo_positions')
+        # K1 also leaves the event rows themselves in a staging area ([chunk, atom, cap] rows), so
+        # that K2 only compacts them instead of re-reading 8 B/atom-frame of states
+        stage = overflow = None
+        cap = 0
+        if self.stage_events:  # GD_EVENTS_STAGE_CAP overrides the default rows per (chunk, atom) segment
+            cap = int(os.environ.get('GD_EVENTS_STAGE_CAP', '0')) or int(lib.gd_events_stage_cap(n_frames, n_atoms))
+        if cap > 0:
+            stage = self._tensor('stage', (int(lib.gd_events_stage_elems(n_frames, n_atoms, cap)),), torch.int32)
+            overflow = self._tensor('overflow', (1,), torch.int32)
+            overflow.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        _lib.check(lib.gd_site_states(dv.ptr(pos), n_frames, n_atoms, dv.ptr(next_pos),
-                                      dv.ptr(self.grid.d_blob), self.grid.h_blob.ctypes.data,
-                                      dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band),
-                                      dv.ptr(work), dv.ptr(changed), s))
+        _lib.check(lib.gd_site_states_staged(dv.ptr(pos), n_frames, n_atoms, dv.ptr(next_pos),
+                                             dv.ptr(self.grid.d_blob), self.grid.h_blob.ctypes.data,
+                                             dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band),
+                                             dv.ptr(work), dv.ptr(changed), dv.ptr(stage), cap,
+                                             dv.ptr(overflow), s))
         e1.record()
         self.last_k1_events = (e0, e1)
         launches += 1
+        self._mark('k1_site_states')
 
         # ---- what K2 needs from the other shards, in ONE exchange: the OR of the visited flags
         # (warning + Q2 LUT are global), the OR of the "state ever changes" flags (Q4 "atom is
@@ -196,9 +229,13 @@ class HotPath:
         next_o = next_i = None
         if self.world > 1:
             next_o, next_i = self._exchange_after_k1(visited, changed, outer, inner)
-        host = dv.to_host(torch.cat([visited, changed[:n_atoms].amax().reshape(1)]))
-        vis = host[:-1].astype(bool).reshape(2, self.n_sites)
-        any_outer_change = bool(host[-1])
+        flags = [visited, changed[:n_atoms].amax().reshape(1)]
+        if overflow is not None:
+            flags.append(overflow.to(torch.uint8))
+        host = dv.to_host(torch.cat(flags))
+        vis = host[: 2 * self.n_sites].astype(bool).reshape(2, self.n_sites)
+        any_outer_change = bool(host[2 * self.n_sites])
+        staged_ok = overflow is not None and not bool(host[-1])
         remapped = False
         for arr, v in ((outer, vis[0]), (inner, vis[1])):
             for label, key in zip(self.grid.group_labels, self.grid.group_keys):
@@ -216,6 +253,7 @@ class HotPath:
             if self.rank + 1 < self.world:
                 next_o, next_i = rows[self.rank + 1, 0].contiguous(), rows[self.rank + 1, 1].contiguous()
 
+        self._mark('flags_exchange')
         # ---- K2: scan + fill (the fill writes the halo event with the neighbour's first states)
         offsets = self._tensor('offsets', (n_atoms + 1,), torch.int64)
         n_events = C.c_int64(0)
@@ -229,12 +267,22 @@ class HotPath:
         if not any_outer_change:
             raise ValueError('need at least one array to concatenate')
         rows = dv.empty((max(n_events.value, 1), 6), torch.int32)
-        if n_events.value:
+        self.last_events_route = 'none'
+        if n_events.value and staged_ok and not remapped:
+            _lib.check(lib.gd_events_compact(dv.ptr(stage), cap, n_frames, n_atoms, dv.ptr(work),
+                                             dv.ptr(changed), dv.ptr(offsets), self.frame0, dv.ptr(rows), s))
+            launches += 1
+            self.last_events_route = 'staged'
+        elif n_events.value:
+            # a segment overflowed its staging rows, or the Q2 remap changed the states after K1:
+            # take the rows from the state arrays
             _lib.check(lib.gd_events_fill(dv.ptr(outer), dv.ptr(inner), n_frames, n_atoms, dv.ptr(next_o),
                                           dv.ptr(next_i), dv.ptr(work), dv.ptr(changed), dv.ptr(offsets),
                                           self.frame0, dv.ptr(rows), s))
             launches += 1
+            self.last_events_route = 'reread'
         rows = rows[: n_events.value]
+        self._mark('k2_events')
 
         # ---- K3.  Frame shards hold time slices of every atom while the jump machine is
         # sequential along an atom's history.  Its state forgets the past at every departure
@@ -260,6 +308,7 @@ class HotPath:
                 res.update(events=rows, atom_offsets=offsets, events_layout='atom_block',
                            atom_block=(a_lo, a_hi), jumps=jumps, n_events=n_events_global)
         launches += k3_launches
+        self._mark('k3_jumps')
         res['n_jumps'] = int(res['jumps'].shape[0])
         self.launches_per_run = launches
         return res
@@ -326,7 +375,7 @@ class HotPath:
         # pass 1: every atom's exit record when the slice is run from the empty state
         # (rank 0 really starts from the empty state; for the others all-zero records say "empty, not known")
         entry.zero_()
-        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if me else None, last, None, dv.ptr(jwork),
+        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if me else None, last, 0, None, dv.ptr(jwork),
                                             dv.ptr(exit_rec), None, None, None, s))
         launches += 4
         published = None
@@ -342,7 +391,7 @@ class HotPath:
                 break
             # some shard has events of an atom but no departure among them: its exit depends on
             # its entry.  Run again from what is known so far; every round settles one more shard.
-            _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, None, dv.ptr(jwork),
+            _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, 1, None, dv.ptr(jwork),
                                                 dv.ptr(exit_rec), None, None, None, s))
             launches += 4
         else:
@@ -350,10 +399,10 @@ class HotPath:
         # final pass from the true entry states
         atom_off = self._tensor('jatom_off', (n_atoms + 2,), torch.int64)
         n_jumps, flags = C.c_int64(0), C.c_int32(0)
-        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, dv.ptr(published), dv.ptr(jwork),
+        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, 1, dv.ptr(published), dv.ptr(jwork),
                                             dv.ptr(exit_rec), dv.ptr(atom_off), C.byref(n_jumps),
                                             C.byref(flags), s))
-        launches += 6
+        launches += 5
         jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
         if n_jumps.value:
             _lib.check(lib.gd_jumps_fill(*args, dv.ptr(jwork), dv.ptr(jumps), s))

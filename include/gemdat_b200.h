@@ -114,6 +114,28 @@ gd_status_t gd_site_states(const double *d_pos_frac, int64_t n_frames, int32_t n
                            unsigned long long *d_band_counts, int32_t *d_event_work,
                            uint8_t *d_changed, void *stream);
 
+/* gd_site_states that also writes the event ROWS as it finds them, so that K2 never re-reads
+ * the 8 B/atom-frame of states (gd_events_compact instead of gd_events_fill).
+ *  d_stage     gd_events_stage_elems(n_frames, n_atoms, stage_cap) int32, 8-byte aligned,
+ *              uninitialised: [frame chunk, atom, stage_cap] rows of 6 int32 in the reference's
+ *              column order (transitions.py:455-468), time relative to this shard's first frame;
+ *              only the first (event count) rows of a segment are written.
+ *  stage_cap   rows per (frame chunk, atom) segment; gd_events_stage_cap gives the default
+ *              (a quarter of the chunk's frames).
+ *  d_overflow  one int32, zero-initialised: set when some segment holds more events than
+ *              stage_cap (then use gd_events_fill, which is always valid).
+ * The staged rows carry the states as written here: when gd_remap_states changes them
+ * afterwards, use gd_events_fill. */
+int32_t gd_events_stage_cap(int64_t n_frames, int32_t n_atoms);
+int64_t gd_events_stage_elems(int64_t n_frames, int32_t n_atoms, int32_t stage_cap);
+gd_status_t gd_site_states_staged(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                                  const double *d_next_pos_row, const void *d_blob,
+                                  const void *h_blob, int32_t *d_states_outer,
+                                  int32_t *d_states_inner, uint8_t *d_visited,
+                                  unsigned long long *d_band_counts, int32_t *d_event_work,
+                                  uint8_t *d_changed, int32_t *d_stage, int32_t stage_cap,
+                                  int32_t *d_overflow, void *stream);
+
 /* integer_remap quirk (src/gemdat/utils.py:101-125 via transitions.py:804-805):
  * d_lut [n_sites] int32 maps the natural site index to the index the reference
  * reports; applied in place.  Only needed when a labelled group has a site that
@@ -171,6 +193,15 @@ gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom
                             const int64_t *d_dst_start, int32_t n_atoms, int32_t *d_dst_rows,
                             void *stream);
 
+/* The fill for rows staged by gd_site_states_staged: copies every (frame chunk, atom)
+ * segment's rows to their place in the table (same layout and order as gd_events_fill) and
+ * adds frame0 to the time column.  d_work / d_changed_global / d_atom_offsets as left by
+ * gd_events_scan.  Moves 2 x 24 B per event instead of re-reading 8 B per atom-frame. */
+gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_cap, int64_t n_frames,
+                              int32_t n_atoms, const int32_t *d_work,
+                              const uint8_t *d_changed_global, const int64_t *d_atom_offsets,
+                              int64_t frame0, int32_t *d_events, void *stream);
+
 /* ffill (direction=+1, states_prev) / bfill (direction=-1, states_next) along the
  * frame axis.  d_carry_in [n_atoms] (may be NULL) is the last valid state before
  * (after, for bfill) this shard; d_carry_out [n_atoms] (may be NULL) receives the
@@ -227,12 +258,14 @@ gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets
  * shard holding the trajectory's last frame does.  *h_flags: bit 0 the sequential chain
  * ran, bit 1 a record published as known differs from the true exit state
  * (event tables that are not state-consistent: fall back to exchanging the events).
- * Every call synchronises (the time-parallel chain's proof flag is read back). */
+ * reuse_work != 0: d_work still holds the segment speculation of an earlier call on the same
+ * table (passes 2.. of the protocol skip it).  Every call synchronises (the time-parallel
+ * chain's proof flag is read back). */
 #define GD_JUMP_STATE_BYTES 40
 gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_offsets,
                                  int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
                                  int64_t minimal_residence, const void *d_entry, int is_last_shard,
-                                 const void *d_published, void *d_work, void *d_exit,
+                                 int reuse_work, const void *d_published, void *d_work, void *d_exit,
                                  int64_t *d_atom_jump_offsets, int64_t *h_n_jumps, int32_t *h_flags,
                                  void *stream);
 /* d_all_records [world, n_atoms] records; d_entry [n_atoms] records out; d_unresolved one

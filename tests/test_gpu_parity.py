@@ -345,15 +345,17 @@ def test_c3_shape_properties_and_window_parity():
     assert int(tr.jumps().matrix().sum()) == len(jumps)
 
 
-def _jumps_via_abi(events: np.ndarray, n_atoms: int, n_frames: int, minimal_residence: int) -> np.ndarray:
-    """gd_jumps_count / gd_jumps_fill on a raw [E, 6] event table (sorted by atom, time)."""
+def _jumps_via_abi(events: np.ndarray, n_atoms: int, n_frames: int, minimal_residence: int,
+                   atom_base: int = 0) -> np.ndarray:
+    """gd_jumps_count / gd_jumps_fill on a raw [E, 6] event table (sorted by atom, time).
+    ``atom_base``: the table is an atom block whose first atom has that global index."""
     import ctypes as C
 
     from gemdat_b200 import _device as dv
     from gemdat_b200 import _lib
 
     ev = torch.from_numpy(np.ascontiguousarray(events, dtype=np.int32)).cuda()
-    counts = np.bincount(events[:, 0], minlength=n_atoms)
+    counts = np.bincount(events[:, 0] - atom_base, minlength=n_atoms)
     off = torch.from_numpy(np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)).cuda()
     work = torch.empty(int(_lib.lib.gd_jumps_work_bytes(len(events), n_atoms)), dtype=torch.uint8, device='cuda')
     n = C.c_int64(0)
@@ -425,6 +427,23 @@ def test_jump_machine_time_parallel_segments(mr):
     assert_array_equal(got, exp)
 
 
+def test_jump_rows_of_an_atom_block_keep_global_atom_index():
+    """After the event exchange a rank holds an atom BLOCK (block-local offsets, global atom
+    column); candidates inherited across a segment boundary must still report the global index."""
+    from oracle import jumps as ojumps
+
+    rng = np.random.default_rng(77)
+    rows = []
+    for a in (24, 25, 26):
+        r, t_end = _random_event_stream(rng, 1500, 5, 0.5)
+        rows += [(a,) + x[1:] for x in r]
+    events = np.array(rows, dtype=np.int64)
+    n_frames = int(events[:, 5].max()) + 2
+    exp = ojumps.transitions_to_jumps(events, n_frames, 2)
+    assert len(exp) > 100
+    assert_array_equal(_jumps_via_abi(events, 3, n_frames, 2, atom_base=24), exp)
+
+
 def _jumps_frame_shards_via_abi(events, n_atoms, n_frames, minimal_residence, cuts):
     """The frame-sharded K3 protocol of include/gemdat_b200.h on ONE device: the event table is
     cut at the frame numbers ``cuts`` into time slices (each sorted by atom, time), every slice
@@ -452,19 +471,19 @@ def _jumps_frame_shards_via_abi(events, n_atoms, n_frames, minimal_residence, cu
                            exit=torch.zeros((n_atoms, nb), dtype=torch.uint8, device='cuda'),
                            entry=torch.zeros((n_atoms, nb), dtype=torch.uint8, device='cuda')))
 
-    def count(r, entry, published=None, final=False):
+    def count(r, entry, published=None, final=False, reuse=1):
         sh = shards[r]
         n, fl = C.c_int64(0), C.c_int32(0)
         atom_off = torch.zeros(n_atoms + 1, dtype=torch.int64, device='cuda') if final else None
         _lib.check(lib.gd_jumps_count_shard(
             dv.ptr(sh['ev']) if sh['n'] else None, dv.ptr(sh['off']), sh['n'], n_atoms, n_frames,
-            minimal_residence, dv.ptr(entry), 1 if r == W - 1 else 0, dv.ptr(published), dv.ptr(sh['work']),
+            minimal_residence, dv.ptr(entry), 1 if r == W - 1 else 0, reuse, dv.ptr(published), dv.ptr(sh['work']),
             dv.ptr(sh['exit']), dv.ptr(atom_off), C.byref(n) if final else None,
             C.byref(fl) if final else None, s))
         return n.value, fl.value, atom_off
 
     for r in range(W):  # shard 0 truly starts empty; zeroed records = "empty, not known"
-        count(r, shards[r]['entry'] if r else None)
+        count(r, shards[r]['entry'] if r else None, reuse=0)
     scratch = torch.zeros(4, dtype=torch.int32, device='cuda')
     published = None
     rounds = 0
@@ -608,6 +627,59 @@ def test_k1_strip_walker_shapes(n_frames, n_atoms):
 
     ev2 = _calculate_transition_events(atom_sites=eo, atom_inner_sites=ei)
     assert_array_equal(ev2.to_numpy(), tr.events.to_numpy())
+
+
+@pytest.mark.parametrize('n_frames,n_atoms,scale,cap,route', [
+    (3000, 48, 0.004, 32, 'staged'), (1000, 33, 0.004, 32, 'staged'), (4100, 96, 0.003, 32, 'staged'),
+    (700, 64, 0.05, 0, 'reread'),   # events nearly every frame: default staging (8 rows / 32 frames) overflows
+])
+def test_hotpath_staged_events_equal_reread_and_oracle(monkeypatch, n_frames, n_atoms, scale, cap, route):
+    """K1 stages the event rows while the states are in registers and K2 only compacts them
+    (gd_site_states_staged + gd_events_compact).  Same table as the re-read route
+    (gd_events_fill) and as the oracle, incl. frame0 of a shard, odd atom counts (non-TMA K1),
+    several chunks and the overflow fallback.  One site per atom, atoms start on their site:
+    every site is visited, so the Q2 remap (which also forces the re-read route) stays out."""
+    from gemdat_b200 import Sites
+    from gemdat_b200.pipeline import HotPath
+    from oracle import cstates, events as oevents
+
+    rng = np.random.default_rng(n_frames + n_atoms)
+    lat = np.diag([16.0, 17.5, 15.25])
+    site_frac = np.zeros((0, 3))
+    while len(site_frac) < n_atoms:
+        cand = rng.random(3)
+        d = site_frac - cand
+        d -= np.round(d)
+        if len(site_frac) == 0 or np.sqrt((((d @ lat)) ** 2).sum(axis=1)).min() >= 2.0:
+            site_frac = np.vstack([site_frac, cand])
+    walk = np.cumsum(rng.normal(scale=scale, size=(n_frames, n_atoms, 3)), axis=0)
+    pos = np.mod(site_frac[None] + walk - walk[:1], 1)
+    labels = ['p'] * n_atoms
+    sites = Sites(lat, 'Li', site_frac, labels=labels)
+    frame0 = 12345
+    d_pos = torch.from_numpy(pos).cuda()
+    if cap:
+        monkeypatch.setenv('GD_EVENTS_STAGE_CAP', str(cap))
+    tables = {}
+    for staged in ('1', '0'):
+        monkeypatch.setenv('GD_EVENTS_STAGED', staged)
+        hp = HotPath(sites=sites, lattice=lat, n_atoms=n_atoms, site_radius=0.9, site_inner_fraction=0.6,
+                     minimal_residence=0, n_frames_total=frame0 + n_frames, frame0=frame0)
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            res = hp.run(d_pos)
+        assert hp.last_events_route == (route if staged == '1' else 'reread')
+        tables[staged] = res['events'].cpu().numpy()
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        eo, ei = cstates.calculate_atom_states_pair(
+            site_frac=site_frac, site_labels=labels, positions=pos, lattice_matrix=lat,
+            site_radius={'p': 0.9}, site_inner_fraction={'p': 0.6})
+    exp = oevents.calculate_transition_events(eo, ei)
+    exp[:, 5] += frame0
+    assert len(exp) > 200
+    assert_array_equal(tables['0'], exp)
+    assert_array_equal(tables['1'], exp)
 
 
 @pytest.mark.parametrize('n_atoms', [48, 33])
