@@ -76,6 +76,7 @@ SIGNATURES = {
     'gd_jumps_fill': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _p]),
     'gd_jumps_count_shard': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.c_int, C.c_int, _p, _p, _p, _p,
                                        C.POINTER(_i64), C.POINTER(_i32), _p]),
+    'gd_jumps_work_unresolved_offset': (_i64, [_i64, _i32]),
     'gd_jumps_resolve': (C.c_int, [_p, _i32, _i32, _i32, _p, _p, C.POINTER(_i32), _p]),
     'gd_pair_matrix': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),

@@ -109,6 +109,7 @@ static_assert(sizeof(PackedState) == GD_JUMP_STATE_BYTES, "jump state record siz
 constexpr int32_t kHasEvents = 1;  // the shard holds events of this atom
 constexpr int32_t kSynced = 2;     // ... one of them a departure: the exit state does not depend on the entry
 constexpr int32_t kKnown = 4;      // the state in the record is the true one
+constexpr int32_t kUnproven = 8;   // (work only) the parallel chain could not prove one of the atom's segments
 
 __device__ __forceinline__ PackedState pack(const JumpMachine &m) {
     PackedState s;
@@ -322,7 +323,7 @@ __global__ void __launch_bounds__(64)
         }
         // (otherwise the whole segment was replayed and `truth` already is its exit state)
         if (seg + 1 == s1) {
-            write_atom_exit(atom_exit, a, truth, atom_flags[a], entry_known);
+            write_atom_exit(atom_exit, a, truth, atom_flags[a] & (kHasEvents | kSynced), entry_known);
             if (is_last_shard && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
         }
         counts[seg] = n_true;
@@ -343,7 +344,7 @@ __global__ void __launch_bounds__(128)
                       int64_t minimal_residence, const SegSpec *__restrict__ spec,
                       PackedState *__restrict__ entry, int64_t *__restrict__ counts,
                       int32_t *__restrict__ flag, const PackedState *__restrict__ atom_entry,
-                      PackedState *__restrict__ atom_exit, const int32_t *__restrict__ atom_flags,
+                      PackedState *__restrict__ atom_exit, int32_t *__restrict__ atom_flags,
                       int is_last_shard) {
     const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int32_t a;
@@ -378,13 +379,14 @@ __global__ void __launch_bounds__(128)
         unpack(truth, sp.exit, a);
     } else if (!last) {
         atomicExch(flag, 1);  // the next segment's assumed entry state is not proven
+        atomicOr(atom_flags + a, kUnproven);
     }
     if (last) {
         // entry_known of a later segment: proven by the merge checks of the segments before it
         // (else *flag is set and the sequential chain redoes this); the record's kKnown then
         // follows from the atom's own entry record
         const bool known = first ? entry_known : (!atom_entry || (atom_entry[a].flags & kKnown) != 0);
-        write_atom_exit(atom_exit, a, truth, atom_flags[a], known);
+        write_atom_exit(atom_exit, a, truth, atom_flags[a] & (kHasEvents | kSynced), known);
         if (is_last_shard && truth.have_cand) truth.close_candidate(n_frames_total, emit_true);  // jumps.py:97-105
     }
     counts[seg] = n_true;
@@ -571,6 +573,20 @@ extern "C" int64_t gd_jumps_work_bytes(int64_t n_events, int32_t n_atoms) {
 
 namespace {
 
+// After a parallel chain whose proof is not read back (first pass of a frame shard): the exit
+// record of an atom with an unproven segment says "not known", so the resolve step asks for
+// another (checked) round instead of trusting it.  Clears the work bit for the next pass.
+__global__ void __launch_bounds__(256)
+    k_exit_finish(PackedState *__restrict__ atom_exit, int32_t *__restrict__ atom_flags, int32_t n_atoms) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n_atoms) return;
+    const int32_t fl = atom_flags[a];
+    if (fl & kUnproven) {
+        atom_flags[a] = fl & ~kUnproven;
+        if (atom_exit) atom_exit[a].flags &= ~(kKnown | kSynced);
+    }
+}
+
 // per-atom exclusive jump offsets from the scanned per-segment counts
 __global__ void __launch_bounds__(256)
     k_atom_jump_offsets(const int64_t *__restrict__ counts, const int64_t *__restrict__ seg_off,
@@ -647,12 +663,27 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
         GD_LAUNCH_CHECK();
     }
     GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
-    const int32_t flags0[4] = {0, 0, is_last_shard ? 1 : 0, 0};
-    GD_CUDA_CHECK(cudaMemcpyAsync(w.flag, flags0, 16, cudaMemcpyHostToDevice, st));
+    // flag[0..2]; flag[3] (unresolved entries, left by gd_jumps_resolve) is kept
+    static const int32_t flags_last[3] = {0, 0, 1}, flags_mid[3] = {0, 0, 0};
+    GD_CUDA_CHECK(cudaMemcpyAsync(w.flag, is_last_shard ? flags_last : flags_mid, 12,
+                                  cudaMemcpyHostToDevice, st));
     // GD_JUMPS_SEQUENTIAL=1 forces the sequential chain (tests / A-B timing)
     const char *env = getenv("GD_JUMPS_SEQUENTIAL");
     bool sequential = env && atoi(env) != 0;
-    int32_t h_flag[2] = {0, 0};
+    int32_t h_flag[4] = {0, 0, 0, 0};
+    if (!h_n_jumps && !h_flags && !sequential) {
+        // asynchronous pass: only the exit records are wanted.  The chain's proof is not read
+        // back; atoms with an unproven segment publish "not known" instead (k_exit_finish).
+        GD_REQUIRE(exit_rec && !d_atom_jump_offsets && !d_published, GD_ERR_INVALID,
+                   "gd_jumps_count_shard: an asynchronous pass only produces d_exit");
+        k_jumps_chain_par<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
+            d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
+            w.spec, w.entry, w.counts, w.flag, entry, exit_rec, w.atom_flags, is_last_shard);
+        GD_LAUNCH_CHECK();
+        k_exit_finish<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(exit_rec, w.atom_flags, n_atoms);
+        GD_LAUNCH_CHECK();
+        return GD_OK;
+    }
     for (;;) {
         if (sequential) {
             k_jumps_chain<<<(unsigned)gd_ceil_div(n_atoms, 64), 64, 0, st>>>(
@@ -669,31 +700,33 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
         GD_LAUNCH_CHECK();
         k_scan_add<<<n_tiles, 1024, 0, st>>>(w.counts, w.max_segs, w.tile_tot);
         GD_LAUNCH_CHECK();
+        if (d_atom_jump_offsets) {
+            k_atom_jump_offsets<<<(unsigned)gd_ceil_div(n_atoms + 1, 256), 256, 0, st>>>(
+                w.counts, w.seg_off, n_atoms, d_atom_jump_offsets);
+            GD_LAUNCH_CHECK();
+        }
+        if (d_published) {
+            k_check_published<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(
+                exit_rec, static_cast<const PackedState *>(d_published), n_atoms, w.flag);
+            GD_LAUNCH_CHECK();
+        }
         if (h_n_jumps)
             GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
                                           cudaMemcpyDeviceToHost, st));
-        GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         GD_CUDA_CHECK(cudaStreamSynchronize(st));
         if (sequential || h_flag[0] == 0) break;
         // some segment's entry state could not be proven: redo with the sequential chain
         sequential = true;
         GD_CUDA_CHECK(cudaMemsetAsync(w.counts, 0, (size_t)(w.max_segs + 1) * 8, st));
+        GD_CUDA_CHECK(cudaMemsetAsync(w.flag, 0, 8, st));
     }
-    if (d_atom_jump_offsets) {
-        k_atom_jump_offsets<<<(unsigned)gd_ceil_div(n_atoms + 1, 256), 256, 0, st>>>(
-            w.counts, w.seg_off, n_atoms, d_atom_jump_offsets);
+    // the parallel chain may have left kUnproven bits behind; the next pass must not see them
+    if (h_flag[0]) {
+        k_exit_finish<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(nullptr, w.atom_flags, n_atoms);
         GD_LAUNCH_CHECK();
     }
-    if (d_published) {
-        k_check_published<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(
-            exit_rec, static_cast<const PackedState *>(d_published), n_atoms, w.flag);
-        GD_LAUNCH_CHECK();
-        if (h_flags) {
-            GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-            GD_CUDA_CHECK(cudaStreamSynchronize(st));
-        }
-    }
-    if (h_flags) *h_flags = (sequential ? 1 : 0) | (h_flag[1] ? 2 : 0);
+    if (h_flags) *h_flags = (sequential ? 1 : 0) | (h_flag[1] ? 2 : 0) | (h_flag[3] ? 4 : 0);
     return GD_OK;
 }
 
@@ -710,7 +743,7 @@ extern "C" gd_status_t gd_jumps_count(const int32_t *d_events, const int64_t *d_
 extern "C" gd_status_t gd_jumps_resolve(const void *d_all_records, int32_t world, int32_t rank,
                                         int32_t n_atoms, void *d_entry, int32_t *d_unresolved,
                                         int32_t *h_unresolved, void *stream) {
-    GD_REQUIRE(d_all_records && d_entry && d_unresolved && h_unresolved, GD_ERR_INVALID,
+    GD_REQUIRE(d_all_records && d_entry && d_unresolved, GD_ERR_INVALID,
                "gd_jumps_resolve: null argument");
     GD_REQUIRE(world > 0 && rank >= 0 && rank < world && n_atoms > 0, GD_ERR_INVALID,
                "gd_jumps_resolve: bad shard geometry");
@@ -720,9 +753,17 @@ extern "C" gd_status_t gd_jumps_resolve(const void *d_all_records, int32_t world
         static_cast<const PackedState *>(d_all_records), world, rank, n_atoms,
         static_cast<PackedState *>(d_entry), d_unresolved);
     GD_LAUNCH_CHECK();
-    GD_CUDA_CHECK(cudaMemcpyAsync(h_unresolved, d_unresolved, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-    GD_CUDA_CHECK(cudaStreamSynchronize(st));
+    if (h_unresolved) {
+        GD_CUDA_CHECK(cudaMemcpyAsync(h_unresolved, d_unresolved, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        GD_CUDA_CHECK(cudaStreamSynchronize(st));
+    }
     return GD_OK;
+}
+
+extern "C" int64_t gd_jumps_work_unresolved_offset(int64_t n_events, int32_t n_atoms) {
+    if (n_events < 0 || n_atoms <= 0) return -1;
+    const JumpWork w = jump_work(nullptr, n_events, n_atoms);
+    return (int64_t)(reinterpret_cast<const unsigned char *>(w.flag + 3) - static_cast<const unsigned char *>(nullptr));
 }
 
 extern "C" gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets,

@@ -46,9 +46,22 @@ namespace {
 constexpr uint32_t kMagic = 0x47534447u;  // "GDSG"
 constexpr uint32_t kBlobVersion = 4;
 constexpr int kMaxGroups = 64;
-constexpr int kWarps = 8;  // strips per CTA
+// tuning knobs (scratch/k1_variants.sh builds A/B libraries with -D overrides)
+#ifndef GD_K1_WARPS
+#define GD_K1_WARPS 8
+#endif
+#ifndef GD_K1_STAGES
+#define GD_K1_STAGES 4
+#endif
+#ifndef GD_K1_IMAGE_FILTER
+#define GD_K1_IMAGE_FILTER 1
+#endif
+#ifndef GD_K1_MIN_CTAS
+#define GD_K1_MIN_CTAS 3
+#endif
+constexpr int kWarps = GD_K1_WARPS;  // strips per CTA
 constexpr int kThreads = kWarps * 32;
-constexpr int kStages = 4;        // frame rows in flight per warp
+constexpr int kStages = GD_K1_STAGES;  // frame rows in flight per warp
 constexpr int kRowDoubles = 96;   // 32 atoms x 3
 constexpr int kVisSmemMax = 24 * 1024;  // visited flags kept in shared memory up to this size
 constexpr uint32_t kRankMask = 0xFFFFFu;  // 20 bits of rank, 3 bits of image flags above
@@ -164,6 +177,7 @@ struct StatesParams {
     float cutoff32;
     float inv_cell[3];
     double inv_box[3];
+    double qbox[3];  // box / 4: below this |d| on an axis the atom's periodic image cannot be closer
     double m[9];
     GdGroupRec g0;  // the only group when n_groups == 1 (read from the constant bank)
 };
@@ -279,10 +293,23 @@ __device__ __forceinline__ double staged_d2(const StatesParams &p, double sx, do
                                             float ax, float ay, float az, uint32_t img) {
     double dx = __dsub_rn(sx, (double)ax), dy = __dsub_rn(sy, (double)ay), dz = __dsub_rn(sz, (double)az);
     if (img) {  // a periodic image of the atom can be the closer one
+#if GD_K1_IMAGE_FILTER
+        // ... but only when site and atom sit on opposite sides of the box: the image differs
+        // from the atom by +-L (float32 rounded), so with |d| <= L/4 it is at least 3L/4 - ulp
+        // away and `fabs(e) < fabs(d)` is false whatever the rounding.  Most lanes whose site
+        // lies near a face skip the image arithmetic (and most warps the divergent branch).
+        if (!((img & 1u) && fabs(dx) > p.qbox[0])) img &= ~1u;
+        if (!((img & 2u) && fabs(dy) > p.qbox[1])) img &= ~2u;
+        if (!((img & 4u) && fabs(dz) > p.qbox[2])) img &= ~4u;
+        if (img) {
+#endif
         asm volatile("" : "+f"(ax), "+f"(ay), "+f"(az));  // keep the image arithmetic in here
         if (img & 1u) dx = axis_delta_image(dx, sx, ax, p.box[0], p.cutoff32);
         if (img & 2u) dy = axis_delta_image(dy, sy, ay, p.box[1], p.cutoff32);
         if (img & 4u) dz = axis_delta_image(dz, sz, az, p.box[2], p.cutoff32);
+#if GD_K1_IMAGE_FILTER
+        }
+#endif
     }
     return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
 }
@@ -349,7 +376,7 @@ __device__ __forceinline__ void classify(const StatesParams &p, const GdGroupRec
 }
 
 template <bool kTma, bool kOneGroup, bool kDiag, bool kBand>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
     k_site_states(const __grid_constant__ StatesParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     double *ring = reinterpret_cast<double *>(smem);  // [kWarps][kStages][96]
@@ -1005,6 +1032,7 @@ extern "C" gd_status_t gd_site_states_staged(const double *d_pos_frac, int64_t n
         p.box[j] = h->box[j];
         p.inv_cell[j] = h->inv_cell[j];
         p.inv_box[j] = h->inv_box[j];
+        p.qbox[j] = 0.25 * (double)h->box[j];
     }
     for (int j = 0; j < 9; ++j) p.m[j] = h->matrix[j];
 

@@ -372,37 +372,34 @@ class HotPath:
         scratch = self._tensor('jscratch', (4,), torch.int32)
         args = (dv.ptr(rows), dv.ptr(offsets), n_local, n_atoms, self.n_frames_total, self.minimal_residence)
         launches = 0
-        # pass 1: every atom's exit record when the slice is run from the empty state
+        # pass 1 (asynchronous): every atom's exit record when the slice is run from the empty state
         # (rank 0 really starts from the empty state; for the others all-zero records say "empty, not known")
         entry.zero_()
         _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if me else None, last, 0, None, dv.ptr(jwork),
                                             dv.ptr(exit_rec), None, None, None, s))
-        launches += 4
+        launches += 5
+        d_unresolved = jwork.data_ptr() + int(lib.gd_jumps_work_unresolved_offset(n_local, n_atoms))
+        atom_off = self._tensor('jatom_off', (n_atoms + 2,), torch.int64)
+        n_jumps, flags = C.c_int64(0), C.c_int32(0)
         published = None
         for _ in range(W):
             allrec = self.comm.all_gather(exit_rec)  # [W, A, 40]
             if published is None:
                 published = allrec[me].contiguous()
-            unresolved = C.c_int32(0)
-            _lib.check(lib.gd_jumps_resolve(dv.ptr(allrec), W, me, n_atoms, dv.ptr(entry), dv.ptr(scratch),
-                                            C.byref(unresolved), s))
-            launches += 1
-            if unresolved.value == 0:
+            # entry records from all shards' exits, then (optimistically, same synchronisation)
+            # the final pass from them
+            _lib.check(lib.gd_jumps_resolve(dv.ptr(allrec), W, me, n_atoms, dv.ptr(entry), d_unresolved, None, s))
+            _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, 1, dv.ptr(published), dv.ptr(jwork),
+                                                dv.ptr(exit_rec), dv.ptr(atom_off), C.byref(n_jumps),
+                                                C.byref(flags), s))
+            launches += 6
+            if not flags.value & 4:
                 break
-            # some shard has events of an atom but no departure among them: its exit depends on
-            # its entry.  Run again from what is known so far; every round settles one more shard.
-            _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, 1, None, dv.ptr(jwork),
-                                                dv.ptr(exit_rec), None, None, None, s))
-            launches += 4
+            # some shard has events of an atom but no departure among them (or an unproven chain):
+            # its exit depends on its entry.  The pass above ran from what is known so far (checked,
+            # so its records are right where the entry was); every round settles one more shard.
         else:
             raise RuntimeError('jump machine states did not resolve in world rounds')
-        # final pass from the true entry states
-        atom_off = self._tensor('jatom_off', (n_atoms + 2,), torch.int64)
-        n_jumps, flags = C.c_int64(0), C.c_int32(0)
-        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry), last, 1, dv.ptr(published), dv.ptr(jwork),
-                                            dv.ptr(exit_rec), dv.ptr(atom_off), C.byref(n_jumps),
-                                            C.byref(flags), s))
-        launches += 5
         jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
         if n_jumps.value:
             _lib.check(lib.gd_jumps_fill(*args, dv.ptr(jwork), dv.ptr(jumps), s))

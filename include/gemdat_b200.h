@@ -242,25 +242,30 @@ gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets
  * flags: shard has events of the atom / one of them is a departure, after which the
  * state no longer depends on how the shard was entered / the state is the true one).
  *
- *   1. gd_jumps_count_shard(h_n_jumps = NULL) leaves in d_exit [n_atoms] every atom's record
- *      when run from the empty state: d_entry = NULL on the shard that starts the trajectory
- *      (empty IS its true entry), all-zero records on the others ("empty, not known");
+ *   1. gd_jumps_count_shard(h_n_jumps = NULL, h_flags = NULL) -- asynchronous -- leaves in
+ *      d_exit [n_atoms] every atom's record when run from the empty state: d_entry = NULL on
+ *      the shard that starts the trajectory (empty IS its true entry), all-zero records on the
+ *      others ("empty, not known").  An atom whose time-parallel chain could not be proven
+ *      publishes "not known";
  *   2. the caller all-gathers the records of all shards ([world, n_atoms]);
  *   3. gd_jumps_resolve gives this shard's true entry records and the number of
  *      (shard, atom) pairs over ALL shards whose entry is not yet known (the same number on
  *      every rank).  While it is > 0 (an atom with events but no departure in a shard --
- *      rare): call gd_jumps_count_shard with the current d_entry, gather, resolve again;
- *      at most world-1 rounds;
- *   4. gd_jumps_count_shard(d_entry, d_published = this shard's gathered records) counts,
- *      gd_jumps_fill writes this shard's jumps; d_atom_jump_offsets [n_atoms+1] places them
- *      per atom when the shards' tables are merged (gd_events_merge takes any 6-int32 rows).
+ *      rare): call gd_jumps_count_shard with the current d_entry and h_flags (checked pass),
+ *      gather, resolve again; at most world-1 rounds;
+ *   4. gd_jumps_count_shard(d_entry, d_published = this shard's records of the FIRST gather)
+ *      counts, gd_jumps_fill writes this shard's jumps; d_atom_jump_offsets [n_atoms+1] places
+ *      them per atom when the shards' tables are merged (gd_events_merge takes any 6-int32 rows).
+ *      Steps 3 and 4 need only one synchronisation when gd_jumps_resolve leaves its count at
+ *      d_work + gd_jumps_work_unresolved_offset() (h_unresolved = NULL): step 4 reports it in
+ *      *h_flags bit 2 and the caller repeats from step 3's "while" if it is set.
  * is_last_shard: close pending candidates at n_frames_total (jumps.py:97-105) -- only the
  * shard holding the trajectory's last frame does.  *h_flags: bit 0 the sequential chain
- * ran, bit 1 a record published as known differs from the true exit state
- * (event tables that are not state-consistent: fall back to exchanging the events).
+ * ran, bit 1 a record published as known differs from the true exit state (event tables
+ * that are not state-consistent: fall back to exchanging the events), bit 2 see above.
  * reuse_work != 0: d_work still holds the segment speculation of an earlier call on the same
- * table (passes 2.. of the protocol skip it).  Every call synchronises (the time-parallel
- * chain's proof flag is read back). */
+ * table (passes 2.. of the protocol skip it).  Calls with h_n_jumps or h_flags synchronise
+ * (the time-parallel chain's proof flag is read back). */
 #define GD_JUMP_STATE_BYTES 40
 gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_offsets,
                                  int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
@@ -269,7 +274,8 @@ gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_
                                  int64_t *d_atom_jump_offsets, int64_t *h_n_jumps, int32_t *h_flags,
                                  void *stream);
 /* d_all_records [world, n_atoms] records; d_entry [n_atoms] records out; d_unresolved one
- * int32 of device scratch.  Synchronises. */
+ * int32 of device memory receiving the count.  Synchronises unless h_unresolved is NULL. */
+int64_t gd_jumps_work_unresolved_offset(int64_t n_events, int32_t n_atoms);
 gd_status_t gd_jumps_resolve(const void *d_all_records, int32_t world, int32_t rank, int32_t n_atoms,
                              void *d_entry, int32_t *d_unresolved, int32_t *h_unresolved,
                              void *stream);

@@ -471,20 +471,22 @@ def _jumps_frame_shards_via_abi(events, n_atoms, n_frames, minimal_residence, cu
                            exit=torch.zeros((n_atoms, nb), dtype=torch.uint8, device='cuda'),
                            entry=torch.zeros((n_atoms, nb), dtype=torch.uint8, device='cuda')))
 
-    def count(r, entry, published=None, final=False, reuse=1):
+    def count(r, entry, published=None, mode='async', reuse=1):
+        """mode: 'async' (first pass: exit records only, no read-back), 'checked' (later rounds:
+        the chain's proof flag is read back), 'final' (counts + per-atom offsets + published check)."""
         sh = shards[r]
         n, fl = C.c_int64(0), C.c_int32(0)
+        final = mode == 'final'
         atom_off = torch.zeros(n_atoms + 1, dtype=torch.int64, device='cuda') if final else None
         _lib.check(lib.gd_jumps_count_shard(
             dv.ptr(sh['ev']) if sh['n'] else None, dv.ptr(sh['off']), sh['n'], n_atoms, n_frames,
             minimal_residence, dv.ptr(entry), 1 if r == W - 1 else 0, reuse, dv.ptr(published), dv.ptr(sh['work']),
             dv.ptr(sh['exit']), dv.ptr(atom_off), C.byref(n) if final else None,
-            C.byref(fl) if final else None, s))
+            None if mode == 'async' else C.byref(fl), s))
         return n.value, fl.value, atom_off
 
     for r in range(W):  # shard 0 truly starts empty; zeroed records = "empty, not known"
         count(r, shards[r]['entry'] if r else None, reuse=0)
-    scratch = torch.zeros(4, dtype=torch.int32, device='cuda')
     published = None
     rounds = 0
     while True:
@@ -493,9 +495,11 @@ def _jumps_frame_shards_via_abi(events, n_atoms, n_frames, minimal_residence, cu
             published = allrec.clone()
         unresolved = []
         for r in range(W):
+            # the count is left in the shard's work area and comes back with the next pass's flags
+            d_unres = shards[r]['work'].data_ptr() + int(lib.gd_jumps_work_unresolved_offset(shards[r]['n'], n_atoms))
             u = C.c_int32(0)
             _lib.check(lib.gd_jumps_resolve(dv.ptr(allrec), W, r, n_atoms, dv.ptr(shards[r]['entry']),
-                                            dv.ptr(scratch), C.byref(u), s))
+                                            d_unres, C.byref(u), s))
             unresolved.append(u.value)
         assert len(set(unresolved)) == 1, 'every rank must see the same number of unresolved entries'
         rounds += 1
@@ -503,11 +507,13 @@ def _jumps_frame_shards_via_abi(events, n_atoms, n_frames, minimal_residence, cu
             break
         assert rounds < W, 'states must resolve in at most world - 1 extra rounds'
         for r in range(W):
-            count(r, shards[r]['entry'])
+            _, fl, _ = count(r, shards[r]['entry'], mode='checked')
+            assert fl & 4, 'the unresolved count must come back with the flags of the next pass'
     tables, offs, mismatch = [], [], 0
     for r in range(W):
         sh = shards[r]
-        n, fl, atom_off = count(r, sh['entry'], published[r].contiguous(), final=True)
+        n, fl, atom_off = count(r, sh['entry'], published[r].contiguous(), mode='final')
+        assert not fl & 4
         mismatch |= fl & 2
         out = torch.empty((max(n, 1), 6), dtype=torch.int32, device='cuda')
         if n:
