@@ -138,6 +138,7 @@ class HotPath:
         self.world, self.rank, self.group = world, rank, group
         self.comm = Comm(world, group)
         self.launches_per_run = 0
+        self._jump_cap = 0  # rows per rank reserved in the final jump gather (grows with what is seen)
         self.last_k1_events = None
         # GD_K3_EXCHANGE=1: always exchange the event rows by atom block (the fallback route; A/B)
         self.k3_exchange = os.environ.get('GD_K3_EXCHANGE', '0') not in ('', '0')
@@ -179,10 +180,17 @@ class HotPath:
         launches = 0
         outer = self._tensor('outer', (n_frames, n_atoms), torch.int32)
         inner = self._tensor('inner', (n_frames, n_atoms), torch.int32)
-        visited = self._tensor('visited', (2 * self.n_sites,), torch.uint8)
         band = self._tensor('band', (4,), torch.int64)
-        visited.zero_()
         band.zero_()
+        # every flag the host (and, frame-sharded, the other ranks) must see after K1 lives in ONE
+        # buffer: visited [2S] | changed [2A] | staging overflow (int32), 16-byte aligned sections
+        n_vis, n_chg = 2 * self.n_sites, 2 * n_atoms
+        o_chg = (n_vis + 15) // 16 * 16
+        o_ovf = o_chg + (n_chg + 15) // 16 * 16
+        pack = self._tensor('pack_k1', (o_ovf + 16,), torch.uint8)
+        pack.zero_()
+        visited, changed = pack[:n_vis], pack[o_chg: o_chg + n_chg]
+        overflow = pack[o_ovf: o_ovf + 4].view(torch.int32)
 
         # ---- K1 (+ the event count of K2, fused).  The event at a shard's last frame needs the
         # state of the next shard's first frame: positions are known up front, so the halo ROW OF
@@ -197,45 +205,36 @@ class HotPath:
             if self.rank + 1 < self.world:
                 next_pos = first_rows[self.rank + 1].contiguous()
         work = self._tensor('work', (int(lib.gd_events_work_elems(n_frames, n_atoms)),), torch.int32)
-        changed = self._tensor('changed', (2 * n_atoms,), torch.uint8)
-        changed.zero_()
         self._mark('halo_positions')
         # K1 also leaves the event rows themselves in a staging area ([chunk, atom, cap] rows), so
         # that K2 only compacts them instead of re-reading 8 B/atom-frame of states
-        stage = overflow = None
+        stage = None
         cap = 0
         if self.stage_events:  # GD_EVENTS_STAGE_CAP overrides the default rows per (chunk, atom) segment
             cap = int(os.environ.get('GD_EVENTS_STAGE_CAP', '0')) or int(lib.gd_events_stage_cap(n_frames, n_atoms))
         if cap > 0:
             stage = self._tensor('stage', (int(lib.gd_events_stage_elems(n_frames, n_atoms, cap)),), torch.int32)
-            overflow = self._tensor('overflow', (1,), torch.int32)
-            overflow.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         _lib.check(lib.gd_site_states_staged(dv.ptr(pos), n_frames, n_atoms, dv.ptr(next_pos),
                                              dv.ptr(self.grid.d_blob), self.grid.h_blob.ctypes.data,
                                              dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band),
                                              dv.ptr(work), dv.ptr(changed), dv.ptr(stage), cap,
-                                             dv.ptr(overflow), s))
+                                             dv.ptr(overflow) if stage is not None else None, s))
         e1.record()
         self.last_k1_events = (e0, e1)
         launches += 1
         self._mark('k1_site_states')
 
         # ---- what K2 needs from the other shards, in ONE exchange: the OR of the visited flags
-        # (warning + Q2 LUT are global), the OR of the "state ever changes" flags (Q4 "atom is
-        # skipped" is a whole-trajectory property) and the following shard's first state rows
-        # (destination states of the halo event).
-        next_o = next_i = None
+        # (warning + Q2 LUT are global), of the "state ever changes" flags (Q4 "atom is skipped" is
+        # a whole-trajectory property) and of the overflow flag (all ranks take the same route).
         if self.world > 1:
-            next_o, next_i = self._exchange_after_k1(visited, changed, outer, inner)
-        flags = [visited, changed[:n_atoms].amax().reshape(1)]
-        if overflow is not None:
-            flags.append(overflow.to(torch.uint8))
-        host = dv.to_host(torch.cat(flags))
-        vis = host[: 2 * self.n_sites].astype(bool).reshape(2, self.n_sites)
-        any_outer_change = bool(host[2 * self.n_sites])
-        staged_ok = overflow is not None and not bool(host[-1])
+            pack.copy_(self.comm.all_gather(pack).amax(dim=0))
+        host = dv.to_host(pack)
+        vis = host[:n_vis].astype(bool).reshape(2, self.n_sites)
+        any_outer_change = bool(host[o_chg: o_chg + n_atoms].any())
+        staged_ok = stage is not None and not host[o_ovf: o_ovf + 4].any()
         remapped = False
         for arr, v in ((outer, vis[0]), (inner, vis[1])):
             for label, key in zip(self.grid.group_labels, self.grid.group_keys):
@@ -248,7 +247,10 @@ class HotPath:
                 _lib.check(lib.gd_remap_states(dv.ptr(arr), arr.numel(), dv.ptr(d_lut), self.n_sites, s))
                 launches += 1
                 remapped = True
-        if remapped and self.world > 1:  # rare (Q2): the halo rows must carry the remapped indices
+        next_o = next_i = None
+        if self.world > 1 and (remapped or not staged_ok):
+            # the re-read route needs the following shard's first state rows (destination states of
+            # the halo event; after the Q2 remap they carry the remapped indices)
             rows = self._all_gather(torch.stack([outer[0], inner[0]]))  # [W, 2, A]
             if self.rank + 1 < self.world:
                 next_o, next_i = rows[self.rank + 1, 0].contiguous(), rows[self.rank + 1, 1].contiguous()
@@ -314,27 +316,6 @@ class HotPath:
         return res
 
     # ------------------------------------------------------------------ pieces of the pass
-    def _exchange_after_k1(self, visited, changed, outer, inner):
-        """One all-gather of [visited | changed | first outer row | first inner row] per rank;
-        ORs the flags in place and returns the following shard's first state rows."""
-        n_atoms = int(outer.shape[1])
-        parts = [visited, changed, outer[0].contiguous().view(torch.uint8), inner[0].contiguous().view(torch.uint8)]
-        offs, total = [], 0
-        for p in parts:
-            offs.append(total)
-            total += (p.numel() + 15) // 16 * 16  # int32 sections stay aligned
-        pack = self._tensor('pack_k1', (total,), torch.uint8)
-        for o, p in zip(offs, parts):
-            pack[o: o + p.numel()] = p
-        allp = self.comm.all_gather(pack)  # [W, total]
-        visited.copy_(allp[:, offs[0]: offs[0] + visited.numel()].amax(dim=0))
-        changed.copy_(allp[:, offs[1]: offs[1] + changed.numel()].amax(dim=0))
-        if self.rank + 1 == self.world:
-            return None, None
-        nxt = allp[self.rank + 1]
-        return (nxt[offs[2]: offs[2] + 4 * n_atoms].contiguous().view(torch.int32),
-                nxt[offs[3]: offs[3] + 4 * n_atoms].contiguous().view(torch.int32))
-
     def _jumps_local(self, rows, offsets, n_block):
         """K3 on a table holding the whole history of ``n_block`` atoms (count -> allocate -> fill)."""
         lib = _lib.lib
@@ -379,7 +360,13 @@ class HotPath:
                                             dv.ptr(exit_rec), None, None, None, s))
         launches += 5
         d_unresolved = jwork.data_ptr() + int(lib.gd_jumps_work_unresolved_offset(n_local, n_atoms))
-        atom_off = self._tensor('jatom_off', (n_atoms + 2,), torch.int64)
+        # one buffer for the final gather: per-atom jump offsets [A + 1] + (mismatch, event count)
+        # word as int64, then room for `cap` jump rows -- cap remembered from earlier runs, so that
+        # in steady state offsets and rows travel in ONE all-gather
+        head = 2 * (n_atoms + 2)
+        cap = self._jump_cap
+        jbuf = self._tensor('jbuf', (head + cap * 6,), torch.int32)
+        atom_off = jbuf[:head].view(torch.int64)
         n_jumps, flags = C.c_int64(0), C.c_int32(0)
         published = None
         for _ in range(W):
@@ -400,24 +387,28 @@ class HotPath:
             # so its records are right where the entry was); every round settles one more shard.
         else:
             raise RuntimeError('jump machine states did not resolve in world rounds')
-        jumps = dv.empty((max(n_jumps.value, 1), 6), torch.int32)
+        fits = n_jumps.value <= cap
+        jumps = jbuf[head:].view(cap, 6) if fits else dv.empty((n_jumps.value, 6), torch.int32)
         if n_jumps.value:
             _lib.check(lib.gd_jumps_fill(*args, dv.ptr(jwork), dv.ptr(jumps), s))
             launches += 1
-        jumps = jumps[: n_jumps.value]
-        # gather: per-atom jump offsets + (mismatch flag, local event count) of every shard, then the rows
         atom_off[n_atoms + 1] = (n_local << 1) | (1 if flags.value & 2 else 0)
-        all_off = dv.to_host(self.comm.all_gather(atom_off))  # [W, A + 2]
+        allb = self.comm.all_gather(jbuf)  # [W, head + cap * 6]
+        all_off = dv.to_host(allb[:, :head].contiguous().view(torch.int64))  # [W, A + 2]
         tail = all_off[:, -1]
         if (tail & 1).any():
             return None
         n_events_global = int((tail >> 1).sum())
         all_off = all_off[:, : n_atoms + 1]
         counts = np.diff(all_off, axis=1)
-        cap = max(1, int(all_off[:, -1].max()))
-        padded = self._tensor('jpad', (cap, 6), torch.int32)
-        padded[: jumps.shape[0]] = jumps
-        allj = self.comm.all_gather(padded)  # [W, cap, 6]
+        most = int(all_off[:, -1].max())
+        self._jump_cap = max(self._jump_cap, most + most // 4 + 16)
+        if most <= cap:  # every rank's rows came along
+            allj = [allb[r, head:] for r in range(W)]
+        else:            # first run (or a burst of jumps): second gather with the exact capacity
+            padded = self._tensor('jpad', (most, 6), torch.int32)
+            padded[: n_jumps.value] = jumps[: n_jumps.value]
+            allj = self.comm.all_gather(padded)  # [W, most, 6]
         total_off, dst_start = merge_plan(counts)
         merged = dv.empty((max(int(total_off[-1]), 1), 6), torch.int32)
         d_plan = dv.to_device(np.ascontiguousarray(np.concatenate([all_off, dst_start], axis=1)))  # [W, 2A+1]
