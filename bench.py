@@ -408,7 +408,10 @@ def run_ours(args):
         pass
     if rank == 0:
         peak = float(peaks.get('hbm_gbs', 6650.0))
-        k1_bytes = 32.0 * (f1 - f0) * n_atoms
+        # K1 reads 24 B of positions and writes 2 x 4 B of states per atom-frame; on the staged
+        # route it also writes the 24 B event rows (K2 then only compacts them)
+        staged = hp.last_events_route == 'staged'
+        k1_bytes = 32.0 * (f1 - f0) * n_atoms + (24.0 * hp.last_n_local_events if staged else 0.0)
         achieved = k1_bytes / (k1_avg_ms * 1e-3) / 1e9
         traffic, traffic_src = None, None
         try:  # DRAM bytes per launch from the committed ncu --set full capture of this kernel
@@ -427,7 +430,8 @@ def run_ours(args):
                          'traffic_unit': 'bytes per launch (dram read + write)', 'traffic_source': traffic_src,
                          'algorithmic_bytes_per_launch': k1_bytes,
                          'peak_source': 'MEASURED_PEAKS.json hbm_gbs (of measured)' if peaks else 'fallback',
-                         'algorithmic_bytes_per_atom_frame': 32, 'launch_ms': k1_avg_ms},
+                         'algorithmic_bytes_per_atom_frame': k1_bytes / ((f1 - f0) * n_atoms),
+                         'events_route': hp.last_events_route, 'launch_ms': k1_avg_ms},
             'gpu_launches': hp.launches_per_run * args.steps,
             'clocks': sampler.summary(),
             'results': {'n_events': int(res['n_events']), 'n_jumps': int(res['n_jumps'])},

@@ -88,3 +88,60 @@ def jump_diffusivity(*, pdist: np.ndarray, matrix: np.ndarray, dimensions: int, 
     jump_diff = np.sum(pdist**2 * matrix)
     jump_diff *= angstrom**2 / (2 * dimensions * n_floating * total_time)
     return float(jump_diff)
+
+
+# ---------------------------------------------------------------------------------------------
+# The same machine with its state made explicit, for time slices of an atom's event list.
+# Restates what the frame-sharded K3 protocol (include/gemdat_b200.h, gd_jumps_count_shard)
+# relies on: the state after an event list is a function of (entry state, events), and after
+# a "departure" row (start site != -1 and != destination site) it no longer depends on the
+# entry state when the rows are state-consistent.
+
+EMPTY_STATE = (None, None)  # (pending fromevent (start site, dest site, time), pending candidate)
+
+
+def jump_machine_slice(rows, minimal_residence: int = 0, entry=EMPTY_STATE):
+    """Runs jumps.py:45-95 over ``rows`` (one atom, time ordered) from ``entry``.
+
+    Returns ``(jumps, exit_state, has_departure)``; jumps still include start == destination
+    rows (jumps.py:113 filters them at the very end) -- ``finish_slices`` applies that filter.
+    """
+    frm, cand = entry
+    cand = None if cand is None else list(cand)
+    jumps, has_departure = [], False
+    for atom, s0, s1, i0, i1, t in np.asarray(rows, dtype=np.int64).reshape(-1, 6).tolist():
+        if cand is not None:
+            if s1 == cand[2]:
+                if i1 != -1:
+                    cand[3] = i1
+            else:
+                residence = t - (cand[5] - 1)
+                if residence >= minimal_residence and cand[3] != -1:
+                    jumps.append((cand[0], cand[1], cand[2], cand[4], cand[5], residence))
+                cand = None
+        if s0 != -1 and s0 != s1:
+            frm = (s0, s1, t)
+            has_departure = True
+        if frm is not None:
+            if s1 == frm[0]:
+                frm, cand = None, None
+            elif i1 != -1 or s1 != frm[1]:
+                cand = [atom, frm[0], s1, i1, frm[2], t + 1]
+                frm = None
+    return jumps, (frm, None if cand is None else tuple(cand)), has_departure
+
+
+def close_pending(state, n_frames: int, minimal_residence: int = 0):
+    """jumps.py:97-105: the candidate still pending after an atom's last event."""
+    cand = state[1]
+    if cand is None:
+        return []
+    residence = n_frames - (cand[5] - 1)
+    if residence >= minimal_residence and cand[3] != -1:
+        return [(cand[0], cand[1], cand[2], cand[4], cand[5], residence)]
+    return []
+
+
+def finish_slices(jumps) -> np.ndarray:
+    out = np.array(jumps, dtype=np.int64).reshape(-1, 6)
+    return out[out[:, 1] != out[:, 2]]

@@ -154,6 +154,95 @@ def test_merge_plan_places_rows_by_atom_then_shard():
     np.testing.assert_array_equal(dst, [[0, 3, 7], [2, 3, 10]])
 
 
+def _jump_protocol_worker(rank: int, world: int, port: int, out_path: str):
+    """The frame-sharded K3 protocol (include/gemdat_b200.h) with the oracle's explicit-state
+    machine standing in for the kernels: pass 1 from the empty state, all-gather of the per-atom
+    records, the resolve rule, extra rounds while some entry is unknown, final pass, per-atom
+    merge of the shards' jump tables -- against the sequential oracle on the whole table."""
+    _init(rank, world, port)
+    try:
+        from gemdat_b200.pipeline import merge_plan
+        from oracle import events as oevents
+        from oracle import jumps as ojumps
+
+        rec, pos = _small_case(n_frames=2400)
+        n_frames, n_atoms = pos.shape[:2]
+        so, si = _oracle_states(rec, pos)
+        events = oevents.calculate_transition_events(so, si)
+        # atom 0 keeps only a few inner-only rows in the middle shard(s): events but no departure
+        # there, so its exit depends on its entry and the resolve needs more than one round
+        f0, f1 = n_frames * rank // world, n_frames * (rank + 1) // world
+        mid = (events[:, 5] >= n_frames // world) & (events[:, 5] < n_frames - n_frames // world)
+        drop = (events[:, 0] == 0) & mid & (events[:, 1] != events[:, 2])
+        events = events[~drop]
+        mine = events[(events[:, 5] >= f0) & (events[:, 5] < f1)]
+        per_atom = [mine[mine[:, 0] == a] for a in range(n_atoms)]
+        mr = 3
+
+        def run(entries):
+            out = [ojumps.jump_machine_slice(per_atom[a], mr, entries[a][0]) for a in range(n_atoms)]
+            recs = [(st, len(per_atom[a]) > 0, dep, bool(dep or entries[a][1]))
+                    for a, (_, st, dep) in enumerate(out)]  # (state, has events, synced, known)
+            return [j for j, _, _ in out], recs
+
+        def resolve(allrecs, q):
+            entry, unknown = [], 0
+            for a in range(n_atoms):
+                e = (ojumps.EMPTY_STATE, True)
+                for p in range(q - 1, -1, -1):
+                    st, has, _, known = allrecs[p][a]
+                    if not has:
+                        continue
+                    e = (st, known)
+                    break
+                unknown += 0 if e[1] else 1
+                entry.append(e)
+            return entry, unknown
+
+        entries = [(ojumps.EMPTY_STATE, rank == 0)] * n_atoms
+        rounds = 0
+        while True:
+            jumps, recs = run(entries)
+            allrecs = [None] * world
+            dist.all_gather_object(allrecs, recs)
+            entries, _ = resolve(allrecs, rank)
+            unresolved = sum(resolve(allrecs, q)[1] for q in range(world))  # same on every rank
+            rounds += 1
+            if unresolved == 0:
+                break
+            assert rounds < world
+        jumps, recs = run(entries)
+        if rank == world - 1:
+            for a in range(n_atoms):
+                jumps[a] = jumps[a] + ojumps.close_pending(recs[a][0], n_frames, mr)
+        tables = [None] * world
+        dist.all_gather_object(tables, jumps)
+        counts = np.array([[len(t[a]) for a in range(n_atoms)] for t in tables])
+        total_off, dst = merge_plan(counts)
+        merged = np.zeros((int(total_off[-1]), 6), dtype=np.int64)
+        for r in range(world):
+            for a in range(n_atoms):
+                if counts[r, a]:
+                    merged[dst[r, a]: dst[r, a] + counts[r, a]] = np.array(tables[r][a])
+        merged = merged[merged[:, 1] != merged[:, 2]]
+        expected = ojumps.transitions_to_jumps(events, n_frames, mr)
+        np.testing.assert_array_equal(merged, expected)
+        if rank == 0:
+            Path(out_path).write_text(f'ok {len(expected)} {rounds}')
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_jump_state_protocol_gloo_cpu(tmp_path, world):
+    out = tmp_path / 'result.txt'
+    mp.spawn(_jump_protocol_worker, args=(world, _free_port(), str(out)), nprocs=world, join=True)
+    tag, n_jumps, rounds = out.read_text().split()
+    assert tag == 'ok' and int(n_jumps) > 20
+    if world == 3:
+        assert int(rounds) >= 2, 'the thinned atom should have needed a second resolve round'
+
+
 # ------------------------------------------------------------------------------------ GPU
 
 

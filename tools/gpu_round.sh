@@ -24,7 +24,7 @@ if [[ "${2:-}" != "skip-ncu" ]]; then
       --log-file $out/${tag}_launches.csv python bench.py $small > $out/${tag}_ncu_launches.log 2>&1
   echo "ncu launch list exit $?"
   timeout 900 ncu --set full --clock-control none --import-source on \
-      -k 'regex:k_site_states|k_events' -c 2 -f -o $out/${tag}_k1_k2 \
+      -k 'regex:k_site_states|k_events_compact|k_jumps_spec' -c 3 -f -o $out/${tag}_k1_k2 \
       python bench.py $small > $out/${tag}_ncu_full.log 2>&1
   echo "ncu full exit $?"
 fi
