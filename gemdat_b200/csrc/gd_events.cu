@@ -129,7 +129,13 @@ __global__ void __launch_bounds__(256)
 // kLanes lanes copy one (chunk, atom) segment: its rows are contiguous on both sides, so the copy
 // moves 8-byte words with coalesced pieces of kLanes * 8 bytes; the shard's first frame is added
 // to the time column on the way.
-constexpr int kCompactLanes = 16;
+#ifndef GD_COMPACT_LANES
+#define GD_COMPACT_LANES 16
+#endif
+#ifndef GD_COMPACT_ATOM_MAJOR
+#define GD_COMPACT_ATOM_MAJOR 0
+#endif
+constexpr int kCompactLanes = GD_COMPACT_LANES;
 __global__ void __launch_bounds__(256)
     k_events_compact(const int2 *__restrict__ stage, int32_t cap, Geometry g,
                      const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
@@ -138,14 +144,20 @@ __global__ void __launch_bounds__(256)
     const int64_t item = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / kCompactLanes;
     const int sub = threadIdx.x % kCompactLanes;
     if (item >= g.n_chunks * g.n_atoms) return;
+#if GD_COMPACT_ATOM_MAJOR
+    // neighbouring groups copy neighbouring chunks of one atom: contiguous destination
+    const int32_t a = (int32_t)(item / g.n_chunks);
+    const int64_t c = item - (int64_t)a * g.n_chunks;
+#else
     const int64_t c = item / g.n_atoms;
     const int32_t a = (int32_t)(item - c * g.n_atoms);
+#endif
     if (!changed_global[a]) return;  // outer state never changes: atom is skipped
     const int32_t *w = work + (int64_t)a * g.n_chunks + c;
     const int32_t first = w[0];
     const int32_t last = (c + 1 < g.n_chunks) ? w[1] : (int32_t)(atom_offsets[a + 1] - atom_offsets[a]);
     const int n_words = 3 * (last - first);
-    const int2 *src = stage + item * (int64_t)cap * 3;
+    const int2 *src = stage + (c * g.n_atoms + a) * (int64_t)cap * 3;
     int2 *dst = events + (atom_offsets[a] + first) * 3;
     for (int k = sub; k < n_words; k += kCompactLanes) {
         int2 v = __ldcs(src + k);

@@ -94,8 +94,13 @@ struct JumpMachine {
 //      each segment from its true entry state and writes its jumps in place.
 // Output order = segment order = (atom, time), exactly the reference's.
 
-constexpr int kSeg = 128;  // event rows per segment
-constexpr int kBatch = 8;  // rows fetched ahead of the machine
+#ifndef GD_K3_SEG
+#define GD_K3_SEG 128
+#endif
+#ifndef GD_K3_SPEC_MIN_CTAS
+#define GD_K3_SPEC_MIN_CTAS 1
+#endif
+constexpr int kSeg = GD_K3_SEG;      // event rows per segment
 
 struct PackedState {  // 40 bytes == GD_JUMP_STATE_BYTES
     int32_t have;  // bit 0: from pending, bit 1: candidate pending
@@ -161,6 +166,37 @@ __device__ __forceinline__ Row load_row(const int32_t *__restrict__ events, int6
     return Row{a.x, a.y, b.x, b.y, c.x, c.y};
 }
 
+// Walks rows [r0, r0 + n) in order, calling f(k, row) (return false to stop).  One thread owns
+// the run, so every load instruction of a warp touches 32 different lines and the L1 tag stage
+// (one line per cycle) is the limit: rows are therefore fetched with 16-byte loads, 8 rows =
+// 12 loads ahead of the machine.  Rows are 24 B, so a row pair starting at an even row is
+// 16-byte aligned when the table is (`wide`); an odd first row and the tail go one by one.
+template <typename F>
+__device__ __forceinline__ void walk_rows(const int32_t *__restrict__ events, int64_t r0, int n,
+                                          bool wide, F &&f) {
+    int k = 0;
+    if (wide) {
+        if ((r0 & 1) && n > 0) {
+            if (!f(0, load_row(events, r0))) return;
+            k = 1;
+        }
+        for (; k + 8 <= n; k += 8) {
+            const int4 *q = reinterpret_cast<const int4 *>(events + (r0 + k) * 6);
+            int4 v[12];
+#pragma unroll
+            for (int j = 0; j < 12; ++j) v[j] = __ldg(q + j);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {  // 3 int4 = 2 rows
+                const int4 a = v[3 * j], b = v[3 * j + 1], c = v[3 * j + 2];
+                if (!f(k + 2 * j, Row{a.x, a.y, a.z, a.w, b.x, b.y})) return;
+                if (!f(k + 2 * j + 1, Row{b.z, b.w, c.x, c.y, c.z, c.w})) return;
+            }
+        }
+    }
+    for (; k < n; ++k)
+        if (!f(k, load_row(events, r0 + k))) return;
+}
+
 struct SegSpec {  // 48 bytes: result of the speculative run of one segment
     PackedState exit;
     int32_t sync;     // rows [0, sync) must be replayed from the true entry state
@@ -220,7 +256,7 @@ __device__ __forceinline__ bool locate_segment(int64_t seg, const int64_t *__res
     return true;
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, GD_K3_SPEC_MIN_CTAS)
     k_jumps_spec(const int32_t *__restrict__ events, const int64_t *__restrict__ atom_offsets,
                  const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t minimal_residence,
                  SegSpec *__restrict__ spec, int32_t *__restrict__ atom_flags) {
@@ -233,25 +269,14 @@ __global__ void __launch_bounds__(128)
     int sync = n, n_after = 0;
     bool synced = false;
     auto emit = [&](const Jump &) { n_after += synced ? 1 : 0; };
-    // rows do not depend on the machine: fetch kBatch of them before stepping (the walk is
-    // latency bound, one thread per segment)
-    for (int k0 = 0; k0 < n; k0 += kBatch) {
-        Row rows[kBatch];
-#pragma unroll
-        for (int j = 0; j < kBatch; ++j) rows[j] = load_row(events, r0 + min(k0 + j, n - 1));
-#pragma unroll
-        for (int j = 0; j < kBatch; ++j) {
-            const int k = k0 + j;
-            if (k < n) {
-                const Row e = rows[j];
-                m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
-                if (!synced && e.s0 != GD_NOSITE && e.s0 != e.s1) {
-                    synced = true;
-                    sync = k + 1;
-                }
-            }
+    walk_rows(events, r0, n, (reinterpret_cast<uintptr_t>(events) & 15) == 0, [&](int k, const Row &e) {
+        m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+        if (!synced && e.s0 != GD_NOSITE && e.s0 != e.s1) {
+            synced = true;
+            sync = k + 1;
         }
-    }
+        return true;
+    });
     SegSpec out;
     out.exit = pack(m);
     out.sync = sync;
@@ -417,16 +442,10 @@ __global__ void __launch_bounds__(128)
         o[2] = make_int2(j.stop_time, j.residence);
         ++out;
     };
-    for (int k0 = 0; k0 < n && out < out1; k0 += kBatch) {
-        Row rows[kBatch];
-#pragma unroll
-        for (int j = 0; j < kBatch; ++j) rows[j] = load_row(events, r0 + min(k0 + j, n - 1));
-#pragma unroll
-        for (int j = 0; j < kBatch; ++j) {
-            const Row e = rows[j];
-            if (k0 + j < n && out < out1) m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
-        }
-    }
+    walk_rows(events, r0, n, (reinterpret_cast<uintptr_t>(events) & 15) == 0, [&](int, const Row &e) {
+        m.step(e.atom, e.s0, e.s1, e.i1, e.t, emit);
+        return out < out1;  // all of this segment's jumps are out: the rest of its rows is moot
+    });
     const bool last_of_atom = r0 + n == atom_offsets[atom + 1];
     // shard_flag[2]: this is the trajectory's last frame shard (left by the count call)
     if (last_of_atom && shard_flag[2] != 0 && m.have_cand && out < out1) m.close_candidate(n_frames_total, emit);

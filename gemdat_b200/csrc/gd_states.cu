@@ -241,8 +241,12 @@ __device__ __forceinline__ Staged stage_atom(const StatesParams &p, double f0, d
     s.az = __double2float_rn(cz);
     s.cell = 0;
     // positions handed over by Trajectory.positions are in [0, 1): one test, wrap out of line
-    const bool inside = (s.ax >= 0.0f) & (s.ax < p.box[0]) & (s.ay >= 0.0f) & (s.ay < p.box[1]) &
-                        (s.az >= 0.0f) & (s.az < p.box[2]);
+    // 0 <= x < L in ONE unsigned compare per axis: non-negative floats order like their bit
+    // patterns, negative ones (and -0, NaN) have the sign bit set and land on the slow path,
+    // which is exact for them
+    const bool inside = (__float_as_uint(s.ax) < __float_as_uint(p.box[0])) &
+                        (__float_as_uint(s.ay) < __float_as_uint(p.box[1])) &
+                        (__float_as_uint(s.az) < __float_as_uint(p.box[2]));
     if (__builtin_expect(!inside, 0)) {
         s.ax = wrap_slow(s.ax, p.box[0], p.inv_box[0]);
         s.ay = wrap_slow(s.ay, p.box[1], p.inv_box[1]);
@@ -452,9 +456,10 @@ __global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
             stage_row = reinterpret_cast<int2 *>(p.stage) +
                         (chunk * p.n_atoms + a) * (int64_t)p.stage_cap * 3;
         const int stage_cap = p.stage_cap;
-        int32_t t_cur = (int32_t)t0;
+        const int32_t t_first = (int32_t)t0;
 
-        auto process = [&](double f0, double f1, double f2, bool own) {
+        // t_row: frame (inside this shard) of the row being processed -- warp-uniform
+        auto process = [&](double f0, double f1, double f2, bool own, int32_t t_row) {
             Staged st = stage_atom<kDiag>(p, f0, f1, f2);
             int32_t so, si;
             bool multi = false;
@@ -473,27 +478,24 @@ __global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
                 classify<kOneGroup, kBand>(p, s_groups, st, lane_on, so, si, multi, cache, bc);
             }
             const bool d_o = so != prev_o, d_i = si != prev_i;
-            if (d_o) ++n_do;
-            if (d_i) ++n_di;
-            if (d_o | d_i) {
+            if (d_o | d_i) {  // everything a change triggers lives in this (divergent) block
+                if (d_o) ++n_do;
+                if (d_i) ++n_di;
                 // cnt counts the chunk's first row as a pseudo event: real event k is cnt == k + 1
                 if (stage_row != nullptr && cnt >= 1 && cnt <= stage_cap) {
                     int2 *e = stage_row + 3 * (cnt - 1);
                     e[0] = make_int2(a, prev_o);
                     e[1] = make_int2(so, prev_i);
-                    e[2] = make_int2(si, t_cur - 1);
+                    e[2] = make_int2(si, t_row - 1);
                 }
                 ++cnt;
-            }
-            ++t_cur;
-            // a site is visited when a state switches to it (or in mark_all_hits when several
-            // sites contain the atom at once)
-            if (vis_mode == 1) {
-                if (d_o & (so >= 0)) s_vis[so] = 1;
-                if (d_i & (si >= 0)) s_vis[nst + si] = 1;
-            } else if (vis_mode == 2) {
-                if (d_o & (so >= 0)) vis_g[so] = 1;
-                if (d_i & (si >= 0)) vis_g[nst + si] = 1;
+                // a site is visited when a state switches to it (or in mark_all_hits when
+                // several sites contain the atom at once)
+                uint8_t *vis = vis_mode == 1 ? s_vis : vis_g;  // generic pointer: shared or global
+                if (vis_mode != 0) {
+                    if (d_o & (so >= 0)) vis[so] = 1;
+                    if (d_i & (si >= 0)) vis[nst + si] = 1;
+                }
             }
             if (__builtin_expect(multi && vis_mode != 0, 0))
                 mark_all_hits<kOneGroup>(p, s_groups, vis_mode == 1 ? s_vis : vis_g, st);
@@ -541,7 +543,7 @@ __global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
                             gd_tma_load_1d(my_ring + s * kRowDoubles, next_src, row_bytes, &my_full[s]);
                         }
                         next_src += A3;
-                        process(f0, f1, f2, true);
+                        process(f0, f1, f2, true, t_first + k + s);
                     }
                 }
                 phase ^= 1u;
@@ -558,12 +560,12 @@ __global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
                     n1 = __ldg(q + 1);
                     n2 = __ldg(q + 2);
                 }
-                process(f0, f1, f2, true);
+                process(f0, f1, f2, true, t_first + k);
             }
         }
         if (halo_row != nullptr) {
             const double *q = halo_row + 3 * lsrc;
-            process(__ldg(q), __ldg(q + 1), __ldg(q + 2), false);
+            process(__ldg(q), __ldg(q + 1), __ldg(q + 2), false, t_first + n_own);
         }
         if (p.work && lane_on) {
             p.work[(int64_t)a * p.n_chunks + chunk] = cnt - 1;

@@ -20,6 +20,13 @@ for i in range(8):
     if i >= 3:
         ms.append(a.elapsed_time(b))
 t = sum(ms) / len(ms)
+hp.profile_phases = True
+acc = {}
+for i in range(4):
+    hp.run(pos)
+    for k, v in hp.last_phases.items():
+        acc[k] = acc.get(k, 0.0) + v / 4
+phases = {k: round(v, 3) for k, v in acc.items() if k in ('k2_events', 'k3_jumps')}
 print(json.dumps({'grid_k': os.environ.get('GD_GRID_K'), 'spg': os.environ.get('GD_K1_SPG'), 'frames': frames,
                   'k1_ms': round(t, 4), 'GBps': round(32 * frames * rec.n_atoms / t / 1e6, 1),
-                  'blob_bytes': int(hp.grid.h_blob.nbytes)}))
+                  'phases_ms': phases}))
