@@ -314,8 +314,12 @@ def run_extras(args, rec, world, rank, peaks):
     _lib.check(lib.gd_transpose_soa(dv.ptr(cart), T, A, dv.ptr(soa), s))
     torch.cuda.synchronize()
     del cart
-    lo = 1 + args.msd_lags * rank // world
-    hi = 1 + args.msd_lags * (rank + 1) // world
+    # the lag axis is the sharded one (positions replicated): every rank takes its own block of
+    # msd_lags lags (one CTA column of the kernel covers 2048 lags, so smaller blocks per rank
+    # would leave threads idle); the whole job covers msd_lags x world lags
+    n_lags_total = args.msd_lags * world
+    lo = 1 + args.msd_lags * rank
+    hi = lo + args.msd_lags
     msd = dv.empty((A, hi - lo), torch.float64)
 
     def k4():
@@ -324,16 +328,15 @@ def run_extras(args, rec, world, rank, peaks):
     ms = reduce_max(timed(k4, reps=2))
     peak = C.c_double(0.0)
     _lib.check(lib.gd_fp64_peak(1 << 14, C.byref(peak), s))
-    pairs = float(sum(T - k for k in range(1, args.msd_lags + 1))) * A
+    pairs = float(sum(T - k for k in range(1, n_lags_total + 1))) * A
     # atom-averaged curve: every rank holds its lag range -> all-gather of the partial results
     curve = msd.mean(dim=0)
     if world > 1:
-        parts = [torch.empty(((1 + args.msd_lags * (r + 1) // world) - (1 + args.msd_lags * r // world),),
-                             dtype=torch.float64, device='cuda') for r in range(world)]
+        parts = [torch.empty((args.msd_lags,), dtype=torch.float64, device='cuda') for r in range(world)]
         dist.all_gather(parts, curve)
         curve = torch.cat(parts)
     out['msd'] = {
-        'ms': ms, 'lags': args.msd_lags, 'lags_per_s': args.msd_lags / (ms * 1e-3),
+        'ms': ms, 'lags': n_lags_total, 'lags_per_s': n_lags_total / (ms * 1e-3),
         'pair_terms_per_s': pairs / (ms * 1e-3),
         'fp64_inst_per_pair': 6,
         'fp64_peak_dfma_per_s_measured': peak.value * world,
@@ -501,7 +504,7 @@ def run_ours(args):
             'frames_per_step': e2e_frames, 'ms_per_step': 1e3 * e2e_dt,
             'api': 'Trajectory.transitions_between_sites + Transitions.jumps (numpy in, numpy/pandas out)',
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only
             v, cores, units, wall = cpu_reference_parallel(args)
             line['cpu_baseline'] = {
                 'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
