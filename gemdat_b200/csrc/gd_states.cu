@@ -525,28 +525,29 @@ __global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
             }
             const double *next_src = row0 + (int64_t)kStages * A3;  // row k + kStages
             const double *my_row = my_ring + 3 * lsrc;
-            uint32_t phase = 0;
-            for (int k = 0; k < n_own; k += kStages) {
-#pragma unroll
-                for (int s = 0; s < kStages; ++s) {
-                    if (k + s < n_own) {  // warp-uniform
-                        gd_mbar_wait(&my_full[s], phase);
-                        const double *sp = my_row + s * kRowDoubles;
-                        const double f0 = sp[0], f1 = sp[1], f2 = sp[2];
-                        // The slot is refilled by the async proxy (TMA); the reads above are
-                        // generic-proxy LDS.  Order them before the refill (observed on B200
-                        // without the fence: whole warps read the data of a later row).
-                        gd_fence_proxy_async();
-                        __syncwarp();
-                        if (k + s + kStages < n_own && lane == 0) {
-                            gd_mbar_arrive_expect_tx(&my_full[s], row_bytes);
-                            gd_tma_load_1d(my_ring + s * kRowDoubles, next_src, row_bytes, &my_full[s]);
-                        }
-                        next_src += A3;
-                        process(f0, f1, f2, true, t_first + k + s);
-                    }
+            // ONE copy of the row body in the loop (the kernel is ~2000 SASS instructions; with the
+            // ring slots unrolled, four copies of it overflow the instruction cache: +11 % time,
+            // `no_instruction` stalls): slot and phase are computed from the row number instead.
+            // (Folding the halo row into this loop as row n_own was measured too: 6 % slower.)
+            static_assert((kStages & (kStages - 1)) == 0, "kStages must be a power of two");
+#pragma unroll 1
+            for (int k = 0; k < n_own; ++k) {
+                const int s = k & (kStages - 1);
+                const uint32_t phase = (uint32_t)(k / kStages) & 1u;
+                gd_mbar_wait(&my_full[s], phase);
+                const double *sp = my_row + s * kRowDoubles;
+                const double f0 = sp[0], f1 = sp[1], f2 = sp[2];
+                // The slot is refilled by the async proxy (TMA); the reads above are generic-proxy
+                // LDS.  Order them before the refill (observed on B200 without the fence: whole
+                // warps read the data of a later row).
+                gd_fence_proxy_async();
+                __syncwarp();
+                if (k + kStages < n_own && lane == 0) {
+                    gd_mbar_arrive_expect_tx(&my_full[s], row_bytes);
+                    gd_tma_load_1d(my_ring + s * kRowDoubles, next_src, row_bytes, &my_full[s]);
                 }
-                phase ^= 1u;
+                next_src += A3;
+                process(f0, f1, f2, true, t_first + k);
             }
         } else {
             // odd n_atoms: rows are only 8-byte aligned, no bulk copies; register prefetch

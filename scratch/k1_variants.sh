@@ -14,7 +14,5 @@ build() { # name, source stem (gd_states | gd_events | gd_jumps), defines...
   echo "$name built"
 }
 build base gd_states &
-build k1w4c7 gd_states -DGD_K1_WARPS=4 -DGD_K1_MIN_CTAS=7 &
-build k1w2c14 gd_states -DGD_K1_WARPS=2 -DGD_K1_MIN_CTAS=14 &
-build k1w4c6 gd_states -DGD_K1_WARPS=4 -DGD_K1_MIN_CTAS=6 &
+build unrolled gd_states -DGD_K1_UNROLL_STAGES=1 &
 wait
