@@ -48,7 +48,7 @@ constexpr uint32_t kBlobVersion = 4;
 constexpr int kMaxGroups = 64;
 // tuning knobs (scratch/k1_variants.sh builds A/B libraries with -D overrides)
 #ifndef GD_K1_WARPS
-#define GD_K1_WARPS 8
+#define GD_K1_WARPS 4
 #endif
 #ifndef GD_K1_STAGES
 #define GD_K1_STAGES 4
@@ -56,8 +56,16 @@ constexpr int kMaxGroups = 64;
 #ifndef GD_K1_IMAGE_FILTER
 #define GD_K1_IMAGE_FILTER 1
 #endif
+#ifndef GD_K1_EXPECT_HIT
+#define GD_K1_EXPECT_HIT 0
+#endif
+#if GD_K1_EXPECT_HIT
+#define GD_K1_LIKELY(x) __builtin_expect(!!(x), 1)
+#else
+#define GD_K1_LIKELY(x) (x)
+#endif
 #ifndef GD_K1_MIN_CTAS
-#define GD_K1_MIN_CTAS 3
+#define GD_K1_MIN_CTAS 6
 #endif
 constexpr int kWarps = GD_K1_WARPS;  // strips per CTA
 constexpr int kThreads = kWarps * 32;
@@ -467,7 +475,7 @@ __global__ void __launch_bounds__(kThreads, GD_K1_MIN_CTAS)
             // alone decides both states (no table reads)
             const uint32_t c_img = ((uint32_t)cache.natgrp >> kSiteImgShift) & 7u;
             const double d2c = staged_d2(p, cache.x, cache.y, cache.z, st.ax, st.ay, st.az, c_img);
-            if (d2c <= cache.excl2) {
+            if (GD_K1_LIKELY(d2c <= cache.excl2)) {
                 const GdGroupRec &g = kOneGroup ? p.g0 : s_groups[cache.natgrp >> 24];
                 const int natural = cache.natgrp & (int)kRankMask;
                 so = d2c <= g.r2_outer ? natural : GD_NOSITE;
