@@ -1049,6 +1049,9 @@ extern "C" gd_status_t gd_site_states_staged(const double *d_pos_frac, int64_t n
 
     const size_t vis_bytes = 2 * (size_t)h->n_sites_total;
     p.vis_mode = d_visited == nullptr ? 0 : (vis_bytes <= (size_t)kVisSmemMax ? 1 : 2);
+#ifdef GD_K1_PROBE_NO_VIS  // scratch/k1_variants.sh: upper bound of what the visited marks cost
+    p.vis_mode = 0;
+#endif
     p.g0 = *reinterpret_cast<const GdGroupRec *>(static_cast<const unsigned char *>(h_blob) + h->off_groups);
     const size_t smem = (size_t)kWarps * kStages * kRowDoubles * 8 + kWarps * kStages * sizeof(uint64_t) +
                         kMaxGroups * sizeof(GdGroupRec) +

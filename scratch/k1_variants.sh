@@ -14,7 +14,5 @@ build() { # name, source stem (gd_states | gd_events | gd_jumps), defines...
   echo "$name built"
 }
 build base gd_states &
-build w2 gd_states -DGD_K1_WARPS=2 -DGD_K1_MIN_CTAS=12 &
-build w1 gd_states -DGD_K1_WARPS=1 -DGD_K1_MIN_CTAS=24 &
-build w4spg gd_states &
+build novis gd_states -DGD_K1_PROBE_NO_VIS=1 &
 wait
