@@ -26,6 +26,7 @@ GD_ERR_NO_EVENTS = 8
 GD_ERR_NO_JUMPS = 9
 GD_ERR_RANGE = 10
 GD_JUMP_STATE_BYTES = 40
+GD_JUMPS_TAIL_MISMATCH, GD_JUMPS_TAIL_UNPROVEN, GD_JUMPS_TAIL_UNRESOLVED, GD_JUMPS_TAIL_ROWS_OVERFLOW = 1, 2, 4, 8
 
 
 class GemdatB200Error(RuntimeError):
@@ -62,7 +63,7 @@ SIGNATURES = {
     'gd_events_stage_cap': (_i32, [_i64, _i32]),
     'gd_events_stage_elems': (_i64, [_i64, _i32, _i32]),
     'gd_site_states_staged': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _p]),
-    'gd_events_compact': (C.c_int, [_p, _i32, _i64, _i32, _p, _p, _p, _i64, _p, _p]),
+    'gd_events_compact': (C.c_int, [_p, _i32, _i64, _i32, _p, _p, _p, _i64, _p, _i64, _p]),
     'gd_remap_states': (C.c_int, [_p, _i64, _p, _i32, _p]),
     'gd_widen_i32_i64': (C.c_int, [_p, _p, _i64, _p]),
     'gd_events_work_elems': (_i64, [_i64, _i32]),
@@ -74,6 +75,7 @@ SIGNATURES = {
     'gd_jumps_work_bytes': (_i64, [_i64, _i32]),
     'gd_jumps_count': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
     'gd_jumps_fill': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _p]),
+    'gd_jumps_fill_capped': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _i64, _p]),
     'gd_jumps_count_shard': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.c_int, C.c_int, _p, _p, _p, _p,
                                        C.POINTER(_i64), C.POINTER(_i32), _p]),
     'gd_jumps_work_unresolved_offset': (_i64, [_i64, _i32]),

@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(256)
     k_events_compact(const int2 *__restrict__ stage, int32_t cap, Geometry g,
                      const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
                      const int64_t *__restrict__ atom_offsets, int32_t frame0,
-                     int2 *__restrict__ events) {
+                     int2 *__restrict__ events, int64_t row_capacity) {
     const int64_t item = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / kCompactLanes;
     const int sub = threadIdx.x % kCompactLanes;
     if (item >= g.n_chunks * g.n_atoms) return;
@@ -157,6 +157,9 @@ __global__ void __launch_bounds__(256)
     const int32_t first = w[0];
     const int32_t last = (c + 1 < g.n_chunks) ? w[1] : (int32_t)(atom_offsets[a + 1] - atom_offsets[a]);
     const int n_words = 3 * (last - first);
+    // a table smaller than the row count (capacity guessed from an earlier run): write nothing
+    // out of bounds, the caller sees the count and repeats with the right size
+    if (atom_offsets[a] + last > row_capacity) return;
     const int2 *src = stage + (c * g.n_atoms + a) * (int64_t)cap * 3;
     int2 *dst = events + (atom_offsets[a] + first) * 3;
     for (int k = sub; k < n_words; k += kCompactLanes) {
@@ -355,7 +358,7 @@ extern "C" gd_status_t gd_events_count(const int32_t *d_states_outer, const int3
 extern "C" gd_status_t gd_events_scan(int32_t *d_work, int64_t n_frames, int32_t n_atoms,
                                       const uint8_t *d_changed_global, int64_t *d_atom_offsets,
                                       int64_t *h_n_events, void *stream) {
-    GD_REQUIRE(d_work && d_changed_global && d_atom_offsets && h_n_events, GD_ERR_INVALID,
+    GD_REQUIRE(d_work && d_changed_global && d_atom_offsets, GD_ERR_INVALID,
                "gd_events_scan: null argument");
     GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_events_scan: empty input");
     cudaStream_t st = (cudaStream_t)stream;
@@ -367,6 +370,9 @@ extern "C" gd_status_t gd_events_scan(int32_t *d_work, int64_t n_frames, int32_t
     GD_LAUNCH_CHECK();
     k_scan_atoms<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms);
     GD_LAUNCH_CHECK();
+    // asynchronous use: the total stays in d_atom_offsets[n_atoms], the INNER_CONSTANT flag in
+    // d_work[gd_events_work_elems() - 16]; the caller reads both later
+    if (h_n_events == nullptr) return GD_OK;
     int32_t h_err = 0;
     GD_CUDA_CHECK(cudaMemcpyAsync(h_n_events, d_atom_offsets + n_atoms, sizeof(int64_t),
                                   cudaMemcpyDeviceToHost, st));
@@ -400,7 +406,7 @@ extern "C" gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_c
                                          int32_t n_atoms, const int32_t *d_work,
                                          const uint8_t *d_changed_global,
                                          const int64_t *d_atom_offsets, int64_t frame0,
-                                         int32_t *d_events, void *stream) {
+                                         int32_t *d_events, int64_t row_capacity, void *stream) {
     GD_REQUIRE(d_stage && d_work && d_changed_global && d_atom_offsets && d_events, GD_ERR_INVALID,
                "gd_events_compact: null argument");
     GD_REQUIRE(n_frames > 0 && n_atoms > 0 && stage_cap > 0, GD_ERR_INVALID,
@@ -413,7 +419,8 @@ extern "C" gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_c
     const int64_t threads = g.n_chunks * g.n_atoms * kCompactLanes;
     k_events_compact<<<blocks_for(threads, 256), 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const int2 *>(d_stage), stage_cap, g, d_work, d_changed_global,
-        d_atom_offsets, (int32_t)frame0, reinterpret_cast<int2 *>(d_events));
+        d_atom_offsets, (int32_t)frame0, reinterpret_cast<int2 *>(d_events),
+        row_capacity > 0 ? row_capacity : INT64_MAX);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

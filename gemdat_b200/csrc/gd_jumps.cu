@@ -206,16 +206,24 @@ struct SegSpec {  // 48 bytes: result of the speculative run of one segment
 // segment bookkeeping: seg_off[a] = first segment of atom a (exclusive scan of
 // ceil(n_events_a / kSeg)); single block
 __global__ void __launch_bounds__(1024)
-    k_seg_offsets(const int64_t *__restrict__ atom_offsets, int32_t n_atoms, int64_t *__restrict__ seg_off) {
+    k_seg_offsets(const int64_t *__restrict__ atom_offsets, int32_t n_atoms, int64_t *__restrict__ seg_off,
+                  int64_t row_cap, int32_t *__restrict__ flag) {
     __shared__ int64_t warp_tot[32];
     __shared__ int64_t running_s;
-    if (threadIdx.x == 0) running_s = 0;
+    // the table may hold fewer rows than the offsets say (capacity guessed from an earlier run,
+    // the count not read back yet): then there are NO segments, nothing downstream touches a
+    // row, and flag[4] tells the caller to repeat with the right size
+    const bool over = atom_offsets[n_atoms] > row_cap;
+    if (threadIdx.x == 0) {
+        running_s = 0;
+        flag[4] = over ? 1 : 0;
+    }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int base = 0; base < n_atoms; base += 1024) {
         const int idx = base + threadIdx.x;
         int64_t v = 0;  // every atom owns at least one (possibly empty) segment: its last segment
-        if (idx < n_atoms) {  // carries the atom's exit state and the end-of-trajectory close
+        if (idx < n_atoms && !over) {  // carries the atom's exit state and the end-of-trajectory close
             v = (atom_offsets[idx + 1] - atom_offsets[idx] + kSeg - 1) / kSeg;
             if (v < 1) v = 1;
         }
@@ -422,14 +430,14 @@ __global__ void __launch_bounds__(128)
                  const int64_t *__restrict__ seg_off, int32_t n_atoms, int64_t n_frames_total,
                  int64_t minimal_residence, const PackedState *__restrict__ entry,
                  const int64_t *__restrict__ counts, int32_t *__restrict__ jumps,
-                 const int32_t *__restrict__ shard_flag) {
+                 const int32_t *__restrict__ shard_flag, int64_t jump_capacity) {
     const int64_t seg = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int32_t atom;
     int64_t r0;
     int n;
     if (!locate_segment(seg, seg_off, atom_offsets, n_atoms, atom, r0, n)) return;
     const int64_t out0 = counts[seg], out1 = counts[seg + 1];  // exclusive offsets after the scan
-    if (out1 == out0) return;
+    if (out1 == out0 || out1 > jump_capacity) return;  // (a too small table is never overrun)
     JumpMachine m(minimal_residence);
     // `atom` is the index inside this table (an atom block after the event exchange); jump rows
     // carry the atom index of the event rows, also for a candidate inherited from the entry state
@@ -521,8 +529,9 @@ struct JumpWork {
     int64_t *counts;     // [max_segs + 1]
     SegSpec *spec;       // [max_segs]
     PackedState *entry;  // [max_segs]
-    int32_t *flag;       // [4]: [0] parallel chain could not prove a segment's entry state,
-                         //      [1] a published shard record differs from the true exit, [2] is_last_shard
+    int32_t *flag;       // [8]: [0] parallel chain could not prove a segment's entry state,
+                         //      [1] a published shard record differs from the true exit, [2] is_last_shard,
+                         //      [3] unresolved entries (gd_jumps_resolve), [4] more rows than the table holds
     int32_t *atom_flags; // [n_atoms]: kHasEvents | kSynced of this shard's events per atom
     int64_t *tile_tot;   // [max_segs / kScanTile + 1] scan tile totals
     size_t bytes;
@@ -542,7 +551,7 @@ inline JumpWork jump_work(void *base, int64_t n_events, int32_t n_atoms) {
     w.entry = reinterpret_cast<PackedState *>(p + off);
     off += up((size_t)w.max_segs * sizeof(PackedState));
     w.flag = reinterpret_cast<int32_t *>(p + off);
-    off += 16;
+    off += 32;
     w.atom_flags = reinterpret_cast<int32_t *>(p + off);
     off += up((size_t)n_atoms * 4);
     w.tile_tot = reinterpret_cast<int64_t *>(p + off);
@@ -609,9 +618,14 @@ __global__ void __launch_bounds__(256)
 // per-atom exclusive jump offsets from the scanned per-segment counts
 __global__ void __launch_bounds__(256)
     k_atom_jump_offsets(const int64_t *__restrict__ counts, const int64_t *__restrict__ seg_off,
-                        int32_t n_atoms, int64_t *__restrict__ out) {
+                        int32_t n_atoms, int64_t *__restrict__ out, const int32_t *__restrict__ flag,
+                        const int64_t *__restrict__ atom_offsets, int write_tail) {
     const int a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a <= n_atoms) out[a] = counts[seg_off[a]];
+    if (a == 0 && write_tail)  // status word of a pass whose flags are not read back by the host
+        out[n_atoms + 1] = (atom_offsets[n_atoms] << 8) | (flag[1] ? GD_JUMPS_TAIL_MISMATCH : 0) |
+                           (flag[0] ? GD_JUMPS_TAIL_UNPROVEN : 0) | (flag[3] ? GD_JUMPS_TAIL_UNRESOLVED : 0) |
+                           (flag[4] ? GD_JUMPS_TAIL_ROWS_OVERFLOW : 0);
 }
 
 // a record published as known (entry independent, or run from a known entry) must equal the
@@ -674,7 +688,8 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
     const PackedState *entry = static_cast<const PackedState *>(d_entry);
     PackedState *exit_rec = static_cast<PackedState *>(d_exit);
     if (!reuse_work) {  // segment bookkeeping + speculation: independent of the entry records
-        k_seg_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms, w.seg_off);
+        GD_CUDA_CHECK(cudaMemsetAsync(w.flag, 0, 32, st));  // incl. flag[3]: no unresolved entries yet
+        k_seg_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, n_atoms, w.seg_off, n_events, w.flag);
         GD_LAUNCH_CHECK();
         GD_CUDA_CHECK(cudaMemsetAsync(w.atom_flags, 0, (size_t)n_atoms * 4, st));
         k_jumps_spec<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
@@ -689,17 +704,42 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
     // GD_JUMPS_SEQUENTIAL=1 forces the sequential chain (tests / A-B timing)
     const char *env = getenv("GD_JUMPS_SEQUENTIAL");
     bool sequential = env && atoi(env) != 0;
-    int32_t h_flag[4] = {0, 0, 0, 0};
-    if (!h_n_jumps && !h_flags && !sequential) {
+    int32_t h_flag[5] = {0, 0, 0, 0, 0};
+    if (!h_n_jumps && !h_flags && !sequential && !d_atom_jump_offsets) {
         // asynchronous pass: only the exit records are wanted.  The chain's proof is not read
         // back; atoms with an unproven segment publish "not known" instead (k_exit_finish).
-        GD_REQUIRE(exit_rec && !d_atom_jump_offsets && !d_published, GD_ERR_INVALID,
+        GD_REQUIRE(exit_rec && !d_published, GD_ERR_INVALID,
                    "gd_jumps_count_shard: an asynchronous pass only produces d_exit");
         k_jumps_chain_par<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
             d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
             w.spec, w.entry, w.counts, w.flag, entry, exit_rec, w.atom_flags, is_last_shard);
         GD_LAUNCH_CHECK();
         k_exit_finish<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(exit_rec, w.atom_flags, n_atoms);
+        GD_LAUNCH_CHECK();
+        return GD_OK;
+    }
+    if (!h_n_jumps && !h_flags && !sequential) {
+        // asynchronous FINAL pass: counts, per-atom offsets and a status word (d_atom_jump_offsets
+        // [n_atoms + 1]) are left on the device; the caller reads them when it reads the jump
+        // offsets anyway and repeats with a checked pass if a status bit is set.
+        k_jumps_chain_par<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, st>>>(
+            d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence,
+            w.spec, w.entry, w.counts, w.flag, entry, exit_rec, w.atom_flags, is_last_shard);
+        GD_LAUNCH_CHECK();
+        const unsigned n_tiles = (unsigned)gd_ceil_div(w.max_segs, kScanTile);
+        k_scan_tiles<<<n_tiles, 1024, 0, st>>>(w.counts, w.max_segs, w.tile_tot);
+        GD_LAUNCH_CHECK();
+        k_scan_add<<<n_tiles, 1024, 0, st>>>(w.counts, w.max_segs, w.tile_tot);
+        GD_LAUNCH_CHECK();
+        if (d_published) {
+            k_check_published<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(
+                exit_rec, static_cast<const PackedState *>(d_published), n_atoms, w.flag);
+            GD_LAUNCH_CHECK();
+        }
+        k_atom_jump_offsets<<<(unsigned)gd_ceil_div(n_atoms + 1, 256), 256, 0, st>>>(
+            w.counts, w.seg_off, n_atoms, d_atom_jump_offsets, w.flag, d_atom_offsets, 1);
+        GD_LAUNCH_CHECK();
+        k_exit_finish<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(nullptr, w.atom_flags, n_atoms);
         GD_LAUNCH_CHECK();
         return GD_OK;
     }
@@ -721,7 +761,7 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
         GD_LAUNCH_CHECK();
         if (d_atom_jump_offsets) {
             k_atom_jump_offsets<<<(unsigned)gd_ceil_div(n_atoms + 1, 256), 256, 0, st>>>(
-                w.counts, w.seg_off, n_atoms, d_atom_jump_offsets);
+                w.counts, w.seg_off, n_atoms, d_atom_jump_offsets, w.flag, d_atom_offsets, 0);
             GD_LAUNCH_CHECK();
         }
         if (d_published) {
@@ -732,7 +772,7 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
         if (h_n_jumps)
             GD_CUDA_CHECK(cudaMemcpyAsync(h_n_jumps, w.counts + w.max_segs, sizeof(int64_t),
                                           cudaMemcpyDeviceToHost, st));
-        GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        GD_CUDA_CHECK(cudaMemcpyAsync(h_flag, w.flag, 5 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
         GD_CUDA_CHECK(cudaStreamSynchronize(st));
         if (sequential || h_flag[0] == 0) break;
         // some segment's entry state could not be proven: redo with the sequential chain
@@ -745,7 +785,7 @@ extern "C" gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64
         k_exit_finish<<<(unsigned)gd_ceil_div(n_atoms, 256), 256, 0, st>>>(nullptr, w.atom_flags, n_atoms);
         GD_LAUNCH_CHECK();
     }
-    if (h_flags) *h_flags = (sequential ? 1 : 0) | (h_flag[1] ? 2 : 0) | (h_flag[3] ? 4 : 0);
+    if (h_flags) *h_flags = (sequential ? 1 : 0) | (h_flag[1] ? 2 : 0) | (h_flag[3] ? 4 : 0) | (h_flag[4] ? 8 : 0);
     return GD_OK;
 }
 
@@ -785,19 +825,27 @@ extern "C" int64_t gd_jumps_work_unresolved_offset(int64_t n_events, int32_t n_a
     return (int64_t)(reinterpret_cast<const unsigned char *>(w.flag + 3) - static_cast<const unsigned char *>(nullptr));
 }
 
+extern "C" gd_status_t gd_jumps_fill_capped(const int32_t *d_events, const int64_t *d_atom_offsets,
+                                            int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                            int64_t minimal_residence, const void *d_work,
+                                            int32_t *d_jumps, int64_t jump_capacity, void *stream) {
+    GD_REQUIRE(d_atom_offsets && d_work && d_jumps, GD_ERR_INVALID, "gd_jumps_fill: null argument");
+    GD_REQUIRE(n_atoms > 0 && n_events >= 0 && (n_events == 0 || d_events) && jump_capacity >= 0,
+               GD_ERR_INVALID, "gd_jumps_fill: bad size");
+    const JumpWork w = jump_work(const_cast<void *>(d_work), n_events, n_atoms);
+    k_jumps_fill<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, (cudaStream_t)stream>>>(
+        d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence, w.entry,
+        w.counts, d_jumps, w.flag, jump_capacity);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
 extern "C" gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets,
                                      int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
                                      int64_t minimal_residence, const void *d_work,
                                      int32_t *d_jumps, void *stream) {
-    GD_REQUIRE(d_atom_offsets && d_work && d_jumps, GD_ERR_INVALID, "gd_jumps_fill: null argument");
-    GD_REQUIRE(n_atoms > 0 && n_events >= 0 && (n_events == 0 || d_events), GD_ERR_INVALID,
-               "gd_jumps_fill: bad size");
-    const JumpWork w = jump_work(const_cast<void *>(d_work), n_events, n_atoms);
-    k_jumps_fill<<<(unsigned)gd_ceil_div(w.max_segs, 128), 128, 0, (cudaStream_t)stream>>>(
-        d_events, d_atom_offsets, w.seg_off, n_atoms, n_frames_total, minimal_residence, w.entry,
-        w.counts, d_jumps, w.flag);
-    GD_LAUNCH_CHECK();
-    return GD_OK;
+    return gd_jumps_fill_capped(d_events, d_atom_offsets, n_events, n_atoms, n_frames_total,
+                                minimal_residence, d_work, d_jumps, INT64_MAX, stream);
 }
 
 extern "C" gd_status_t gd_pair_matrix(const int32_t *d_rows, int64_t n_rows, int32_t row_stride,

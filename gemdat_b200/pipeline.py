@@ -139,6 +139,11 @@ class HotPath:
         self.comm = Comm(world, group)
         self.launches_per_run = 0
         self._jump_cap = 0  # rows per rank reserved in the final jump gather (grows with what is seen)
+        self._cap_events = 0  # event rows of this rank's table, remembered for the optimistic pass
+        # GD_OPTIMISTIC=0: always the checked pass (A/B)
+        self.optimistic = os.environ.get('GD_OPTIMISTIC', '1') not in ('', '0')
+        self.last_pass = 'none'
+        self.last_optimistic_reject = None
         self.last_k1_events = None
         # GD_K3_EXCHANGE=1: always exchange the event rows by atom block (the fallback route; A/B)
         self.k3_exchange = os.environ.get('GD_K3_EXCHANGE', '0') not in ('', '0')
@@ -172,7 +177,9 @@ class HotPath:
         self._t_mark = now
 
     # ------------------------------------------------------------------ the pass
-    def run(self, pos: torch.Tensor) -> dict:
+    def _launch_k1(self, pos: torch.Tensor):
+        """K1 on this rank's frames (states, event counts, staged event rows, flags); nothing is
+        read back.  Returns the tensors the rest of the pass works on."""
         lib = _lib.lib
         s = dv.stream_ptr()
         n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
@@ -225,6 +232,30 @@ class HotPath:
         self.last_k1_events = (e0, e1)
         launches += 1
         self._mark('k1_site_states')
+        from types import SimpleNamespace
+        return SimpleNamespace(outer=outer, inner=inner, band=band, pack=pack, visited=visited, changed=changed,
+                               overflow=overflow, work=work, stage=stage, cap=cap, n_vis=n_vis, o_chg=o_chg,
+                               o_ovf=o_ovf, launches=launches, n_frames=n_frames, n_atoms=n_atoms)
+
+    def run(self, pos: torch.Tensor) -> dict:
+        """One pass of the hot path over this rank's frames.  With capacities remembered from an
+        earlier run the whole pass is queued without reading anything back (`_run_optimistic`: one
+        host synchronisation at the very end); whatever it cannot prove there -- a table that
+        outgrew its remembered size, an unresolved jump-machine entry, the Q2 remap, an error
+        condition -- is redone by the checked pass below, which reads every count where it needs it."""
+        if self.optimistic and self._cap_events > 0:
+            res = self._run_optimistic(pos)
+            if res is not None:
+                return res
+        return self._run_checked(pos)
+
+    def _run_checked(self, pos: torch.Tensor) -> dict:
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        k1 = self._launch_k1(pos)
+        outer, inner, band, pack, visited, changed = k1.outer, k1.inner, k1.band, k1.pack, k1.visited, k1.changed
+        work, stage, cap, n_vis, o_chg, o_ovf = k1.work, k1.stage, k1.cap, k1.n_vis, k1.o_chg, k1.o_ovf
+        launches, n_frames, n_atoms = k1.launches, k1.n_frames, k1.n_atoms
 
         # ---- what K2 needs from the other shards, in ONE exchange: the OR of the visited flags
         # (warning + Q2 LUT are global), of the "state ever changes" flags (Q4 "atom is skipped" is
@@ -272,7 +303,7 @@ class HotPath:
         self.last_events_route = 'none'
         if n_events.value and staged_ok and not remapped:
             _lib.check(lib.gd_events_compact(dv.ptr(stage), cap, n_frames, n_atoms, dv.ptr(work),
-                                             dv.ptr(changed), dv.ptr(offsets), self.frame0, dv.ptr(rows), s))
+                                             dv.ptr(changed), dv.ptr(offsets), self.frame0, dv.ptr(rows), 0, s))
             launches += 1
             self.last_events_route = 'staged'
         elif n_events.value:
@@ -313,7 +344,124 @@ class HotPath:
         self._mark('k3_jumps')
         res['n_jumps'] = int(res['jumps'].shape[0])
         self.launches_per_run = launches
+        self.last_pass = 'checked'
+        if res['events_layout'] != 'atom_block':
+            self._cap_events = max(self._cap_events, n_events.value + n_events.value // 8 + 1024)
+        if self.world == 1:
+            self._jump_cap = max(self._jump_cap, res['n_jumps'] + res['n_jumps'] // 4 + 16)
         return res
+
+    def _run_optimistic(self, pos: torch.Tensor):
+        """The whole pass queued on the stream with table sizes remembered from an earlier run:
+        K1 -> (flag OR over ranks, on the device) -> K2 scan + compact into a table of
+        `_cap_events` rows -> K3 first pass -> record all-gather -> resolve -> K3 final pass ->
+        fill into `_jump_cap` rows -> ONE all-gather of offsets + status + rows -> ONE host read.
+        Returns None (every rank takes the same decision: all status words are gathered and the
+        flag buffer is OR-ed over ranks) when anything needs the checked pass."""
+        lib = _lib.lib
+        s = dv.stream_ptr()
+        W, me = self.world, self.rank
+        k1 = self._launch_k1(pos)
+        n_frames, n_atoms, launches = k1.n_frames, k1.n_atoms, k1.launches
+        if k1.stage is None:
+            return None
+        if W > 1:
+            k1.pack.copy_(self.comm.all_gather(k1.pack).amax(dim=0))
+        # ---- K2: nothing read back; the row count stays in offsets[n_atoms]
+        offsets = self._tensor('offsets', (n_atoms + 1,), torch.int64)
+        _lib.check(lib.gd_events_scan(dv.ptr(k1.work), n_frames, n_atoms, dv.ptr(k1.changed), dv.ptr(offsets),
+                                      None, s))
+        ecap = self._cap_events
+        rows = self._tensor('rows_cap', (ecap, 6), torch.int32)
+        _lib.check(lib.gd_events_compact(dv.ptr(k1.stage), k1.cap, n_frames, n_atoms, dv.ptr(k1.work),
+                                         dv.ptr(k1.changed), dv.ptr(offsets), self.frame0, dv.ptr(rows), ecap, s))
+        launches += 3
+        self._mark('k2_events')
+        # ---- K3 on the capacity-sized table
+        last = 1 if me + 1 == W else 0
+        nbytes = _lib.GD_JUMP_STATE_BYTES
+        jwork = self._tensor('jwork', (int(lib.gd_jumps_work_bytes(ecap, n_atoms)),), torch.uint8)
+        exit_rec = self._tensor('jexit', (n_atoms, nbytes), torch.uint8)
+        entry = self._tensor('jentry', (n_atoms, nbytes), torch.uint8)
+        args = (dv.ptr(rows), dv.ptr(offsets), ecap, n_atoms, self.n_frames_total, self.minimal_residence)
+        head = 2 * (n_atoms + 3)  # int64: jump offsets [A + 1] | status word | K2 error flag
+        jcap = self._jump_cap
+        jbuf = self._tensor('jbuf_opt', (head + jcap * 6,), torch.int32)
+        atom_off = jbuf[:head].view(torch.int64)
+        published = None
+        if W > 1:
+            entry.zero_()
+            _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if me else None, last, 0, None,
+                                                dv.ptr(jwork), dv.ptr(exit_rec), None, None, None, s))
+            allrec = self.comm.all_gather(exit_rec)  # [W, A, 40]
+            published = allrec[me].contiguous()
+            d_unresolved = jwork.data_ptr() + int(lib.gd_jumps_work_unresolved_offset(ecap, n_atoms))
+            _lib.check(lib.gd_jumps_resolve(dv.ptr(allrec), W, me, n_atoms, dv.ptr(entry), d_unresolved, None, s))
+            launches += 7
+        _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if W > 1 else None, last, 1 if W > 1 else 0,
+                                            dv.ptr(published), dv.ptr(jwork), dv.ptr(exit_rec), dv.ptr(atom_off),
+                                            None, None, s))
+        jumps = jbuf[head:].view(jcap, 6)
+        if jcap:
+            _lib.check(lib.gd_jumps_fill_capped(*args, dv.ptr(jwork), dv.ptr(jumps), jcap, s))
+        # the INNER_CONSTANT flag of the scan travels with the status words
+        n_work = int(lib.gd_events_work_elems(n_frames, n_atoms))
+        jbuf[head - 2: head - 1].copy_(k1.work[n_work - 16: n_work - 15])
+        launches += 8
+        allb = self.comm.all_gather(jbuf) if W > 1 else jbuf.unsqueeze(0)
+        all_off = dv.to_host(allb[:, :head].contiguous().view(torch.int64))  # [W, A + 3]  <- the one sync
+        host = dv.to_host(k1.pack)
+        self._mark('k3_jumps')
+        status, k2_err = all_off[:, n_atoms + 1], all_off[:, n_atoms + 2]
+        n_jumps_rank = all_off[:, n_atoms]
+        n_local = int(status[me] >> 8)
+        vis = host[: k1.n_vis].astype(bool).reshape(2, self.n_sites)
+        why = None  # the first reason to hand the pass to the checked route (same on every rank)
+        if (status & 0xFF).any():
+            why = f'jump pass status {int(np.bitwise_or.reduce(status & 0xFF))}'
+        elif (k2_err & 0xFFFFFFFF).any():
+            why = 'outer state changes but inner never does'
+        elif int(n_jumps_rank.max()) > jcap:
+            why = 'jump table outgrew its remembered size'
+        elif host[k1.o_ovf: k1.o_ovf + 4].any():
+            why = 'event staging overflow'
+        elif not host[k1.o_chg: k1.o_chg + n_atoms].any():
+            why = 'no outer state change'
+        elif any(self.grid.remap_lut(v) is not None for v in vis):
+            why = 'Q2 remap'
+        self.last_optimistic_reject = why
+        if why is not None:
+            return None
+        for v in vis:
+            for label, key in zip(self.grid.group_labels, self.grid.group_keys):
+                if not (v.any() if key is None else v[key].any()):
+                    radius = self.radius[label]
+                    warnings.warn(f'No floating species in range of {label} ({radius=})', stacklevel=3)
+        counts = np.diff(all_off[:, : n_atoms + 1], axis=1)
+        if W > 1:
+            total_off, dst_start = merge_plan(counts)
+            merged = dv.empty((max(int(total_off[-1]), 1), 6), torch.int32)
+            d_plan = dv.to_device(np.ascontiguousarray(np.concatenate([all_off[:, : n_atoms + 1], dst_start], axis=1)))
+            for r in range(W):
+                if n_jumps_rank[r]:
+                    _lib.check(lib.gd_events_merge(dv.ptr(allb[r, head:]), dv.ptr(d_plan[r]),
+                                                   dv.ptr(d_plan[r, n_atoms + 1:]), n_atoms, dv.ptr(merged), s))
+                    launches += 1
+            jumps_out = merged[: int(total_off[-1])]
+        else:
+            jumps_out = jumps[: int(n_jumps_rank[0])].clone()
+        self._mark('k3_merge')
+        self._cap_events = max(self._cap_events, n_local + n_local // 8 + 1024)
+        most = int(n_jumps_rank.max())
+        self._jump_cap = max(self._jump_cap, most + most // 4 + 16)
+        self.last_n_local_events = n_local
+        self.last_events_route = 'staged'
+        self.launches_per_run = launches
+        self.last_pass = 'optimistic'
+        return {'outer': k1.outer, 'inner': k1.inner, 'visited': vis, 'band': k1.band,
+                'events': rows[:n_local], 'atom_offsets': offsets,
+                'events_layout': 'frame_shard' if W > 1 else 'whole', 'jumps': jumps_out,
+                'n_events': int((status >> 8).sum()), 'n_jumps': int(jumps_out.shape[0])}
 
     # ------------------------------------------------------------------ pieces of the pass
     def _jumps_local(self, rows, offsets, n_block):
@@ -359,6 +507,7 @@ class HotPath:
         _lib.check(lib.gd_jumps_count_shard(*args, dv.ptr(entry) if me else None, last, 0, None, dv.ptr(jwork),
                                             dv.ptr(exit_rec), None, None, None, s))
         launches += 5
+        self._mark('k3a_pass1')
         d_unresolved = jwork.data_ptr() + int(lib.gd_jumps_work_unresolved_offset(n_local, n_atoms))
         # one buffer for the final gather: per-atom jump offsets [A + 1] + (mismatch, event count)
         # word as int64, then room for `cap` jump rows -- cap remembered from earlier runs, so that
@@ -371,6 +520,7 @@ class HotPath:
         published = None
         for _ in range(W):
             allrec = self.comm.all_gather(exit_rec)  # [W, A, 40]
+            self._mark('k3b_gather_records')
             if published is None:
                 published = allrec[me].contiguous()
             # entry records from all shards' exits, then (optimistically, same synchronisation)
@@ -380,6 +530,7 @@ class HotPath:
                                                 dv.ptr(exit_rec), dv.ptr(atom_off), C.byref(n_jumps),
                                                 C.byref(flags), s))
             launches += 6
+            self._mark('k3c_final_count')
             if not flags.value & 4:
                 break
             # some shard has events of an atom but no departure among them (or an unproven chain):
@@ -392,13 +543,15 @@ class HotPath:
         if n_jumps.value:
             _lib.check(lib.gd_jumps_fill(*args, dv.ptr(jwork), dv.ptr(jumps), s))
             launches += 1
-        atom_off[n_atoms + 1] = (n_local << 1) | (1 if flags.value & 2 else 0)
+        atom_off[n_atoms + 1] = (n_local << 8) | (_lib.GD_JUMPS_TAIL_MISMATCH if flags.value & 2 else 0)
+        self._mark('k3d_fill')
         allb = self.comm.all_gather(jbuf)  # [W, head + cap * 6]
         all_off = dv.to_host(allb[:, :head].contiguous().view(torch.int64))  # [W, A + 2]
+        self._mark('k3e_gather_jumps')
         tail = all_off[:, -1]
         if (tail & 1).any():
             return None
-        n_events_global = int((tail >> 1).sum())
+        n_events_global = int((tail >> 8).sum())
         all_off = all_off[:, : n_atoms + 1]
         counts = np.diff(all_off, axis=1)
         most = int(all_off[:, -1].max())

@@ -171,7 +171,9 @@ gd_status_t gd_events_count(const int32_t *d_states_outer, const int32_t *d_stat
  * this shard in *h_n_events and the status of the reference's error paths
  * (GD_ERR_INNER_CONSTANT, GD_ERR_NO_EVENTS is left to the caller because it
  * is a whole-trajectory property).  d_atom_offsets [n_atoms+1] int64 receives
- * the first row of every atom.  Synchronises the stream. */
+ * the first row of every atom.  Synchronises the stream -- unless h_n_events is NULL:
+ * then the total stays in d_atom_offsets[n_atoms] and the GD_ERR_INNER_CONSTANT condition
+ * in d_work[gd_events_work_elems() - 16] (non-zero) for the caller to read later. */
 gd_status_t gd_events_scan(int32_t *d_work, int64_t n_frames, int32_t n_atoms,
                            const uint8_t *d_changed_global, int64_t *d_atom_offsets,
                            int64_t *h_n_events, void *stream);
@@ -196,11 +198,13 @@ gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom
 /* The fill for rows staged by gd_site_states_staged: copies every (frame chunk, atom)
  * segment's rows to their place in the table (same layout and order as gd_events_fill) and
  * adds frame0 to the time column.  d_work / d_changed_global / d_atom_offsets as left by
- * gd_events_scan.  Moves 2 x 24 B per event instead of re-reading 8 B per atom-frame. */
+ * gd_events_scan.  Moves 2 x 24 B per event instead of re-reading 8 B per atom-frame.
+ * row_capacity > 0: d_events holds that many rows (a size remembered from an earlier run, the
+ * count not yet read back); rows beyond it are not written. */
 gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_cap, int64_t n_frames,
                               int32_t n_atoms, const int32_t *d_work,
                               const uint8_t *d_changed_global, const int64_t *d_atom_offsets,
-                              int64_t frame0, int32_t *d_events, void *stream);
+                              int64_t frame0, int32_t *d_events, int64_t row_capacity, void *stream);
 
 /* ffill (direction=+1, states_prev) / bfill (direction=-1, states_next) along the
  * frame axis.  d_carry_in [n_atoms] (may be NULL) is the last valid state before
@@ -262,11 +266,21 @@ gd_status_t gd_jumps_fill(const int32_t *d_events, const int64_t *d_atom_offsets
  * is_last_shard: close pending candidates at n_frames_total (jumps.py:97-105) -- only the
  * shard holding the trajectory's last frame does.  *h_flags: bit 0 the sequential chain
  * ran, bit 1 a record published as known differs from the true exit state (event tables
- * that are not state-consistent: fall back to exchanging the events), bit 2 see above.
+ * that are not state-consistent: fall back to exchanging the events), bit 2 see above,
+ * bit 3 d_atom_offsets says more rows than n_events (nothing was done).
  * reuse_work != 0: d_work still holds the segment speculation of an earlier call on the same
  * table (passes 2.. of the protocol skip it).  Calls with h_n_jumps or h_flags synchronise
  * (the time-parallel chain's proof flag is read back). */
 #define GD_JUMP_STATE_BYTES 40
+/* Asynchronous FINAL pass (h_n_jumps = h_flags = NULL, d_atom_jump_offsets given, [n_atoms + 2]):
+ * nothing is read back; d_atom_jump_offsets[n_atoms] is the jump count and [n_atoms + 1] a status
+ * word = (rows of this shard << 8) | GD_JUMPS_TAIL_* bits.  n_events is then the CAPACITY of
+ * d_events (a size remembered from an earlier run): with more rows than that the pass does
+ * nothing and sets GD_JUMPS_TAIL_ROWS_OVERFLOW.  Any bit set: repeat with a checked pass. */
+#define GD_JUMPS_TAIL_MISMATCH 1      /* a record published as known differs from the truth */
+#define GD_JUMPS_TAIL_UNPROVEN 2      /* the time-parallel chain could not prove a segment  */
+#define GD_JUMPS_TAIL_UNRESOLVED 4    /* gd_jumps_resolve left entries unknown              */
+#define GD_JUMPS_TAIL_ROWS_OVERFLOW 8 /* more event rows than n_events                      */
 gd_status_t gd_jumps_count_shard(const int32_t *d_events, const int64_t *d_atom_offsets,
                                  int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
                                  int64_t minimal_residence, const void *d_entry, int is_last_shard,
@@ -279,6 +293,13 @@ int64_t gd_jumps_work_unresolved_offset(int64_t n_events, int32_t n_atoms);
 gd_status_t gd_jumps_resolve(const void *d_all_records, int32_t world, int32_t rank, int32_t n_atoms,
                              void *d_entry, int32_t *d_unresolved, int32_t *h_unresolved,
                              void *stream);
+
+/* gd_jumps_fill into a table of jump_capacity rows (a size remembered from an earlier run, the
+ * count not read back yet): segments whose jumps would not fit are not written. */
+gd_status_t gd_jumps_fill_capped(const int32_t *d_events, const int64_t *d_atom_offsets,
+                                 int64_t n_events, int32_t n_atoms, int64_t n_frames_total,
+                                 int64_t minimal_residence, const void *d_work, int32_t *d_jumps,
+                                 int64_t jump_capacity, void *stream);
 
 /* (start, destination) count matrix: _calculate_transitions_matrix,
  * src/gemdat/transitions.py:812-834.  d_rows [n_rows,row_stride] int32 with the

@@ -688,6 +688,44 @@ def test_hotpath_staged_events_equal_reread_and_oracle(monkeypatch, n_frames, n_
     assert_array_equal(tables['1'], exp)
 
 
+def test_hotpath_optimistic_pass_equals_checked_pass(monkeypatch):
+    """With table sizes remembered from an earlier run HotPath queues the whole pass without
+    reading anything back (one synchronisation at the end).  Same tables as the checked pass;
+    a table that outgrew its remembered size, or jumps that do, send it back to the checked pass."""
+    from gemdat_b200 import synth
+    from gemdat_b200.pipeline import HotPath
+
+    monkeypatch.setenv('GD_EVENTS_STAGE_CAP', '32')  # chunks are 32 frames here: staging never overflows
+    rec = synth.config_c3(n_frames=6000)  # (departures are frequent: the time-parallel chain proves itself)
+    pos = rec.device_positions(0, 6000)
+    hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=rec.n_atoms, site_radius=0.6,
+                 site_inner_fraction=0.5, minimal_residence=3, n_frames_total=6000)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        first = hp.run(pos)
+        assert hp.last_pass == 'checked'
+        ref = {k: first[k].cpu().numpy().copy() for k in ('outer', 'inner', 'events', 'jumps')}
+        assert len(ref['events']) > 500 and len(ref['jumps']) > 5
+        second = hp.run(pos)
+        assert hp.last_pass == 'optimistic', hp.last_optimistic_reject
+        for k, v in ref.items():
+            assert_array_equal(second[k].cpu().numpy(), v)
+        assert second['n_events'] == len(ref['events']) and second['n_jumps'] == len(ref['jumps'])
+        hp._cap_events = len(ref['events']) - 7     # the event table no longer fits
+        third = hp.run(pos)
+        assert hp.last_pass == 'checked' and 'status 8' in hp.last_optimistic_reject
+        assert_array_equal(third['events'].cpu().numpy(), ref['events'])
+        assert_array_equal(third['jumps'].cpu().numpy(), ref['jumps'])
+        hp._jump_cap = len(ref['jumps']) - 1        # the jump table no longer fits
+        fourth = hp.run(pos)
+        assert hp.last_pass == 'checked' and 'jump table' in hp.last_optimistic_reject
+        assert_array_equal(fourth['jumps'].cpu().numpy(), ref['jumps'])
+        fifth = hp.run(pos)
+        assert hp.last_pass == 'optimistic', hp.last_optimistic_reject
+        assert_array_equal(fifth['jumps'].cpu().numpy(), ref['jumps'])
+        assert_array_equal(fifth['events'].cpu().numpy(), ref['events'])
+
+
 @pytest.mark.parametrize('n_atoms', [48, 33])
 def test_pipelined_host_path_equals_resident_path(monkeypatch, n_atoms):
     """Host numpy input large enough for the upload / K1 / download pipeline (forced here) gives
