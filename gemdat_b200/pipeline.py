@@ -144,6 +144,10 @@ class HotPath:
         self.optimistic = os.environ.get('GD_OPTIMISTIC', '1') not in ('', '0')
         self.last_pass = 'none'
         self.last_optimistic_reject = None
+        # GD_GRAPH=0: launch the optimistic pass kernel by kernel instead of replaying a CUDA graph
+        self.use_graph = os.environ.get('GD_GRAPH', '1') not in ('', '0')
+        self._graph = self._graph_key = self._graph_state = self._eager_key = None
+        self.last_launch_mode = 'eager'
         self.last_k1_events = None
         # GD_K3_EXCHANGE=1: always exchange the event rows by atom block (the fallback route; A/B)
         self.k3_exchange = os.environ.get('GD_K3_EXCHANGE', '0') not in ('', '0')
@@ -177,7 +181,7 @@ class HotPath:
         self._t_mark = now
 
     # ------------------------------------------------------------------ the pass
-    def _launch_k1(self, pos: torch.Tensor):
+    def _launch_k1(self, pos: torch.Tensor, timed: bool = True):
         """K1 on this rank's frames (states, event counts, staged event rows, flags); nothing is
         read back.  Returns the tensors the rest of the pass works on."""
         lib = _lib.lib
@@ -221,15 +225,17 @@ class HotPath:
             cap = int(os.environ.get('GD_EVENTS_STAGE_CAP', '0')) or int(lib.gd_events_stage_cap(n_frames, n_atoms))
         if cap > 0:
             stage = self._tensor('stage', (int(lib.gd_events_stage_elems(n_frames, n_atoms, cap)),), torch.int32)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
+        if timed:  # (timing events cannot be recorded inside a graph capture)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         _lib.check(lib.gd_site_states_staged(dv.ptr(pos), n_frames, n_atoms, dv.ptr(next_pos),
                                              dv.ptr(self.grid.d_blob), self.grid.h_blob.ctypes.data,
                                              dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band),
                                              dv.ptr(work), dv.ptr(changed), dv.ptr(stage), cap,
                                              dv.ptr(overflow) if stage is not None else None, s))
-        e1.record()
-        self.last_k1_events = (e0, e1)
+        if timed:
+            e1.record()
+            self.last_k1_events = (e0, e1)
         launches += 1
         self._mark('k1_site_states')
         from types import SimpleNamespace
@@ -351,8 +357,9 @@ class HotPath:
             self._jump_cap = max(self._jump_cap, res['n_jumps'] + res['n_jumps'] // 4 + 16)
         return res
 
-    def _run_optimistic(self, pos: torch.Tensor):
-        """The whole pass queued on the stream with table sizes remembered from an earlier run:
+    def _enqueue_optimistic(self, pos: torch.Tensor, timed: bool):
+        """Everything of the optimistic pass that needs no host decision (capturable in a CUDA
+        graph): the whole pass queued on the stream with table sizes remembered from an earlier run:
         K1 -> (flag OR over ranks, on the device) -> K2 scan + compact into a table of
         `_cap_events` rows -> K3 first pass -> record all-gather -> resolve -> K3 final pass ->
         fill into `_jump_cap` rows -> ONE all-gather of offsets + status + rows -> ONE host read.
@@ -361,10 +368,9 @@ class HotPath:
         lib = _lib.lib
         s = dv.stream_ptr()
         W, me = self.world, self.rank
-        k1 = self._launch_k1(pos)
+        k1 = self._launch_k1(pos, timed=timed)
         n_frames, n_atoms, launches = k1.n_frames, k1.n_atoms, k1.launches
-        if k1.stage is None:
-            return None
+        assert k1.stage is not None
         if W > 1:
             k1.pack.copy_(self.comm.all_gather(k1.pack).amax(dim=0))
         # ---- K2: nothing read back; the row count stays in offsets[n_atoms]
@@ -409,7 +415,43 @@ class HotPath:
         jbuf[head - 2: head - 1].copy_(k1.work[n_work - 16: n_work - 15])
         launches += 8
         allb = self.comm.all_gather(jbuf) if W > 1 else jbuf.unsqueeze(0)
-        all_off = dv.to_host(allb[:, :head].contiguous().view(torch.int64))  # [W, A + 3]  <- the one sync
+        heads = allb[:, :head].contiguous().view(torch.int64)  # [W, A + 3]
+        from types import SimpleNamespace
+        return SimpleNamespace(k1=k1, offsets=offsets, rows=rows, jbuf=jbuf, jumps=jumps, allb=allb, heads=heads,
+                               head=head, jcap=jcap, launches=launches)
+
+    def _run_optimistic(self, pos: torch.Tensor):
+        """Optimistic pass = `_enqueue_optimistic` (eagerly the first time, then replayed as ONE
+        CUDA graph launch: the ~60 small launches and collectives of a step are launch bound when
+        a rank's shard is small) + one host read + the per-atom merge of the gathered jump rows."""
+        lib = _lib.lib
+        W, me = self.world, self.rank
+        if not self.stage_events:
+            return None
+        key = (pos.data_ptr(), tuple(pos.shape), self._cap_events, self._jump_cap)
+        graphable = self.use_graph and not self.profile_phases and (W == 1 or self.comm.direct)
+        if graphable and self._graph_key == key and self._graph is not None:
+            self._graph.replay()
+            st = self._graph_state
+            self.last_launch_mode = 'graph'
+        elif graphable and self._eager_key == key:
+            # second pass with the same buffers and sizes: capture it
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                st = self._enqueue_optimistic(pos, timed=False)
+            g.replay()
+            self._graph, self._graph_key, self._graph_state = g, key, st
+            self.last_launch_mode = 'graph'
+        else:
+            self._graph, self._graph_key, self._graph_state = None, None, None
+            st = self._enqueue_optimistic(pos, timed=True)
+            self._eager_key = key
+            self.last_launch_mode = 'eager'
+        s = dv.stream_ptr()
+        k1, offsets, rows, jumps, allb, head, jcap = st.k1, st.offsets, st.rows, st.jumps, st.allb, st.head, st.jcap
+        n_atoms, launches = k1.n_atoms, st.launches
+        all_off = dv.to_host(st.heads)  # <- the one synchronisation
         host = dv.to_host(k1.pack)
         self._mark('k3_jumps')
         status, k2_err = all_off[:, n_atoms + 1], all_off[:, n_atoms + 2]

@@ -711,6 +711,12 @@ def test_hotpath_optimistic_pass_equals_checked_pass(monkeypatch):
         for k, v in ref.items():
             assert_array_equal(second[k].cpu().numpy(), v)
         assert second['n_events'] == len(ref['events']) and second['n_jumps'] == len(ref['jumps'])
+        assert hp.last_launch_mode == 'eager'
+        for _ in range(3):  # same buffers and sizes again: captured as one CUDA graph, then replayed
+            again = hp.run(pos)
+            assert hp.last_pass == 'optimistic' and hp.last_launch_mode == 'graph'
+            for k, v in ref.items():
+                assert_array_equal(again[k].cpu().numpy(), v)
         hp._cap_events = len(ref['events']) - 7     # the event table no longer fits
         third = hp.run(pos)
         assert hp.last_pass == 'checked' and 'status 8' in hp.last_optimistic_reject
