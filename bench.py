@@ -369,6 +369,11 @@ def run_ours(args):
     f0 = args.frames * rank // world
     f1 = args.frames * (rank + 1) // world
     pos = rec.device_positions(f0, f1 - f0)
+    # the frame after this shard (every rank reads it from its own input; no halo exchange)
+    next_row = rec.device_positions(f1, 1)[0].contiguous() if (world > 1 and rank + 1 < world) else None
+    halo = dict(next_pos_row=next_row) if world > 1 else {}
+    if world > 1 and next_row is None:
+        halo = dict(next_pos_row=pos[0])  # last rank: says "I bring my own halo" (the row is not used)
     hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=n_atoms, site_radius=RADIUS,
                  site_inner_fraction=INNER, minimal_residence=MIN_RES, n_frames_total=args.frames,
                  frame0=f0, world=world, rank=rank)
@@ -379,7 +384,7 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     for _ in range(args.warmup):
-        res = hp.run(pos)
+        res = hp.run(pos, **halo)
     barrier()
     k1_ms = []
     sampler = ClockSampler(local_rank)
@@ -389,7 +394,7 @@ def run_ours(args):
         e1 = torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(args.steps):
-            res = hp.run(pos)
+            res = hp.run(pos, **halo)
         e1.record()
         barrier()
         launch_mode, pass_route = hp.last_launch_mode, hp.last_pass
@@ -398,7 +403,7 @@ def run_ours(args):
         # once more launch by launch, still under the clock sampler, for the per-kernel number.
         use_graph, hp.use_graph = hp.use_graph, False
         for _ in range(args.steps):
-            hp.run(pos)
+            hp.run(pos, **halo)
             k1_ms.append(hp.last_k1_events)
         hp.use_graph = use_graph
         barrier()
@@ -456,7 +461,7 @@ def run_ours(args):
         acc = {}
         for _ in range(3):
             barrier()
-            hp.run(pos)
+            hp.run(pos, **halo)
             for k, v in hp.last_phases.items():
                 acc[k] = acc.get(k, 0.0) + v / 3
         hp.profile_phases = False

@@ -71,6 +71,7 @@ SIGNATURES = {
     'gd_events_scan': (C.c_int, [_p, _i64, _i32, _p, _p, C.POINTER(_i64), _p]),
     'gd_events_fill': (C.c_int, [_p, _p, _i64, _i32, _p, _p, _p, _p, _p, _i64, _p, _p]),
     'gd_events_merge': (C.c_int, [_p, _p, _p, _i32, _p, _p]),
+    'gd_events_merge_capped': (C.c_int, [_p, _p, _p, _i32, _p, _i64, _i64, _p]),
     'gd_fill_states': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p, _p]),
     'gd_jumps_work_bytes': (_i64, [_i64, _i32]),
     'gd_jumps_count': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),

@@ -319,9 +319,13 @@ __global__ void __launch_bounds__(256)
 // one block per atom: copy this shard's rows of the atom to their place in the merged table
 __global__ void __launch_bounds__(128)
     k_merge_rows(const int32_t *__restrict__ src, const int64_t *__restrict__ src_off,
-                 const int64_t *__restrict__ dst_start, int32_t *__restrict__ dst) {
+                 const int64_t *__restrict__ dst_start, int32_t *__restrict__ dst, int64_t src_cap,
+                 int64_t dst_cap) {
     const int a = blockIdx.x;
-    const int64_t r0 = src_off[a], n = (src_off[a + 1] - r0) * 6;
+    const int64_t r0 = src_off[a], r1 = src_off[a + 1], d0 = dst_start[a];
+    // offsets that were not validated by the host yet (optimistic pass): never leave the tables
+    if (r0 < 0 || r1 < r0 || r1 > src_cap || d0 < 0 || d0 + (r1 - r0) > dst_cap) return;
+    const int64_t n = (r1 - r0) * 6;
     const int32_t *s = src + r0 * 6;
     int32_t *d = dst + dst_start[a] * 6;
     for (int64_t k = threadIdx.x; k < n; k += blockDim.x) d[k] = s[k];
@@ -446,13 +450,21 @@ extern "C" gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames,
     return GD_OK;
 }
 
-extern "C" gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom_offsets,
-                                       const int64_t *d_dst_start, int32_t n_atoms,
-                                       int32_t *d_dst_rows, void *stream) {
+extern "C" gd_status_t gd_events_merge_capped(const int32_t *d_src_rows, const int64_t *d_src_atom_offsets,
+                                              const int64_t *d_dst_start, int32_t n_atoms,
+                                              int32_t *d_dst_rows, int64_t src_capacity,
+                                              int64_t dst_capacity, void *stream) {
     GD_REQUIRE(d_src_atom_offsets && d_dst_start && d_dst_rows && n_atoms > 0, GD_ERR_INVALID,
                "gd_events_merge: bad argument");
     k_merge_rows<<<(unsigned)n_atoms, 128, 0, (cudaStream_t)stream>>>(
-        d_src_rows, d_src_atom_offsets, d_dst_start, d_dst_rows);
+        d_src_rows, d_src_atom_offsets, d_dst_start, d_dst_rows, src_capacity, dst_capacity);
     GD_LAUNCH_CHECK();
     return GD_OK;
+}
+
+extern "C" gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom_offsets,
+                                       const int64_t *d_dst_start, int32_t n_atoms,
+                                       int32_t *d_dst_rows, void *stream) {
+    return gd_events_merge_capped(d_src_rows, d_src_atom_offsets, d_dst_start, n_atoms, d_dst_rows,
+                                  INT64_MAX, INT64_MAX, stream);
 }

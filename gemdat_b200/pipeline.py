@@ -147,6 +147,7 @@ class HotPath:
         # GD_GRAPH=0: launch the optimistic pass kernel by kernel instead of replaying a CUDA graph
         self.use_graph = os.environ.get('GD_GRAPH', '1') not in ('', '0')
         self._graph = self._graph_key = self._graph_state = self._eager_key = None
+        self._next_row, self._own_halo = None, False
         self.last_launch_mode = 'eager'
         self.last_k1_events = None
         # GD_K3_EXCHANGE=1: always exchange the event rows by atom block (the fallback route; A/B)
@@ -210,8 +211,8 @@ class HotPath:
         if self.profile_phases:
             torch.cuda.synchronize()
             self.last_phases, self._t_mark = {}, time.perf_counter()
-        next_pos = None
-        if self.world > 1:
+        next_pos = self._next_row  # the caller may hand over the following shard's first row itself
+        if self.world > 1 and not self._own_halo:
             first_rows = self._all_gather(pos[0].contiguous())  # [W, A, 3]
             if self.rank + 1 < self.world:
                 next_pos = first_rows[self.rank + 1].contiguous()
@@ -243,12 +244,18 @@ class HotPath:
                                overflow=overflow, work=work, stage=stage, cap=cap, n_vis=n_vis, o_chg=o_chg,
                                o_ovf=o_ovf, launches=launches, n_frames=n_frames, n_atoms=n_atoms)
 
-    def run(self, pos: torch.Tensor) -> dict:
-        """One pass of the hot path over this rank's frames.  With capacities remembered from an
+    def run(self, pos: torch.Tensor, next_pos_row: torch.Tensor | None = None) -> dict:
+        """One pass of the hot path over this rank's frames.  ``next_pos_row`` [n_atoms, 3]: the
+        positions of the frame after this shard, if the caller can read them itself (every rank but
+        the last; saves the halo all-gather) -- all ranks must then do the same.  With capacities remembered from an
         earlier run the whole pass is queued without reading anything back (`_run_optimistic`: one
         host synchronisation at the very end); whatever it cannot prove there -- a table that
         outgrew its remembered size, an unresolved jump-machine entry, the Q2 remap, an error
         condition -- is redone by the checked pass below, which reads every count where it needs it."""
+        self._next_row = None
+        if next_pos_row is not None and self.rank + 1 < self.world:
+            self._next_row = next_pos_row.contiguous()
+        self._own_halo = next_pos_row is not None or self.world == 1
         if self.optimistic and self._cap_events > 0:
             res = self._run_optimistic(pos)
             if res is not None:
@@ -416,9 +423,23 @@ class HotPath:
         launches += 8
         allb = self.comm.all_gather(jbuf) if W > 1 else jbuf.unsqueeze(0)
         heads = allb[:, :head].contiguous().view(torch.int64)  # [W, A + 3]
+        merged = None
+        if W > 1:
+            # per-atom placement of every shard's jump rows, computed on the device from offsets
+            # the host has not seen yet (the capped merge never leaves the tables)
+            offs = heads[:, : n_atoms + 1].contiguous()
+            counts = offs[:, 1:] - offs[:, :-1]                      # [W, A]
+            per_atom = counts.sum(dim=0)
+            atom_start = torch.cumsum(per_atom, dim=0) - per_atom    # rows of atoms before a
+            dst_start = (atom_start.unsqueeze(0) + torch.cumsum(counts, dim=0) - counts).contiguous()
+            merged = self._tensor('jmerged', (max(W * jcap, 1), 6), torch.int32)
+            for r in range(W):
+                _lib.check(lib.gd_events_merge_capped(dv.ptr(allb[r, head:]), dv.ptr(offs[r]), dv.ptr(dst_start[r]),
+                                                      n_atoms, dv.ptr(merged), jcap, W * jcap, s))
+            launches += W
         from types import SimpleNamespace
         return SimpleNamespace(k1=k1, offsets=offsets, rows=rows, jbuf=jbuf, jumps=jumps, allb=allb, heads=heads,
-                               head=head, jcap=jcap, launches=launches)
+                               head=head, jcap=jcap, launches=launches, merged=merged)
 
     def _run_optimistic(self, pos: torch.Tensor):
         """Optimistic pass = `_enqueue_optimistic` (eagerly the first time, then replayed as ONE
@@ -428,7 +449,8 @@ class HotPath:
         W, me = self.world, self.rank
         if not self.stage_events:
             return None
-        key = (pos.data_ptr(), tuple(pos.shape), self._cap_events, self._jump_cap)
+        key = (pos.data_ptr(), tuple(pos.shape), self._cap_events, self._jump_cap,
+               None if self._next_row is None else self._next_row.data_ptr(), self._own_halo)
         graphable = self.use_graph and not self.profile_phases and (W == 1 or self.comm.direct)
         if graphable and self._graph_key == key and self._graph is not None:
             self._graph.replay()
@@ -479,19 +501,10 @@ class HotPath:
                 if not (v.any() if key is None else v[key].any()):
                     radius = self.radius[label]
                     warnings.warn(f'No floating species in range of {label} ({radius=})', stacklevel=3)
-        counts = np.diff(all_off[:, : n_atoms + 1], axis=1)
         if W > 1:
-            total_off, dst_start = merge_plan(counts)
-            merged = dv.empty((max(int(total_off[-1]), 1), 6), torch.int32)
-            d_plan = dv.to_device(np.ascontiguousarray(np.concatenate([all_off[:, : n_atoms + 1], dst_start], axis=1)))
-            for r in range(W):
-                if n_jumps_rank[r]:
-                    _lib.check(lib.gd_events_merge(dv.ptr(allb[r, head:]), dv.ptr(d_plan[r]),
-                                                   dv.ptr(d_plan[r, n_atoms + 1:]), n_atoms, dv.ptr(merged), s))
-                    launches += 1
-            jumps_out = merged[: int(total_off[-1])]
+            jumps_out = st.merged[: int(n_jumps_rank.sum())]
         else:
-            jumps_out = jumps[: int(n_jumps_rank[0])].clone()
+            jumps_out = jumps[: int(n_jumps_rank[0])]
         self._mark('k3_merge')
         self._cap_events = max(self._cap_events, n_local + n_local // 8 + 1024)
         most = int(n_jumps_rank.max())

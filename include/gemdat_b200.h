@@ -195,6 +195,13 @@ gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t *d_src_atom
                             const int64_t *d_dst_start, int32_t n_atoms, int32_t *d_dst_rows,
                             void *stream);
 
+/* gd_events_merge with offsets the host has not validated yet (optimistic pass): atoms whose
+ * rows would leave the source (src_capacity rows) or the destination (dst_capacity rows) are
+ * skipped instead of copied. */
+gd_status_t gd_events_merge_capped(const int32_t *d_src_rows, const int64_t *d_src_atom_offsets,
+                                   const int64_t *d_dst_start, int32_t n_atoms, int32_t *d_dst_rows,
+                                   int64_t src_capacity, int64_t dst_capacity, void *stream);
+
 /* The fill for rows staged by gd_site_states_staged: copies every (frame chunk, atom)
  * segment's rows to their place in the table (same layout and order as gd_events_fill) and
  * adds frame0 to the time column.  d_work / d_changed_global / d_atom_offsets as left by
