@@ -350,6 +350,33 @@ def run_extras(args, rec, world, rank, peaks):
 # ------------------------------------------------------------------------------ GPU arm
 
 
+def pin_to_gpu_numa_node(local_rank: int):
+    """One process per GPU: run on the CPU cores NVML lists as local to that GPU, so that the
+    pinned host buffers of the e2e leg are first touched on the GPU's own NUMA node (8 ranks
+    move ~35 GB per e2e step between host memory and their GPUs).  Best effort; returns the
+    number of cores, or None when NVML / the scheduler call is unavailable."""
+    try:
+        import pynvml
+        import torch
+
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(local_rank).uuid)
+        uuid = uuid if uuid.startswith('GPU-') else 'GPU-' + uuid
+        h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        allowed = os.sched_getaffinity(0)
+        cpus = {64 * w + b for w, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1} & allowed
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -361,6 +388,7 @@ def run_ours(args):
     rank = int(os.environ.get('RANK', '0'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local_rank)
+    affinity = pin_to_gpu_numa_node(local_rank) if world > 1 else None
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     rec = synth.config_c3(n_frames=args.frames)
@@ -517,7 +545,7 @@ def run_ours(args):
                                       + jumps.data.to_numpy().nbytes),
             'breakdown_ms': dict(zip(['upload+transitions', 'jumps', 'states_d2h', 'events_d2h'],
                                      (1e3 * np.mean(np.array(e2e_marks), axis=0)).round(2).tolist())),
-            'frames_per_step': e2e_frames, 'ms_per_step': 1e3 * e2e_dt,
+            'frames_per_step': e2e_frames, 'ms_per_step': 1e3 * e2e_dt, 'cpu_affinity_cores': affinity,
             'api': 'Trajectory.transitions_between_sites + Transitions.jumps (numpy in, numpy/pandas out)',
         }
         if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only
