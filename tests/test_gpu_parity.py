@@ -345,6 +345,67 @@ def test_c3_shape_properties_and_window_parity():
     assert int(tr.jumps().matrix().sum()) == len(jumps)
 
 
+def test_c3_full_size_properties():
+    """BASELINE config 3 at its FULL size (1008 Li x 10^6 frames, 24 GB of positions resident in
+    HBM) through the device-resident route the bench times.  Size-independent properties checked on
+    the device: every event row agrees with the state arrays it was cut from, the row count is the
+    number of state changes of the non-skipped atoms, rows are sorted by (atom, time), jumps are
+    well formed; the checked, optimistic and graph-replayed passes give identical tables; sampled
+    frame windows equal the C oracle; and the table sizes are the known answers of this recipe."""
+    from gemdat_b200 import synth
+    from gemdat_b200.pipeline import HotPath
+    from oracle import cstates
+
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60e9:
+        pytest.skip('needs ~50 GB of free HBM')
+    T = 1_000_000
+    rec = synth.config_c3(n_frames=T)
+    pos = rec.device_positions(0, T)
+    hp = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=rec.n_atoms, site_radius=0.6,
+                 site_inner_fraction=0.5, minimal_residence=3, n_frames_total=T)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        first = hp.run(pos)
+        ev, jumps = first['events'].clone(), first['jumps'].clone()
+        outer, inner = first['outer'], first['inner']
+        assert hp.last_events_route == 'staged'
+        for expect in ('eager', 'graph', 'graph'):
+            again = hp.run(pos)
+            assert hp.last_pass == 'optimistic' and hp.last_launch_mode == expect, hp.last_optimistic_reject
+            assert torch.equal(again['events'], ev) and torch.equal(again['jumps'], jumps)
+    assert ev.shape[0] == 71_449_167 and jumps.shape[0] == 79_291  # known answers of the C3 recipe
+    a, t = ev[:, 0].long(), ev[:, 5].long()
+    # rows agree with the states they were cut from, and each is a real change
+    assert torch.equal(outer[t, a], ev[:, 1]) and torch.equal(outer[t + 1, a], ev[:, 2])
+    assert torch.equal(inner[t, a], ev[:, 3]) and torch.equal(inner[t + 1, a], ev[:, 4])
+    assert bool(((ev[:, 1] != ev[:, 2]) | (ev[:, 3] != ev[:, 4])).all())
+    # sorted by (atom, time), strictly
+    assert bool(((a[1:] > a[:-1]) | ((a[1:] == a[:-1]) & (t[1:] > t[:-1]))).all())
+    del a, t
+    # row count = state changes of the atoms whose outer state changes at all (transitions.py:442)
+    d_o = outer[1:] != outer[:-1]
+    keep = d_o.any(dim=0)
+    n_changes = int(((d_o | (inner[1:] != inner[:-1]))[:, keep]).sum())
+    del d_o
+    assert n_changes == ev.shape[0]
+    # jumps: start != destination, stop > start, residence >= minimal_residence, sorted by atom
+    j = jumps.long()
+    assert bool((j[:, 1] != j[:, 2]).all()) and bool((j[:, 4] > j[:, 3]).all()) and bool((j[:, 5] >= 3).all())
+    assert bool((j[1:, 0] >= j[:-1, 0]).all())
+    # inner sphere inside the outer sphere of the same site
+    assert bool(((inner == -1) | (inner == outer)).all())
+    for frame0 in (0, 499_990, 999_950):
+        p = rec.host_positions(frame0, 50)
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            eo, ei = cstates.calculate_atom_states_pair(
+                site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels, positions=p,
+                lattice_matrix=rec.lattice, site_radius={'': 0.6}, site_inner_fraction={'': 0.5})
+        assert_array_equal(outer[frame0:frame0 + 50].cpu().numpy(), eo)
+        assert_array_equal(inner[frame0:frame0 + 50].cpu().numpy(), ei)
+
+
 def _jumps_via_abi(events: np.ndarray, n_atoms: int, n_frames: int, minimal_residence: int,
                    atom_base: int = 0) -> np.ndarray:
     """gd_jumps_count / gd_jumps_fill on a raw [E, 6] event table (sorted by atom, time).
