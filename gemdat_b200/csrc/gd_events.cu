@@ -162,9 +162,24 @@ __global__ void __launch_bounds__(256)
     if (atom_offsets[a] + last > row_capacity) return;
     const int2 *src = stage + (c * g.n_atoms + a) * (int64_t)cap * 3;
     int2 *dst = events + (atom_offsets[a] + first) * 3;
-    for (int k = sub; k < n_words; k += kCompactLanes) {
+    // (the copy is latency bound -- a segment is ~54 words, 3-4 trips of 16 lanes: all of a
+    // lane's loads are issued before its first store)
+    constexpr int kTrips = 4;
+    int k = sub;
+    for (; k + (kTrips - 1) * kCompactLanes < n_words; k += kTrips * kCompactLanes) {
+        int2 v[kTrips];
+#pragma unroll
+        for (int j = 0; j < kTrips; ++j) v[j] = __ldcs(src + k + j * kCompactLanes);
+#pragma unroll
+        for (int j = 0; j < kTrips; ++j) {
+            const int kk = k + j * kCompactLanes;
+            if (kk % 3 == 2) v[j].y += frame0;  // (destination inner site, time)
+            dst[kk] = v[j];
+        }
+    }
+    for (; k < n_words; k += kCompactLanes) {
         int2 v = __ldcs(src + k);
-        if (k % 3 == 2) v.y += frame0;  // (destination inner site, time)
+        if (k % 3 == 2) v.y += frame0;
         dst[k] = v;
     }
 }
