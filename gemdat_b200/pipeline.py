@@ -1,14 +1,23 @@
 """Device-resident, frame-sharded run of the hot path (K1 -> K2 -> K3).
 
-One process per GPU; each rank owns a contiguous block of frames.  K1 (site states
-fused with the event count) needs one halo row of POSITIONS from the following shard,
-exchanged before the kernel starts.  K2 needs that shard's first state row for the halo
-event itself and the OR of the per-atom "state changes at all" flags; the compacted event tables are
-all-gathered and merged per atom, after which every rank holds the whole table and
-runs K3 on it.  All exchanges are O(n_atoms) or O(n_events) and go through
-``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in the CPU tests of the
-host logic).  The single-GPU public API (``Trajectory.transitions_between_sites``) runs
-the same kernels through ``gemdat_b200.transitions``.
+One process per GPU; each rank owns a contiguous block of frames and nothing O(frames) or
+O(events) ever leaves it:
+
+* K1 (site states + event counts + staged event rows) needs one halo row of POSITIONS from the
+  following shard -- handed in by the caller or all-gathered before the kernel starts;
+* the flags K2 needs globally (visited sites, "state ever changes" per atom, staging overflow)
+  travel in one small all-gather and are OR-ed locally;
+* K3 runs every atom's jump machine on the rank's own time slice; only the machine's per-atom
+  state (40 bytes) crosses a shard boundary (`gd_jumps_count_shard` / `gd_jumps_resolve`);
+* the jump tables (small) are all-gathered and merged per atom, so every rank ends with the
+  whole table in the reference's order; `gather_events` assembles the event table on demand.
+
+`HotPath.run` has a checked pass (reads every count where it needs it) and an optimistic pass
+(table sizes remembered from an earlier run, nothing read back until one host read at the end,
+replayed as a single CUDA graph); see DESIGN.md section 5.  All exchanges go through
+``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in the CPU tests of the host
+logic).  The single-GPU public API (``Trajectory.transitions_between_sites``) runs the same
+kernels through ``gemdat_b200.transitions``.
 """
 
 from __future__ import annotations
