@@ -5,14 +5,19 @@ Mirror of reference src/gemdat/metrics.py:21-231 for ``speed`` (:35-47),
 (:190-207) and ``particle_density`` (:49-62).  The per-frame distances come from the K0
 kernel (``gd_unwrap``) instead of the reference's Python loop over frames; the
 amplitude run-length bookkeeping is O(sign flips) host work on the returned array.
-Attempt frequency, conductivity, Haven ratio and the Arrhenius helpers are out of
-scope (DESIGN.md "next rows").
+``attempt_frequency`` (:167-188) runs on the device array too: the
+per-atom spectrum comes from cuFFT through ``torch.fft`` (a library transform, not one of
+this package's kernels), the periodogram weighting and the mean-frequency reductions of
+``utils.py:128-160`` follow it on the device.  Conductivity, Haven ratio and the Arrhenius
+helpers are out of scope (DESIGN.md "next rows").
 """
 
 from __future__ import annotations
 
 import numpy as np
+import torch
 
+from . import _device as dv
 from .caching import weak_lru_cache
 from .lattice import FloatWithUnit
 
@@ -31,6 +36,42 @@ class TrajectoryMetrics:
     def speed(self) -> np.ndarray:
         """metrics.py:35-47: change of the distance from the base position per step, [A, T]."""
         return np.diff(self._distances(), prepend=0)
+
+    @weak_lru_cache()
+    def _meanfreq(self) -> np.ndarray:
+        """utils.py:128-160 on the device: mean frequency of every atom's speed, [A, 1].
+
+        ``scipy.signal.periodogram`` defaults restated: constant detrend, boxcar window,
+        density scaling 1/(fs N), one-sided spectrum with every bin but DC (and Nyquist for
+        even N) doubled; ``mnfreq = sum(P f) / sum(P)`` with ``P = Pxx (f[1] - f[0])``.
+        """
+        dv.require_cuda()
+        dist = self.trajectory._unwrap(want_dist=True, keep_on_device=True)['dist']  # [A, T] device
+        n = int(dist.shape[1])
+        fs = float(self.trajectory.sampling_frequency)
+        speed = torch.cat([dist[:, :1], dist[:, 1:] - dist[:, :-1]], dim=1)  # np.diff(prepend=0)
+        del dist
+        x = speed - speed.mean(dim=1, keepdim=True)
+        del speed
+        spec = torch.fft.rfft(x, dim=1)
+        del x
+        pxx = (spec.real * spec.real + spec.imag * spec.imag) * (1.0 / (fs * n))
+        del spec
+        if n % 2 == 0:
+            pxx[:, 1:-1] *= 2.0
+        else:
+            pxx[:, 1:] *= 2.0
+        f = torch.fft.rfftfreq(n, d=1.0 / fs, dtype=torch.float64, device=pxx.device)
+        width = (f[1] - f[0]) if n > 1 else f.new_tensor(float('nan'))
+        p = pxx * width
+        mnfreq = (p @ f.reshape(-1, 1)) / p.sum(dim=1, keepdim=True)
+        return dv.to_host(mnfreq)
+
+    @weak_lru_cache()
+    def attempt_frequency(self) -> tuple[FloatWithUnit, FloatWithUnit]:
+        """metrics.py:167-188: mean and standard deviation over atoms of the mean frequency, Hz."""
+        freq_mean = self._meanfreq()
+        return FloatWithUnit(np.mean(freq_mean), 'hz'), FloatWithUnit(np.std(freq_mean), 'hz')
 
     @weak_lru_cache()
     def particle_density(self) -> FloatWithUnit:

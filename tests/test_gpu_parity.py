@@ -129,6 +129,29 @@ def test_density_volume(displacement_golden, tag, res):
     assert_array_equal(traj.to_volume(resolution=res).data, vol.data)
 
 
+@pytest.mark.parametrize('tag', ['unit', 'walk', 'c2'])
+def test_attempt_frequency(displacement_golden, tag):
+    """metrics.py:167-188 / utils.py:128-160 (scipy.signal.periodogram) --
+    goldens from executing the reference (tests/golden/make_golden_attempt.py).  The spectrum is
+    fp64 cuFFT vs pocketfft: 1e-10 relative; atoms that never move give 0/0 = NaN in both."""
+    from gemdat_b200 import Trajectory
+    from gemdat_b200.metrics import TrajectoryMetrics
+
+    g = displacement_golden
+    from conftest import load_golden
+
+    a = load_golden('attempt_frequency')
+    p = g[f'{tag}_positions']
+    traj = Trajectory(species=['Li'] * p.shape[1], coords=p, lattice=g[f'{tag}_lattice'],
+                      time_step=float(g[f'{tag}_time_step']))
+    m = TrajectoryMetrics(traj)
+    with np.errstate(invalid='ignore'):
+        freq, std = m.attempt_frequency()
+    assert_allclose(m._meanfreq(), a[f'{tag}_meanfreq'], rtol=1e-10, equal_nan=True)
+    assert_allclose(float(freq), float(a[f'{tag}_attempt_frequency']), rtol=1e-10, equal_nan=True)
+    assert_allclose(float(std), float(a[f'{tag}_attempt_frequency_std']), rtol=1e-9, equal_nan=True)
+
+
 def test_density_rejects_out_of_range():
     from gemdat_b200 import Trajectory
 

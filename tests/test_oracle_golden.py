@@ -162,3 +162,19 @@ def test_event_quirks():
     inner[4:, 0] = 1
     ev = events.calculate_transition_events(outer, inner)
     assert_array_equal(ev, [[0, 0, 1, 0, 0, 2], [0, 1, 1, 0, 1, 3]])
+
+
+@pytest.mark.parametrize('tag', ['unit', 'walk', 'c2'])
+def test_oracle_attempt_frequency_vs_reference_golden(tag):
+    """the numpy restatement of scipy.signal.periodogram + meanfreq against values
+    from executing the reference's metrics.py / utils.py (tests/golden/make_golden_attempt.py)."""
+    from conftest import load_golden
+    from oracle import spectrum
+
+    g, a = load_golden('displacement_metrics'), load_golden('attempt_frequency')
+    fs = 1.0 / float(g[f'{tag}_time_step'])
+    np.testing.assert_allclose(spectrum.meanfreq(g[f'{tag}_speed'], fs), a[f'{tag}_meanfreq'],
+                               rtol=1e-12, equal_nan=True)
+    freq, std = spectrum.attempt_frequency(g[f'{tag}_speed'], fs)
+    np.testing.assert_allclose(freq, float(a[f'{tag}_attempt_frequency']), rtol=1e-12, equal_nan=True)
+    np.testing.assert_allclose(std, float(a[f'{tag}_attempt_frequency_std']), rtol=1e-10, equal_nan=True)
