@@ -178,3 +178,24 @@ def test_oracle_attempt_frequency_vs_reference_golden(tag):
     freq, std = spectrum.attempt_frequency(g[f'{tag}_speed'], fs)
     np.testing.assert_allclose(freq, float(a[f'{tag}_attempt_frequency']), rtol=1e-12, equal_nan=True)
     np.testing.assert_allclose(std, float(a[f'{tag}_attempt_frequency_std']), rtol=1e-10, equal_nan=True)
+
+
+@pytest.mark.parametrize('case', [0, 1, 2, 3])
+def test_oracle_collective_vs_reference_golden(case):
+    """oracle/collective.py against pairs from executing the reference's
+    collective.py:61-106 (tests/golden/make_golden_collective.py), including the sort order and
+    the early ``break`` of the inner loop."""
+    from conftest import load_golden
+    from oracle import collective as oc
+
+    g = load_golden('collective')
+    t = f'case{case}'
+    src = load_golden(str(g[f'{t}_fixture']))
+    jumps = src[str(g[f'{t}_jumps_key'])]
+    ev, pairs = oc.collective_pairs(jumps, src['site_frac'], src['lattice'], int(g[f'{t}_max_steps']),
+                                    float(g[f'{t}_max_dist']))
+    np.testing.assert_array_equal(ev, g[f'{t}_sorted_jumps'])
+    np.testing.assert_array_equal(pairs, g[f'{t}_pairs'])
+    np.testing.assert_array_equal(oc.coll_jumps(ev, pairs), g[f'{t}_coll_jumps'])
+    assert oc.solo_count(len(ev), pairs) == int(g[f'{t}_n_solo_jumps'])
+    assert len(ev) - oc.solo_count(len(ev), pairs) == int(g[f'{t}_n_coll_jumps'])
