@@ -82,6 +82,11 @@ SIGNATURES = {
     'gd_jumps_work_unresolved_offset': (_i64, [_i64, _i32]),
     'gd_jumps_resolve': (C.c_int, [_p, _i32, _i32, _i32, _p, _p, C.POINTER(_i32), _p]),
     'gd_pair_matrix': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p]),
+    'gd_collective_work_bytes': (_i64, [_i64]),
+    'gd_collective_sort': (C.c_int, [_p, _i64, _p, _p, _p]),
+    'gd_collective_close': (C.c_int, [_p, _i32, C.c_double, _p, _p]),
+    'gd_collective_count': (C.c_int, [_p, _i64, _p, _i32, _i32, _p, C.POINTER(_i64), C.POINTER(_i64), _p]),
+    'gd_collective_fill': (C.c_int, [_p, _i64, _p, _i32, _i32, _p, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),
     'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     'gd_transpose_soa': (C.c_int, [_p, _i64, _i32, _p, _p]),

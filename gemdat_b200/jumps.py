@@ -5,9 +5,9 @@ reference's plug-in hook: any ``Callable[[Transitions, minimal_residence=int],
 DataFrame]``.  The default method is the CUDA state machine (``gd_jumps_count`` /
 ``gd_jumps_fill``, K3) standing in for the pandas ``groupby``/``iterrows`` loop of
 ``_generic_transitions_to_jumps`` (:24-119).  ``matrix`` (:212-221) and
-``jump_diffusivity`` (:185-210) follow the reference formulae.  Collective jumps,
-rates, activation energies and graphs are consumers of this table and out of scope
-(DESIGN.md "next rows").
+``jump_diffusivity`` (:185-210) follow the reference formulae.  ``collective`` (:223-251)
+hands the device table to ``gemdat_b200.collective.Collective``.  Rates, activation
+energies and graphs are consumers of this table and out of scope (DESIGN.md "next rows").
 """
 
 from __future__ import annotations
@@ -15,6 +15,7 @@ from __future__ import annotations
 import ctypes as C
 from collections import Counter
 from itertools import product
+from math import ceil
 from typing import Callable
 
 import numpy as np
@@ -24,6 +25,7 @@ import torch
 from . import _device as dv
 from . import _lib
 from .caching import weak_lru_cache
+from .collective import Collective
 from .lattice import FloatWithUnit, site_arrays
 from .transitions import Transitions, _pair_matrix_device
 
@@ -81,14 +83,26 @@ class Jumps:
         self.conversion_method = conversion_method
         self.data = conversion_method(transitions, minimal_residence=minimal_residence)
         self.minimal_residence = minimal_residence
+        # device copy of the table when the default method made it (used by collective())
+        self._d_table = transitions._dev.pop('jumps', None) if hasattr(transitions, '_dev') else None
 
     @property
     def n_jumps(self) -> int:
         return len(self.data)
 
     @property
+    def n_solo_jumps(self) -> int:
+        """jumps.py:158-161."""
+        return self.collective().n_solo_jumps
+
+    @property
     def n_floating(self) -> int:
         return len(self.trajectory.species)
+
+    @property
+    def solo_fraction(self) -> float:
+        """jumps.py:168-171."""
+        return self.n_solo_jumps / self.n_jumps
 
     @property
     def site_pairs(self) -> list[tuple[str, str]]:
@@ -116,6 +130,17 @@ class Jumps:
         )
         rows = dv.to_device(pairs) if len(pairs) else None
         return _pair_matrix_device(rows, len(pairs), 2, 0, 1, self.transitions.n_sites)
+
+    @weak_lru_cache()
+    def collective(self, max_dist: float = 1) -> Collective:
+        """jumps.py:223-251: window of 1 / attempt frequency, in frames."""
+        from .metrics import TrajectoryMetrics
+
+        trajectory = self.trajectory
+        attempt_freq, _ = TrajectoryMetrics(trajectory).attempt_frequency()
+        max_steps = ceil(1.0 / (attempt_freq * trajectory.time_step))
+        return Collective(jumps=self, sites=self.transitions.sites, lattice=trajectory.get_lattice(),
+                          max_steps=max_steps, max_dist=max_dist)
 
     @weak_lru_cache()
     def counter(self) -> Counter:

@@ -319,6 +319,41 @@ gd_status_t gd_pair_matrix(const int32_t *d_rows, int64_t n_rows, int32_t row_st
                            unsigned long long *d_scratch, long long *d_matrix, void *stream);
 
 /* ------------------------------------------------------------------------- *
+ * N3  collective jumps
+ * replaces: Collective._compute, src/gemdat/collective.py:61-106 (the pandas
+ * double loop over jump pairs), called from Jumps.collective, jumps.py:223-251.
+ * ------------------------------------------------------------------------- */
+
+/* Scratch bytes for the four calls below (sort keys, counts, offsets, flags). */
+int64_t gd_collective_work_bytes(int64_t n_jumps);
+
+/* d_jumps [n_jumps,6] int32 (the K3 table) -> d_sorted, rows ordered by
+ * (stop time, start time), equal keys in their incoming order
+ * (sort_values(['stop time','start time']), collective.py:68). */
+gd_status_t gd_collective_sort(const int32_t *d_jumps, int64_t n_jumps, void *d_work,
+                               int32_t *d_sorted, void *stream);
+
+/* d_close[a,b] = d_dist[a,b] < max_dist over the [n_sites,n_sites] fp64 distance
+ * matrix from gd_pbc_distances (np.any(dists < max_dist), collective.py:86-88). */
+gd_status_t gd_collective_close(const double *d_dist, int32_t n_sites, double max_dist,
+                                uint8_t *d_close, void *stream);
+
+/* Walks every jump i over its partners j > i of the sorted table with the
+ * reference's break / continue rules (collective.py:76-81).  Returns the number of
+ * collective pairs and the number of jumps that are in no pair (n_solo_jumps,
+ * :100-101); leaves the per-jump pair offsets in d_work for the fill.
+ * Synchronises the stream. */
+gd_status_t gd_collective_count(const int32_t *d_sorted, int64_t n_jumps, const uint8_t *d_close,
+                                int32_t n_sites, int32_t max_steps, void *d_work,
+                                int64_t *h_n_pairs, int64_t *h_n_solo, void *stream);
+
+/* d_pairs [n_pairs,2] int32: row numbers (i, j) in the sorted table, in the order the
+ * reference appends them (i ascending, then j ascending). */
+gd_status_t gd_collective_fill(const int32_t *d_sorted, int64_t n_jumps, const uint8_t *d_close,
+                               int32_t n_sites, int32_t max_steps, const void *d_work,
+                               int32_t *d_pairs, void *stream);
+
+/* ------------------------------------------------------------------------- *
  * K0  displacement / unwrap
  * replaces: pymatgen Trajectory.to_displacements via Trajectory.displacements
  *           (src/gemdat/trajectory.py:182-193), cumulative_displacements

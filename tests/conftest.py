@@ -31,10 +31,9 @@ def load_golden(name: str) -> dict:
         return {k: z[k] for k in z.files}
 
 
-@pytest.fixture(params=PIPELINE_CASES)
-def pipeline_case(request):
-    g = load_golden(request.param)
-    g['name'] = request.param
+def load_pipeline_case(name: str) -> dict:
+    g = load_golden(name)
+    g['name'] = name
     keys = [str(k) for k in g['radius_keys']]
     g['site_radius'] = {k: float(v) for k, v in zip(keys, g['radius_values'])}
     g['inner_fraction'] = {k: float(v) for k, v in zip(keys, g['inner_values'])}
@@ -45,6 +44,11 @@ def pipeline_case(request):
     else:
         g['floating_mask'] = np.ones(g['positions'].shape[1], dtype=bool)
     return g
+
+
+@pytest.fixture(params=PIPELINE_CASES)
+def pipeline_case(request):
+    return load_pipeline_case(request.param)
 
 
 @pytest.fixture(scope='session')

@@ -54,6 +54,13 @@ def main():
         out[f'{t}_coll_jumps'] = np.array(coll.coll_jumps, dtype=np.int64).reshape(-1, 2, 2)
         out[f'{t}_n_solo_jumps'] = np.array(int(coll.n_solo_jumps))
         out[f'{t}_n_coll_jumps'] = np.array(int(coll.n_coll_jumps))
+        # collective.py:108-166; the label-pair order comes from a set, so it is stored too
+        out[f'{t}_site_pair_labels'] = np.array(coll.site_pair_count_matrix_labels(), dtype=str).reshape(-1, 2)
+        out[f'{t}_site_pair_count_matrix'] = coll.site_pair_count_matrix()
+        if len(pairs):
+            mj, mc = coll.multiple_collective()
+            out[f'{t}_multiple_jumps'] = np.stack([mj['start'], mj['stop']], axis=-1).astype(np.int64)
+            out[f'{t}_multiple_counts'] = mc.astype(np.int64)
         print(t, fixture, key, 'jumps', len(data), 'pairs', len(pairs), 'solo', int(coll.n_solo_jumps))
     out['n_cases'] = np.array(len(CASES))
     np.savez_compressed(HERE / 'collective.npz', **out)

@@ -838,3 +838,103 @@ def test_pipelined_host_path_equals_resident_path(monkeypatch, n_atoms):
     assert_array_equal(tr.events.to_numpy(), ref.events.to_numpy())
     assert_array_equal(tr.jumps(minimal_residence=3).data.to_numpy(), ref.jumps(minimal_residence=3).data.to_numpy())
     assert tr.info['band_4e-6'] == ref.info['band_4e-6']
+
+
+# ------------------------------------------------------------------ N3: collective jumps
+@pytest.mark.parametrize('case', [0, 1, 2, 3])
+def test_collective_vs_reference_golden(case):
+    """Collective (collective.py:61-166) against pairs from executing the
+    reference (tests/golden/make_golden_collective.py): sort order, emission order of the pairs,
+    solo count, site-pair matrix, multiple_collective."""
+    import pandas as pd
+    from types import SimpleNamespace
+
+    from conftest import load_golden
+    from gemdat_b200 import Sites
+    from gemdat_b200.collective import Collective
+    from gemdat_b200.lattice import Lattice
+
+    g = load_golden('collective')
+    t = f'case{case}'
+    src = load_golden(str(g[f'{t}_fixture']))
+    data = pd.DataFrame(src[str(g[f'{t}_jumps_key'])], columns=[str(x) for x in src['jump_columns']])
+    labels = [str(x) for x in src['site_labels']]
+    sites = Sites(src['lattice'], 'Li', src['site_frac'], labels=labels)
+    coll = Collective(jumps=SimpleNamespace(data=data), sites=sites, lattice=Lattice(src['lattice']),
+                      max_steps=int(g[f'{t}_max_steps']), max_dist=float(g[f'{t}_max_dist']))
+    assert_array_equal(coll.events.to_numpy(), g[f'{t}_sorted_jumps'])
+    assert_array_equal(coll.pairs, g[f'{t}_pairs'])
+    assert coll.n_solo_jumps == int(g[f'{t}_n_solo_jumps'])
+    assert coll.n_coll_jumps == int(g[f'{t}_n_coll_jumps'])
+    assert_array_equal(np.array(coll.coll_jumps, dtype=np.int64).reshape(-1, 2, 2), g[f'{t}_coll_jumps'])
+    if case < 3:  # one pandas row per pair, like the reference's `collective` list
+        rows = coll.collective
+        assert len(rows) == len(g[f'{t}_pairs'])
+        for (ei, ej), (i, j) in zip(rows, g[f'{t}_pairs']):
+            assert_array_equal(ei.to_numpy(), g[f'{t}_sorted_jumps'][i])
+            assert_array_equal(ej.to_numpy(), g[f'{t}_sorted_jumps'][j])
+    # label pairs come from a set: compare through the stored order
+    mine = coll.site_pair_count_matrix_labels()
+    ref_pairs = [tuple(p) for p in g[f'{t}_site_pair_labels'].tolist()]
+    assert sorted(mine) == sorted(ref_pairs)
+    perm = [mine.index(p) for p in ref_pairs]
+    assert_array_equal(coll.site_pair_count_matrix()[np.ix_(perm, perm)], g[f'{t}_site_pair_count_matrix'])
+    mj, mc = coll.multiple_collective()
+    assert_array_equal(np.stack([mj['start'], mj['stop']], axis=-1), g[f'{t}_multiple_jumps'])
+    assert_array_equal(mc, g[f'{t}_multiple_counts'])
+
+
+@pytest.mark.parametrize('n_jumps,max_steps,max_dist', [(1, 5, 2.0), (2, 5, 50.0), (700, 8, 2.5),
+                                                        (3000, 40, 1.8), (3000, 0, 3.0)])
+def test_collective_random_tables_vs_oracle(n_jumps, max_steps, max_dist):
+    """Random jump tables with many equal (stop, start) keys and long jumps, so that the stable
+    sort and the early `break` on a non-monotonic key (collective.py:76-77) both matter."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200.collective import _close_matrix, collective_pairs_device
+    from oracle import collective as oc
+
+    rng = np.random.default_rng(n_jumps * 7 + max_steps)
+    n_sites, n_atoms = 23, 9
+    lat = np.array([[7.0, 0.0, 0.0], [1.0, 6.5, 0.0], [0.5, -0.8, 8.0]])
+    site_frac = rng.random((n_sites, 3))
+    start = rng.integers(0, max(4, n_jumps // 3), n_jumps)
+    dur = np.where(rng.random(n_jumps) < 0.15, rng.integers(1, 60, n_jumps), rng.integers(1, 4, n_jumps))
+    jumps = np.stack([rng.integers(0, n_atoms, n_jumps), rng.integers(0, n_sites, n_jumps),
+                      rng.integers(0, n_sites, n_jumps), start, start + dur,
+                      rng.integers(0, 9, n_jumps)], axis=1).astype(np.int64)
+    ev, pairs = oc.collective_pairs(jumps, site_frac, lat, max_steps, max_dist)
+    close = _close_matrix(lat, site_frac, max_dist)
+    d_ev, d_pairs, n_solo = collective_pairs_device(dv.to_device(jumps.astype(np.int32)), close, max_steps)
+    assert_array_equal(dv.to_host(d_ev), ev)
+    assert_array_equal(dv.to_host(d_pairs).reshape(-1, 2), pairs)
+    assert n_solo == oc.solo_count(n_jumps, pairs)
+
+
+def test_jumps_collective_through_the_api():
+    """Jumps.collective (jumps.py:223-251) end to end: attempt frequency -> max_steps -> pairs,
+    against the oracle run on the same jump table."""
+    from math import ceil
+
+    from oracle import collective as oc
+    from oracle import spectrum
+
+    from conftest import load_pipeline_case
+
+    case = load_pipeline_case('pipeline_box_mixed')
+    traj, sites = _product(case)
+    radius, inner = _radius_args(case)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        tr = traj.transitions_between_sites(sites, 'Li', site_radius=radius, site_inner_fraction=inner,
+                                            fraction_of_overlap=float(case['fraction_of_overlap']))
+    jumps = tr.jumps()
+    coll = jumps.collective(max_dist=2.5)
+    from gemdat_b200.metrics import TrajectoryMetrics
+
+    freq, _ = TrajectoryMetrics(jumps.trajectory).attempt_frequency()
+    assert coll.max_steps == ceil(1.0 / (float(freq) * jumps.trajectory.time_step))
+    ev, pairs = oc.collective_pairs(jumps.data.to_numpy(), case['site_frac'], case['lattice'], coll.max_steps, 2.5)
+    assert_array_equal(coll.events.to_numpy(), ev)
+    assert_array_equal(coll.pairs, pairs)
+    assert jumps.n_solo_jumps == oc.solo_count(len(ev), pairs)
+    assert jumps.solo_fraction == jumps.n_solo_jumps / jumps.n_jumps

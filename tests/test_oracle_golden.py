@@ -199,3 +199,12 @@ def test_oracle_collective_vs_reference_golden(case):
     np.testing.assert_array_equal(oc.coll_jumps(ev, pairs), g[f'{t}_coll_jumps'])
     assert oc.solo_count(len(ev), pairs) == int(g[f'{t}_n_solo_jumps'])
     assert len(ev) - oc.solo_count(len(ev), pairs) == int(g[f'{t}_n_coll_jumps'])
+    # derived tables (collective.py:108-166)
+    cj = oc.coll_jumps(ev, pairs)
+    labels = [str(x) for x in src['site_labels']]
+    site_pairs = [tuple(p) for p in g[f'{t}_site_pair_labels'].tolist()]
+    np.testing.assert_array_equal(oc.site_pair_count_matrix(cj, labels, site_pairs),
+                                  g[f'{t}_site_pair_count_matrix'])
+    mj, mc = oc.multiple_collective(cj)
+    np.testing.assert_array_equal(np.stack([mj['start'], mj['stop']], axis=-1), g[f'{t}_multiple_jumps'])
+    np.testing.assert_array_equal(mc, g[f'{t}_multiple_counts'])
