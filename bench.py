@@ -235,7 +235,7 @@ def workload_config(rec, args):
 # ------------------------------------------------------------------------------ MSD / K0 / K5
 
 
-def run_extras(args, rec, world, rank, peaks):
+def run_extras(args, rec, world, rank, peaks, jumps=None):
     """The other kernels of the path on the same C3 trajectory, timed with CUDA events:
     K0 unwrap (HBM bound), K4 direct MSD over a bounded lag range (fp64 pipe bound; the lag axis
     is sharded over the ranks, positions replicated), K5 density histogram at 0.1 A."""
@@ -344,6 +344,39 @@ def run_extras(args, rec, world, rank, peaks):
         'lag_axis_sharded_over': world, 'msd_at_last_lag_A2': float(curve[-1].item()),
         'note': 'unit lag = one lag over all atoms and all frame pairs of the 1e6-frame trajectory',
     }
+    del soa, msd
+
+    # ---- N3: collective-jump pair search on the step's own jump table (rank-local, N=1 only)
+    if jumps is not None and world == 1 and int(jumps.shape[0]) > 1:
+        from gemdat_b200.collective import _close_matrix, collective_pairs_device
+
+        frac = np.ascontiguousarray(rec.sites.frac_coords, dtype=np.float64)
+        max_steps, max_dist = 200, 4.0
+        close = _close_matrix(rec.lattice, frac, max_dist)
+        found = {}
+
+        def n3():
+            found['ev'], found['pairs'], found['solo'] = collective_pairs_device(jumps, close, max_steps)
+
+        ms = timed(n3)
+        J, P = int(jumps.shape[0]), int(found['pairs'].shape[0])
+        out['collective'] = {'ms': ms, 'jumps': J, 'pairs': P, 'n_solo_jumps': int(found['solo']),
+                             'max_steps': max_steps, 'max_dist_A': max_dist, 'jumps_per_s': J / (ms * 1e-3),
+                             'includes': 'sort + count + scan + fill, two host reads'}
+        if not args.no_cpu_baseline:
+            from oracle import collective as ocoll  # checker / CPU baseline leg only
+
+            n0 = min(J, 4000)
+            head = found['ev'][:n0].cpu().numpy()
+            host_close = ocoll.close_matrix(frac, rec.lattice, max_dist)  # untimed on both sides
+            t0 = time.perf_counter()
+            _, ref_pairs = ocoll.collective_pairs(head, frac, rec.lattice, max_steps, max_dist, host_close)
+            dt = time.perf_counter() - t0
+            mine = found['pairs'].cpu().numpy()
+            mine = mine[(mine[:, 0] < n0) & (mine[:, 1] < n0)]
+            # a time prefix of the sorted table: every i < n0 breaks at the same j or at the cut
+            out['collective']['cpu_port'] = {'jumps': n0, 's': dt, 'jumps_per_s': n0 / dt,
+                                             'pairs_equal': bool(np.array_equal(mine, ref_pairs))}
     return out
 
 
@@ -498,9 +531,10 @@ def run_ours(args):
 
     extras = None
     if not args.no_extras:
+        step_jumps = res['jumps'].clone() if world == 1 else None
         del res
         hp._buf.clear()
-        extras = run_extras(args, rec, world, rank, peaks)
+        extras = run_extras(args, rec, world, rank, peaks, step_jumps)
 
     # ---- e2e through the public API with pinned host buffers (rank-local window)
     from gemdat_b200 import Trajectory

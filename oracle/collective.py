@@ -36,13 +36,19 @@ def sort_jumps(jumps: np.ndarray) -> np.ndarray:
     return jumps[order]
 
 
+def close_matrix(site_frac: np.ndarray, lattice: np.ndarray, max_dist: float) -> np.ndarray:
+    """[n_sites, n_sites] bool: ``lattice.get_all_distances(...) < max_dist`` (collective.py:86-88)."""
+    dist = Lattice(np.asarray(lattice, dtype=np.float64)).get_all_distances(site_frac, site_frac)
+    return dist < max_dist
+
+
 def collective_pairs(jumps: np.ndarray, site_frac: np.ndarray, lattice: np.ndarray, max_steps: int,
-                     max_dist: float):
+                     max_dist: float, close: np.ndarray | None = None):
     """Returns (sorted_jumps, pairs[P, 2] of row numbers in the sorted table, in emission order)."""
     ev = sort_jumps(jumps)
     n = len(ev)
-    dist = Lattice(np.asarray(lattice, dtype=np.float64)).get_all_distances(site_frac, site_frac)
-    close = dist < max_dist  # [n_sites, n_sites]
+    if close is None:
+        close = close_matrix(site_frac, lattice, max_dist)
     start = ev[:, START_TIME].astype(np.int64)
     stop = ev[:, STOP_TIME].astype(np.int64)
     pairs = []
