@@ -96,6 +96,15 @@ class Structure:
         return [s.label for s in self._sites]
 
     @property
+    def species(self):
+        return [s.specie for s in self._sites]
+
+    @property
+    def symbol_set(self):
+        # pymatgen: sorted tuple of the element symbols present  [recalled]
+        return tuple(sorted({s.specie.symbol for s in self._sites}))
+
+    @property
     def is_ordered(self):
         return True
 
@@ -147,6 +156,11 @@ class PymatgenTrajectory:
 
     def __len__(self):
         return len(self.coords)
+
+    def get_structure(self, idx):
+        # pymatgen Trajectory.get_structure: positions of frame idx  [recalled]
+        self.to_positions()
+        return Structure(Lattice(self.lattice), [sp.symbol for sp in self.species], self.coords[idx])
 
     def to_positions(self):
         if not self.coords_are_displacement:
@@ -245,5 +259,5 @@ def load_reference():
 
 def _import_all():
     for name in ('utils', 'caching', 'metrics', 'transitions', 'collective', 'jumps',
-                 'trajectory', 'volume'):
+                 'trajectory', 'volume', 'rdf'):
         _loaded[name] = importlib.import_module(f'gemdat.{name}')

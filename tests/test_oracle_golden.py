@@ -208,3 +208,49 @@ def test_oracle_collective_vs_reference_golden(case):
     mj, mc = oc.multiple_collective(cj)
     np.testing.assert_array_equal(np.stack([mj['start'], mj['stop']], axis=-1), g[f'{t}_multiple_jumps'])
     np.testing.assert_array_equal(mc, g[f'{t}_multiple_counts'])
+
+
+def test_oracle_rdf_vs_reference_golden():
+    """oracle/rdf.py against rdf.py executed by tests/golden/make_golden_rdf.py --
+    the label off-by-one of _uniqify_labels, the state names, the per-state histograms in the
+    reference's key order, and the species-species RDF."""
+    from conftest import load_golden
+    from oracle import rdf as orf
+
+    g = load_golden('rdf')
+    src = load_golden(str(g['fixture']))
+    labels = [str(x) for x in src['site_labels']]
+    uniq = [str(x) for x in g['unique_labels']]
+    species = [str(s) for s in src['species']]
+    np.testing.assert_array_equal(orf.uniqify(src['states'], labels, uniq), g['uniqify_states'])
+    names = orf.state_names(uniq)
+    assert list(names.keys()) == g['states2str_codes'].tolist()
+    assert list(names.values()) == [str(x) for x in g['states2str_names']]
+    codes = orf.states_array(src['states'], src['states_prev'], src['states_next'], labels, uniq)
+    np.testing.assert_array_equal(codes, g['states_array'])
+    for n in (0, 1):
+        t = f'rdf{n}'
+        res = orf.radial_distribution(positions=src['positions'], symbols=species, floating_specie='Li',
+                                      codes=codes, unique_labels=uniq, lattice=src['lattice'],
+                                      max_dist=float(g[f'{t}_max_dist']), resolution=float(g[f'{t}_resolution']))
+        # the reference groups its curves by state (dict of lists): same grouping here
+        grouped = {}
+        for (state, sym), (x, y) in res.items():
+            grouped.setdefault(state, []).append((sym, x, y))
+        flat = [(state, sym, x, y) for state, curves in grouped.items() for sym, x, y in curves]
+        assert [f[0] for f in flat] == [str(s) for s in g[f'{t}_states']]
+        assert [f[1] for f in flat] == [str(s) for s in g[f'{t}_symbols']]
+        np.testing.assert_array_equal(flat[0][2], g[f'{t}_x'])
+        np.testing.assert_array_equal(np.stack([f[3] for f in flat]), g[f'{t}_y'])
+    pos = src['positions']
+    sel = lambda want: pos[:, [s in want for s in species]]  # noqa: E731
+    for n in (0, 1, 2):
+        t = f'between{n}'
+        s1 = g[f'{t}_specie_1'].tolist()
+        s2 = g[f'{t}_specie_2'].tolist()
+        w1 = [s1] if isinstance(s1, str) else s1
+        w2 = [s2] if isinstance(s2, str) else s2
+        x, y = orf.between_species(coords_1=sel(w1), coords_2=sel(w2), same=(s1 == s2), lattice=src['lattice'],
+                                   max_dist=float(g[f'{t}_max_dist']), resolution=float(g[f'{t}_resolution']))
+        np.testing.assert_array_equal(x, g[f'{t}_x'])
+        np.testing.assert_allclose(y, g[f'{t}_y'], rtol=1e-13)
