@@ -9,15 +9,18 @@ there is no CPU fallback.
 from __future__ import annotations
 
 from . import _lib  # fails loudly if libgemdat_b200.so is missing
+from .collective import Collective
 from .jumps import Jumps
 from .lattice import FloatWithUnit, Lattice, Sites
 from .metrics import TrajectoryMetrics
+from .rdf import radial_distribution
 from .trajectory import Trajectory
 from .transitions import SiteRadius, Transitions
 from .volume import Volume, trajectory_to_volume
 
 __version__ = '0.1.0'
 __all__ = [
+    'Collective',
     'Jumps',
     'Lattice',
     'Sites',
@@ -26,5 +29,6 @@ __all__ = [
     'TrajectoryMetrics',
     'Transitions',
     'Volume',
+    'radial_distribution',
     'trajectory_to_volume',
 ]

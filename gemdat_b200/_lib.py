@@ -87,6 +87,9 @@ SIGNATURES = {
     'gd_collective_close': (C.c_int, [_p, _i32, C.c_double, _p, _p]),
     'gd_collective_count': (C.c_int, [_p, _i64, _p, _i32, _i32, _p, C.POINTER(_i64), C.POINTER(_i64), _p]),
     'gd_collective_fill': (C.c_int, [_p, _i64, _p, _i32, _i32, _p, _p, _p]),
+    'gd_rdf_classes': (C.c_int, [_p, _p, _p, _i64, _i32, _p, _i32, _i32, _p, _p, _p, _p]),
+    'gd_rdf_hist': (C.c_int, [_p, _i64, _i32, _p, _p, _i32, _p, _i32, _p, _p, _i32, _i32, _p, _i32,
+                              C.c_double, _i32, _i32, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),
     'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     'gd_transpose_soa': (C.c_int, [_p, _i64, _i32, _p, _p]),

@@ -1,0 +1,244 @@
+// Radial distribution histograms: reference src/gemdat/rdf.py:111-268.
+//
+//   gd_rdf_classes  per (frame, floating atom): the transition state it is in
+//                   (_get_states_array, rdf.py:53-61, with _uniqify_labels' off-by-one kept)
+//                   as an index into the caller's table of state names, plus for every state
+//                   the first (frame, code) at which it occurs (the order of the reference's
+//                   result dict)
+//   gd_rdf_hist     per frame: minimum-image distances source atoms x target atoms
+//                   (Lattice.get_all_distances: both wrapped to [0,1), 27 images, same
+//                   operation order as gd_pbc_distances), np.digitize(right=True) or
+//                   np.histogram binning against the caller's exact edges, counted per
+//                   (class of the source, group of the target, bin)
+//
+// One CTA per (frame, slice of the sources); the frame's targets sit in shared memory wrapped
+// to [0,1); one warp per source, lanes over targets, a warp-private shared-memory histogram
+// flushed to the global uint64 table per (source, target tile).  The kernel is fp64-pipe
+// bound: ~300 fp64 instructions per pair for a general cell (the 27 images share their 27
+// products and 27 partial sums), ~35 for a diagonal cell, where the minimum separates per axis
+// (rounding is monotonic, so min over images of fl(fl(X+Y)+Z) = fl(fl(minX+minY)+minZ)).
+#include "gd_common.cuh"
+
+namespace {
+
+constexpr int kWarps = 8;
+
+struct RdfParams {
+    const double *pos;  // [T, N, 3] fractional
+    int64_t n_frames;
+    int32_t n_atoms;
+    const int32_t *idx1;  // [n1] source atoms
+    int32_t n1;
+    const int32_t *cls;  // [T, n1] class of the source in that frame, <0 = skip; NULL = 0
+    const int32_t *idx2;   // [n2] target atoms
+    const int32_t *group;  // [n2] group of the target; NULL = 0
+    int32_t n2;
+    int32_t n_group;
+    const double *edges;  // [n_edges]
+    int32_t n_edges;
+    int32_t mode;  // 0: digitize(right=True) -> #edges < d;  1: histogram -> #edges <= d
+    int32_t skip_same;
+    int32_t tile;  // targets per shared-memory tile
+    int32_t diag;
+    double inv_res;
+    double m[9];
+    unsigned long long *hist;  // [n_class, n_group, n_edges + 1]
+};
+
+__device__ __forceinline__ double wrap01(double x) { return x - floor(x); }
+
+__device__ __forceinline__ double min_image_d2(const RdfParams &p, const double a[3], const double b[3]) {
+    double v[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        v[k][0] = (b[k] + -1.0) - a[k];
+        v[k][1] = (b[k] + 0.0) - a[k];
+        v[k][2] = (b[k] + 1.0) - a[k];
+    }
+    if (p.diag) {
+        double mn[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const double mk = p.m[4 * k];
+            const double c0 = v[k][0] * mk, c1 = v[k][1] * mk, c2 = v[k][2] * mk;
+            mn[k] = fmin(fmin(c0 * c0, c1 * c1), c2 * c2);
+        }
+        return (mn[0] + mn[1]) + mn[2];
+    }
+    // general cell: cart_c = (vx*m[0+c] + vy*m[3+c]) + vz*m[6+c], d2 = (cx^2 + cy^2) + cz^2
+    double best = 1e300;
+#pragma unroll
+    for (int ix = 0; ix < 3; ++ix) {
+        const double x0 = v[0][ix] * p.m[0], x1 = v[0][ix] * p.m[1], x2 = v[0][ix] * p.m[2];
+#pragma unroll
+        for (int iy = 0; iy < 3; ++iy) {
+            const double s0 = x0 + v[1][iy] * p.m[3], s1 = x1 + v[1][iy] * p.m[4], s2 = x2 + v[1][iy] * p.m[5];
+#pragma unroll
+            for (int iz = 0; iz < 3; ++iz) {
+                const double c0 = s0 + v[2][iz] * p.m[6], c1 = s1 + v[2][iz] * p.m[7], c2 = s2 + v[2][iz] * p.m[8];
+                best = fmin(best, (c0 * c0 + c1 * c1) + c2 * c2);
+            }
+        }
+    }
+    return best;
+}
+
+__global__ void __launch_bounds__(kWarps * 32) k_rdf_hist(const __grid_constant__ RdfParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int nb = p.n_edges + 1;
+    const int hist_len = p.n_group * nb;
+    double *s_b = reinterpret_cast<double *>(smem);                 // [tile][3]
+    double *s_edges = s_b + 3 * (size_t)p.tile;                      // [n_edges]
+    int32_t *s_atom = reinterpret_cast<int32_t *>(s_edges + p.n_edges);  // [tile]
+    int32_t *s_group = s_atom + p.tile;                              // [tile]
+    uint32_t *s_hist = reinterpret_cast<uint32_t *>(s_group + p.tile);   // [kWarps][hist_len]
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t *my_hist = s_hist + (size_t)warp * hist_len;
+    for (int k = threadIdx.x; k < p.n_edges; k += blockDim.x) s_edges[k] = p.edges[k];
+    for (int k = threadIdx.x; k < kWarps * hist_len; k += blockDim.x) s_hist[k] = 0;
+
+    for (int64_t t = blockIdx.x; t < p.n_frames; t += gridDim.x) {
+        const double *frame = p.pos + t * (int64_t)p.n_atoms * 3;
+        for (int j0 = 0; j0 < p.n2; j0 += p.tile) {
+            const int nt = min(p.tile, p.n2 - j0);
+            __syncthreads();
+            for (int k = threadIdx.x; k < nt; k += blockDim.x) {
+                const int32_t atom = p.idx2[j0 + k];
+                s_atom[k] = atom;
+                s_group[k] = p.group ? p.group[j0 + k] : 0;
+                const double *q = frame + 3 * (int64_t)atom;
+                s_b[3 * k] = wrap01(q[0]);
+                s_b[3 * k + 1] = wrap01(q[1]);
+                s_b[3 * k + 2] = wrap01(q[2]);
+            }
+            __syncthreads();
+            for (int i = blockIdx.y * kWarps + warp; i < p.n1; i += gridDim.y * kWarps) {
+                const int32_t c = p.cls ? p.cls[t * p.n1 + i] : 0;
+                if (c < 0) continue;
+                const int32_t atom_i = p.idx1[i];
+                const double *q = frame + 3 * (int64_t)atom_i;
+                const double a[3] = {wrap01(q[0]), wrap01(q[1]), wrap01(q[2])};
+                for (int k = lane; k < nt; k += 32) {
+                    if (p.skip_same && s_atom[k] == atom_i) continue;
+                    const double b[3] = {s_b[3 * k], s_b[3 * k + 1], s_b[3 * k + 2]};
+                    const double d = sqrt(min_image_d2(p, a, b));
+                    int g = (int)fmin(d * p.inv_res, (double)p.n_edges);
+                    if (p.mode == 0) {
+                        while (g > 0 && !(s_edges[g - 1] < d)) --g;
+                        while (g < p.n_edges && s_edges[g] < d) ++g;
+                    } else {
+                        while (g > 0 && !(s_edges[g - 1] <= d)) --g;
+                        while (g < p.n_edges && s_edges[g] <= d) ++g;
+                        // np.histogram closes the last bin on the right
+                        if (g == p.n_edges && d == s_edges[p.n_edges - 1]) g = p.n_edges - 1;
+                    }
+                    atomicAdd(&my_hist[s_group[k] * nb + g], 1u);
+                }
+                __syncwarp();
+                unsigned long long *dst = p.hist + (size_t)c * hist_len;
+                for (int k = lane; k < hist_len; k += 32) {
+                    const uint32_t n = my_hist[k];
+                    if (n) {
+                        atomicAdd(dst + k, (unsigned long long)n);
+                        my_hist[k] = 0;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+}
+
+__global__ void k_rdf_classes(const int32_t *__restrict__ now, const int32_t *__restrict__ prev,
+                              const int32_t *__restrict__ next, int64_t n_frames, int32_t n1,
+                              const int32_t *__restrict__ site_label, int32_t n_sites, int32_t n_labels,
+                              const int32_t *__restrict__ lut, int32_t *__restrict__ cls,
+                              unsigned long long *__restrict__ first_key) {
+    const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (idx >= n_frames * n1) return;
+    // _uniqify_labels (rdf.py:19-27): digitize(right=True) sends -1 and 0 to "no site" and a
+    // state s >= 1 to the label of site s-1
+    auto lab = [&](int32_t s) { return (s >= 1 && s <= n_sites) ? site_label[s - 1] : -1; };
+    const int32_t w = n_labels + 1;
+    const int32_t code = ((lab(now[idx]) + 1) * w + (lab(prev[idx]) + 1)) * w + (lab(next[idx]) + 1);
+    const int32_t c = lut[code];
+    cls[idx] = c;
+    const unsigned long long key = ((unsigned long long)(idx / n1) << 32) | (uint32_t)code;
+    if (c >= 0 && first_key[c] > key) atomicMin(first_key + c, key);
+}
+
+}  // namespace
+
+extern "C" gd_status_t gd_rdf_classes(const int32_t *d_states, const int32_t *d_states_prev,
+                                      const int32_t *d_states_next, int64_t n_frames, int32_t n_floating,
+                                      const int32_t *d_site_label, int32_t n_sites, int32_t n_labels,
+                                      const int32_t *d_lut, int32_t *d_class,
+                                      unsigned long long *d_first_key, void *stream) {
+    GD_REQUIRE(n_frames >= 0 && n_floating >= 0 && n_sites >= 0 && n_labels >= 0 && n_labels < 1000, GD_ERR_INVALID,
+               "gd_rdf_classes: bad size");
+    if (n_frames == 0 || n_floating == 0) return GD_OK;
+    GD_REQUIRE(d_states && d_states_prev && d_states_next && d_site_label && d_lut && d_class && d_first_key,
+               GD_ERR_INVALID, "gd_rdf_classes: null pointer");
+    const int64_t n = n_frames * n_floating;
+    k_rdf_classes<<<(unsigned)gd_ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(
+        d_states, d_states_prev, d_states_next, n_frames, n_floating, d_site_label, n_sites, n_labels, d_lut,
+        d_class, d_first_key);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                                   const double *h_lattice, const int32_t *d_idx1, int32_t n1,
+                                   const int32_t *d_class, int32_t n_class, const int32_t *d_idx2,
+                                   const int32_t *d_group, int32_t n2, int32_t n_group,
+                                   const double *d_edges, int32_t n_edges, double resolution, int32_t mode,
+                                   int32_t skip_same_atom, unsigned long long *d_hist, void *stream) {
+    GD_REQUIRE(n_frames >= 0 && n_atoms > 0 && n1 >= 0 && n2 >= 0 && n_class > 0 && n_group > 0 && n_edges >= 2 &&
+                   (mode == 0 || mode == 1) && resolution > 0.0,
+               GD_ERR_INVALID, "gd_rdf_hist: bad argument");
+    if (n_frames == 0 || n1 == 0 || n2 == 0) return GD_OK;
+    GD_REQUIRE(d_pos_frac && h_lattice && d_idx1 && d_idx2 && d_edges && d_hist, GD_ERR_INVALID,
+               "gd_rdf_hist: null pointer");
+    RdfParams p;
+    p.pos = d_pos_frac;
+    p.n_frames = n_frames;
+    p.n_atoms = n_atoms;
+    p.idx1 = d_idx1;
+    p.n1 = n1;
+    p.cls = d_class;
+    p.idx2 = d_idx2;
+    p.group = d_group;
+    p.n2 = n2;
+    p.n_group = n_group;
+    p.edges = d_edges;
+    p.n_edges = n_edges;
+    p.mode = mode;
+    p.skip_same = skip_same_atom;
+    p.inv_res = 1.0 / resolution;
+    p.hist = d_hist;
+    memcpy(p.m, h_lattice, sizeof(p.m));
+    p.diag = (p.m[1] == 0.0 && p.m[2] == 0.0 && p.m[3] == 0.0 && p.m[5] == 0.0 && p.m[6] == 0.0 && p.m[7] == 0.0);
+    const GdDeviceInfo &dev = gd_device_info();
+    const size_t smem_cap = (size_t)(dev.max_smem_optin > 0 ? dev.max_smem_optin : 200 * 1024);
+    const size_t fixed = (size_t)n_edges * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
+    GD_REQUIRE(fixed + 32 * 32 <= smem_cap, GD_ERR_CAPACITY,
+               "gd_rdf_hist: %d groups x %d bins do not fit the per-warp shared-memory histograms", n_group,
+               n_edges + 1);
+    int64_t tile = (int64_t)((smem_cap - fixed) / 32);
+    if (tile > n2) tile = n2;
+    if (tile > 4096) tile = 4096;
+    p.tile = (int32_t)tile;
+    const size_t smem = (size_t)p.tile * 32 + fixed;
+    GD_CUDA_CHECK(cudaFuncSetAttribute(k_rdf_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int sms = dev.sm_count > 0 ? dev.sm_count : 148;
+    int64_t gy = gd_ceil_div((int64_t)sms * 4, n_frames);
+    const int64_t gy_max = gd_ceil_div(n1, kWarps);
+    if (gy > gy_max) gy = gy_max;
+    if (gy < 1) gy = 1;
+    int64_t gx = n_frames < (int64_t)sms * 64 ? n_frames : (int64_t)sms * 64;
+    dim3 grid((unsigned)gx, (unsigned)gy);
+    k_rdf_hist<<<grid, kWarps * 32, smem, (cudaStream_t)stream>>>(p);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}

@@ -302,3 +302,9 @@ class Trajectory:
         from .metrics import TrajectoryMetrics
 
         return TrajectoryMetrics(trajectory=self)
+
+    def radial_distribution_between_species(self, **kwargs):
+        """trajectory.py:1118-1124."""
+        from . import rdf
+
+        return rdf.radial_distribution_between_species(trajectory=self, **kwargs)

@@ -553,6 +553,12 @@ class Transitions:
 
         return Jumps(self, **kwargs)
 
+    def radial_distribution(self, **kwargs):
+        """transitions.py:204-223."""
+        from .rdf import radial_distribution
+
+        return radial_distribution(transitions=self, **kwargs)
+
     @property
     def n_floating(self) -> int:
         return len(self.diff_trajectory.species)

@@ -354,6 +354,48 @@ gd_status_t gd_collective_fill(const int32_t *d_sorted, int64_t n_jumps, const u
                                int32_t *d_pairs, void *stream);
 
 /* ------------------------------------------------------------------------- *
+ * N4  radial distribution functions
+ * replaces: radial_distribution, src/gemdat/rdf.py:111-190 (per-frame loop over
+ * lattice.get_all_distances + np.digitize + np.bincount per transition state) and
+ * radial_distribution_between_species, rdf.py:193-268 (np.histogram per frame).
+ * ------------------------------------------------------------------------- */
+
+/* Transition state of every floating atom in every frame (_get_states_array,
+ * rdf.py:53-61).  d_states / _prev / _next [n_frames,n_floating] int32 (site index or
+ * -1; prev = ffill, next = bfill, gd_fill_states).  d_site_label [n_sites]: label
+ * index of each site, n_labels < 1000.  _uniqify_labels' off-by-one is kept: a state
+ * s >= 1 takes the label of site s-1, states 0 and -1 count as "no site" (:19-27).
+ * d_lut [(n_labels+1)^3]: class of the dense code ((i+1)(L+1) + (j+1))(L+1) + (k+1),
+ * i/j/k = label of now/prev/next or -1 (the caller maps codes to state names,
+ * rdf.py:30-50; a negative entry drops the atom-frame).  d_class [n_frames,n_floating]
+ * is written; d_first_key [n_class] uint64, initialised by the caller to a large value,
+ * receives min((frame << 32) | code) per class: the order in which the reference's
+ * result dict gains its keys. */
+gd_status_t gd_rdf_classes(const int32_t *d_states, const int32_t *d_states_prev,
+                           const int32_t *d_states_next, int64_t n_frames, int32_t n_floating,
+                           const int32_t *d_site_label, int32_t n_sites, int32_t n_labels,
+                           const int32_t *d_lut, int32_t *d_class,
+                           unsigned long long *d_first_key, void *stream);
+
+/* Distance histograms over all frames.  d_pos_frac [n_frames,n_atoms,3] fractional;
+ * sources d_idx1 [n1] and targets d_idx2 [n2] are atom indices; d_class [n_frames,n1]
+ * (NULL: one class) and d_group [n2] (NULL: one group) select the table the pair is
+ * counted in.  Distances follow Lattice.get_all_distances (both ends wrapped to [0,1),
+ * shortest of the 27 images).  d_edges [n_edges] are the caller's exact bin edges
+ * (np.arange(0, max_dist + resolution, resolution)), `resolution` only seeds the
+ * search.  mode 0: np.digitize(d, edges, right=True), index = #edges < d;
+ * mode 1: np.histogram(d, edges), index = #edges <= d with d == edges[-1] counted in
+ * the last bin, i.e. bin b of np.histogram is index b+1.  skip_same_atom drops pairs
+ * of an atom with itself.  d_hist [n_class,n_group,n_edges+1] uint64 is ADDED to
+ * (zero it first). */
+gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                        const double *h_lattice, const int32_t *d_idx1, int32_t n1,
+                        const int32_t *d_class, int32_t n_class, const int32_t *d_idx2,
+                        const int32_t *d_group, int32_t n2, int32_t n_group,
+                        const double *d_edges, int32_t n_edges, double resolution, int32_t mode,
+                        int32_t skip_same_atom, unsigned long long *d_hist, void *stream);
+
+/* ------------------------------------------------------------------------- *
  * K0  displacement / unwrap
  * replaces: pymatgen Trajectory.to_displacements via Trajectory.displacements
  *           (src/gemdat/trajectory.py:182-193), cumulative_displacements

@@ -938,3 +938,81 @@ def test_jumps_collective_through_the_api():
     assert_array_equal(coll.pairs, pairs)
     assert jumps.n_solo_jumps == oc.solo_count(len(ev), pairs)
     assert jumps.solo_fraction == jumps.n_solo_jumps / jumps.n_jumps
+
+
+# ------------------------------------------------------------------ N4: radial distribution
+def _rdf_case():
+    from conftest import load_golden, load_pipeline_case
+
+    g = load_golden('rdf')
+    case = load_pipeline_case(str(g['fixture']))
+    traj, sites = _product(case)
+    radius, inner = _radius_args(case)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        tr = traj.transitions_between_sites(sites, 'Li', site_radius=radius, site_inner_fraction=inner,
+                                            fraction_of_overlap=float(case['fraction_of_overlap']))
+    return g, case, traj, tr
+
+
+@pytest.mark.parametrize('n', [0, 1])
+def test_radial_distribution_vs_reference_golden(n, monkeypatch):
+    """rdf.py:111-190 against curves from executing the reference
+    (tests/golden/make_golden_rdf.py); integer counts, bit-exact, in the reference's key order.
+    ``list(set(labels))`` is pinned to the order the golden run saw (it names the '~>' states)."""
+    import gemdat_b200.rdf as rdf_mod
+
+    g, case, traj, tr = _rdf_case()
+    uniq = [str(x) for x in g['unique_labels']]
+
+    class _PinnedSet(set):
+        def __iter__(self):
+            pinned = len(self) == len(uniq) and all(u in self for u in uniq)
+            return iter(uniq) if pinned else super().__iter__()
+
+    monkeypatch.setattr(rdf_mod, 'set', _PinnedSet, raising=False)
+    t = f'rdf{n}'
+    res = tr.radial_distribution(floating_specie='Li', max_dist=float(g[f'{t}_max_dist']),
+                                 resolution=float(g[f'{t}_resolution']))
+    flat = [(state, d) for state, coll in res.items() for d in coll]
+    assert [f[0] for f in flat] == [str(s) for s in g[f'{t}_states']]
+    assert [f[1].state for f in flat] == [str(s) for s in g[f'{t}_states']]
+    assert [f[1].label for f in flat] == [str(s) for s in g[f'{t}_symbols']]
+    assert_array_equal(flat[0][1].x, g[f'{t}_x'])
+    assert_array_equal(np.stack([f[1].y for f in flat]), g[f'{t}_y'])
+
+
+@pytest.mark.parametrize('n', [0, 1, 2])
+def test_radial_distribution_between_species_vs_reference_golden(n):
+    """rdf.py:193-268: integer histogram on the device, fp64 normalisation on the host; the
+    reference divides frame by frame and sums, here the sum is divided once: 1e-12 relative."""
+    g, case, traj, tr = _rdf_case()
+    t = f'between{n}'
+    s1, s2 = g[f'{t}_specie_1'].tolist(), g[f'{t}_specie_2'].tolist()
+    d = traj.radial_distribution_between_species(specie_1=s1, specie_2=s2, max_dist=float(g[f'{t}_max_dist']),
+                                                 resolution=float(g[f'{t}_resolution']))
+    assert d.label == str(g[f'{t}_label']) and d.state == ''
+    assert_array_equal(d.x, g[f'{t}_x'])
+    assert_allclose(d.y, g[f'{t}_y'], rtol=1e-12, atol=0)
+
+
+@pytest.mark.parametrize('triclinic', [False, True])
+def test_rdf_hist_random_vs_oracle(triclinic):
+    """gd_rdf_hist on a random mixed-species trajectory (general and diagonal cell, several target
+    tiles' worth of atoms, coordinates outside [0,1)) against oracle/rdf.py."""
+    from gemdat_b200 import Trajectory
+    from oracle import rdf as orf
+
+    rng = np.random.default_rng(11 + triclinic)
+    lat = np.array([[9.0, 0.0, 0.0], [1.5, 8.0, 0.0], [-0.7, 0.9, 10.0]]) if triclinic else np.diag([9.0, 8.0, 10.0])
+    species = ['Li'] * 37 + ['O'] * 150 + ['La'] * 20
+    pos = rng.random((12, len(species), 3)) * 1.4 - 0.2
+    traj = Trajectory(species=species, coords=pos, lattice=lat, time_step=1e-15)
+    for s1, s2, md, res in [('Li', 'O', 5.0, 0.1), ('O', 'O', 4.0, 0.25), (['Li', 'La'], 'O', 6.0, 0.3)]:
+        d = traj.radial_distribution_between_species(specie_1=s1, specie_2=s2, max_dist=md, resolution=res)
+        w1, w2 = ([s1] if isinstance(s1, str) else s1), ([s2] if isinstance(s2, str) else s2)
+        sel = lambda want: pos[:, [s in want for s in species]]  # noqa: E731
+        x, y = orf.between_species(coords_1=sel(w1), coords_2=sel(w2), same=(s1 == s2), lattice=lat, max_dist=md,
+                                   resolution=res)
+        assert_array_equal(d.x, x)
+        assert_allclose(d.y, y, rtol=1e-12, atol=0)
