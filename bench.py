@@ -346,6 +346,37 @@ def run_extras(args, rec, world, rank, peaks, jumps=None):
     }
     del soa, msd
 
+    # ---- N4: species-species distance histogram (rdf.py:193-268) over a bounded frame window
+    if world == 1:
+        from gemdat_b200.rdf import _hist
+
+        rdf_frames = min(T, 2000)
+        bins = np.arange(0, 5.0 + 0.1, 0.1)
+        atoms = np.arange(A)
+        got = {}
+
+        def n4():
+            got['h'] = _hist(pos[:rdf_frames], rec.lattice, atoms, None, 1, atoms, None, 1, bins, 0.1, 1, True)
+
+        ms = timed(n4, reps=2)
+        n_pairs = float(rdf_frames) * A * (A - 1)
+        out['rdf'] = {'ms': ms, 'frames': rdf_frames, 'pairs_per_s': n_pairs / (ms * 1e-3),
+                      'counted': int(got['h'].sum()), 'bins': len(bins) - 1, 'max_dist_A': 5.0,
+                      'includes': 'index/edge upload, kernel, histogram read-back',
+                      'note': 'diagonal cell: 9 image terms per pair instead of 27 (exact, see gd_rdf.cu)'}
+        if not args.no_cpu_baseline:
+            from oracle import rdf as ordf  # checker / CPU baseline leg only
+
+            host = pos[:2].cpu().numpy()
+            t0 = time.perf_counter()
+            _, y = ordf.between_species(coords_1=host, coords_2=host, same=True, lattice=rec.lattice)
+            dt = time.perf_counter() - t0
+            mine = _hist(pos[:2], rec.lattice, atoms, None, 1, atoms, None, 1, bins, 0.1, 1, True)[0, 0, 1:len(bins)]
+            shell = (bins + 0.1) ** 3 - bins**3
+            norm = ((A * A / float(abs(np.linalg.det(np.asarray(rec.lattice, dtype=np.float64))))) * (4 / 3) * np.pi * shell)[:-1]
+            out['rdf']['cpu_port'] = {'frames': 2, 's': dt, 'pairs_per_s': 2.0 * A * (A - 1) / dt,
+                                      'equal': bool(np.allclose(mine / norm / 2, y, rtol=1e-12, atol=0))}
+
     # ---- N3: collective-jump pair search on the step's own jump table (rank-local, N=1 only)
     if jumps is not None and world == 1 and int(jumps.shape[0]) > 1:
         from gemdat_b200.collective import _close_matrix, collective_pairs_device

@@ -108,10 +108,14 @@ def radial_distribution(*, transitions, floating_specie: str, max_dist: float = 
     assert int(states.shape[1]) == len(floating), 'transitions do not belong to this floating specie'
     cls = dv.empty((n_frames, len(floating)), torch.int32)
     first_key = torch.full((len(names),), torch.iinfo(torch.int64).max, dtype=torch.int64, device=pos.device)
+    # named so that the buffers outlive the launch (a temporary would hand its block back to the
+    # caching allocator, and the next temporary would overwrite it before the kernel runs)
+    prev, nxt = _fill_device(states, +1), _fill_device(states, -1)
+    d_site_label, d_lut = dv.to_device(site_label), dv.to_device(lut)
     _lib.check(_lib.lib.gd_rdf_classes(
-        dv.ptr(states), dv.ptr(_fill_device(states, +1)), dv.ptr(_fill_device(states, -1)), n_frames,
-        len(floating), dv.ptr(dv.to_device(site_label)), len(labels), len(unique_labels),
-        dv.ptr(dv.to_device(lut)), dv.ptr(cls), dv.ptr(first_key), dv.stream_ptr()))
+        dv.ptr(states), dv.ptr(prev), dv.ptr(nxt), n_frames, len(floating), dv.ptr(d_site_label),
+        len(labels), len(unique_labels), dv.ptr(d_lut), dv.ptr(cls), dv.ptr(first_key), dv.stream_ptr()))
+    del prev, nxt
     group = np.array([symbol_set.index(s) for s in symbols], dtype=np.int32)
     hist = _hist(pos, trajectory.get_lattice(), floating, cls, len(names), np.arange(len(symbols)), group,
                  len(symbol_set), bins, resolution, 0, False)
