@@ -8,8 +8,10 @@
 //   gd_rdf_hist     per frame: minimum-image distances source atoms x target atoms
 //                   (Lattice.get_all_distances: both wrapped to [0,1), 27 images, same
 //                   operation order as gd_pbc_distances), np.digitize(right=True) or
-//                   np.histogram binning against the caller's exact edges, counted per
-//                   (class of the source, group of the target, bin)
+//                   np.histogram binning against the caller's exact edges -- on the squared
+//                   distance, through per-edge thresholds that reproduce the comparison with
+//                   the rounded square root exactly -- counted per (class of the source,
+//                   group of the target, bin)
 //
 // One CTA per (frame, slice of the sources); the frame's targets sit in shared memory wrapped
 // to [0,1); one warp per source, lanes over targets, a warp-private shared-memory histogram
@@ -83,19 +85,37 @@ __device__ __forceinline__ double min_image_d2(const RdfParams &p, const double 
     return best;
 }
 
+// Smallest x >= 0 whose correctly rounded square root is >= e (strict: > e).  sqrt is monotonic,
+// so "e <= fl(sqrt(d2))" is the same test as "x <= d2": the bins are found on d2 itself and the
+// pair loop needs no fp64 square root.  About two doubles share one rounded root, so the walk
+// from fl(e*e) is a handful of steps.
+__device__ double sqrt_threshold(double e, bool strict) {
+    if (!(e > 0.0)) return (strict || e < 0.0) ? (e < 0.0 ? 0.0 : __longlong_as_double(1)) : 0.0;
+    double x = e * e;
+    auto ok = [&](double v) { return strict ? sqrt(v) > e : sqrt(v) >= e; };
+    while (x > 0.0 && ok(x)) x = __longlong_as_double(__double_as_longlong(x) - 1);
+    while (!ok(x)) x = __longlong_as_double(__double_as_longlong(x) + 1);
+    return x;
+}
+
 __global__ void __launch_bounds__(kWarps * 32) k_rdf_hist(const __grid_constant__ RdfParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int nb = p.n_edges + 1;
     const int hist_len = p.n_group * nb;
     double *s_b = reinterpret_cast<double *>(smem);                 // [tile][3]
-    double *s_edges = s_b + 3 * (size_t)p.tile;                      // [n_edges]
-    int32_t *s_atom = reinterpret_cast<int32_t *>(s_edges + p.n_edges);  // [tile]
+    double *s_edges = s_b + 3 * (size_t)p.tile;                      // [n_edges + 1] thresholds on d2
+    int32_t *s_atom = reinterpret_cast<int32_t *>(s_edges + p.n_edges + 1);  // [tile]
     int32_t *s_group = s_atom + p.tile;                              // [tile]
     uint32_t *s_hist = reinterpret_cast<uint32_t *>(s_group + p.tile);   // [kWarps][hist_len]
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float inv_res = (float)p.inv_res;
     uint32_t *my_hist = s_hist + (size_t)warp * hist_len;
-    for (int k = threadIdx.x; k < p.n_edges; k += blockDim.x) s_edges[k] = p.edges[k];
+    // s_edges[k] = threshold on d2 for edge k (mode 0: edge < d, mode 1: edge <= d);
+    // s_edges[n_edges] = where d2 leaves "d == last edge" (np.histogram's closed last bin)
+    for (int k = threadIdx.x; k <= p.n_edges; k += blockDim.x)
+        s_edges[k] = k < p.n_edges ? sqrt_threshold(p.edges[k], p.mode == 0)
+                                   : sqrt_threshold(p.edges[p.n_edges - 1], true);
     for (int k = threadIdx.x; k < kWarps * hist_len; k += blockDim.x) s_hist[k] = 0;
 
     for (int64_t t = blockIdx.x; t < p.n_frames; t += gridDim.x) {
@@ -122,17 +142,13 @@ __global__ void __launch_bounds__(kWarps * 32) k_rdf_hist(const __grid_constant_
                 for (int k = lane; k < nt; k += 32) {
                     if (p.skip_same && s_atom[k] == atom_i) continue;
                     const double b[3] = {s_b[3 * k], s_b[3 * k + 1], s_b[3 * k + 2]};
-                    const double d = sqrt(min_image_d2(p, a, b));
-                    int g = (int)fmin(d * p.inv_res, (double)p.n_edges);
-                    if (p.mode == 0) {
-                        while (g > 0 && !(s_edges[g - 1] < d)) --g;
-                        while (g < p.n_edges && s_edges[g] < d) ++g;
-                    } else {
-                        while (g > 0 && !(s_edges[g - 1] <= d)) --g;
-                        while (g < p.n_edges && s_edges[g] <= d) ++g;
-                        // np.histogram closes the last bin on the right
-                        if (g == p.n_edges && d == s_edges[p.n_edges - 1]) g = p.n_edges - 1;
-                    }
+                    const double d2 = min_image_d2(p, a, b);
+                    // fp32 guess of the bin, corrected against the exact thresholds
+                    int g = (int)fminf(sqrtf((float)d2) * inv_res, (float)p.n_edges);
+                    while (g > 0 && !(s_edges[g - 1] <= d2)) --g;
+                    while (g < p.n_edges && s_edges[g] <= d2) ++g;
+                    // np.histogram closes the last bin on the right: d == last edge
+                    if (p.mode == 1 && g == p.n_edges && d2 < s_edges[p.n_edges]) g = p.n_edges - 1;
                     atomicAdd(&my_hist[s_group[k] * nb + g], 1u);
                 }
                 __syncwarp();
@@ -221,7 +237,7 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
     p.diag = (p.m[1] == 0.0 && p.m[2] == 0.0 && p.m[3] == 0.0 && p.m[5] == 0.0 && p.m[6] == 0.0 && p.m[7] == 0.0);
     const GdDeviceInfo &dev = gd_device_info();
     const size_t smem_cap = (size_t)(dev.max_smem_optin > 0 ? dev.max_smem_optin : 200 * 1024);
-    const size_t fixed = (size_t)n_edges * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
+    const size_t fixed = (size_t)(n_edges + 1) * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
     GD_REQUIRE(fixed + 32 * 32 <= smem_cap, GD_ERR_CAPACITY,
                "gd_rdf_hist: %d groups x %d bins do not fit the per-warp shared-memory histograms", n_group,
                n_edges + 1);
