@@ -269,3 +269,46 @@ def test_exclusive_ball_decides_alone(lengths, n_sites, radius, inner, pattern):
         got_i = np.where(got_i >= 0, lut_i[np.clip(got_i, 0, None)], -1)
     np.testing.assert_array_equal(got_o[inside], exp_o[inside, 0])
     np.testing.assert_array_equal(got_i[inside], exp_i[inside, 0])
+
+
+def test_rdf_state_table_matches_the_reference_names():
+    """Host side of N4: gemdat_b200.rdf._state_names (dense code -> name index) against the
+    code -> name dict the reference's _get_states produced for the golden run, through the
+    reference's own integer codes (rdf.py:30-50)."""
+    from conftest import load_golden
+    from gemdat_b200 import rdf
+
+    g = load_golden('rdf')
+    uniq = [str(x) for x in g['unique_labels']]
+    lut, names = rdf._state_names(uniq)
+    ref = dict(zip(g['states2str_codes'].tolist(), [str(x) for x in g['states2str_names']]))
+    n = len(uniq)
+    assert len(lut) == (n + 1) ** 3 and len(ref) == len(lut)
+    for i in range(-1, n):
+        for j in range(-1, n):
+            for k in range(-1, n):
+                dense = ((i + 1) * (n + 1) + (j + 1)) * (n + 1) + (k + 1)
+                assert names[lut[dense]] == ref[int(i * 1e6 + j * 1e3 + k)]
+    # dense codes order states like the reference's signed codes do (key order of the result)
+    codes = [int(i * 1e6 + j * 1e3 + k) for i in range(-1, n) for j in range(-1, n) for k in range(-1, n)]
+    assert codes == sorted(codes)
+
+
+def test_collective_and_rdf_entry_points_reject_bad_arguments_without_a_gpu():
+    """Argument checks run before any CUDA call, so they are testable here."""
+    lib = _lib.lib
+    assert lib.gd_collective_work_bytes(-1) == -1
+    n_pairs, n_solo = C.c_int64(7), C.c_int64(7)
+    assert lib.gd_collective_count(None, 0, None, 0, 5, None, C.byref(n_pairs), C.byref(n_solo), None) == 0
+    assert (n_pairs.value, n_solo.value) == (0, 0)
+    assert lib.gd_collective_count(None, 3, None, 1, 5, None, C.byref(n_pairs), C.byref(n_solo), None) != 0
+    assert 'null pointer' in _lib.last_error()
+    assert lib.gd_collective_sort(None, -1, None, None, None) != 0
+    lat = np.eye(3) * 5.0
+    assert lib.gd_rdf_hist(None, 4, 3, lat.ctypes.data, None, 2, None, 1, None, None, 2, 1, None, 1, 0.1, 0, 0,
+                           None, None) != 0  # fewer than two edges
+    assert 'gd_rdf_hist' in _lib.last_error()
+    assert lib.gd_rdf_hist(None, 0, 3, lat.ctypes.data, None, 2, None, 1, None, None, 2, 1, None, 5, 0.1, 0, 0,
+                           None, None) == 0  # no frames: nothing to do
+    assert lib.gd_rdf_classes(None, None, None, 0, 4, None, 3, 2, None, None, None, None) == 0
+    assert lib.gd_rdf_classes(None, None, None, 2, 4, None, 3, 1000, None, None, None, None) != 0
