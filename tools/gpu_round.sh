@@ -27,5 +27,10 @@ if [[ "${2:-}" != "skip-ncu" ]]; then
       -k 'regex:k_site_states|k_events_compact|k_jumps_spec' -c 3 -f -o $out/${tag}_k1_k2 \
       python bench.py $small > $out/${tag}_ncu_full.log 2>&1
   echo "ncu full exit $?"
+  # N4: the RDF kernel on its own (tools/rdf_time.py: diagonal and triclinic cell, both binnings)
+  timeout 120 python tools/rdf_time.py > $out/${tag}_rdf_time.txt 2>&1
+  timeout 600 ncu --set full --clock-control none --import-source on -k 'regex:k_rdf_hist' -c 4 -f \
+      -o $out/${tag}_rdf python tools/rdf_time.py > $out/${tag}_ncu_rdf.log 2>&1
+  echo "ncu rdf exit $?"
 fi
 ls -la $out | tail -20
