@@ -312,3 +312,33 @@ def test_collective_and_rdf_entry_points_reject_bad_arguments_without_a_gpu():
                            None, None) == 0  # no frames: nothing to do
     assert lib.gd_rdf_classes(None, None, None, 0, 4, None, 3, 2, None, None, None, None) == 0
     assert lib.gd_rdf_classes(None, None, None, 2, 4, None, 3, 1000, None, None, None, None) != 0
+
+
+def test_sqrt_threshold_argument_of_the_rdf_binning():
+    """gd_rdf.cu bins on the squared distance: for every edge e it walks from fl(e*e) to the
+    smallest double x with fl(sqrt(x)) > e (or >= e).  The same walk in numpy (np.sqrt is correctly
+    rounded like the device's) must make `x <= d2` agree with the comparison on the rounded root
+    for every double around the threshold."""
+    def threshold(e, strict):
+        if not e > 0.0:
+            return np.nextafter(0.0, 1.0) if strict else 0.0
+        ok = (lambda v: np.sqrt(v) > e) if strict else (lambda v: np.sqrt(v) >= e)
+        x = np.float64(e) * np.float64(e)
+        while x > 0.0 and ok(x):
+            x = np.nextafter(x, -np.inf)
+        while not ok(x):
+            x = np.nextafter(x, np.inf)
+        return x
+
+    for edges in (np.arange(0, 5.0 + 0.1, 0.1), np.arange(0, 3.3 + 0.25, 0.25), np.array([0.0, 1e-9, 2.0, 1e4])):
+        for strict in (True, False):
+            for e in edges:
+                x = threshold(float(e), strict)
+                around = [x]
+                for _ in range(6):
+                    around = [np.nextafter(around[0], -np.inf)] + around + [np.nextafter(around[-1], np.inf)]
+                for d2 in around:
+                    if d2 < 0:
+                        continue
+                    d = np.sqrt(d2)
+                    assert (d > e if strict else d >= e) == (x <= d2), (e, strict, d2)
