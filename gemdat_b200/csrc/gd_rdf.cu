@@ -21,6 +21,16 @@
 // (rounding is monotonic, so min over images of fl(fl(X+Y)+Z) = fl(fl(minX+minY)+minZ)).
 #include "gd_common.cuh"
 
+// Tuning knobs for A/B builds (tools/rdf_variants.sh); the defaults are the measured ones.
+#ifndef GD_RDF_DIAG_SELECT
+#define GD_RDF_DIAG_SELECT 0
+#endif
+#ifdef GD_RDF_MIN_CTAS  // resident CTAs per SM the register allocation must allow
+#define GD_RDF_BOUNDS __launch_bounds__(8 * 32, GD_RDF_MIN_CTAS)
+#else
+#define GD_RDF_BOUNDS __launch_bounds__(8 * 32)
+#endif
+
 namespace {
 
 constexpr int kWarps = 8;
@@ -62,6 +72,19 @@ __device__ __forceinline__ double min_image_d2(const RdfParams &p, const double 
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             const double mk = p.m[4 * k];
+#if GD_RDF_DIAG_SELECT
+            // Experiment (off by default, not yet measured): |v| -> fl(fl(v*mk)^2) is monotonic,
+            // so the minimum is taken by the candidate of smallest magnitude, and away from
+            // |b - a| = 1/2 that candidate is known from b - a alone (the candidates' magnitudes
+            // differ by 1 - 2|b - a|, far above their rounding errors).
+            const double u = b[k] - a[k];
+            if (fabs(fabs(u) - 0.5) > 1e-6) {
+                const double vk = u > 0.5 ? v[k][0] : (u < -0.5 ? v[k][2] : v[k][1]);
+                const double c = vk * mk;
+                mn[k] = c * c;
+                continue;
+            }
+#endif
             const double c0 = v[k][0] * mk, c1 = v[k][1] * mk, c2 = v[k][2] * mk;
             mn[k] = fmin(fmin(c0 * c0, c1 * c1), c2 * c2);
         }
@@ -98,7 +121,7 @@ __device__ double sqrt_threshold(double e, bool strict) {
     return x;
 }
 
-__global__ void __launch_bounds__(kWarps * 32) k_rdf_hist(const __grid_constant__ RdfParams p) {
+__global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int nb = p.n_edges + 1;
     const int hist_len = p.n_group * nb;
