@@ -254,3 +254,51 @@ def test_oracle_rdf_vs_reference_golden():
                                    max_dist=float(g[f'{t}_max_dist']), resolution=float(g[f'{t}_resolution']))
         np.testing.assert_array_equal(x, g[f'{t}_x'])
         np.testing.assert_allclose(y, g[f'{t}_y'], rtol=1e-13)
+
+
+def test_oracle_collective_edge_cases():
+    """Empty and one-row tables, a window of zero frames, and the early break: a partner whose
+    start lies beyond the window ends the walk of i even if a later row would qualify."""
+    from oracle import collective as oc
+
+    lat = np.eye(3) * 10.0
+    frac = np.array([[0.1, 0.1, 0.1], [0.15, 0.1, 0.1], [0.6, 0.6, 0.6]])
+    empty = np.zeros((0, 6), dtype=np.int64)
+    ev, pairs = oc.collective_pairs(empty, frac, lat, 5, 1.0)
+    assert ev.shape == (0, 6) and pairs.shape == (0, 2) and oc.solo_count(0, pairs) == 0
+    one = np.array([[0, 0, 1, 3, 4, 0]])
+    ev, pairs = oc.collective_pairs(one, frac, lat, 5, 1.0)
+    assert pairs.shape == (0, 2) and oc.solo_count(1, pairs) == 1
+    # rows sorted by (stop, start): B starts late and stops at 30, C starts early and stops at 31
+    #   A: atom 0, start 0, stop 1;  B: atom 1, start 29, stop 30;  C: atom 2, start 2, stop 31
+    table = np.array([[0, 0, 1, 0, 1, 0], [1, 2, 2, 29, 30, 0], [2, 1, 0, 2, 31, 0]])
+    ev, pairs = oc.collective_pairs(table, frac, lat, 5, 1.0)
+    # A-C would qualify (start_C - stop_A = 1, sites 0/1 are 0.5 A apart) but B breaks A's walk first
+    assert pairs.tolist() == []
+    ev, pairs = oc.collective_pairs(table[[0, 2]], frac, lat, 5, 1.0)
+    assert pairs.tolist() == [[0, 1]] and oc.solo_count(2, pairs) == 0
+    # same atom is never paired with itself
+    same = table[[0, 2]].copy()
+    same[:, 0] = 7
+    assert oc.collective_pairs(same, frac, lat, 5, 1.0)[1].shape == (0, 2)
+
+
+def test_oracle_rdf_edge_cases():
+    """Self distance lands in bin 0 of the state-resolved RDF; distances beyond max_dist fall in the
+    dropped overflow bin; a distance exactly on an edge belongs to the bin it closes (right=True)
+    and, for np.histogram, to the bin it opens."""
+    from oracle import rdf as orf
+
+    lat = np.eye(3) * 10.0
+    pos = np.array([[[0.0, 0.0, 0.0], [0.05, 0.0, 0.0], [0.5, 0.5, 0.5]]])  # 0.5 A and 8.66 A away
+    codes = np.array([[orf.state_code(0, 0, 0)]])
+    res = orf.radial_distribution(positions=pos, symbols=['Li', 'O', 'O'], floating_specie='Li', codes=codes,
+                                  unique_labels=['a'], lattice=lat, max_dist=1.0, resolution=0.5)
+    (x_li, y_li), (x_o, y_o) = res[('@a', 'Li')], res[('@a', 'O')]
+    np.testing.assert_array_equal(x_li, [0.0, 0.5, 1.0])
+    np.testing.assert_array_equal(y_li, [1, 0, 0])  # the atom itself, d = 0
+    np.testing.assert_array_equal(y_o, [0, 1, 0])   # d = 0.5 closes bin (0, 0.5]; 8.66 A is dropped
+    x, y = orf.between_species(coords_1=pos[:, :1], coords_2=pos[:, 1:], same=False, lattice=lat, max_dist=1.0,
+                               resolution=0.5)
+    np.testing.assert_array_equal(x, [0.0, 0.5])
+    assert y[0] == 0.0 and y[1] > 0.0  # np.histogram: d = 0.5 opens [0.5, 1.0]
