@@ -42,7 +42,7 @@ def parse_args():
     ap.add_argument('--e2e-frames', type=int, default=100_000, help='frames per e2e step (host buffers)')
     ap.add_argument('--cpu-frames', type=int, default=2_000, help='frames of the CPU baseline sample')
     ap.add_argument('--no-cpu-baseline', action='store_true')
-    ap.add_argument('--no-extras', action='store_true', help='skip the MSD / unwrap / density section')
+    ap.add_argument('--no-extras', action='store_true', help='skip the MSD / unwrap / density / RDF / collective-jump section')
     ap.add_argument('--phases', action='store_true',
                     help='after the timed region, run 3 more steps synchronising at phase boundaries '
                          'and report wall ms per phase (diagnostics)')
@@ -238,7 +238,9 @@ def workload_config(rec, args):
 def run_extras(args, rec, world, rank, peaks, jumps=None):
     """The other kernels of the path on the same C3 trajectory, timed with CUDA events:
     K0 unwrap (HBM bound), K4 direct MSD over a bounded lag range (fp64 pipe bound; the lag axis
-    is sharded over the ranks, positions replicated), K5 density histogram at 0.1 A."""
+    is sharded over the ranks, positions replicated), K5 density histogram at 0.1 A; at N=1 also
+    the next rows N4 (species RDF over a 2000-frame window) and N3 (collective pairs of the
+    step's own jump table), each beside its numpy port on a bounded sample."""
     import ctypes as C
 
     import torch
