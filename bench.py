@@ -288,7 +288,7 @@ def run_extras(args, rec, world, rank, peaks, jumps=None):
 
     def k0():
         _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None, dv.ptr(work),
-                                 None, dv.ptr(cart), None, dv.ptr(wind), s))
+                                 None, dv.ptr(cart), None, None, dv.ptr(wind), s))
 
     ms = reduce_max(timed(k0))
     gbs = 72.0 * T * A / (ms * 1e-3) / 1e9  # 24 B read twice (winding pass + apply) + 24 B written

@@ -73,6 +73,14 @@ SIGNATURES = {
     'gd_events_merge': (C.c_int, [_p, _p, _p, _i32, _p, _p]),
     'gd_events_merge_capped': (C.c_int, [_p, _p, _p, _i32, _p, _i64, _i64, _p]),
     'gd_fill_states': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p, _p]),
+    'gd_fill_last_valid': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p]),
+    'gd_fill_apply': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p]),
+    'gd_occupancy': (C.c_int, [_p, _i64, _i32, _p, _p]),
+    'gd_residence_work_bytes': (_i64, [_i64]),
+    'gd_residence_count': (C.c_int, [_p, _i64, _p, C.POINTER(_i64), _p]),
+    'gd_residence_fill': (C.c_int, [_p, _i64, _p, _p, _p]),
+    'gd_events_split_count': (C.c_int, [_p, _p, _i32, _p, _i32, _p, _p, _p]),
+    'gd_events_split_fill': (C.c_int, [_p, _i32, _p, _i32, _p, _p, _p, _p, _p, _p]),
     'gd_jumps_work_bytes': (_i64, [_i64, _i32]),
     'gd_jumps_count': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, C.POINTER(_i64), _p]),
     'gd_jumps_fill': (C.c_int, [_p, _p, _i64, _i32, _i64, _i64, _p, _p, _p]),
@@ -91,10 +99,20 @@ SIGNATURES = {
     'gd_rdf_hist': (C.c_int, [_p, _i64, _i32, _p, _p, _i32, _p, _i32, _p, _p, _i32, _i32, _p, _i32,
                               C.c_double, _i32, _i32, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),
-    'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_unwrap_windings': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p]),
+    'gd_unwrap_apply': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    'gd_amplitudes_work_bytes': (_i64, [_i64, _i32]),
+    'gd_amplitudes_count': (C.c_int, [_p, _i64, _i32, _p, _p, C.POINTER(_i64), _p]),
+    'gd_amplitudes_fill': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p]),
+    'gd_mean_std_work_bytes': (_i64, []),
+    'gd_mean_std': (C.c_int, [_p, _i64, _p, C.POINTER(C.c_double), C.POINTER(C.c_double), _p]),
+    'gd_transpose_f64': (C.c_int, [_p, _i64, _i64, _p, _p]),
+    'gd_wrap_unit': (C.c_int, [_p, _p, _i64, _p, _p]),
     'gd_transpose_soa': (C.c_int, [_p, _i64, _i32, _p, _p]),
     'gd_msd_direct': (C.c_int, [_p, _i64, _i32, _i64, _i64, _p, _p]),
     'gd_density': (C.c_int, [_p, _i64, _p, _p, _p, _p]),
+    'gd_lll_reduce_host': (C.c_int, [_p, _p, _p]),
     'gd_pbc_distances': (C.c_int, [_p, _p, _i32, _p, _i32, _p, _p]),
     'gd_synth_positions': (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _p, _u64, _i64, _i64, _p, _p]),
     'gd_fp64_peak': (C.c_int, [_i64, C.POINTER(C.c_double), _p]),

@@ -9,7 +9,9 @@ mkdir -p _build
 pids=()
 for f in gd_*.cu; do
   o=_build/${f%.cu}.o
-  if [[ ! -f $o || $f -nt $o || gd_common.cuh -nt $o || ../../include/gemdat_b200.h -nt $o ]]; then
+  stale=0
+  for dep in "$f" gd_*.cuh ../../include/gemdat_b200.h build.sh; do [[ $dep -nt $o ]] && stale=1; done
+  if [[ ! -f $o || $stale == 1 ]]; then
     ( "$NVCC" "${FLAGS[@]}" -c "$f" -o "$o" > "_build/${f%.cu}.log" 2>&1 || { cat "_build/${f%.cu}.log"; exit 1; } ) &
     pids+=($!)
   fi

@@ -157,4 +157,37 @@ __device__ __forceinline__ int gd_warp_sum(int v) {
     return v;
 }
 
+// single block of 1024 threads: v[0] = 0, v[1..n] -> inclusive scan in place, i.e. v[0..n]
+// become exclusive offsets with the total in v[n] (tables of per-atom / per-block counts)
+template <int kUnused = 0>
+__global__ void __launch_bounds__(1024) gd_k_scan_offsets(int64_t *__restrict__ v, int64_t n) {
+    __shared__ int64_t warp_tot[32];
+    __shared__ int64_t running_s;
+    if (threadIdx.x == 0) {
+        running_s = 0;
+        v[0] = 0;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t base = 0; base < n; base += 1024) {
+        const int64_t idx = base + threadIdx.x;
+        const int64_t x = idx < n ? v[idx + 1] : 0;
+        int64_t incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int64_t y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        int64_t warp_base = 0;
+        for (int w = 0; w < warp; ++w) warp_base += warp_tot[w];
+        const int64_t running = running_s;
+        __syncthreads();
+        if (idx < n) v[idx + 1] = running + warp_base + incl;
+        if (threadIdx.x == 1023) running_s = running + warp_base + incl;
+        __syncthreads();
+    }
+}
+
 #endif  // __CUDACC__

@@ -71,6 +71,38 @@ extern "C" gd_status_t gd_widen_i32_i64(const int32_t *d_in, int64_t *d_out, int
     return GD_OK;
 }
 
+// ------------------------------------------------------------------ wrap to [0, 1)
+// Trajectory.to_positions ends with np.mod(coords, 1) (reference src/gemdat/trajectory.py:121-127).
+// d_out == NULL: only report whether any coordinate lies outside [0, 1).
+__global__ void __launch_bounds__(256) k_wrap_unit(const double *__restrict__ in,
+                                                   double *__restrict__ out, int64_t n,
+                                                   int32_t *__restrict__ flag) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    bool outside = false;
+    for (; i < n; i += stride) {
+        const double x = in[i];
+        const bool bad = !(x >= 0.0 && x < 1.0);
+        outside |= bad;
+        if (out) out[i] = bad ? x - floor(x) : x;  // np.mod(x, 1): fmod, +1 when negative
+    }
+    if (outside) *flag = 1;
+}
+
+extern "C" gd_status_t gd_wrap_unit(const double *d_in, double *d_out, int64_t n,
+                                    int32_t *d_flag, void *stream) {
+    GD_REQUIRE(n >= 0 && d_flag && (n == 0 || d_in), GD_ERR_INVALID, "gd_wrap_unit: bad args");
+    if (n == 0) return GD_OK;
+    const GdDeviceInfo &dev = gd_device_info();
+    GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");
+    int64_t blocks = gd_ceil_div(n, 256);
+    const int64_t cap = (int64_t)dev.sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    k_wrap_unit<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, d_flag);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
 // ------------------------------------------------------------------ LUT remap
 __global__ void __launch_bounds__(256) k_remap(int32_t *__restrict__ s, int64_t n,
                                                const int32_t *__restrict__ lut, int32_t n_sites) {

@@ -19,6 +19,7 @@
 #include <string.h>
 
 #include "gd_common.cuh"
+#include "gd_pbc.cuh"
 
 namespace {
 
@@ -114,8 +115,9 @@ __global__ void __launch_bounds__(128)
 __global__ void __launch_bounds__(256)
     k_unwrap_apply(const double *__restrict__ pos, UGeom g, const double *__restrict__ prev_row,
                    const double *__restrict__ base_pos, const int32_t *__restrict__ work,
-                   const __grid_constant__ Mat9 L, double *__restrict__ cum_frac,
-                   double *__restrict__ cum_cart, double *__restrict__ dist) {
+                   const int32_t *__restrict__ extra_winding, const __grid_constant__ Mat9 L,
+                   double *__restrict__ cum_frac, double *__restrict__ cum_cart,
+                   double *__restrict__ dist, double *__restrict__ speed) {
     const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (item >= g.n_chunks * g.n_atoms) return;
     const int64_t c = item / g.n_atoms;
@@ -126,6 +128,11 @@ __global__ void __launch_bounds__(256)
     const double bx = b[0], by = b[1], bz = b[2];
     const int32_t *w = work + (c * g.n_atoms + a) * 3;
     int wx = w[0], wy = w[1], wz = w[2];
+    if (extra_winding) {  // windings of the preceding shards (work was scanned from zero)
+        wx += extra_winding[3 * a];
+        wy += extra_winding[3 * a + 1];
+        wz += extra_winding[3 * a + 2];
+    }
     double px, py, pz;
     bool first_is_zero = false;
     if (t0 == 0) {
@@ -145,6 +152,19 @@ __global__ void __launch_bounds__(256)
         py = q[1];
         pz = q[2];
     }
+    // metric-tensor length of a fractional displacement (_lengths, trajectory.py:40-60)
+    auto length = [&](double cx, double cy, double cz) {
+        const double gx = fma(cz, L.g[6], fma(cy, L.g[3], cx * L.g[0]));
+        const double gy = fma(cz, L.g[7], fma(cy, L.g[4], cx * L.g[1]));
+        const double gz = fma(cz, L.g[8], fma(cy, L.g[5], cx * L.g[2]));
+        return sqrt(fmax(fma(gz, cz, fma(gy, cy, gx * cx)), 0.0));
+    };
+    // speed = np.diff(distance, prepend=0) (metrics.py:46-47): distance of the frame before
+    // this segment, from the position before it and the winding up to it
+    double pd = 0.0;
+    if (speed && !first_is_zero)
+        pd = length(__dsub_rn(__dsub_rn(px, bx), (double)wx), __dsub_rn(__dsub_rn(py, by), (double)wy),
+                    __dsub_rn(__dsub_rn(pz, bz), (double)wz));
 #pragma unroll 2
     for (int64_t t = t0; t < t1; ++t) {
         const double *q = pos + t * A3 + 3 * a;
@@ -171,44 +191,28 @@ __global__ void __launch_bounds__(256)
             cum_cart[o + 1] = fma(cz, L.m[7], fma(cy, L.m[4], cx * L.m[1]));
             cum_cart[o + 2] = fma(cz, L.m[8], fma(cy, L.m[5], cx * L.m[2]));
         }
-        if (dist) {
-            // sqrt(v G v^T)
-            const double gx = fma(cz, L.g[6], fma(cy, L.g[3], cx * L.g[0]));
-            const double gy = fma(cz, L.g[7], fma(cy, L.g[4], cx * L.g[1]));
-            const double gz = fma(cz, L.g[8], fma(cy, L.g[5], cx * L.g[2]));
-            const double d2 = fma(gz, cz, fma(gy, cy, gx * cx));
-            dist[(int64_t)a * g.n_frames + t] = sqrt(fmax(d2, 0.0));
+        if (dist || speed) {
+            const double d = length(cx, cy, cz);
+            if (dist) dist[(int64_t)a * g.n_frames + t] = d;
+            if (speed) speed[t * (int64_t)g.n_atoms + a] = d - pd;  // time-major: lane = atom
+            pd = d;
         }
     }
 }
 
 // ---------------------------------------------------------------- minimum-image distances
+// (pymatgen Lattice.get_all_distances: LLL-reduced basis, 27 images; see gd_pbc.cuh)
 
 __global__ void __launch_bounds__(256)
     k_pbc_distances(const double *__restrict__ f1, int32_t n1, const double *__restrict__ f2,
-                    int32_t n2, const __grid_constant__ Mat9 L, double *__restrict__ out) {
+                    int32_t n2, const __grid_constant__ GdPbc P, double *__restrict__ out) {
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (int64_t)n1 * n2) return;
     const int32_t i = (int32_t)(idx / n2), j = (int32_t)(idx - (int64_t)i * n2);
     double a[3], b[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        a[k] = f1[3 * i + k];
-        a[k] -= floor(a[k]);
-        b[k] = f2[3 * j + k];
-        b[k] -= floor(b[k]);
-    }
-    double best = 1e300;
-    for (int ix = -1; ix <= 1; ++ix)
-        for (int iy = -1; iy <= 1; ++iy)
-            for (int iz = -1; iz <= 1; ++iz) {
-                const double vx = (b[0] + ix) - a[0], vy = (b[1] + iy) - a[1], vz = (b[2] + iz) - a[2];
-                const double cx = vx * L.m[0] + vy * L.m[3] + vz * L.m[6];
-                const double cy = vx * L.m[1] + vy * L.m[4] + vz * L.m[7];
-                const double cz = vx * L.m[2] + vy * L.m[5] + vz * L.m[8];
-                best = fmin(best, cx * cx + cy * cy + cz * cz);
-            }
-    out[idx] = sqrt(best);
+    gd_pbc_cart(P, f1[3 * i], f1[3 * i + 1], f1[3 * i + 2], a);
+    gd_pbc_cart(P, f2[3 * j], f2[3 * j + 1], f2[3 * j + 2], b);
+    out[idx] = sqrt(gd_pbc_d2(P, a, b));
 }
 
 Mat9 make_mat(const double *h_lattice) {
@@ -230,32 +234,89 @@ extern "C" int64_t gd_unwrap_chunks(int64_t n_frames, int32_t n_atoms) {
     return gd_ceil_div(n_frames, unwrap_chunk_frames(n_frames, n_atoms));
 }
 
-extern "C" gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
-                                 const double *h_lattice, const double *d_prev_row,
-                                 const int32_t *d_base_winding, const double *d_base_pos,
-                                 int32_t *d_work, double *d_cum_frac, double *d_cum_cart,
-                                 double *d_dist, int32_t *d_winding_out, void *stream) {
-    GD_REQUIRE(d_pos_frac && h_lattice && d_work, GD_ERR_INVALID, "gd_unwrap: null argument");
-    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_unwrap: empty input");
-    cudaStream_t st = (cudaStream_t)stream;
+namespace {
+
+UGeom unwrap_geometry(int64_t n_frames, int32_t n_atoms) {
     UGeom g;
     g.n_frames = n_frames;
     g.n_atoms = n_atoms;
     g.f = unwrap_chunk_frames(n_frames, n_atoms);
     g.n_chunks = gd_ceil_div(n_frames, g.f);
-    const int64_t items = g.n_chunks * n_atoms;
+    return g;
+}
+
+gd_status_t launch_windings(const double *d_pos_frac, const UGeom &g, const double *d_prev_row,
+                            const int32_t *d_base_winding, int32_t *d_work,
+                            int32_t *d_winding_out, cudaStream_t st) {
+    const int64_t items = g.n_chunks * g.n_atoms;
     k_unwrap_count<<<(unsigned)gd_ceil_div(items, 256), 256, 0, st>>>(d_pos_frac, g, d_prev_row,
                                                                     d_work);
     GD_LAUNCH_CHECK();
-    k_unwrap_scan<<<(unsigned)gd_ceil_div((int64_t)n_atoms * 3, 128), 128, 0, st>>>(
+    k_unwrap_scan<<<(unsigned)gd_ceil_div((int64_t)g.n_atoms * 3, 128), 128, 0, st>>>(
         g, d_base_winding, d_work, d_winding_out);
     GD_LAUNCH_CHECK();
-    if (d_cum_frac || d_cum_cart || d_dist) {
-        const Mat9 L = make_mat(h_lattice);
-        k_unwrap_apply<<<(unsigned)gd_ceil_div(items, 256), 256, 0, st>>>(
-            d_pos_frac, g, d_prev_row, d_base_pos, d_work, L, d_cum_frac, d_cum_cart, d_dist);
-        GD_LAUNCH_CHECK();
-    }
+    return GD_OK;
+}
+
+gd_status_t launch_apply(const double *d_pos_frac, const UGeom &g, const double *h_lattice,
+                         const double *d_prev_row, const double *d_base_pos, const int32_t *d_work,
+                         const int32_t *d_extra_winding, double *d_cum_frac, double *d_cum_cart,
+                         double *d_dist, double *d_speed, cudaStream_t st) {
+    if (!(d_cum_frac || d_cum_cart || d_dist || d_speed)) return GD_OK;
+    const Mat9 L = make_mat(h_lattice);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    k_unwrap_apply<<<(unsigned)gd_ceil_div(items, 256), 256, 0, st>>>(
+        d_pos_frac, g, d_prev_row, d_base_pos, d_work, d_extra_winding, L, d_cum_frac, d_cum_cart,
+        d_dist, d_speed);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+}  // namespace
+
+extern "C" gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                                 const double *h_lattice, const double *d_prev_row,
+                                 const int32_t *d_base_winding, const double *d_base_pos,
+                                 int32_t *d_work, double *d_cum_frac, double *d_cum_cart,
+                                 double *d_dist, double *d_speed, int32_t *d_winding_out,
+                                 void *stream) {
+    GD_REQUIRE(d_pos_frac && h_lattice && d_work, GD_ERR_INVALID, "gd_unwrap: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_unwrap: empty input");
+    cudaStream_t st = (cudaStream_t)stream;
+    const UGeom g = unwrap_geometry(n_frames, n_atoms);
+    gd_status_t rc = launch_windings(d_pos_frac, g, d_prev_row, d_base_winding, d_work,
+                                     d_winding_out, st);
+    if (rc != GD_OK) return rc;
+    return launch_apply(d_pos_frac, g, h_lattice, d_prev_row, d_base_pos, d_work, nullptr,
+                        d_cum_frac, d_cum_cart, d_dist, d_speed, st);
+}
+
+extern "C" gd_status_t gd_unwrap_windings(const double *d_pos_frac, int64_t n_frames,
+                                          int32_t n_atoms, const double *d_prev_row,
+                                          int32_t *d_work, int32_t *d_winding_out, void *stream) {
+    GD_REQUIRE(d_pos_frac && d_work && d_winding_out, GD_ERR_INVALID,
+               "gd_unwrap_windings: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_unwrap_windings: empty input");
+    return launch_windings(d_pos_frac, unwrap_geometry(n_frames, n_atoms), d_prev_row, nullptr,
+                           d_work, d_winding_out, (cudaStream_t)stream);
+}
+
+extern "C" gd_status_t gd_unwrap_apply(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                                       const double *h_lattice, const double *d_prev_row,
+                                       const int32_t *d_base_winding, const double *d_base_pos,
+                                       const int32_t *d_work, double *d_cum_frac,
+                                       double *d_cum_cart, double *d_dist, double *d_speed,
+                                       void *stream) {
+    GD_REQUIRE(d_pos_frac && h_lattice && d_work, GD_ERR_INVALID, "gd_unwrap_apply: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_unwrap_apply: empty input");
+    return launch_apply(d_pos_frac, unwrap_geometry(n_frames, n_atoms), h_lattice, d_prev_row,
+                        d_base_pos, d_work, d_base_winding, d_cum_frac, d_cum_cart, d_dist, d_speed,
+                        (cudaStream_t)stream);
+}
+
+extern "C" gd_status_t gd_lll_reduce_host(const double *h_lattice, double *h_lll, double *h_mapping) {
+    GD_REQUIRE(h_lattice && h_lll && h_mapping, GD_ERR_INVALID, "gd_lll_reduce_host: null argument");
+    gd_lll_reduce(h_lattice, h_lll, h_mapping);
     return GD_OK;
 }
 
@@ -264,10 +325,10 @@ extern "C" gd_status_t gd_pbc_distances(const double *h_lattice, const double *d
                                         void *stream) {
     GD_REQUIRE(h_lattice && d_frac1 && d_frac2 && d_out && n1 > 0 && n2 > 0, GD_ERR_INVALID,
                "gd_pbc_distances: bad argument");
-    const Mat9 L = make_mat(h_lattice);
+    const GdPbc P = gd_pbc_build(h_lattice);
     const int64_t n = (int64_t)n1 * n2;
     k_pbc_distances<<<(unsigned)gd_ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(
-        d_frac1, n1, d_frac2, n2, L, d_out);
+        d_frac1, n1, d_frac2, n2, P, d_out);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

@@ -307,13 +307,17 @@ __global__ void __launch_bounds__(128)
 // phase 3: apply
 __global__ void __launch_bounds__(256)
     k_fill_apply(const int32_t *__restrict__ s, Geometry g, int direction,
-                 const int32_t *__restrict__ work, int32_t *__restrict__ out) {
+                 const int32_t *__restrict__ work, const int32_t *__restrict__ shard_carry,
+                 int32_t *__restrict__ out) {
     const int64_t item = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (item >= g.n_chunks * g.n_atoms) return;
     const int64_t c = item / g.n_atoms;
     const int32_t a = (int32_t)(item - c * g.n_atoms);
     const int64_t t0 = c * g.f, t1 = min(g.n_frames, t0 + g.f);
     int32_t last = work[c * g.n_atoms + a];
+    // chunk carries computed without knowing the neighbouring shard: where no valid state was
+    // seen yet inside this shard, the state carried over the shard boundary applies
+    if (shard_carry && last == GD_NOSITE) last = shard_carry[a];
     if (direction > 0) {
 #pragma unroll 4
         for (int64_t t = t0; t < t1; ++t) {
@@ -460,7 +464,42 @@ extern "C" gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames,
     k_fill_carry<<<blocks_for(n_atoms, 128), 128, 0, st>>>(g, direction, d_carry_in, d_carry_out,
                                                           d_work);
     GD_LAUNCH_CHECK();
-    k_fill_apply<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work, d_out);
+    k_fill_apply<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work, nullptr,
+                                                         d_out);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_fill_last_valid(const int32_t *d_states, int64_t n_frames,
+                                          int32_t n_atoms, int direction, int32_t *d_work,
+                                          int32_t *d_last_valid, void *stream) {
+    GD_REQUIRE(d_states && d_work && d_last_valid, GD_ERR_INVALID,
+               "gd_fill_last_valid: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_fill_last_valid: empty input");
+    GD_REQUIRE(direction == 1 || direction == -1, GD_ERR_INVALID,
+               "gd_fill_last_valid: direction must be +1 (ffill) or -1 (bfill)");
+    cudaStream_t st = (cudaStream_t)stream;
+    Geometry g = geometry(n_frames, n_atoms);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    k_fill_summary<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work);
+    GD_LAUNCH_CHECK();
+    k_fill_carry<<<blocks_for(n_atoms, 128), 128, 0, st>>>(g, direction, nullptr, d_last_valid,
+                                                          d_work);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+extern "C" gd_status_t gd_fill_apply(const int32_t *d_states, int64_t n_frames, int32_t n_atoms,
+                                     int direction, const int32_t *d_carry_in,
+                                     const int32_t *d_work, int32_t *d_out, void *stream) {
+    GD_REQUIRE(d_states && d_work && d_out, GD_ERR_INVALID, "gd_fill_apply: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_fill_apply: empty input");
+    GD_REQUIRE(direction == 1 || direction == -1, GD_ERR_INVALID,
+               "gd_fill_apply: direction must be +1 (ffill) or -1 (bfill)");
+    Geometry g = geometry(n_frames, n_atoms);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    k_fill_apply<<<blocks_for(items, 256), 256, 0, (cudaStream_t)stream>>>(
+        d_states, g, direction, d_work, d_carry_in, d_out);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

@@ -145,6 +145,17 @@ extern "C" gd_status_t gd_transpose_soa(const double *d_in, int64_t n_frames, in
     return GD_OK;
 }
 
+extern "C" gd_status_t gd_transpose_f64(const double *d_in, int64_t n_rows, int64_t n_cols,
+                                        double *d_out, void *stream) {
+    GD_REQUIRE(d_in && d_out && n_rows > 0 && n_cols > 0, GD_ERR_INVALID,
+               "gd_transpose_f64: bad argument");
+    dim3 grid((unsigned)gd_ceil_div(n_rows, 32), (unsigned)gd_ceil_div(n_cols, 32));
+    GD_REQUIRE(grid.y <= 65535, GD_ERR_INVALID, "gd_transpose_f64: too many columns");
+    k_to_soa<<<grid, 256, 0, (cudaStream_t)stream>>>(d_in, n_rows, n_cols, d_out);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
 extern "C" gd_status_t gd_msd_direct(const double *d_soa, int64_t n_frames, int32_t n_atoms,
                                      int64_t lag0, int64_t n_lags, double *d_msd, void *stream) {
     GD_REQUIRE(d_soa && d_msd, GD_ERR_INVALID, "gd_msd_direct: null argument");

@@ -20,6 +20,7 @@
 // products and 27 partial sums), ~35 for a diagonal cell, where the minimum separates per axis
 // (rounding is monotonic, so min over images of fl(fl(X+Y)+Z) = fl(fl(minX+minY)+minZ)).
 #include "gd_common.cuh"
+#include "gd_pbc.cuh"
 
 // Tuning knobs for A/B builds (tools/rdf_variants.sh); the defaults are the measured ones.
 #ifndef GD_RDF_DIAG_SELECT
@@ -51,62 +52,10 @@ struct RdfParams {
     int32_t mode;  // 0: digitize(right=True) -> #edges < d;  1: histogram -> #edges <= d
     int32_t skip_same;
     int32_t tile;  // targets per shared-memory tile
-    int32_t diag;
     double inv_res;
-    double m[9];
+    GdPbc pbc;
     unsigned long long *hist;  // [n_class, n_group, n_edges + 1]
 };
-
-__device__ __forceinline__ double wrap01(double x) { return x - floor(x); }
-
-__device__ __forceinline__ double min_image_d2(const RdfParams &p, const double a[3], const double b[3]) {
-    double v[3][3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        v[k][0] = (b[k] + -1.0) - a[k];
-        v[k][1] = (b[k] + 0.0) - a[k];
-        v[k][2] = (b[k] + 1.0) - a[k];
-    }
-    if (p.diag) {
-        double mn[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const double mk = p.m[4 * k];
-#if GD_RDF_DIAG_SELECT
-            // Experiment (off by default, not yet measured): |v| -> fl(fl(v*mk)^2) is monotonic,
-            // so the minimum is taken by the candidate of smallest magnitude, and away from
-            // |b - a| = 1/2 that candidate is known from b - a alone (the candidates' magnitudes
-            // differ by 1 - 2|b - a|, far above their rounding errors).
-            const double u = b[k] - a[k];
-            if (fabs(fabs(u) - 0.5) > 1e-6) {
-                const double vk = u > 0.5 ? v[k][0] : (u < -0.5 ? v[k][2] : v[k][1]);
-                const double c = vk * mk;
-                mn[k] = c * c;
-                continue;
-            }
-#endif
-            const double c0 = v[k][0] * mk, c1 = v[k][1] * mk, c2 = v[k][2] * mk;
-            mn[k] = fmin(fmin(c0 * c0, c1 * c1), c2 * c2);
-        }
-        return (mn[0] + mn[1]) + mn[2];
-    }
-    // general cell: cart_c = (vx*m[0+c] + vy*m[3+c]) + vz*m[6+c], d2 = (cx^2 + cy^2) + cz^2
-    double best = 1e300;
-#pragma unroll
-    for (int ix = 0; ix < 3; ++ix) {
-        const double x0 = v[0][ix] * p.m[0], x1 = v[0][ix] * p.m[1], x2 = v[0][ix] * p.m[2];
-#pragma unroll
-        for (int iy = 0; iy < 3; ++iy) {
-            const double s0 = x0 + v[1][iy] * p.m[3], s1 = x1 + v[1][iy] * p.m[4], s2 = x2 + v[1][iy] * p.m[5];
-#pragma unroll
-            for (int iz = 0; iz < 3; ++iz) {
-                const double c0 = s0 + v[2][iz] * p.m[6], c1 = s1 + v[2][iz] * p.m[7], c2 = s2 + v[2][iz] * p.m[8];
-                best = fmin(best, (c0 * c0 + c1 * c1) + c2 * c2);
-            }
-        }
-    }
-    return best;
-}
 
 // Smallest x >= 0 whose correctly rounded square root is >= e (strict: > e).  sqrt is monotonic,
 // so "e <= fl(sqrt(d2))" is the same test as "x <= d2": the bins are found on d2 itself and the
@@ -151,9 +100,7 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                 s_atom[k] = atom;
                 s_group[k] = p.group ? p.group[j0 + k] : 0;
                 const double *q = frame + 3 * (int64_t)atom;
-                s_b[3 * k] = wrap01(q[0]);
-                s_b[3 * k + 1] = wrap01(q[1]);
-                s_b[3 * k + 2] = wrap01(q[2]);
+                gd_pbc_cart(p.pbc, q[0], q[1], q[2], s_b + 3 * k);
             }
             __syncthreads();
             for (int i = blockIdx.y * kWarps + warp; i < p.n1; i += gridDim.y * kWarps) {
@@ -161,11 +108,12 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                 if (c < 0) continue;
                 const int32_t atom_i = p.idx1[i];
                 const double *q = frame + 3 * (int64_t)atom_i;
-                const double a[3] = {wrap01(q[0]), wrap01(q[1]), wrap01(q[2])};
+                double a[3];
+                gd_pbc_cart(p.pbc, q[0], q[1], q[2], a);
                 for (int k = lane; k < nt; k += 32) {
                     if (p.skip_same && s_atom[k] == atom_i) continue;
                     const double b[3] = {s_b[3 * k], s_b[3 * k + 1], s_b[3 * k + 2]};
-                    const double d2 = min_image_d2(p, a, b);
+                    const double d2 = gd_pbc_d2(p.pbc, a, b);
                     // fp32 guess of the bin, corrected against the exact thresholds
                     int g = (int)fminf(sqrtf((float)d2) * inv_res, (float)p.n_edges);
                     while (g > 0 && !(s_edges[g - 1] <= d2)) --g;
@@ -256,8 +204,7 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
     p.skip_same = skip_same_atom;
     p.inv_res = 1.0 / resolution;
     p.hist = d_hist;
-    memcpy(p.m, h_lattice, sizeof(p.m));
-    p.diag = (p.m[1] == 0.0 && p.m[2] == 0.0 && p.m[3] == 0.0 && p.m[5] == 0.0 && p.m[6] == 0.0 && p.m[7] == 0.0);
+    p.pbc = gd_pbc_build(h_lattice);
     const GdDeviceInfo &dev = gd_device_info();
     const size_t smem_cap = (size_t)(dev.max_smem_optin > 0 ? dev.max_smem_optin : 200 * 1024);
     const size_t fixed = (size_t)(n_edges + 1) * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;

@@ -2,22 +2,26 @@
 
 Mirror of reference src/gemdat/metrics.py:21-231 for ``speed`` (:35-47),
 ``tracer_diffusivity`` (:76-97), ``amplitudes`` (:209-231), ``vibration_amplitude``
-(:190-207) and ``particle_density`` (:49-62).  The per-frame distances come from the K0
-kernel (``gd_unwrap``) instead of the reference's Python loop over frames; the
-amplitude run-length bookkeeping is O(sign flips) host work on the returned array.
-``attempt_frequency`` (:167-188) runs on the device array too: the
-per-atom spectrum comes from cuFFT through ``torch.fft`` (a library transform, not one of
-this package's kernels), the periodogram weighting and the mean-frequency reductions of
+(:190-207) and ``particle_density`` (:49-62).  Everything O(frames x atoms) stays in HBM:
+K0 (``gd_unwrap``) writes the speed array time-major, ``gd_amplitudes_count/fill`` cut it at the
+sign flips and sum the pieces, ``gd_mean_std`` reduces them -- ``vibration_amplitude()`` (the
+``site_radius=None`` route of ``transitions_between_sites``) never downloads an [A, T] array.
+``attempt_frequency`` (:167-188) runs on the same device array: the per-atom
+spectrum comes from cuFFT through ``torch.fft`` (a library transform, not one of this
+package's kernels), the periodogram weighting and the mean-frequency reductions of
 ``utils.py:128-160`` follow it on the device.  Conductivity, Haven ratio and the Arrhenius
-helpers are out of scope (DESIGN.md "next rows").
+helpers are out of scope.
 """
 
 from __future__ import annotations
+
+import ctypes as C
 
 import numpy as np
 import torch
 
 from . import _device as dv
+from . import _lib
 from .caching import weak_lru_cache
 from .lattice import FloatWithUnit
 
@@ -28,14 +32,36 @@ class TrajectoryMetrics:
     def __init__(self, trajectory):
         self.trajectory = trajectory
 
+    # ---- device-resident intermediates (cached per object like the reference's results)
     @weak_lru_cache()
-    def _distances(self) -> np.ndarray:
-        return self.trajectory.distances_from_base_position()
+    def _speed_tm(self) -> torch.Tensor:
+        """np.diff(distance, prepend=0) as a TIME-major [n_frames, n_atoms] device array."""
+        dv.require_cuda()
+        return self.trajectory._unwrap(want_speed=True, keep_on_device=True)['speed']
+
+    @weak_lru_cache()
+    def _amplitudes_device(self) -> torch.Tensor:
+        speed = self._speed_tm()
+        n_frames, n_atoms = int(speed.shape[0]), int(speed.shape[1])
+        lib, s = _lib.lib, dv.stream_ptr()
+        work = dv.empty((int(lib.gd_amplitudes_work_bytes(n_frames, n_atoms)),), torch.uint8)
+        offsets = dv.empty((n_atoms + 1,), torch.int64)
+        n_amp = C.c_int64(0)
+        _lib.check(lib.gd_amplitudes_count(dv.ptr(speed), n_frames, n_atoms, dv.ptr(work),
+                                           dv.ptr(offsets), C.byref(n_amp), s))
+        amp = dv.empty((n_amp.value,), torch.float64)
+        _lib.check(lib.gd_amplitudes_fill(dv.ptr(speed), n_frames, n_atoms, dv.ptr(work),
+                                          dv.ptr(offsets), dv.ptr(amp), s))
+        return amp
 
     @weak_lru_cache()
     def speed(self) -> np.ndarray:
         """metrics.py:35-47: change of the distance from the base position per step, [A, T]."""
-        return np.diff(self._distances(), prepend=0)
+        tm = self._speed_tm()
+        out = dv.empty((int(tm.shape[1]), int(tm.shape[0])), torch.float64)
+        _lib.check(_lib.lib.gd_transpose_f64(dv.ptr(tm), int(tm.shape[0]), int(tm.shape[1]), dv.ptr(out),
+                                             dv.stream_ptr()))
+        return dv.to_host(out)
 
     @weak_lru_cache()
     def _meanfreq(self) -> np.ndarray:
@@ -45,27 +71,23 @@ class TrajectoryMetrics:
         density scaling 1/(fs N), one-sided spectrum with every bin but DC (and Nyquist for
         even N) doubled; ``mnfreq = sum(P f) / sum(P)`` with ``P = Pxx (f[1] - f[0])``.
         """
-        dv.require_cuda()
-        dist = self.trajectory._unwrap(want_dist=True, keep_on_device=True)['dist']  # [A, T] device
-        n = int(dist.shape[1])
+        speed = self._speed_tm()  # [T, A]
+        n = int(speed.shape[0])
         fs = float(self.trajectory.sampling_frequency)
-        speed = torch.cat([dist[:, :1], dist[:, 1:] - dist[:, :-1]], dim=1)  # np.diff(prepend=0)
-        del dist
-        x = speed - speed.mean(dim=1, keepdim=True)
-        del speed
-        spec = torch.fft.rfft(x, dim=1)
+        x = speed - speed.mean(dim=0, keepdim=True)
+        spec = torch.fft.rfft(x, dim=0)
         del x
         pxx = (spec.real * spec.real + spec.imag * spec.imag) * (1.0 / (fs * n))
         del spec
         if n % 2 == 0:
-            pxx[:, 1:-1] *= 2.0
+            pxx[1:-1] *= 2.0
         else:
-            pxx[:, 1:] *= 2.0
+            pxx[1:] *= 2.0
         f = torch.fft.rfftfreq(n, d=1.0 / fs, dtype=torch.float64, device=pxx.device)
         width = (f[1] - f[0]) if n > 1 else f.new_tensor(float('nan'))
         p = pxx * width
-        mnfreq = (p @ f.reshape(-1, 1)) / p.sum(dim=1, keepdim=True)
-        return dv.to_host(mnfreq)
+        mnfreq = (f.reshape(1, -1) @ p) / p.sum(dim=0, keepdim=True)
+        return dv.to_host(mnfreq.reshape(-1, 1))
 
     @weak_lru_cache()
     def attempt_frequency(self) -> tuple[FloatWithUnit, FloatWithUnit]:
@@ -91,22 +113,19 @@ class TrajectoryMetrics:
 
     @weak_lru_cache()
     def amplitudes(self) -> np.ndarray:
-        """metrics.py:209-231: sums of ``speed`` over runs of equal sign.
-
-        The reference splits each atom's speed at every sign flip except the first and
-        the last one (``splits[1:-1]``) and sums each piece.
-        """
-        out = []
-        for row in self.speed():
-            signs = np.sign(row)
-            flips = np.nonzero(signs != np.roll(signs, shift=-1))[0]
-            cuts = flips[1:-1] + 1
-            starts = np.concatenate([[0], cuts])
-            if len(row):
-                out.append(np.add.reduceat(row, starts))
-        return np.concatenate(out) if out else np.zeros(0)
+        """metrics.py:209-231: every atom's speed row cut after each sign flip except the first
+        and the last one (``splits[1:-1]``), each piece summed; atoms in order, pieces in time
+        order (``gd_amplitudes_count`` / ``gd_amplitudes_fill``)."""
+        return dv.to_host(self._amplitudes_device())
 
     @weak_lru_cache()
     def vibration_amplitude(self) -> FloatWithUnit:
-        """metrics.py:190-207: standard deviation of the amplitudes, Angstrom."""
-        return FloatWithUnit(np.std(self.amplitudes()), 'ang')
+        """metrics.py:190-207: standard deviation of the amplitudes, Angstrom (``gd_mean_std``
+        on the device array: nothing O(frames) is downloaded)."""
+        amp = self._amplitudes_device()
+        lib = _lib.lib
+        work = dv.empty((int(lib.gd_mean_std_work_bytes()),), torch.uint8)
+        mean, std = C.c_double(0.0), C.c_double(0.0)
+        _lib.check(lib.gd_mean_std(dv.ptr(amp), amp.numel(), dv.ptr(work), C.byref(mean), C.byref(std),
+                                   dv.stream_ptr()))
+        return FloatWithUnit(std.value, 'ang')

@@ -117,17 +117,51 @@ class Comm:
             out.append(allp[q, start: start + int(sends_h[q, me])].contiguous())
         return out
 
-    def all_reduce_max(self, t: torch.Tensor) -> torch.Tensor:
-        """In-place elementwise maximum over the ranks."""
+    def _all_reduce(self, t: torch.Tensor, op) -> torch.Tensor:
         if self.world == 1:
             return t
         if self.direct:
-            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+            self.dist.all_reduce(t, op=op, group=self.group)
         else:
             h = t.detach().cpu()
-            self.dist.all_reduce(h, op=self.dist.ReduceOp.MAX, group=self.group)
+            self.dist.all_reduce(h, op=op, group=self.group)
             t.copy_(h)
         return t
+
+    def all_reduce_max(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place elementwise maximum over the ranks."""
+        return self._all_reduce(t, self.dist.ReduceOp.MAX if self.world > 1 else None)
+
+    def all_reduce_min(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place elementwise minimum over the ranks."""
+        return self._all_reduce(t, self.dist.ReduceOp.MIN if self.world > 1 else None)
+
+    def all_reduce_sum(self, t: torch.Tensor) -> torch.Tensor:
+        """In-place elementwise sum over the ranks (voxel grids, histograms, per-lag partial sums)."""
+        return self._all_reduce(t, self.dist.ReduceOp.SUM if self.world > 1 else None)
+
+    def all_to_all_flat(self, flat: torch.Tensor, send: list[int], recv: list[int]) -> list[torch.Tensor]:
+        """Rank r receives, from every rank q, the ``send[r]`` elements of q's 1-D ``flat`` meant
+        for r (``flat`` holds the pieces for ranks 0..W-1 back to back); ``recv[q]`` = elements
+        coming from rank q.  Pieces may differ in size (ranks own different numbers of frames)."""
+        if self.world == 1:
+            return [flat]
+        if self.direct:
+            out = torch.empty((sum(recv),), dtype=flat.dtype, device=flat.device)
+            self.dist.all_to_all_single(out, flat.contiguous(), output_split_sizes=recv,
+                                        input_split_sizes=send, group=self.group)
+            return list(torch.split(out, recv))
+        me = self.dist.get_rank(self.group)
+        sends_h = self.all_gather(torch.tensor(send, dtype=torch.int64)).cpu().numpy()  # [W, W]
+        cap = max(1, int(sends_h.sum(axis=1).max()))
+        padded = torch.zeros((cap,), dtype=flat.dtype, device=flat.device)
+        padded[: flat.numel()] = flat
+        allp = self.all_gather(padded)
+        out = []
+        for q in range(self.world):
+            start = int(sends_h[q, :me].sum())
+            out.append(allp[q, start: start + int(sends_h[q, me])].contiguous())
+        return out
 
 
 class HotPath:

@@ -71,7 +71,14 @@ def _state_names(unique_labels: list[str]):
 
 def _hist(pos: torch.Tensor, lattice, idx1, cls, n_class, idx2, group, n_group, bins: np.ndarray,
           resolution: float, mode: int, skip_same: bool) -> np.ndarray:
-    """uint64 counts [n_class, n_group, len(bins) + 1] from gd_rdf_hist."""
+    """uint64 counts [n_class, n_group, len(bins) + 1] from gd_rdf_hist (host copy)."""
+    return dv.to_host(_hist_device(pos, lattice, idx1, cls, n_class, idx2, group, n_group, bins,
+                                   resolution, mode, skip_same))
+
+
+def _hist_device(pos: torch.Tensor, lattice, idx1, cls, n_class, idx2, group, n_group, bins: np.ndarray,
+                 resolution: float, mode: int, skip_same: bool) -> torch.Tensor:
+    """The same table left on the device (frame shards add theirs up with an all-reduce)."""
     n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
     d_idx1 = dv.to_device(np.ascontiguousarray(idx1, dtype=np.int32))
     d_idx2 = dv.to_device(np.ascontiguousarray(idx2, dtype=np.int32))
@@ -84,7 +91,7 @@ def _hist(pos: torch.Tensor, lattice, idx1, cls, n_class, idx2, group, n_group, 
         dv.ptr(cls) if cls is not None else None, n_class, dv.ptr(d_idx2),
         dv.ptr(d_group) if d_group is not None else None, len(idx2), n_group, dv.ptr(d_edges), len(bins),
         float(resolution), mode, int(skip_same), dv.ptr(hist), dv.stream_ptr()))
-    return dv.to_host(hist)
+    return hist
 
 
 def radial_distribution(*, transitions, floating_specie: str, max_dist: float = 5.0,

@@ -41,6 +41,19 @@ def _symbol(sp) -> str:
     return out or s
 
 
+def _wrap_unit_device(t: torch.Tensor, *, in_place: bool) -> torch.Tensor | None:
+    """``np.mod(t, 1)`` on the device if some element lies outside [0, 1); None when all are
+    inside (one read-only pass, ``gd_wrap_unit``).  ``in_place=False`` leaves ``t`` untouched."""
+    flag = dv.zeros((1,), torch.int32)
+    lib, s = _lib.lib, dv.stream_ptr()
+    _lib.check(lib.gd_wrap_unit(dv.ptr(t), None, t.numel(), dv.ptr(flag), s))
+    if int(flag.item()) == 0:
+        return None
+    out = t if in_place else torch.empty_like(t)
+    _lib.check(lib.gd_wrap_unit(dv.ptr(t), dv.ptr(out), t.numel(), dv.ptr(flag), s))
+    return out
+
+
 class Trajectory:
     def __init__(
         self,
@@ -75,6 +88,8 @@ class Trajectory:
             self.base_positions = self.coords[0] if base_positions is None else base_positions
         else:
             self.base_positions = self.coords[0]
+        # positions known to lie in [0, 1)?  None = not checked yet (see `positions`)
+        self._unit_wrapped: bool | None = None
 
     # ------------------------------------------------------------------ container protocol
     def __len__(self) -> int:
@@ -100,14 +115,39 @@ class Trajectory:
 
     # ------------------------------------------------------------------ representations
     def to_positions(self):
-        """trajectory.py:121-127 (base + cumsum, then mod 1).  Data-model accessor, host numpy."""
-        if not self.coords_are_displacement:
+        """trajectory.py:121-127: positions representation, then ``np.mod(coords, 1)``.
+
+        The reference applies the modulo on every call; here it is applied once per coords
+        array (it is idempotent): coordinates outside [0, 1) are detected -- on the device for
+        CUDA tensors (``gd_wrap_unit``), with one min/max pass for numpy arrays -- and only then
+        a wrapped copy replaces ``coords``."""
+        if self.coords_are_displacement:
+            coords = self._host_coords()
+            base = np.asarray(dv.to_host(self.base_positions) if dv.is_device(self.base_positions)
+                              else self.base_positions)
+            self.coords = np.mod(base + np.cumsum(coords, axis=0), 1)
+            self.coords_are_displacement = False
+            self._unit_wrapped = True
             return
-        coords = self._host_coords()
-        base = np.asarray(dv.to_host(self.base_positions) if dv.is_device(self.base_positions)
-                          else self.base_positions)
-        self.coords = np.mod(base + np.cumsum(coords, axis=0), 1)
-        self.coords_are_displacement = False
+        if self._unit_wrapped:
+            return
+        coords = self.coords
+        if dv.is_device(coords):
+            wrapped = _wrap_unit_device(coords, in_place=False)
+            if wrapped is not None:
+                self.coords = wrapped
+        elif coords.size and (coords.min() < 0.0 or coords.max() >= 1.0):
+            self._rebind_coords(np.mod(coords, 1))
+        self._unit_wrapped = True
+
+    def _rebind_coords(self, new_coords: np.ndarray) -> None:
+        """Replace the host array, keeping the cached device copy (which holds the wrapped
+        values already) attached to the new object."""
+        holder = self.__dict__.get('_dev_holder') or {}
+        cached = holder.get('pos')
+        if cached is not None and cached[0] is self.coords:
+            holder['pos'] = (new_coords, cached[1])
+        self.coords = new_coords
 
     def to_displacements(self):
         """pymatgen ``to_displacements``: wrapped frame-to-frame steps, frame 0 = 0."""
@@ -141,7 +181,8 @@ class Trajectory:
         ``transitions_between_sites`` + ``metrics`` + ``to_volume`` on one trajectory pay for
         one host->device copy, not three.
         """
-        self.to_positions()
+        if self.coords_are_displacement or dv.is_device(self.coords):
+            self.to_positions()
         if dv.is_device(self.coords):
             return dv.to_device(self.coords, torch.float64)
         holder = self.__dict__.setdefault('_dev_holder', {})
@@ -149,6 +190,10 @@ class Trajectory:
         if cached is not None and cached[0] is self.coords:
             return cached[1]
         t = dv.to_device(self.coords, torch.float64)
+        # np.mod(coords, 1) of to_positions, on the device copy (ours: wrapped in place); the
+        # host array is only rewritten if someone reads `positions` from it
+        if not self._unit_wrapped and _wrap_unit_device(t, in_place=True) is None:
+            self._unit_wrapped = True
         holder['pos'] = (self.coords, t)
         return t
 
@@ -178,7 +223,9 @@ class Trajectory:
             species = [species]
         wanted = {_symbol(s) for s in species}
         idx = [_symbol(sp) in wanted for sp in self.species]
-        pos = self.positions
+        # (positions are wrapped lazily: by `positions` on the host, by `_device_positions` on
+        # the device copy -- filtering commutes with the elementwise modulo)
+        pos = self.positions if self.coords_are_displacement else self.coords
         keep_all = all(idx)
         if keep_all:
             # the reference copies (trajectory.py:854); coords are never modified in place here
@@ -196,6 +243,7 @@ class Trajectory:
             metadata=self.metadata,
             time_step=self.time_step,
         )
+        out._unit_wrapped = self._unit_wrapped
         if keep_all:  # same coords object: parent and child share one device copy
             out._dev_holder = self.__dict__.setdefault('_dev_holder', {})
         return out
@@ -210,7 +258,10 @@ class Trajectory:
         return parts
 
     # ------------------------------------------------------------------ K0: displacement path
-    def _unwrap(self, *, want_frac=False, want_cart=False, want_dist=False, keep_on_device=False):
+    def _unwrap(self, *, want_frac=False, want_cart=False, want_dist=False, want_speed=False,
+                keep_on_device=False):
+        """K0.  ``speed`` comes out TIME-major [n_frames, n_atoms] (the layout the amplitude
+        kernels stream); ``dist`` atom-major like the reference's array."""
         pos = self._device_positions()
         n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
         n_chunks = int(_lib.lib.gd_unwrap_chunks(n_frames, n_atoms))
@@ -218,15 +269,16 @@ class Trajectory:
         frac = dv.empty((n_frames, n_atoms, 3), torch.float64) if want_frac else None
         cart = dv.empty((n_frames, n_atoms, 3), torch.float64) if want_cart else None
         dist = dv.empty((n_atoms, n_frames), torch.float64) if want_dist else None
+        speed = dv.empty((n_frames, n_atoms), torch.float64) if want_speed else None
         wind = dv.empty((n_atoms, 3), torch.int32)
         _lib.check(
             _lib.lib.gd_unwrap(
                 dv.ptr(pos), n_frames, n_atoms, self.lattice.ctypes.data, None, None, None,
-                dv.ptr(work), dv.ptr(frac), dv.ptr(cart), dv.ptr(dist), dv.ptr(wind),
+                dv.ptr(work), dv.ptr(frac), dv.ptr(cart), dv.ptr(dist), dv.ptr(speed), dv.ptr(wind),
                 dv.stream_ptr(),
             )
         )
-        out = {'frac': frac, 'cart': cart, 'dist': dist, 'winding': wind, 'pos': pos}
+        out = {'frac': frac, 'cart': cart, 'dist': dist, 'speed': speed, 'winding': wind, 'pos': pos}
         if not keep_on_device:
             out = {k: (dv.to_host(v) if v is not None and k != 'pos' else v) for k, v in out.items()}
         return out

@@ -19,9 +19,8 @@ from __future__ import annotations
 
 import ctypes as C
 import typing
-from collections import defaultdict
 from dataclasses import dataclass
-from itertools import combinations_with_replacement, pairwise
+from itertools import combinations_with_replacement
 from warnings import warn
 
 import numpy as np
@@ -134,14 +133,22 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
         site_inner_fraction=site_inner_fraction,
     )
     host_future = None
+    resident = True
     if _wants_pipeline(trajectory, count_events):
         # host-resident input: upload, K1 and the download of the int64 states run as a
         # three-stage pipeline over frame parts (PCIe is full duplex); events are counted by the
         # stand-alone pass afterwards (it re-reads 8 B/atom-frame from HBM, noise next to PCIe)
-        pos, outer, inner, visited, band, host_future = _pipelined_states(trajectory, grid)
+        pos, outer, inner, visited, band, host_future, outside = _pipelined_states(trajectory, grid)
         n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
         work = changed = None
-    else:
+        # some coordinate was outside [0, 1): the device copy was wrapped afterwards (np.mod of
+        # to_positions) and K1 runs again over it (rare: inputs are normally wrapped)
+        resident = outside
+        if outside:
+            host_future = None
+        else:
+            trajectory._unit_wrapped = True
+    if resident:
         pos = trajectory._device_positions()
         n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
         outer = dv.empty((n_frames, n_atoms), torch.int32)
@@ -231,6 +238,7 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
     inner = dv.empty((n_frames, n_atoms), torch.int32)
     visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
     band = dv.zeros((4,), torch.int64)
+    outside = dv.zeros((1,), torch.int32)  # set when a coordinate lies outside [0, 1)
     host_o = torch.empty((n_frames, n_atoms), dtype=torch.int64, pin_memory=True)
     host_i = torch.empty((n_frames, n_atoms), dtype=torch.int64, pin_memory=True)
     n_parts = min(PIPELINE_PARTS, n_frames)
@@ -259,6 +267,8 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
             upload(k + 1)
         f0, f1 = bounds[k], bounds[k + 1]
         main.wait_event(uploaded[k])
+        _lib.check(lib.gd_wrap_unit(dv.ptr(pos[f0:f1]), None, (f1 - f0) * n_atoms * 3, dv.ptr(outside),
+                                    main.cuda_stream))
         _lib.check(lib.gd_site_states(
             dv.ptr(pos[f0:f1]), f1 - f0, n_atoms, None, dv.ptr(d_blob), grid.h_blob.ctypes.data,
             dv.ptr(outer[f0:f1]), dv.ptr(inner[f0:f1]), dv.ptr(visited), dv.ptr(band), None, None,
@@ -285,9 +295,12 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
     # ordered after both side streams
     main.wait_stream(up)
     main.wait_stream(down)
+    was_outside = bool(int(outside.item()))
+    if was_outside:
+        _lib.check(lib.gd_wrap_unit(dv.ptr(pos), dv.ptr(pos), pos.numel(), dv.ptr(outside), main.cuda_stream))
     holder = trajectory.__dict__.setdefault('_dev_holder', {})
     holder['pos'] = (coords, pos)
-    return pos, outer, inner, visited, band, HostStates(host_o, host_i, done)
+    return pos, outer, inner, visited, band, HostStates(host_o, host_i, done), was_outside
 
 
 def widen_to_host(t: torch.Tensor) -> np.ndarray:
@@ -327,12 +340,13 @@ class EventTable:
     def __len__(self):
         return int(self.rows.shape[0])
 
-    def to_dataframe(self) -> pd.DataFrame:
+    def to_dataframe(self, index: torch.Tensor | None = None) -> pd.DataFrame:
         # widened to the reference's int64 on the device, one DMA to pinned memory, no host copy
-        return pd.DataFrame(data=widen_to_host(self.rows), columns=EVENT_COLUMNS, copy=False)
+        labels = None if index is None else dv.to_host(index)
+        return pd.DataFrame(data=widen_to_host(self.rows), columns=EVENT_COLUMNS, index=labels, copy=False)
 
     @classmethod
-    def from_dataframe(cls, events: pd.DataFrame, n_atoms: int | None = None) -> 'EventTable':
+    def from_dataframe(cls, events: pd.DataFrame, n_atoms: int | None = None, return_order: bool = False):
         data = np.ascontiguousarray(events[EVENT_COLUMNS].to_numpy(dtype=np.int64))
         order = np.argsort(data[:, 0], kind='stable')
         data = data[order]
@@ -340,7 +354,9 @@ class EventTable:
             n_atoms = int(data[:, 0].max()) + 1 if len(data) else 1
         counts = np.bincount(data[:, 0], minlength=n_atoms)
         offsets = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
-        return cls(dv.to_device(data.astype(np.int32)), dv.to_device(offsets), n_atoms)
+        rows = dv.to_device(data.astype(np.int32)) if len(data) else dv.empty((0, 6), torch.int32)
+        table = cls(rows, dv.to_device(offsets), n_atoms)
+        return (table, order) if return_order else table
 
 
 def _events_device(outer: torch.Tensor, inner: torch.Tensor, work: torch.Tensor | None = None,
@@ -477,7 +493,7 @@ class Transitions:
     @property
     def events(self) -> pd.DataFrame:
         if self._events is None:
-            self._events = self._dev['events'].to_dataframe()
+            self._events = self._dev['events'].to_dataframe(self._dev.get('events_index'))
         return self._events
 
     @property
@@ -595,82 +611,149 @@ class Transitions:
         """transitions.py:267-278 (ffill along time)."""
         return widen_to_host(_fill_device(self.d_states, +1))
 
+    # -- N1: reductions over the device-resident tables (gd_sitestats.cu)
+    def site_counts(self) -> np.ndarray:
+        """int64 [n_sites + 1]: number of (frame, atom) entries at NOSITE ([0]) and at every
+        site ([s + 1]), counted by ``gd_occupancy`` on the int32 device states."""
+        st = self.d_states
+        counts = dv.zeros((self.n_sites + 1,), torch.int64)
+        _lib.check(_lib.lib.gd_occupancy(dv.ptr(st), st.numel(), self.n_sites, dv.ptr(counts),
+                                         dv.stream_ptr()))
+        return dv.to_host(counts)
+
     def occupancy(self) -> Sites:
-        """transitions.py:280-306: fraction of frames each site is occupied."""
+        """Drop-in for transitions.py:280-306: the sites with the fraction of frames each one is
+        occupied as their occupancy (the reference's ``np.unique`` count / ``len(states)``)."""
         frac, labels, _ = site_arrays(self.sites)
-        unq, counts = np.unique(self.states, return_counts=True)
-        occ = dict(zip(unq.tolist(), (counts / self.n_states).tolist()))
+        visits = self.site_counts()[1:]
         symbols = getattr(self.sites, 'symbols', None) or [
             str(getattr(getattr(s, 'specie', None), 'name', 'X')) for s in self.sites
         ]
-        return Sites(
-            getattr(self.sites, 'lattice'), symbols, frac, labels,
-            occupancies=[occ.get(i, 0) for i in range(len(frac))],
-        )
+        return Sites(getattr(self.sites, 'lattice'), symbols, frac, labels,
+                     occupancies=visits / self.n_states)
+
+    def _occupancy_by_label(self) -> dict[str, list[float]]:
+        occ = self.occupancy()
+        groups: dict[str, list[float]] = {}
+        for label, value in zip(occ.labels, occ.occupancies.tolist()):
+            groups.setdefault(label, []).append(value)
+        return groups
 
     def occupancy_by_site_type(self) -> dict[str, float]:
-        """transitions.py:308-321."""
-        by_label = defaultdict(list)
-        occ = self.occupancy()
-        for label, value in zip(occ.labels, occ.occupancies):
-            by_label[label].append(float(value))
-        return {k: sum(v) / len(v) for k, v in by_label.items()}
+        """Drop-in for transitions.py:308-321: mean occupancy of the sites of each label."""
+        return {label: sum(vals) / len(vals) for label, vals in self._occupancy_by_label().items()}
 
     def atom_locations(self) -> dict[str, float]:
-        """transitions.py:323-337."""
-        n = self.n_floating
-        by_label = defaultdict(list)
-        occ = self.occupancy()
-        for label, value in zip(occ.labels, occ.occupancies):
-            by_label[label].append(float(value))
-        return {k: sum(v) / n for k, v in by_label.items()}
+        """Drop-in for transitions.py:323-337: fraction of time the atoms spend on each label."""
+        n_floating = self.n_floating
+        return {label: sum(vals) / n_floating for label, vals in self._occupancy_by_label().items()}
+
+    def _outer_change_table(self) -> torch.Tensor | None:
+        """Event rows to derive the visits from: the K2 table when it describes ``states`` (the
+        parts made by ``split`` cut states and events at different frames, like the reference),
+        else the outer changes re-extracted from the states (K2 with inner = outer)."""
+        if 'events' in self._dev and self._dev.get('events_match_states', True):
+            return self._dev['events'].rows
+        st = self.d_states
+        try:
+            return _events_device(st, st).rows
+        except ValueError:  # no atom ever changes site
+            return None
 
     def residence_time(self) -> pd.DataFrame:
-        """transitions.py:339-373: one row per completed site visit."""
-        states = self.states
+        """Drop-in for transitions.py:339-373: one row per completed visit of a site
+        (``gd_residence_count`` / ``gd_residence_fill`` on the event table: a state change of the
+        reference's ``np.diff`` is an event row whose start and destination site differ)."""
         _, labels, _ = site_arrays(self.sites)
-        rows = []
-        for atom in range(states.shape[1]):
-            col = states[:, atom]
-            boundaries = np.nonzero(np.diff(col))[0] + 1
-            starts, ends = boundaries[:-1], boundaries[1:]
-            site = col[starts]
-            keep = site != NOSITE
-            for s, e, k in zip(starts[keep], ends[keep], site[keep]):
-                rows.append((atom, k, labels[k], int(e - s)))
-        return pd.DataFrame(rows, columns=['atom index', 'site', 'label', 'time'])
+        columns = ['atom index', 'site', 'label', 'time']
+        rows = self._outer_change_table()
+        n_rows = C.c_int64(0)
+        if rows is not None and len(rows):
+            lib, s = _lib.lib, dv.stream_ptr()
+            n_events = int(rows.shape[0])
+            work = dv.empty((int(lib.gd_residence_work_bytes(n_events)),), torch.uint8)
+            _lib.check(lib.gd_residence_count(dv.ptr(rows), n_events, dv.ptr(work), C.byref(n_rows), s))
+        if n_rows.value == 0:
+            return pd.DataFrame([], columns=columns)
+        visits = dv.empty((n_rows.value, 3), torch.int32)
+        _lib.check(lib.gd_residence_fill(dv.ptr(rows), n_events, dv.ptr(work), dv.ptr(visits), s))
+        v = dv.to_host(visits).astype(np.int64)
+        site_labels = np.asarray(labels, dtype=object)
+        return pd.DataFrame({'atom index': v[:, 0], 'site': v[:, 1], 'label': site_labels[v[:, 1]],
+                             'time': v[:, 2]}, columns=columns)
 
     def split(self, n_parts: int = 10) -> list['Transitions']:
-        """transitions.py:375-410."""
-        split_states = np.array_split(self.states, n_parts)
-        split_inner_states = np.array_split(self.inner_states, n_parts)
-        split_events = _split_transitions_events(self.events, self.n_states, n_parts)
-        split_trajectory = self.trajectory.split(n_parts)
-        split_diff_trajectory = self.diff_trajectory.split(n_parts)
-        return [
-            self.__class__(
-                sites=self.sites, trajectory=split_trajectory[i],
-                diff_trajectory=split_diff_trajectory[i], states=split_states[i],
-                inner_states=split_inner_states[i], events=split_events[i],
-                site_radius=self.site_radius,
-            )
-            for i in range(n_parts)
-        ]
+        """Drop-in for transitions.py:375-410.  The parts share this object's device arrays:
+        states are frame slices (``np.array_split`` bounds), every part's event table is cut out
+        of the (atom, time)-sorted table by ``gd_events_split_count/fill``."""
+        n_states = self.n_states
+        event_parts = _split_events_device(self.d_events, n_states, n_parts)
+        outer, inner = self.d_states, self.d_inner_states
+        trajectories = self.trajectory.split(n_parts)
+        diff_trajectories = self.diff_trajectory.split(n_parts)
+        big, small = n_states % n_parts, n_states // n_parts
+        parts, lo = [], 0
+        for i in range(n_parts):
+            hi = lo + small + (1 if i < big else 0)
+            table, index = event_parts[i]
+            parts.append(self.__class__(
+                sites=self.sites, trajectory=trajectories[i], diff_trajectory=diff_trajectories[i],
+                states=None, inner_states=None, events=None, site_radius=self.site_radius,
+                _device={'outer': outer[lo:hi], 'inner': inner[lo:hi], 'events': table,
+                         'events_index': index, 'events_match_states': False},
+            ))
+            lo = hi
+        return parts
+
+
+def _split_events_device(table: 'EventTable', n_states: int, n_parts: int):
+    """[(EventTable, source row numbers int64 device tensor)] per part of transitions.py:837-879."""
+    if len(table) < n_parts:
+        raise ValueError(f'Not enough transitions per part to split into {n_parts}')
+    lib, s = _lib.lib, dv.stream_ptr()
+    n_atoms = table.n_atoms
+    bins = np.linspace(0, n_states + 1, n_parts + 1, dtype=int).astype(np.int64)
+    d_bins = dv.to_device(bins)
+    part_off = dv.empty((n_parts, n_atoms + 1), torch.int64)
+    src_lo = dv.empty((n_parts, n_atoms), torch.int64)
+    _lib.check(lib.gd_events_split_count(dv.ptr(table.rows), dv.ptr(table.atom_offsets), n_atoms,
+                                         dv.ptr(d_bins), n_parts, dv.ptr(part_off), dv.ptr(src_lo), s))
+    sizes = dv.to_host(part_off[:, n_atoms].contiguous())
+    base = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    total = int(base[-1])
+    rows = dv.empty((max(total, 1), 6), torch.int32)
+    index = dv.empty((max(total, 1),), torch.int64)
+    if total:
+        d_base = dv.to_device(base[:-1].copy())
+        _lib.check(lib.gd_events_split_fill(dv.ptr(table.rows), n_atoms, dv.ptr(d_bins), n_parts,
+                                            dv.ptr(part_off), dv.ptr(src_lo), dv.ptr(d_base),
+                                            dv.ptr(rows), dv.ptr(index), s))
+    return [(EventTable(rows[base[p]:base[p + 1]], part_off[p], n_atoms), index[base[p]:base[p + 1]])
+            for p in range(n_parts)]
 
 
 def _split_transitions_events(events: pd.DataFrame, n_states: int, n_parts=10, split_key='time',
                               dependent_keys='time') -> list[pd.DataFrame]:
-    """transitions.py:837-879."""
+    """Drop-in for transitions.py:837-879 on a DataFrame: rows with ``bins[p] <= time <
+    bins[p + 1]`` per part, the time column shifted to the part's first frame, the original
+    index labels kept."""
+    if split_key != 'time' or dependent_keys != 'time':
+        raise NotImplementedError('the device split works on the time column')
     if len(events) < n_parts:
         raise ValueError(f'Not enough transitions per part to split into {n_parts}')
-    bins = np.linspace(0, n_states + 1, n_parts + 1, dtype=int)
-    parts = [
-        events[(events[split_key] >= start) & (events[split_key] < stop)].copy()
-        for start, stop in pairwise(bins)
-    ]
-    for offset, part in zip(bins[:-1], parts):
-        part[dependent_keys] -= offset
-    return parts
+    table, order = EventTable.from_dataframe(events, return_order=True)
+    labels = events.index.to_numpy()
+    extra = [c for c in events.columns if c not in EVENT_COLUMNS]
+    out = []
+    for part, src in _split_events_device(table, n_states, n_parts):
+        src_h = order[dv.to_host(src)] if len(part) else np.zeros(0, dtype=np.int64)
+        data = widen_to_host(part.rows)
+        keep = np.argsort(src_h, kind='stable')  # the reference keeps the incoming row order
+        df = pd.DataFrame(data[keep], columns=EVENT_COLUMNS, index=labels[src_h[keep]])
+        for c in extra:
+            df[c] = events[c].to_numpy()[src_h[keep]]
+        out.append(df[list(events.columns)])
+    return out
 
 
 def remove_partial_occupancies_from_structure(structure):

@@ -221,6 +221,19 @@ gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames, int32_t n_
                            const int32_t *d_carry_in, int32_t *d_carry_out, int32_t *d_work,
                            int32_t *d_out, void *stream);
 
+/* The same fill in two steps, for frame shards (one pass over the states less than calling
+ * gd_fill_states twice):
+ *   1. gd_fill_last_valid: d_last_valid [n_atoms] = last valid state of this shard in scan
+ *      direction (NOSITE if it has none); leaves the per-chunk carries in d_work;
+ *   2. the caller all-gathers d_last_valid and picks, per atom, the nearest valid entry of
+ *      the shards before (ffill) / after (bfill) this one -> d_carry_in (NULL: none);
+ *   3. gd_fill_apply writes d_out from d_work and d_carry_in. */
+gd_status_t gd_fill_last_valid(const int32_t *d_states, int64_t n_frames, int32_t n_atoms,
+                               int direction, int32_t *d_work, int32_t *d_last_valid, void *stream);
+gd_status_t gd_fill_apply(const int32_t *d_states, int64_t n_frames, int32_t n_atoms, int direction,
+                          const int32_t *d_carry_in, const int32_t *d_work, int32_t *d_out,
+                          void *stream);
+
 /* ------------------------------------------------------------------------- *
  * K3  transitions -> jumps
  * replaces: _generic_transitions_to_jumps, src/gemdat/jumps.py:24-119 (the
@@ -319,6 +332,51 @@ gd_status_t gd_pair_matrix(const int32_t *d_rows, int64_t n_rows, int32_t row_st
                            unsigned long long *d_scratch, long long *d_matrix, void *stream);
 
 /* ------------------------------------------------------------------------- *
+ * N1  occupancy, residence times, split
+ * replaces: Transitions.occupancy (src/gemdat/transitions.py:280-306: np.unique over the
+ *           [T, A] states), Transitions.residence_time (:339-373: Python loop over atoms,
+ *           np.diff / np.nonzero per column), Transitions.split and
+ *           _split_transitions_events (:375-410, :837-879: boolean masks per part)
+ * ------------------------------------------------------------------------- */
+
+/* d_counts [n_sites + 1] uint64, ADDED to (zero it first): d_counts[0] = number of NOSITE
+ * entries, d_counts[s + 1] = number of entries equal to site s, over the n int32 entries of
+ * d_states (any shape; frame shards add up).  occupancy of site s = d_counts[s + 1] / n_frames. */
+gd_status_t gd_occupancy(const int32_t *d_states, int64_t n, int32_t n_sites,
+                         unsigned long long *d_counts, void *stream);
+
+/* Residence times from the event table (d_events [n_events, 6] int32, sorted by atom, then
+ * time).  A boundary of the reference's np.diff(states[:, atom]) is exactly a row whose start
+ * site differs from its destination site; the visit it opens lasts until the next such row of
+ * the same atom.  Reported: (atom index, site, time) int32 per visit in (atom, time) order,
+ * without visits of NOSITE and without an atom's first and last visit (transitions.py:359-367).
+ * Two-phase: gd_residence_count returns the number of rows (synchronises), the caller
+ * allocates d_rows [n_rows, 3], gd_residence_fill writes them.  d_work:
+ * gd_residence_work_bytes(n_events) bytes, 8-byte aligned. */
+int64_t gd_residence_work_bytes(int64_t n_events);
+gd_status_t gd_residence_count(const int32_t *d_events, int64_t n_events, void *d_work,
+                               int64_t *h_n_rows, void *stream);
+gd_status_t gd_residence_fill(const int32_t *d_events, int64_t n_events, const void *d_work,
+                              int32_t *d_rows, void *stream);
+
+/* _split_transitions_events: part p holds the rows with d_bins[p] <= time < d_bins[p + 1]
+ * (d_bins [n_parts + 1] int64 on the device, np.linspace(0, n_states + 1, n_parts + 1,
+ * dtype=int)), in their (atom, time) order, with d_bins[p] subtracted from the time column.
+ *   gd_events_split_count: d_part_offsets [n_parts, n_atoms + 1] int64 = per-atom row offsets
+ *     inside every part (last column = rows of the part), d_src_lo [n_parts, n_atoms] int64 =
+ *     first source row of (part, atom).  Asynchronous.
+ *   gd_events_split_fill: d_part_base [n_parts] int64 = first row of part p in d_rows (all
+ *     parts back to back, [sum of rows, 6] int32); d_index (may be NULL) receives the source
+ *     row number of every row -- the index labels the reference's boolean mask keeps. */
+gd_status_t gd_events_split_count(const int32_t *d_events, const int64_t *d_atom_offsets,
+                                  int32_t n_atoms, const int64_t *d_bins, int32_t n_parts,
+                                  int64_t *d_part_offsets, int64_t *d_src_lo, void *stream);
+gd_status_t gd_events_split_fill(const int32_t *d_events, int32_t n_atoms, const int64_t *d_bins,
+                                 int32_t n_parts, const int64_t *d_part_offsets,
+                                 const int64_t *d_src_lo, const int64_t *d_part_base,
+                                 int32_t *d_rows, int64_t *d_index, void *stream);
+
+/* ------------------------------------------------------------------------- *
  * N3  collective jumps
  * replaces: Collective._compute, src/gemdat/collective.py:61-106 (the pandas
  * double loop over jump pairs), called from Jumps.collective, jumps.py:223-251.
@@ -380,8 +438,8 @@ gd_status_t gd_rdf_classes(const int32_t *d_states, const int32_t *d_states_prev
 /* Distance histograms over all frames.  d_pos_frac [n_frames,n_atoms,3] fractional;
  * sources d_idx1 [n1] and targets d_idx2 [n2] are atom indices; d_class [n_frames,n1]
  * (NULL: one class) and d_group [n2] (NULL: one group) select the table the pair is
- * counted in.  Distances follow Lattice.get_all_distances (both ends wrapped to [0,1),
- * shortest of the 27 images).  d_edges [n_edges] are the caller's exact bin edges
+ * counted in.  Distances follow Lattice.get_all_distances (LLL-reduced basis, both ends wrapped
+ * to [0,1) there, shortest of the 27 images; as gd_pbc_distances).  d_edges [n_edges] are the caller's exact bin edges
  * (np.arange(0, max_dist + resolution, resolution)), `resolution` only seeds the
  * search.  mode 0: np.digitize(d, edges, right=True), index = #edges < d;
  * mode 1: np.histogram(d, edges), index = #edges <= d with d == edges[-1] counted in
@@ -410,14 +468,62 @@ gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, int32_t n_at
  * Outputs (any may be NULL): d_cum_frac [n_frames,n_atoms,3] cumulative fractional
  *   displacement; d_cum_cart same in Angstrom (cum_frac @ lattice); d_dist
  *   [n_atoms,n_frames] distance from the base position (note: atom-major, as the
- *   reference returns it); d_winding_out [n_atoms,3] int32 winding at shard end.
+ *   reference returns it); d_speed [n_frames,n_atoms] = np.diff(distance, prepend=0) along
+ *   time (TrajectoryMetrics.speed, src/gemdat/metrics.py:35-47) -- TIME-major, the layout
+ *   gd_amplitudes_* stream (gd_transpose_f64 gives the reference's [n_atoms,n_frames]);
+ *   d_winding_out [n_atoms,3] int32 winding at shard end.
  * d_work: n_chunks*n_atoms*3 int32, n_chunks = gd_unwrap_chunks(n_frames, n_atoms). */
 int64_t gd_unwrap_chunks(int64_t n_frames, int32_t n_atoms);
 gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
                       const double *h_lattice, const double *d_prev_row,
                       const int32_t *d_base_winding, const double *d_base_pos, int32_t *d_work,
-                      double *d_cum_frac, double *d_cum_cart, double *d_dist,
+                      double *d_cum_frac, double *d_cum_cart, double *d_dist, double *d_speed,
                       int32_t *d_winding_out, void *stream);
+
+/* gd_unwrap in two steps, for frame shards (the winding a shard starts from is known only
+ * after every shard has counted its own):
+ *   1. gd_unwrap_windings: d_winding_out [n_atoms,3] = lattice translations inside this shard
+ *      (incl. the step from d_prev_row into its first frame); d_work keeps the per-chunk
+ *      prefixes;
+ *   2. the caller all-gathers d_winding_out and sums the shards before this one (integers:
+ *      exact) -> d_base_winding;
+ *   3. gd_unwrap_apply writes the outputs from d_work (as left by step 1) + d_base_winding. */
+gd_status_t gd_unwrap_windings(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                               const double *d_prev_row, int32_t *d_work, int32_t *d_winding_out,
+                               void *stream);
+gd_status_t gd_unwrap_apply(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                            const double *h_lattice, const double *d_prev_row,
+                            const int32_t *d_base_winding, const double *d_base_pos,
+                            const int32_t *d_work, double *d_cum_frac, double *d_cum_cart,
+                            double *d_dist, double *d_speed, void *stream);
+
+/* ------------------------------------------------------------------------- *
+ * a4  vibration amplitudes
+ * replaces: TrajectoryMetrics.amplitudes (src/gemdat/metrics.py:209-231: Python loop over
+ *           atoms, np.sign / np.roll / np.array_split / np.sum) and the np.mean / np.std of
+ *           vibration_amplitude (:190-207)
+ * ------------------------------------------------------------------------- */
+
+/* d_speed_tm [n_frames,n_atoms] (gd_unwrap d_speed).  Every atom's row is cut after each sign
+ * flip except its first and last one and the pieces are summed; amplitudes of atom a are
+ * d_amplitudes[d_atom_offsets[a] .. d_atom_offsets[a+1]) in time order, atoms ascending -- the
+ * order of the reference's list.  Two-phase: gd_amplitudes_count fills d_atom_offsets
+ * [n_atoms+1] int64 and returns the total (synchronises when h_n_amplitudes is given);
+ * gd_amplitudes_fill writes d_amplitudes.  d_work: gd_amplitudes_work_bytes() bytes, 16-byte
+ * aligned, untouched between the two calls. */
+int64_t gd_amplitudes_work_bytes(int64_t n_frames, int32_t n_atoms);
+gd_status_t gd_amplitudes_count(const double *d_speed_tm, int64_t n_frames, int32_t n_atoms,
+                                void *d_work, int64_t *d_atom_offsets, int64_t *h_n_amplitudes,
+                                void *stream);
+gd_status_t gd_amplitudes_fill(const double *d_speed_tm, int64_t n_frames, int32_t n_atoms,
+                               const void *d_work, const int64_t *d_atom_offsets,
+                               double *d_amplitudes, void *stream);
+
+/* np.mean(x) and np.std(x) (population: sqrt(mean((x - mean)^2))) of n doubles in two
+ * deterministic reduction passes.  d_work: gd_mean_std_work_bytes() bytes.  Synchronises. */
+int64_t gd_mean_std_work_bytes(void);
+gd_status_t gd_mean_std(const double *d_x, int64_t n, void *d_work, double *h_mean, double *h_std,
+                        void *stream);
 
 /* ------------------------------------------------------------------------- *
  * K4  all-lag mean squared displacement
@@ -428,6 +534,10 @@ gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int32_t n_atom
 /* [n_frames,n_atoms,3] -> component-major per atom [n_atoms,3,n_frames] (the layout
  * gd_msd_direct streams). */
 gd_status_t gd_transpose_soa(const double *d_in, int64_t n_frames, int32_t n_atoms, double *d_out,
+                             void *stream);
+
+/* out[c, r] = in[r, c] for a row-major [n_rows, n_cols] float64 array. */
+gd_status_t gd_transpose_f64(const double *d_in, int64_t n_rows, int64_t n_cols, double *d_out,
                              void *stream);
 
 /* d_soa [n_atoms,3,n_frames] unwrapped Cartesian displacement (gd_unwrap d_cum_cart
@@ -453,9 +563,21 @@ gd_status_t gd_density(const double *d_pos_frac, int64_t n_atom_frames, const in
  * helpers
  * ------------------------------------------------------------------------- */
 
+/* np.mod(coords, 1) of Trajectory.to_positions (src/gemdat/trajectory.py:121-127).
+ * d_flag [1] int32 (zero-initialised) is set when some coordinate lies outside [0, 1);
+ * d_out (may alias d_in; NULL = only check) receives the wrapped coordinates. */
+gd_status_t gd_wrap_unit(const double *d_in, double *d_out, int64_t n, int32_t *d_flag,
+                         void *stream);
+
 /* minimum-image distance matrix between two fractional coordinate sets
  * (pymatgen Lattice.get_all_distances as used at transitions.py:543,595 and
- * jumps.py:203).  d_out [n1,n2] float64. */
+ * jumps.py:203): both sets are mapped into the LLL-reduced basis and wrapped to [0,1)
+ * there, then the shortest of the 27 neighbouring images is taken (pbc_shortest_vectors).
+ * d_out [n1,n2] float64. */
+/* The basis reduction behind it, host only (no device needed): h_lll [9] = LLL-reduced rows
+ * (pymatgen Lattice.lll_matrix, delta = 0.75), h_mapping [9] the unimodular integer matrix
+ * with lll = mapping @ lattice (Lattice.lll_mapping). */
+gd_status_t gd_lll_reduce_host(const double *h_lattice, double *h_lll, double *h_mapping);
 gd_status_t gd_pbc_distances(const double *h_lattice, const double *d_frac1, int32_t n1,
                              const double *d_frac2, int32_t n2, double *d_out, void *stream);
 

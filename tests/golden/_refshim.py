@@ -66,15 +66,22 @@ class Lattice(_pmg.Lattice):
 
 
 class _Composition:
-    def __init__(self, symbol):
+    """pymatgen Composition, reduced: one element, ``num_atoms`` = its amount  [recalled]."""
+
+    def __init__(self, symbol, amount=1.0):
         self.elements = [Element(symbol)]
-        self.num_atoms = 1.0
+        self.num_atoms = float(amount)
 
 
 class PeriodicSite:
     def __init__(self, symbol, frac_coords, label):
+        amount = 1.0
+        if isinstance(symbol, dict):  # Structure(species=[{name: occupancy}, ...]) (transitions.py:294-297)
+            (symbol, amount), = symbol.items()
+        else:
+            symbol = str(symbol)
         self.specie = Element(symbol)
-        self.species = _Composition(symbol)
+        self.species = _Composition(symbol, amount)
         self.frac_coords = np.asarray(frac_coords, dtype=float)
         self.label = label
         self.is_ordered = True
@@ -84,7 +91,7 @@ class Structure:
     def __init__(self, lattice, species, coords, labels=None, site_properties=None):
         self.lattice = lattice if isinstance(lattice, _pmg.Lattice) else Lattice(lattice)
         labels = list(labels) if labels is not None else [str(s) for s in species]
-        self._sites = [PeriodicSite(str(s), c, lab) for s, c, lab in zip(species, coords, labels)]
+        self._sites = [PeriodicSite(s, c, lab) for s, c, lab in zip(species, coords, labels)]
         self.site_properties = site_properties or {}
 
     @property

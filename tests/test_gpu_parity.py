@@ -366,6 +366,15 @@ def test_c3_shape_properties_and_window_parity():
     jumps = tr.jumps().data.to_numpy()
     assert np.all(jumps[:, 1] != jumps[:, 2]) and np.all(jumps[:, 4] > jumps[:, 3])
     assert int(tr.jumps().matrix().sum()) == len(jumps)
+    # the whole event table and the jump tables against the oracle's restatement of
+    # transitions.py:413-482 and jumps.py:24-119 on the downloaded states
+    from oracle import events as oevents
+    from oracle import jumps as ojumps
+
+    assert_array_equal(ev, oevents.calculate_transition_events(states, inner_states))
+    for mr in (0, 3, 100):
+        assert_array_equal(tr.jumps(minimal_residence=mr).data.to_numpy(),
+                           ojumps.transitions_to_jumps(ev, len(traj), mr))
 
 
 def test_c3_full_size_properties():
@@ -374,7 +383,8 @@ def test_c3_full_size_properties():
     the device: every event row agrees with the state arrays it was cut from, the row count is the
     number of state changes of the non-skipped atoms, rows are sorted by (atom, time), jumps are
     well formed; the checked, optimistic and graph-replayed passes give identical tables; sampled
-    frame windows equal the C oracle; and the table sizes are the known answers of this recipe."""
+    frame windows equal the C oracle; the jump rows of sampled atoms equal the oracle's state
+    machine run on their event slices."""
     from gemdat_b200 import synth
     from gemdat_b200.pipeline import HotPath
     from oracle import cstates
@@ -397,7 +407,20 @@ def test_c3_full_size_properties():
             again = hp.run(pos)
             assert hp.last_pass == 'optimistic' and hp.last_launch_mode == expect, hp.last_optimistic_reject
             assert torch.equal(again['events'], ev) and torch.equal(again['jumps'], jumps)
-    assert ev.shape[0] == 71_449_167 and jumps.shape[0] == 79_291  # known answers of the C3 recipe
+    # jump rows of sampled atoms against the oracle's state machine (jumps.py:24-119) on their
+    # event slices (an atom's jumps depend on its own events only)
+    from oracle import jumps as ojumps
+
+    off = first['atom_offsets'].cpu().numpy()
+    jumps_h = jumps.cpu().numpy().astype(np.int64)
+    for atom in (0, 1, 333, 640, rec.n_atoms - 1):
+        rows = ev[off[atom]:off[atom + 1]].cpu().numpy().astype(np.int64)
+        assert len(rows) > 1000
+        try:
+            want = ojumps.transitions_to_jumps(rows, T, 3)
+        except ValueError:
+            want = np.zeros((0, 6), dtype=np.int64)
+        assert_array_equal(jumps_h[jumps_h[:, 0] == atom], want)
     a, t = ev[:, 0].long(), ev[:, 5].long()
     # rows agree with the states they were cut from, and each is a real change
     assert torch.equal(outer[t, a], ev[:, 1]) and torch.equal(outer[t + 1, a], ev[:, 2])
@@ -1016,3 +1039,416 @@ def test_rdf_hist_random_vs_oracle(triclinic):
                                    resolution=res)
         assert_array_equal(d.x, x)
         assert_allclose(d.y, y, rtol=1e-12, atol=0)
+
+
+# ------------------------------------------------------------------ N1: occupancy, residence, split
+
+N1_CASES = ['pipeline_c2_r09_inner05', 'pipeline_c2_dict_radius', 'pipeline_box_mixed']
+
+
+def _n1_transitions(name):
+    from conftest import load_pipeline_case
+
+    c = load_pipeline_case(name)
+    traj, sites = _product(c)
+    r, f = _radius_args(c)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        tr = traj.transitions_between_sites(sites, 'Li', site_radius=r, site_inner_fraction=f,
+                                            fraction_of_overlap=float(c['fraction_of_overlap']))
+    return c, tr
+
+
+@pytest.mark.parametrize('name', N1_CASES)
+def test_n1_vs_reference_golden(name):
+    """occupancy / occupancy_by_site_type / atom_locations / residence_time / split / Jumps.split
+    against the outputs of the reference's transitions.py:280-410, 837-879 and jumps.py:412-433
+    (tests/golden/make_golden_n1.py)."""
+    from conftest import load_golden
+    from gemdat_b200 import Jumps
+
+    g = load_golden('n1')
+    c, tr = _n1_transitions(name)
+    occ = tr.occupancy()
+    assert_array_equal(np.asarray(occ.occupancies), g[f'{name}/occupancy'])
+    assert list(occ.labels) == c['labels']
+    by_type = tr.occupancy_by_site_type()
+    assert list(by_type) == [str(k) for k in g[f'{name}/by_type_keys']]
+    assert_array_equal(np.array(list(by_type.values())), g[f'{name}/by_type_values'])
+    loc = tr.atom_locations()
+    assert list(loc) == [str(k) for k in g[f'{name}/locations_keys']]
+    assert_array_equal(np.array(list(loc.values())), g[f'{name}/locations_values'])
+    rt = tr.residence_time()
+    assert list(rt.columns) == ['atom index', 'site', 'label', 'time']
+    assert_array_equal(rt[['atom index', 'site', 'time']].to_numpy(dtype=np.int64).reshape(-1, 3), g[f'{name}/residence'])
+    assert [str(x) for x in rt['label']] == [str(x) for x in g[f'{name}/residence_labels']]
+    mr = int(g[f'{name}/minimal_residence'])
+    for n in g[f'{name}/splits']:
+        n = int(n)
+        parts = tr.split(n)
+        assert len(parts) == n
+        for i, part in enumerate(parts):
+            tag = f'{name}/split{n}/{i}'
+            assert_array_equal(part.states, g[f'{tag}/states'])
+            assert_array_equal(part.inner_states, g[f'{tag}/inner_states'])
+            assert_array_equal(part.events.to_numpy().reshape(-1, 6), g[f'{tag}/events'])
+            assert_array_equal(part.events.index.to_numpy(), g[f'{tag}/events_index'])
+            assert len(part.trajectory) == int(g[f'{tag}/n_frames_trajectory'])
+            assert_array_equal(np.asarray(part.occupancy().occupancies), g[f'{tag}/occupancy'])
+            assert_array_equal(part.residence_time()[['atom index', 'site', 'time']].to_numpy(dtype=np.int64).reshape(-1, 3),
+                               g[f'{tag}/residence'])
+            if f'{tag}/jumps' in g:
+                assert_array_equal(Jumps(part, minimal_residence=mr).data.to_numpy(), g[f'{tag}/jumps'])
+            else:
+                with pytest.raises(ValueError, match='No jumps found'):
+                    Jumps(part, minimal_residence=mr)
+        # Jumps.split (jumps.py:412-433) on a part size where every part has jumps
+        if all(f'{name}/split{n}/{i}/jumps' in g for i in range(n)):
+            js = tr.jumps(minimal_residence=mr).split(n)
+            assert [j.n_jumps for j in js] == [len(g[f'{name}/split{n}/{i}/jumps']) for i in range(n)]
+    with pytest.raises(ValueError) as exc:
+        tr.split(tr.n_events + 1)
+    assert str(exc.value) == str(g[f'{name}/split_error'])
+    # the private seam on a DataFrame (transitions.py:837-879), with a shuffled-back index
+    from gemdat_b200.transitions import _split_transitions_events
+
+    n = int(g[f'{name}/splits'][0])
+    for i, df in enumerate(_split_transitions_events(tr.events, tr.n_states, n)):
+        assert_array_equal(df.to_numpy().reshape(-1, 6), g[f'{name}/split{n}/{i}/events'])
+        assert_array_equal(df.index.to_numpy(), g[f'{name}/split{n}/{i}/events_index'])
+
+
+@pytest.mark.parametrize('n_frames,n_atoms,n_sites', [(1, 1, 3), (257, 5, 7), (4099, 33, 64), (1000, 17, 60_000)])
+def test_n1_kernels_random_vs_oracle(n_frames, n_atoms, n_sites):
+    """gd_occupancy (shared-memory bins; global atomics beyond 48k bins; unaligned input) and the
+    residence rows from re-extracted outer changes against oracle/sitestats.py."""
+    import ctypes as C
+
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from gemdat_b200.transitions import _events_device
+    from oracle import sitestats
+
+    rng = np.random.default_rng(n_frames + n_atoms)
+    # piecewise-constant states with NOSITE gaps
+    st = rng.integers(-1, min(n_sites, 40), size=(n_frames, n_atoms))
+    hold = rng.random((n_frames, n_atoms)) < 0.8
+    for t in range(1, n_frames):
+        st[t] = np.where(hold[t], st[t - 1], st[t])
+    lib, s = _lib.lib, dv.stream_ptr()
+    for shift in (0, 1):  # 16-byte aligned and not
+        buf = dv.empty((st.size + 1,), torch.int32)
+        d = buf[shift: shift + st.size]
+        d.copy_(torch.from_numpy(st.astype(np.int32).ravel()))
+        counts = dv.zeros((n_sites + 1,), torch.int64)
+        _lib.check(lib.gd_occupancy(dv.ptr(d), st.size, n_sites, dv.ptr(counts), s))
+        want = np.bincount(st.ravel() + 1, minlength=n_sites + 1)
+        assert_array_equal(counts.cpu().numpy(), want)
+    assert_array_equal(counts.cpu().numpy()[1:] / n_frames, sitestats.occupancy(st, n_sites))
+    d_st = dv.to_device(st.astype(np.int32))
+    want_rows = sitestats.residence_time(st)
+    try:
+        rows = _events_device(d_st, d_st).rows
+    except ValueError:
+        assert len(want_rows) == 0
+        return
+    n_rows = C.c_int64(0)
+    work = dv.empty((int(lib.gd_residence_work_bytes(len(rows))),), torch.uint8)
+    _lib.check(lib.gd_residence_count(dv.ptr(rows), len(rows), dv.ptr(work), C.byref(n_rows), s))
+    got = dv.empty((max(n_rows.value, 1), 3), torch.int32)
+    _lib.check(lib.gd_residence_fill(dv.ptr(rows), len(rows), dv.ptr(work), dv.ptr(got), s))
+    assert_array_equal(got[: n_rows.value].cpu().numpy(), want_rows)
+
+
+# ------------------------------------------------------------------ a4: amplitudes on the device
+
+
+@pytest.mark.parametrize('n_frames,n_atoms', [(1, 1), (2, 3), (3, 1), (31, 2), (513, 5), (4100, 37)])
+def test_amplitude_kernels_vs_oracle(n_frames, n_atoms):
+    """gd_amplitudes_count/fill + gd_mean_std on random speed rows (with exact zeros and long
+    constant-sign runs) against the numpy restatement of metrics.py:190-231.  Sums run left to
+    right on the device, numpy's np.sum pairs differently beyond 8 elements: 1e-12 absolute on
+    values of order 1."""
+    import ctypes as C
+
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from oracle import displ
+
+    rng = np.random.default_rng(7 * n_frames + n_atoms)
+    speed = rng.normal(size=(n_atoms, n_frames))
+    speed[rng.random(speed.shape) < 0.1] = 0.0
+    if n_frames > 100:
+        speed[0, 10:90] = np.abs(speed[0, 10:90])  # one long run
+        speed[-1] = 0.0                             # an atom that never moves
+    want = displ.amplitudes(speed)
+    lib, s = _lib.lib, dv.stream_ptr()
+    tm = dv.to_device(np.ascontiguousarray(speed.T))
+    work = dv.empty((int(lib.gd_amplitudes_work_bytes(n_frames, n_atoms)),), torch.uint8)
+    off = dv.empty((n_atoms + 1,), torch.int64)
+    n_amp = C.c_int64(0)
+    _lib.check(lib.gd_amplitudes_count(dv.ptr(tm), n_frames, n_atoms, dv.ptr(work), dv.ptr(off), C.byref(n_amp), s))
+    assert n_amp.value == len(want)
+    amp = dv.empty((n_amp.value,), torch.float64)
+    _lib.check(lib.gd_amplitudes_fill(dv.ptr(tm), n_frames, n_atoms, dv.ptr(work), dv.ptr(off), dv.ptr(amp), s))
+    assert_allclose(amp.cpu().numpy(), want, rtol=0, atol=1e-12)
+    mean, std = C.c_double(0), C.c_double(0)
+    mwork = dv.empty((int(lib.gd_mean_std_work_bytes()),), torch.uint8)
+    _lib.check(lib.gd_mean_std(dv.ptr(amp), n_amp.value, dv.ptr(mwork), C.byref(mean), C.byref(std), s))
+    assert_allclose(mean.value, np.mean(want), rtol=1e-12, atol=1e-14)
+    assert_allclose(std.value, np.std(want), rtol=1e-12, atol=1e-14)
+
+
+def test_default_radius_route_keeps_the_time_axis_on_the_device(monkeypatch):
+    """site_radius=None (transitions.py:141-149): vibration amplitude from K0 + the amplitude
+    kernels; no [A, T] array may be downloaded on the way."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import synth
+
+    rec = synth.config_c2(n_frames=3000, seed=5)
+    traj = rec.trajectory(device=True)
+    big = []
+    real = dv.to_host
+
+    def spy(t):
+        if t.numel() >= 3000:
+            big.append(tuple(t.shape))
+        return real(t)
+
+    monkeypatch.setattr(dv, 'to_host', spy)
+    import gemdat_b200.metrics as gm
+    import gemdat_b200.trajectory as gt
+
+    monkeypatch.setattr(gm.dv, 'to_host', spy)
+    monkeypatch.setattr(gt.dv, 'to_host', spy)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=None)
+    assert big == [], big
+    from oracle import displ
+    from oracle import radius as oradius
+
+    vib = displ.vibration_amplitude(rec.host_positions(), rec.lattice)
+    want = oradius.radius_from_vibration_amplitude(rec.sites.frac_coords, rec.lattice, vib)
+    assert_allclose(tr.site_radius.radius[''], want, rtol=1e-10)
+
+
+# ------------------------------------------------------------------ np.mod(coords, 1) of to_positions
+
+
+@pytest.mark.parametrize('route', ['resident', 'pipelined', 'device'])
+def test_coordinates_outside_the_unit_cell_are_wrapped(monkeypatch, route):
+    """trajectory.py:121-127: positions = np.mod(coords, 1).  Input in [-1, 2) gives the same
+    positions, states, events and volume as the wrapped input (and as the oracle on it)."""
+    import gemdat_b200.transitions as gtr
+    from gemdat_b200 import Trajectory, synth, trajectory_to_volume
+    from oracle import states as ostates
+    from oracle import volume as ovolume
+
+    rec = synth.config_c2(n_frames=400, seed=9)
+    wrapped = rec.host_positions()
+    rng = np.random.default_rng(0)
+    shifted = wrapped + rng.integers(-1, 2, size=wrapped.shape)
+    assert shifted.min() < 0 and shifted.max() >= 1
+    want_pos = np.mod(shifted, 1)
+    if route == 'pipelined':
+        monkeypatch.setattr(gtr, 'PIPELINE_MIN_BYTES', 0)
+    coords = torch.from_numpy(shifted).cuda() if route == 'device' else shifted
+    traj = Trajectory(species=['Li'] * rec.n_atoms, coords=coords, lattice=rec.lattice, time_step=2e-15)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        tr = traj.transitions_between_sites(rec.sites, 'Li', site_radius=0.9, site_inner_fraction=0.5)
+        kw = dict(site_frac=rec.sites.frac_coords, site_labels=rec.sites.labels, positions=want_pos,
+                  lattice_matrix=rec.lattice, site_radius={'': 0.9})
+        assert_array_equal(tr.states, ostates.calculate_atom_states(**kw, site_inner_fraction={'': 1.0}))
+        assert_array_equal(tr.inner_states, ostates.calculate_atom_states(**kw, site_inner_fraction={'': 0.5}))
+    pos = traj.positions
+    pos = pos.cpu().numpy() if route == 'device' else pos
+    assert_array_equal(pos, want_pos)
+    vol = trajectory_to_volume(traj, resolution=0.5)
+    assert_array_equal(vol.data, ovolume.trajectory_to_volume(want_pos, rec.lattice, 0.5))
+
+
+# ------------------------------------------------------------------ minimum image in skewed cells
+
+
+@pytest.mark.parametrize('cell', ['gamma40', 'non_reduced_supercell', 'argyrodite_2x1x1'])
+def test_pbc_distances_in_skewed_cells(cell):
+    """gd_pbc_distances (LLL-reduced basis + 27 images, pymatgen pbc_shortest_vectors) against the
+    oracle operation by operation (1e-13 relative: the LLL coordinates come from np.dot there)
+    and against a brute-force search over 13^3 images of the raw basis."""
+    from gemdat_b200 import Lattice
+    from test_oracle_golden import SKEWED_CELLS, _brute_force_distances
+
+    from oracle.pmg import Lattice as OLattice
+
+    m = SKEWED_CELLS[cell]
+    rng = np.random.default_rng(3)
+    f1, f2 = rng.random((25, 3)) * 3 - 1, rng.random((31, 3)) * 3 - 1
+    got = Lattice(m).get_all_distances(f1, f2)
+    assert_allclose(got, OLattice(m).get_all_distances(f1, f2), rtol=1e-13, atol=1e-13)
+    assert_allclose(got, _brute_force_distances(m, f1, f2), rtol=0, atol=1e-12)
+
+
+# ------------------------------------------------------------------ shard arguments of K0 and the fills
+
+
+@pytest.mark.parametrize('n_shards', [2, 3, 8])
+def test_unwrap_frame_shards_equal_one_shard(n_shards):
+    """gd_unwrap_windings -> (all-gather + exclusive sum over shards) -> gd_unwrap_apply with
+    d_prev_row / d_base_winding / d_base_pos: every output bit-identical to one call over the whole
+    trajectory (windings are integers: the shard scan is exact)."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+
+    rng = np.random.default_rng(n_shards)
+    T, A = 1003, 29
+    lat = np.array([[9.0, 0, 0], [1.0, 10.5, 0], [0.5, -0.7, 12.25]])
+    pos_h = np.mod(0.3 + np.cumsum(rng.normal(scale=0.15, size=(T, A, 3)), axis=0), 1)
+    pos = dv.to_device(pos_h)
+    lib, s = _lib.lib, dv.stream_ptr()
+
+    def outputs(n):
+        return (dv.empty((n, A, 3), torch.float64), dv.empty((n, A, 3), torch.float64),
+                dv.empty((A, n), torch.float64), dv.empty((n, A), torch.float64))
+
+    work = dv.empty((int(lib.gd_unwrap_chunks(T, A)) * A * 3,), torch.int32)
+    whole = outputs(T)
+    wind = dv.empty((A, 3), torch.int32)
+    _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None, dv.ptr(work),
+                             *(dv.ptr(x) for x in whole), dv.ptr(wind), s))
+    cuts = np.linspace(0, T, n_shards + 1).astype(int)
+    totals, works = [], []
+    for r in range(n_shards):
+        f0, f1 = cuts[r], cuts[r + 1]
+        w = dv.empty((int(lib.gd_unwrap_chunks(f1 - f0, A)) * A * 3,), torch.int32)
+        tot = dv.empty((A, 3), torch.int32)
+        prev = pos[f0 - 1].contiguous() if r else None
+        _lib.check(lib.gd_unwrap_windings(dv.ptr(pos[f0:f1]), f1 - f0, A, dv.ptr(prev), dv.ptr(w), dv.ptr(tot), s))
+        totals.append(tot)
+        works.append(w)
+    base = torch.cumsum(torch.stack(totals), dim=0) - torch.stack(totals)  # exclusive over shards
+    assert torch.equal((base[-1] + totals[-1]).int(), wind)
+    for r in range(n_shards):
+        f0, f1 = cuts[r], cuts[r + 1]
+        out = outputs(f1 - f0)
+        prev = pos[f0 - 1].contiguous() if r else None
+        _lib.check(lib.gd_unwrap_apply(dv.ptr(pos[f0:f1]), f1 - f0, A, lat.ctypes.data, dv.ptr(prev),
+                                       dv.ptr(base[r].int().contiguous()), dv.ptr(pos[0].contiguous()),
+                                       dv.ptr(works[r]), *(dv.ptr(x) for x in out), s))
+        assert torch.equal(out[0], whole[0][f0:f1]) and torch.equal(out[1], whole[1][f0:f1])
+        assert torch.equal(out[2], whole[2][:, f0:f1]) and torch.equal(out[3], whole[3][f0:f1])
+        # the one-call form with the same shard arguments
+        out2 = outputs(f1 - f0)
+        _lib.check(lib.gd_unwrap(dv.ptr(pos[f0:f1]), f1 - f0, A, lat.ctypes.data, dv.ptr(prev),
+                                 dv.ptr(base[r].int().contiguous()), dv.ptr(pos[0].contiguous()),
+                                 dv.ptr(works[r]), *(dv.ptr(x) for x in out2), None, s))
+        assert all(torch.equal(a, b) for a, b in zip(out, out2))
+
+
+@pytest.mark.parametrize('n_shards', [2, 3, 8])
+@pytest.mark.parametrize('direction', [1, -1])
+def test_fill_frame_shards_equal_one_shard(n_shards, direction):
+    """ffill / bfill over frame shards: gd_fill_last_valid -> nearest valid entry of the shards
+    before (after) -> gd_fill_apply, and gd_fill_states with d_carry_in / d_carry_out: equal to one
+    call over all frames and to the oracle (utils.py:59-98)."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from oracle import fill as ofill
+
+    rng = np.random.default_rng(10 * n_shards + direction)
+    T, A = 777, 41
+    st = rng.integers(0, 9, size=(T, A))
+    st[rng.random(st.shape) < 0.85] = -1
+    st[:, 0] = -1          # an atom that never has a site
+    st[: T // 2, 1] = -1   # the first shards of this atom are empty
+    want = (ofill.ffill if direction > 0 else ofill.bfill)(st, axis=0)
+    d = dv.to_device(st.astype(np.int32))
+    lib, s = _lib.lib, dv.stream_ptr()
+    cuts = np.linspace(0, T, n_shards + 1).astype(int)
+    last, works = [], []
+    for r in range(n_shards):
+        f0, f1 = cuts[r], cuts[r + 1]
+        w = dv.empty((int(lib.gd_events_work_elems(f1 - f0, A)),), torch.int32)
+        lv = dv.empty((A,), torch.int32)
+        _lib.check(lib.gd_fill_last_valid(dv.ptr(d[f0:f1]), f1 - f0, A, direction, dv.ptr(w), dv.ptr(lv), s))
+        last.append(lv.cpu().numpy())
+        works.append(w)
+    order = range(n_shards) if direction > 0 else range(n_shards - 1, -1, -1)
+    carry = np.full(A, -1, dtype=np.int32)
+    chained = None
+    for r in order:
+        f0, f1 = cuts[r], cuts[r + 1]
+        d_carry = dv.to_device(carry.copy())
+        out = dv.empty((f1 - f0, A), torch.int32)
+        _lib.check(lib.gd_fill_apply(dv.ptr(d[f0:f1]), f1 - f0, A, direction, dv.ptr(d_carry), dv.ptr(works[r]),
+                                     dv.ptr(out), s))
+        assert_array_equal(out.cpu().numpy(), want[f0:f1])
+        # the one-call form, chaining d_carry_out -> d_carry_in
+        w2 = dv.empty((int(lib.gd_events_work_elems(f1 - f0, A)),), torch.int32)
+        out2, c_out = dv.empty((f1 - f0, A), torch.int32), dv.empty((A,), torch.int32)
+        _lib.check(lib.gd_fill_states(dv.ptr(d[f0:f1]), f1 - f0, A, direction, dv.ptr(chained), dv.ptr(c_out),
+                                      dv.ptr(w2), dv.ptr(out2), s))
+        assert_array_equal(out2.cpu().numpy(), want[f0:f1])
+        chained = c_out
+        carry = np.where(last[r] != -1, last[r], carry).astype(np.int32)
+        assert_array_equal(c_out.cpu().numpy(), carry)
+
+
+# ------------------------------------------------------------------ K4 / K5 at the BASELINE sizes
+
+
+def test_msd_accumulation_at_a_million_frames():
+    """K4 at T = 10^6 (config 4's trajectory length): 64 lags spread over [1, T) for 4 atoms against
+    the long-double direct sum of oracle/msd.py -- (i) on the device's own unwrapped coordinates
+    (isolates the accumulation of k_msd: 1e-12 relative), (ii) end to end from the wrapped positions
+    against the oracle's sequential np.cumsum unwrap (1e-10 relative, north_star's tolerance)."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib, synth
+    from oracle import msd as omsd
+
+    T = 1_000_000
+    rec = synth.make_recipe(synth.garnet_like_sites((3, 3, 2)), 4, T, seed=77, epoch_len=1024, p_hop=0.3)
+    pos = rec.device_positions(0, T)
+    A = rec.n_atoms
+    lib, s = _lib.lib, dv.stream_ptr()
+    lat = np.ascontiguousarray(rec.lattice, dtype=np.float64)
+    work = dv.empty((int(lib.gd_unwrap_chunks(T, A)) * A * 3,), torch.int32)
+    cart = dv.empty((T, A, 3), torch.float64)
+    wind = dv.empty((A, 3), torch.int32)
+    _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None, dv.ptr(work), None,
+                             dv.ptr(cart), None, None, dv.ptr(wind), s))
+    soa = dv.empty((A, 3, T), torch.float64)
+    _lib.check(lib.gd_transpose_soa(dv.ptr(cart), T, A, dv.ptr(soa), s))
+    lags = np.unique(np.concatenate([[1, 2, 3, 7, 2047, 2048, 2049, T - 2, T - 1],
+                                     np.geomspace(10, T - 10, 55).astype(np.int64)]))
+    got = np.zeros((A, len(lags)))
+    one = dv.empty((A, 1), torch.float64)
+    for j, k in enumerate(lags):
+        _lib.check(lib.gd_msd_direct(dv.ptr(soa), T, A, int(k), 1, dv.ptr(one), s))
+        got[:, j] = one.cpu().numpy()[:, 0]
+    r = cart.cpu().numpy().transpose(1, 0, 2)  # [A, T, 3], the device's own unwrap
+    own = np.zeros_like(got)
+    for j, k in enumerate(lags):
+        diff = (r[:, k:, :] - r[:, : T - k, :]).astype(np.longdouble)
+        own[:, j] = (np.sum(diff * diff, axis=(1, 2), dtype=np.longdouble) / (T - k)).astype(np.float64)
+    assert_allclose(got, own, rtol=1e-12, atol=0)
+    want = omsd.msd_direct(rec.host_positions(), rec.lattice, lags=lags)
+    assert_allclose(got, want, rtol=1e-10, atol=0)
+
+
+def test_density_at_a_tenth_of_an_angstrom_on_a_c3_window():
+    """K5 at BASELINE config 5's resolution (0.1 A, grid 389 x 389 x 259 on the C3 cell) on a
+    2000-frame window of the C3 trajectory: bit-exact against np.digitize + np.unique
+    (volume.py:471-503)."""
+    from gemdat_b200 import synth, trajectory_to_volume
+    from oracle import volume as ovolume
+
+    rec = synth.config_c3(n_frames=1_000_000)
+    frame0, n = 654_321, 2000
+    traj = rec.trajectory(device=True, frame0=frame0, n_frames=n)
+    vol = trajectory_to_volume(traj, resolution=0.1)
+    want = ovolume.trajectory_to_volume(rec.host_positions(frame0, n), rec.lattice, 0.1)
+    assert vol.data.shape == want.shape == (389, 389, 259)
+    assert int(vol.data.sum()) == n * rec.n_atoms
+    assert_array_equal(vol.data, want)

@@ -314,3 +314,144 @@ def test_hotpath_frame_shards_equal_one(tmp_path, world, exchange):
         else:         # each rank keeps the rows of its frames, sorted by (atom, time)
             assert str(r['layout']) == 'frame_shard'
             np.testing.assert_array_equal(r['local_events'], ev[(ev[:, 5] >= lo) & (ev[:, 5] < hi)])
+
+
+# ------------------------------------------------------------------------------------ K0 / fills / K4 / K5 shards
+
+
+def _walk_case(n_frames=900, n_atoms=13, seed=4):
+    rng = np.random.default_rng(seed)
+    pos = np.mod(0.3 + np.cumsum(rng.normal(scale=0.2, size=(n_frames, n_atoms, 3)), axis=0), 1)
+    lat = np.array([[9.0, 0, 0], [1.0, 10.5, 0], [0.5, -0.7, 12.25]])
+    states = rng.integers(0, 7, size=(n_frames, n_atoms))
+    states[rng.random(states.shape) < 0.9] = -1
+    states[:, 0] = -1
+    states[: n_frames // 2 + 50, 1] = -1
+    return pos, lat, states
+
+
+def _shard_rules_worker(rank: int, world: int, port: int, out_path: str):
+    """Host-side rules of gemdat_b200/sharded.py with numpy standing in for the kernels."""
+    _init(rank, world, port)
+    try:
+        from gemdat_b200.sharded import FrameShards, shard_base_winding, shard_fill_carry
+        from oracle import displ as odispl
+        from oracle import fill as ofill
+
+        pos, lat, states = _walk_case()
+        T, A = pos.shape[:2]
+        fs = FrameShards(lattice=lat, n_atoms=A, n_frames_total=T, world=world, rank=rank)
+        f0, f1 = fs.frame_bounds[rank]
+        mine = pos[f0:f1]
+        # K0: halo row, local integer windings, exclusive sum over shards, apply
+        ends = fs.comm.all_gather(torch.from_numpy(np.stack([mine[0], mine[-1]])))
+        base_pos = ends[0, 0].numpy()
+        prev = ends[rank - 1, 1].numpy() if rank else mine[0]
+        steps = np.diff(np.concatenate([prev[None], mine]), axis=0)
+        wind = np.cumsum(np.rint(steps).astype(np.int32), axis=0)  # inclusive prefix inside the shard
+        totals = fs.comm.all_gather(torch.from_numpy(wind[-1].copy()))
+        base = shard_base_winding(totals, rank).numpy()
+        cum = (mine - base_pos) - (base + wind)
+        want = odispl.cumulative_displacements(pos)[f0:f1]
+        np.testing.assert_allclose(cum, want, rtol=0, atol=1e-12)
+        # fills: last valid state per shard, nearest valid shard before / after
+        for direction, ref in ((1, ofill.ffill), (-1, ofill.bfill)):
+            st = states[f0:f1]
+            local = ref(st, axis=0)
+            last = local[-1] if direction > 0 else local[0]
+            all_last = fs.comm.all_gather(torch.from_numpy(last.astype(np.int32)))
+            carry = shard_fill_carry(all_last, rank, direction).numpy()
+            filled = np.where(local == -1, carry[None, :], local)
+            np.testing.assert_array_equal(filled, ref(states, axis=0)[f0:f1])
+        # K4: frames -> atoms regrouping (all-to-all of uneven pieces), per-lag partial sums
+        cart = torch.from_numpy(pos[f0:f1] @ lat)
+        soa = cart.permute(1, 2, 0).contiguous()
+        block = fs.exchange_atom_blocks(soa)
+        a_lo, a_hi = fs.atoms_of_rank()
+        np.testing.assert_array_equal(block.numpy(), np.transpose(pos @ lat, (1, 2, 0))[a_lo:a_hi])
+        part = block.sum(dim=(0, 1))[:5].clone()
+        fs.comm.all_reduce_sum(part)
+        np.testing.assert_allclose(part.numpy(), np.transpose(pos @ lat, (1, 2, 0)).sum(axis=(0, 1))[:5], rtol=1e-12)
+        key = torch.tensor([7 + rank, 2**62], dtype=torch.int64)
+        fs.comm.all_reduce_min(key)
+        assert key.tolist() == [7, 2**62]
+        if rank == 0:
+            Path(out_path).write_text('ok')
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_shard_rules_gloo_cpu(tmp_path, world):
+    out = tmp_path / 'result.txt'
+    mp.spawn(_shard_rules_worker, args=(world, _free_port(), str(out)), nprocs=world, join=True)
+    assert out.read_text() == 'ok'
+
+
+def _gpu_shards_worker(rank: int, world: int, port: int, out_path: str):
+    _init(rank, world, port)
+    try:
+        torch.cuda.set_device(0)
+        from gemdat_b200.sharded import FrameShards
+        from gemdat_b200.volume import grid_edges
+        from gemdat_b200.lattice import Lattice
+
+        pos, lat, states = _walk_case()
+        T, A = pos.shape[:2]
+        fs = FrameShards(lattice=lat, n_atoms=A, n_frames_total=T, world=world, rank=rank)
+        f0, f1 = fs.frame_bounds[rank]
+        d_pos = torch.from_numpy(pos[f0:f1]).cuda()
+        d_states = torch.from_numpy(states[f0:f1].astype(np.int32)).cuda()
+        k0 = fs.unwrap(d_pos, want_frac=True, want_cart=True, want_dist=True, want_speed=True)
+        msd, (a_lo, a_hi), curve = fs.msd(d_pos)
+        idx = np.arange(A)
+        bins = np.arange(0, 5.0 + 0.25, 0.25)
+        np.savez(f'{out_path}.{rank}.npz',
+                 frac=k0['frac'].cpu().numpy(), cart=k0['cart'].cpu().numpy(), dist=k0['dist'].cpu().numpy(),
+                 speed=k0['speed'].cpu().numpy(), winding=k0['winding'].cpu().numpy(),
+                 prev=fs.fill(d_states, 1).cpu().numpy(), nxt=fs.fill(d_states, -1).cpu().numpy(),
+                 grid=fs.density(d_pos, grid_edges(Lattice(lat), 0.5)).cpu().numpy(),
+                 counts=fs.site_counts(d_states, 7).cpu().numpy(),
+                 msd=msd.cpu().numpy(), block=np.array([a_lo, a_hi]), curve=curve.cpu().numpy(),
+                 rdf=fs.species_rdf_counts(d_pos, idx, idx, bins, 0.25, True).cpu().numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('world', [2, 3])
+def test_frame_shards_equal_one(tmp_path, world):
+    """K0, ffill/bfill, K5, N1 counts, K4 (frames regrouped by atom, per-lag partial sums
+    all-reduced) and the species RDF over frame shards (ranks sharing cuda:0, gloo transport)
+    against one shard: bit-identical, the atom-averaged MSD curve to 1e-12."""
+    from gemdat_b200.sharded import FrameShards
+    from gemdat_b200.volume import grid_edges
+    from gemdat_b200.lattice import Lattice
+
+    out = str(tmp_path / 'rank')
+    mp.spawn(_gpu_shards_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    pos, lat, states = _walk_case()
+    T, A = pos.shape[:2]
+    fs = FrameShards(lattice=lat, n_atoms=A, n_frames_total=T)
+    d_pos, d_states = torch.from_numpy(pos).cuda(), torch.from_numpy(states.astype(np.int32)).cuda()
+    k0 = fs.unwrap(d_pos, want_frac=True, want_cart=True, want_dist=True, want_speed=True)
+    msd, _, curve = fs.msd(d_pos)
+    idx, bins = np.arange(A), np.arange(0, 5.0 + 0.25, 0.25)
+    ranks = [np.load(f'{out}.{r}.npz') for r in range(world)]
+    np.testing.assert_array_equal(np.vstack([r['frac'] for r in ranks]), k0['frac'].cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r['cart'] for r in ranks]), k0['cart'].cpu().numpy())
+    np.testing.assert_array_equal(np.hstack([r['dist'] for r in ranks]), k0['dist'].cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r['speed'] for r in ranks]), k0['speed'].cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r['prev'] for r in ranks]), fs.fill(d_states, 1).cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r['nxt'] for r in ranks]), fs.fill(d_states, -1).cpu().numpy())
+    np.testing.assert_array_equal(np.vstack([r['msd'] for r in ranks]), msd.cpu().numpy())
+    grid = fs.density(d_pos, grid_edges(Lattice(lat), 0.5)).cpu().numpy()
+    counts = fs.site_counts(d_states, 7).cpu().numpy()
+    rdf = fs.species_rdf_counts(d_pos, idx, idx, bins, 0.25, True).cpu().numpy()
+    for r in ranks:
+        np.testing.assert_array_equal(r['winding'], k0['winding'].cpu().numpy())
+        np.testing.assert_array_equal(r['grid'], grid)
+        np.testing.assert_array_equal(r['counts'], counts)
+        np.testing.assert_array_equal(r['rdf'], rdf)
+        np.testing.assert_allclose(r['curve'], curve.cpu().numpy(), rtol=1e-12)
+    assert int(grid.sum()) == T * A and int(counts.sum()) == T * A

@@ -302,3 +302,115 @@ def test_oracle_rdf_edge_cases():
                                resolution=0.5)
     np.testing.assert_array_equal(x, [0.0, 0.5])
     assert y[0] == 0.0 and y[1] > 0.0  # np.histogram: d = 0.5 opens [0.5, 1.0]
+
+
+# ------------------------------------------------------------------ N1 (occupancy, residence, split)
+
+N1_CASES = ['pipeline_c2_r09_inner05', 'pipeline_c2_dict_radius', 'pipeline_box_mixed']
+
+
+@pytest.fixture(scope='module')
+def n1_golden():
+    from conftest import load_golden
+
+    return load_golden('n1')
+
+
+@pytest.mark.parametrize('name', N1_CASES)
+def test_oracle_n1_vs_reference_golden(n1_golden, name):
+    """oracle/sitestats.py against the outputs of the reference's transitions.py:280-410, 837-879."""
+    from conftest import load_pipeline_case
+    from oracle import sitestats
+
+    g, c = n1_golden, load_pipeline_case(name)
+    st, n_sites = c['states'], len(c['labels'])
+    n_floating = int(c['floating_mask'].sum())
+    occ = sitestats.occupancy(st, n_sites)
+    assert_array_equal(occ, g[f'{name}/occupancy'])
+    by_type = sitestats.by_label(occ, c['labels'], True)
+    assert list(by_type) == [str(k) for k in g[f'{name}/by_type_keys']]
+    assert_array_equal(np.array(list(by_type.values())), g[f'{name}/by_type_values'])
+    loc = sitestats.by_label(occ, c['labels'], False, n_floating)
+    assert list(loc) == [str(k) for k in g[f'{name}/locations_keys']]
+    assert_array_equal(np.array(list(loc.values())), g[f'{name}/locations_values'])
+    assert_array_equal(sitestats.residence_time(st), g[f'{name}/residence'])
+    for n in g[f'{name}/splits']:
+        bounds, _ = sitestats.split_bounds(len(st), int(n))
+        parts = sitestats.split_events(c['events'], len(st), int(n))
+        for i, (rows, src) in enumerate(parts):
+            tag = f'{name}/split{n}/{i}'
+            assert_array_equal(st[bounds[i]:bounds[i + 1]], g[f'{tag}/states'])
+            assert_array_equal(rows, g[f'{tag}/events'])
+            assert_array_equal(src, g[f'{tag}/events_index'])
+            assert_array_equal(sitestats.occupancy(g[f'{tag}/states'], n_sites), g[f'{tag}/occupancy'])
+            assert_array_equal(sitestats.residence_time(g[f'{tag}/states']), g[f'{tag}/residence'])
+            mr = int(g[f'{name}/minimal_residence'])
+            if f'{tag}/jumps' in g:
+                got = jumps.transitions_to_jumps(rows, int(g[f'{tag}/n_frames_trajectory']), mr)
+                assert_array_equal(got, g[f'{tag}/jumps'])
+            else:
+                assert str(g[f'{tag}/jumps_error']) == 'No jumps found'
+                with pytest.raises(ValueError, match='No jumps found'):
+                    jumps.transitions_to_jumps(rows, int(g[f'{tag}/n_frames_trajectory']), mr)
+    with pytest.raises(ValueError) as exc:
+        sitestats.split_events(c['events'], len(st), len(c['events']) + 1)
+    assert str(exc.value) == str(g[f'{name}/split_error'])
+
+
+# ------------------------------------------------------------------ minimum image in skewed cells
+
+SKEWED_CELLS = {
+    'gamma40': np.array([[10.0, 0, 0], [9.5 * np.cos(np.radians(40)), 9.5 * np.sin(np.radians(40)), 0], [1.0, 2.0, 8.0]]),
+    'non_reduced_supercell': np.array([[5.0, 0, 0], [10.0, 5.0, 0], [15.0, 10.0, 7.0]]),
+    'argyrodite_2x1x1': np.diag([19.848, 9.924, 9.924]),
+}
+
+
+def _brute_force_distances(m, f1, f2, reach=6):
+    imgs = np.array([[i, j, k] for i in range(-reach, reach + 1) for j in range(-reach, reach + 1)
+                     for k in range(-reach, reach + 1)], dtype=float)
+    diff = f2[None, :, :] - f1[:, None, :]
+    cart = (diff[:, :, None, :] + imgs[None, None, :, :]) @ m
+    return np.sqrt((cart**2).sum(-1).min(-1))
+
+
+@pytest.mark.parametrize('cell', list(SKEWED_CELLS))
+def test_oracle_distances_are_minimum_image_in_skewed_cells(cell):
+    """Lattice.get_all_distances searches the 27 images of the LLL-reduced basis (pymatgen
+    pbc_shortest_vectors): equal to a brute-force search over 13^3 images of the raw basis,
+    which the 27 raw-basis images are not for these cells."""
+    m = SKEWED_CELLS[cell]
+    rng = np.random.default_rng(3)
+    f1, f2 = rng.random((25, 3)) * 3 - 1, rng.random((31, 3)) * 3 - 1
+    got = Lattice(m).get_all_distances(f1, f2)
+    assert_allclose(got, _brute_force_distances(m, f1, f2), rtol=0, atol=1e-12)
+    if cell == 'non_reduced_supercell':
+        a, b = f1 - np.floor(f1), f2 - np.floor(f2)
+        raw = np.full(got.shape, np.inf)
+        for img in np.array([[i, j, k] for i in (-1, 0, 1) for j in (-1, 0, 1) for k in (-1, 0, 1)], dtype=float):
+            v = ((b[None, :, :] + img) - a[:, None, :]) @ m
+            raw = np.minimum(raw, np.sqrt((v * v).sum(-1)))
+        assert (raw > got + 1e-9).any(), 'this cell should defeat the raw-basis 27-image search'
+
+
+def test_library_lll_equals_oracle_lll():
+    """gd_lll_reduce_host (C++, the product's reduction) against oracle/pmg.py's restatement of
+    pymatgen's _calculate_lll: same unimodular mapping on random, skewed and non-reduced cells."""
+    from gemdat_b200 import _lib
+
+    rng = np.random.default_rng(11)
+    cells = list(SKEWED_CELLS.values())
+    while len(cells) < 400:
+        m = rng.normal(size=(3, 3)) * rng.uniform(1, 10)
+        if len(cells) % 3 == 0:
+            m = rng.integers(-3, 4, size=(3, 3)) @ m
+        if abs(np.linalg.det(m)) > 1e-2:
+            cells.append(m)
+    for m in cells:
+        m = np.ascontiguousarray(m, dtype=np.float64)
+        lll, mapping = np.zeros(9), np.zeros(9)
+        assert _lib.lib.gd_lll_reduce_host(m.ctypes.data, lll.ctypes.data, mapping.ctypes.data) == 0
+        want_lll, want_map = Lattice(m)._calculate_lll()
+        assert_array_equal(mapping.reshape(3, 3), want_map)
+        assert_allclose(lll.reshape(3, 3), want_lll, rtol=1e-12, atol=1e-12)
+        assert abs(abs(np.linalg.det(mapping.reshape(3, 3))) - 1.0) < 1e-9
