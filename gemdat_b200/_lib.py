@@ -36,16 +36,39 @@ class GemdatB200Error(RuntimeError):
         self.message = message
 
 
-def _load() -> C.CDLL:
+def _require_library() -> None:
     if not LIB_PATH.exists():
         raise ImportError(
             f'{LIB_PATH} is missing: build it with `python -c "import __graft_entry__ as g; g.build()"` '
             'or gemdat_b200/csrc/build.sh (nvcc, sm_100a). gemdat_b200 has no CPU fallback.'
         )
-    return C.CDLL(str(LIB_PATH))
 
 
-lib = _load()
+_require_library()  # importing the package without the built library fails loudly
+
+
+class _Library:
+    """The shared library, mapped on first use: a process that only needs the pure-numpy helpers
+    of the package (the synthetic recipe in bench.py's CPU reference arm) never loads it."""
+
+    _cdll = None
+
+    def load(self) -> C.CDLL:
+        if self._cdll is None:
+            _require_library()
+            cdll = C.CDLL(str(LIB_PATH))
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(cdll, name)  # AttributeError here = the .so is stale: rebuild
+                fn.restype = res
+                fn.argtypes = args
+            type(self)._cdll = cdll
+        return self._cdll
+
+    def __getattr__(self, name):
+        return getattr(self.load(), name)
+
+
+lib = _Library()
 
 _p = C.c_void_p
 _i32 = C.c_int32
@@ -72,6 +95,7 @@ SIGNATURES = {
     'gd_events_fill': (C.c_int, [_p, _p, _i64, _i32, _p, _p, _p, _p, _p, _i64, _p, _p]),
     'gd_events_merge': (C.c_int, [_p, _p, _p, _i32, _p, _p]),
     'gd_events_merge_capped': (C.c_int, [_p, _p, _p, _i32, _p, _i64, _i64, _p]),
+    'gd_jumps_merge_shards': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i64, _p, _i64, _p]),
     'gd_fill_states': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p, _p]),
     'gd_fill_last_valid': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p]),
     'gd_fill_apply': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p]),
@@ -112,17 +136,12 @@ SIGNATURES = {
     'gd_transpose_soa': (C.c_int, [_p, _i64, _i32, _p, _p]),
     'gd_msd_direct': (C.c_int, [_p, _i64, _i32, _i64, _i64, _p, _p]),
     'gd_density': (C.c_int, [_p, _i64, _p, _p, _p, _p]),
+    'gd_density_frames': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p]),
     'gd_lll_reduce_host': (C.c_int, [_p, _p, _p]),
     'gd_pbc_distances': (C.c_int, [_p, _p, _i32, _p, _i32, _p, _p]),
     'gd_synth_positions': (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _p, _u64, _i64, _i64, _p, _p]),
     'gd_fp64_peak': (C.c_int, [_i64, C.POINTER(C.c_double), _p]),
 }
-
-for _name, (_res, _args) in SIGNATURES.items():
-    _fn = getattr(lib, _name)  # AttributeError here = the .so is stale: rebuild
-    _fn.restype = _res
-    _fn.argtypes = _args
-
 
 def last_error() -> str:
     return lib.gd_last_error().decode('utf-8', 'replace')

@@ -17,5 +17,7 @@ for f in gd_*.cu; do
   fi
 done
 for p in "${pids[@]:-}"; do [[ -n "$p" ]] && wait "$p"; done
-"$NVCC" -shared -o libgemdat_b200.so _build/gd_*.o -lcudart
+# link beside the target, then rename: a reader (or a gpurun snapshot) never sees a partial file
+"$NVCC" -shared -o _build/libgemdat_b200.so.tmp _build/gd_*.o -lcudart
+mv -f _build/libgemdat_b200.so.tmp libgemdat_b200.so
 echo "built $(pwd)/libgemdat_b200.so"

@@ -114,27 +114,54 @@ __global__ void __launch_bounds__(256)
     }
 }
 
-// thread per atom: exclusive scan of the flip counts over the chunks, sum carried into every
-// chunk, amplitude count of the atom -> amp_count[a + 1]
+// warp per atom: exclusive scan over the chunks of (flips, open sum) with the segmented-sum
+// operator  (n1, s1) o (n2, s2) = (n1 + n2, n2 > 0 ? s2 : s1 + s2), 32 chunks per step;
+// amplitude count of the atom -> amp_count[a + 1]
 __global__ void __launch_bounds__(128)
     k_amp_carry(Geometry g, AmpWork w, int64_t *__restrict__ amp_count) {
-    const int32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    const int32_t a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (a >= g.n_atoms) return;
     int32_t run = 0;
     double carry = 0.0;
-#pragma unroll 4
-    for (int64_t c = 0; c < g.n_chunks; ++c) {
+    for (int64_t c0 = 0; c0 < g.n_chunks; c0 += 32) {
+        const int64_t c = c0 + lane;
+        const bool on = c < g.n_chunks;
         const int64_t k = c * g.n_atoms + a;
-        const int32_t n = w.rank[k];
-        const double open = w.carry[k];
-        w.rank[k] = run;
-        w.carry[k] = carry;
-        carry = n > 0 ? open : carry + open;
-        run += n;
+        const int32_t n = on ? w.rank[k] : 0;
+        const double open = on ? w.carry[k] : 0.0;
+        int32_t in = n;
+        double is = open;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int32_t un = __shfl_up_sync(0xffffffffu, in, o);
+            const double us = __shfl_up_sync(0xffffffffu, is, o);
+            if (lane >= o) {
+                is = in > 0 ? is : us + is;
+                in += un;
+            }
+        }
+        // exclusive values: the inclusive ones of the lane before, after the running carry
+        int32_t en = __shfl_up_sync(0xffffffffu, in, 1);
+        double es = __shfl_up_sync(0xffffffffu, is, 1);
+        if (lane == 0) {
+            en = 0;
+            es = 0.0;
+        }
+        if (on) {
+            w.rank[k] = run + en;
+            w.carry[k] = en > 0 ? es : carry + es;
+        }
+        const int32_t tn = __shfl_sync(0xffffffffu, in, 31);
+        const double ts = __shfl_sync(0xffffffffu, is, 31);
+        carry = tn > 0 ? ts : carry + ts;
+        run += tn;
     }
-    w.n_flips[a] = run;
-    w.rest[a] = carry;
-    amp_count[a + 1] = run >= 2 ? run - 1 : 1;
+    if (lane == 0) {
+        w.n_flips[a] = run;
+        w.rest[a] = carry;
+        amp_count[a + 1] = run >= 2 ? run - 1 : 1;
+    }
 }
 
 __global__ void __launch_bounds__(128)
@@ -230,7 +257,7 @@ extern "C" gd_status_t gd_amplitudes_count(const double *d_speed_tm, int64_t n_f
     k_amp_walk<false><<<(unsigned)gd_ceil_div(items, 256), 256, 0, st>>>(d_speed_tm, g, w, nullptr,
                                                                          nullptr);
     GD_LAUNCH_CHECK();
-    k_amp_carry<<<(unsigned)gd_ceil_div(n_atoms, 128), 128, 0, st>>>(g, w, d_atom_offsets);
+    k_amp_carry<<<(unsigned)gd_ceil_div((int64_t)n_atoms * 32, 128), 128, 0, st>>>(g, w, d_atom_offsets);
     GD_LAUNCH_CHECK();
     gd_k_scan_offsets<<<1, 1024, 0, st>>>(d_atom_offsets, (int64_t)n_atoms);
     GD_LAUNCH_CHECK();

@@ -16,6 +16,8 @@
 //
 // Algorithmic traffic: 8 B read per atom-frame per pass; events are O(1e-2) of the
 // atom-frames (24 B each).
+#include <stdlib.h>
+
 #include "gd_common.cuh"
 
 namespace {
@@ -136,14 +138,25 @@ __global__ void __launch_bounds__(256)
 #define GD_COMPACT_ATOM_MAJOR 0
 #endif
 constexpr int kCompactLanes = GD_COMPACT_LANES;
-__global__ void __launch_bounds__(256)
-    k_events_compact(const int2 *__restrict__ stage, int32_t cap, Geometry g,
-                     const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
-                     const int64_t *__restrict__ atom_offsets, int32_t frame0,
-                     int2 *__restrict__ events, int64_t row_capacity) {
-    const int64_t item = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / kCompactLanes;
-    const int sub = threadIdx.x % kCompactLanes;
-    if (item >= g.n_chunks * g.n_atoms) return;
+
+// where a (chunk, atom) segment's rows go: n_words 8-byte words from `src` to `dst` (0 = nothing)
+struct CompactJob {
+    const int2 *src;
+    int2 *dst;
+    int n_words;
+};
+
+__device__ __forceinline__ CompactJob compact_job(int64_t item, const int2 *__restrict__ stage,
+                                                  int32_t cap, const Geometry &g,
+                                                  const int32_t *__restrict__ work,
+                                                  const uint8_t *__restrict__ changed_global,
+                                                  const int64_t *__restrict__ atom_offsets,
+                                                  int2 *__restrict__ events, int64_t row_capacity) {
+    CompactJob j;
+    j.src = nullptr;
+    j.dst = nullptr;
+    j.n_words = 0;
+    if (item >= g.n_chunks * g.n_atoms) return j;
 #if GD_COMPACT_ATOM_MAJOR
     // neighbouring groups copy neighbouring chunks of one atom: contiguous destination
     const int32_t a = (int32_t)(item / g.n_chunks);
@@ -152,35 +165,61 @@ __global__ void __launch_bounds__(256)
     const int64_t c = item / g.n_atoms;
     const int32_t a = (int32_t)(item - c * g.n_atoms);
 #endif
-    if (!changed_global[a]) return;  // outer state never changes: atom is skipped
+    if (!changed_global[a]) return j;  // outer state never changes: atom is skipped
     const int32_t *w = work + (int64_t)a * g.n_chunks + c;
+    const int64_t off = atom_offsets[a];
     const int32_t first = w[0];
-    const int32_t last = (c + 1 < g.n_chunks) ? w[1] : (int32_t)(atom_offsets[a + 1] - atom_offsets[a]);
-    const int n_words = 3 * (last - first);
+    const int32_t last = (c + 1 < g.n_chunks) ? w[1] : (int32_t)(atom_offsets[a + 1] - off);
     // a table smaller than the row count (capacity guessed from an earlier run): write nothing
     // out of bounds, the caller sees the count and repeats with the right size
-    if (atom_offsets[a] + last > row_capacity) return;
-    const int2 *src = stage + (c * g.n_atoms + a) * (int64_t)cap * 3;
-    int2 *dst = events + (atom_offsets[a] + first) * 3;
-    // (the copy is latency bound -- a segment is ~54 words, 3-4 trips of 16 lanes: all of a
-    // lane's loads are issued before its first store)
-    constexpr int kTrips = 4;
-    int k = sub;
-    for (; k + (kTrips - 1) * kCompactLanes < n_words; k += kTrips * kCompactLanes) {
-        int2 v[kTrips];
+    if (last <= first || off + last > row_capacity) return j;
+    j.src = stage + (c * g.n_atoms + a) * (int64_t)cap * 3;
+    j.dst = events + (off + first) * 3;
+    j.n_words = 3 * (last - first);
+    return j;
+}
+
+// kLanes lanes own one segment at a time and walk the segments grid-stride.  A segment's copy
+// hangs on a chain of three dependent look-ups (skip flag -> chunk offsets -> atom offset)
+// before its first payload load can start, so the NEXT segment's look-ups are issued before the
+// current segment is copied: the chain overlaps the copy instead of preceding it.
+__global__ void __launch_bounds__(256)
+    k_events_compact(const int2 *__restrict__ stage, int32_t cap, Geometry g,
+                     const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
+                     const int64_t *__restrict__ atom_offsets, int32_t frame0,
+                     int2 *__restrict__ events, int64_t row_capacity) {
+    const int sub = threadIdx.x % kCompactLanes;
+    const int64_t n_items = g.n_chunks * g.n_atoms;
+    const int64_t stride = (int64_t)gridDim.x * (blockDim.x / kCompactLanes);
+    int64_t item = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / kCompactLanes;
+    CompactJob cur = compact_job(item, stage, cap, g, work, changed_global, atom_offsets, events, row_capacity);
+    for (; item < n_items; item += stride) {
+        const CompactJob nxt = compact_job(item + stride, stage, cap, g, work, changed_global,
+                                           atom_offsets, events, row_capacity);
+        const int2 *src = cur.src;
+        int2 *dst = cur.dst;
+        const int n_words = cur.n_words;
+        // (a segment is ~54 words, 3-4 trips of 16 lanes: all of a lane's loads are issued before
+        // its first store)
+        constexpr int kTrips = 4;
+        int k = sub;
+        for (; k + (kTrips - 1) * kCompactLanes < n_words; k += kTrips * kCompactLanes) {
+            int2 v[kTrips];
 #pragma unroll
-        for (int j = 0; j < kTrips; ++j) v[j] = __ldcs(src + k + j * kCompactLanes);
+            for (int j = 0; j < kTrips; ++j) v[j] = __ldcs(src + k + j * kCompactLanes);
 #pragma unroll
-        for (int j = 0; j < kTrips; ++j) {
-            const int kk = k + j * kCompactLanes;
-            if (kk % 3 == 2) v[j].y += frame0;  // (destination inner site, time)
-            dst[kk] = v[j];
+            for (int j = 0; j < kTrips; ++j) {
+                const int kk = k + j * kCompactLanes;
+                if (kk % 3 == 2) v[j].y += frame0;  // (destination inner site, time)
+                dst[kk] = v[j];
+            }
         }
-    }
-    for (; k < n_words; k += kCompactLanes) {
-        int2 v = __ldcs(src + k);
-        if (k % 3 == 2) v.y += frame0;
-        dst[k] = v;
+        for (; k < n_words; k += kCompactLanes) {
+            int2 v = __ldcs(src + k);
+            if (k % 3 == 2) v.y += frame0;
+            dst[k] = v;
+        }
+        cur = nxt;
     }
 }
 
@@ -279,29 +318,35 @@ __global__ void __launch_bounds__(256)
     work[c * g.n_atoms + a] = last;
 }
 
-// phase 2: one thread per atom walks the chunk summaries and turns them into carry-ins
+// phase 2: one WARP per atom turns the chunk summaries into carry-ins: an exclusive scan over
+// the chunks in scan direction with the operator "the later valid state wins" (32 chunks per
+// step through shuffles; a single thread walking ~10^3-10^4 chunks took as long as a pass over
+// the states)
 __global__ void __launch_bounds__(128)
     k_fill_carry(Geometry g, int direction, const int32_t *__restrict__ carry_in,
                  int32_t *__restrict__ carry_out, int32_t *__restrict__ work) {
-    const int32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+    const int32_t a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (a >= g.n_atoms) return;
     int32_t carry = carry_in ? carry_in[a] : GD_NOSITE;
-    if (direction > 0) {
-#pragma unroll 8
-        for (int64_t c = 0; c < g.n_chunks; ++c) {
-            const int32_t v = work[c * g.n_atoms + a];
-            work[c * g.n_atoms + a] = carry;
-            carry = v != GD_NOSITE ? v : carry;
+    for (int64_t p0 = 0; p0 < g.n_chunks; p0 += 32) {
+        const int64_t p = p0 + lane;  // position in scan order
+        const bool on = p < g.n_chunks;
+        const int64_t c = direction > 0 ? p : g.n_chunks - 1 - p;
+        int32_t *slot = work + c * g.n_atoms + a;
+        int32_t incl = on ? *slot : GD_NOSITE;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o && incl == GD_NOSITE) incl = up;
         }
-    } else {
-#pragma unroll 8
-        for (int64_t c = g.n_chunks - 1; c >= 0; --c) {
-            const int32_t v = work[c * g.n_atoms + a];
-            work[c * g.n_atoms + a] = carry;
-            carry = v != GD_NOSITE ? v : carry;
-        }
+        int32_t excl = __shfl_up_sync(0xffffffffu, incl, 1);
+        if (lane == 0) excl = GD_NOSITE;
+        if (on) *slot = excl != GD_NOSITE ? excl : carry;
+        const int32_t last = __shfl_sync(0xffffffffu, incl, 31);
+        carry = last != GD_NOSITE ? last : carry;
     }
-    if (carry_out) carry_out[a] = carry;
+    if (carry_out && lane == 0) carry_out[a] = carry;
 }
 
 // phase 3: apply
@@ -348,6 +393,34 @@ __global__ void __launch_bounds__(128)
     const int32_t *s = src + r0 * 6;
     int32_t *d = dst + dst_start[a] * 6;
     for (int64_t k = threadIdx.x; k < n; k += blockDim.x) d[k] = s[k];
+}
+
+// block (atom, shard): place shard r's jump rows of the atom in the merged (atom, time) table.
+// `gathered` is the all-gather of every shard's buffer [head int64 words: per-atom row offsets
+// [n_atoms + 1] ... | rows]; offs_r[a] = rows of shard r before atom a, so the merged table has
+//   first row of atom a            = sum_r offs_r[a]
+//   shard r's rows of a start at   that + sum_{r' < r} (offs_r'[a + 1] - offs_r'[a])
+// -- the whole placement plan is a handful of loads per block, no scan and no host round trip.
+__global__ void __launch_bounds__(128)
+    k_merge_shards(const int32_t *__restrict__ gathered, int64_t stride_words, int32_t head_words,
+                   int32_t world, int32_t n_atoms, int64_t src_cap, int32_t *__restrict__ dst,
+                   int64_t dst_cap) {
+    const int a = blockIdx.x, r = blockIdx.y;
+    int64_t start = 0;
+    for (int q = 0; q < world; ++q) {
+        const int64_t *off = reinterpret_cast<const int64_t *>(gathered + q * stride_words);
+        const int64_t o0 = off[a];
+        start += o0;
+        if (q < r) start += off[a + 1] - o0;
+    }
+    const int64_t *mine = reinterpret_cast<const int64_t *>(gathered + r * stride_words);
+    const int64_t r0 = mine[a], r1 = mine[a + 1];
+    // offsets the host has not validated yet (optimistic pass): never leave the tables
+    if (r0 < 0 || r1 < r0 || r1 > src_cap || start < 0 || start + (r1 - r0) > dst_cap) return;
+    const int32_t *src = gathered + r * stride_words + head_words + r0 * 6;
+    int32_t *d = dst + start * 6;
+    const int64_t n = (r1 - r0) * 6;
+    for (int64_t k = threadIdx.x; k < n; k += blockDim.x) d[k] = src[k];
 }
 
 inline unsigned blocks_for(int64_t items, int threads) { return (unsigned)gd_ceil_div(items, threads); }
@@ -439,8 +512,14 @@ extern "C" gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_c
     GD_REQUIRE(frame0 >= 0 && frame0 + n_frames < (int64_t(1) << 31), GD_ERR_INVALID,
                "gd_events_compact: frame numbers must fit int32");
     Geometry g = geometry(n_frames, n_atoms);
-    const int64_t threads = g.n_chunks * g.n_atoms * kCompactLanes;
-    k_events_compact<<<blocks_for(threads, 256), 256, 0, (cudaStream_t)stream>>>(
+    const GdDeviceInfo &dev = gd_device_info();
+    GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");
+    // persistent-style grid: every lane group walks ~items / groups segments
+    int64_t blocks = gd_ceil_div(g.n_chunks * g.n_atoms * kCompactLanes, 256);
+    int per_sm = 8;
+    if (const char *e = getenv("GD_COMPACT_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
+    if (blocks > (int64_t)dev.sm_count * per_sm) blocks = (int64_t)dev.sm_count * per_sm;
+    k_events_compact<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const int2 *>(d_stage), stage_cap, g, d_work, d_changed_global,
         d_atom_offsets, (int32_t)frame0, reinterpret_cast<int2 *>(d_events),
         row_capacity > 0 ? row_capacity : INT64_MAX);
@@ -461,7 +540,7 @@ extern "C" gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames,
     const int64_t items = g.n_chunks * g.n_atoms;
     k_fill_summary<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work);
     GD_LAUNCH_CHECK();
-    k_fill_carry<<<blocks_for(n_atoms, 128), 128, 0, st>>>(g, direction, d_carry_in, d_carry_out,
+    k_fill_carry<<<blocks_for((int64_t)n_atoms * 32, 128), 128, 0, st>>>(g, direction, d_carry_in, d_carry_out,
                                                           d_work);
     GD_LAUNCH_CHECK();
     k_fill_apply<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work, nullptr,
@@ -483,7 +562,7 @@ extern "C" gd_status_t gd_fill_last_valid(const int32_t *d_states, int64_t n_fra
     const int64_t items = g.n_chunks * g.n_atoms;
     k_fill_summary<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, d_work);
     GD_LAUNCH_CHECK();
-    k_fill_carry<<<blocks_for(n_atoms, 128), 128, 0, st>>>(g, direction, nullptr, d_last_valid,
+    k_fill_carry<<<blocks_for((int64_t)n_atoms * 32, 128), 128, 0, st>>>(g, direction, nullptr, d_last_valid,
                                                           d_work);
     GD_LAUNCH_CHECK();
     return GD_OK;
@@ -521,4 +600,21 @@ extern "C" gd_status_t gd_events_merge(const int32_t *d_src_rows, const int64_t 
                                        int32_t *d_dst_rows, void *stream) {
     return gd_events_merge_capped(d_src_rows, d_src_atom_offsets, d_dst_start, n_atoms, d_dst_rows,
                                   INT64_MAX, INT64_MAX, stream);
+}
+
+extern "C" gd_status_t gd_jumps_merge_shards(const int32_t *d_gathered, int64_t stride_words,
+                                             int32_t head_words, int32_t world, int32_t n_atoms,
+                                             int64_t src_capacity, int32_t *d_dst_rows,
+                                             int64_t dst_capacity, void *stream) {
+    GD_REQUIRE(d_gathered && d_dst_rows && world > 0 && world <= 65535 && n_atoms > 0 &&
+                   head_words >= 2 * (n_atoms + 1) && stride_words >= head_words,
+               GD_ERR_INVALID, "gd_jumps_merge_shards: bad argument");
+    GD_REQUIRE((reinterpret_cast<uintptr_t>(d_gathered) & 7) == 0 && (stride_words & 1) == 0,
+               GD_ERR_ALIGNMENT, "gd_jumps_merge_shards: buffers must be 8-byte aligned");
+    dim3 grid((unsigned)n_atoms, (unsigned)world);
+    k_merge_shards<<<grid, 128, 0, (cudaStream_t)stream>>>(d_gathered, stride_words, head_words, world,
+                                                          n_atoms, src_capacity, d_dst_rows,
+                                                          dst_capacity);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
 }

@@ -18,7 +18,7 @@ struct GdPbc {
     double inv[9];      // lll_inverse, row-major: frac_lll = frac @ inv
     double m[9];        // lll_matrix, rows = reduced basis vectors (Angstrom)
     double img[27][3];  // image vectors (i, j, k) in (-1, 0, 1)^3, k fastest, @ lll_matrix
-    double axis_len[3]; // axis_aligned: signed length of the basis vector along Cartesian axis c
+    double axis_len[3]; // axis_aligned: length of the basis vector along Cartesian axis c
     int axis_aligned;   // every reduced basis vector lies along one Cartesian axis
 };
 
@@ -120,7 +120,7 @@ inline GdPbc gd_pbc_build(const double *h_lattice) {
             break;
         }
         used[ax] = 1;
-        g.axis_len[ax] = g.m[3 * r + ax];
+        g.axis_len[ax] = fabs(g.m[3 * r + ax]);  // (the image set is symmetric: the sign is irrelevant)
     }
     return g;
 }
@@ -148,12 +148,14 @@ __device__ __forceinline__ double gd_pbc_d2(const GdPbc &g, const double a[3], c
         // axis (rounding is monotonic: min over images of fl(fl(X + Y) + Z) =
         // fl(fl(min X + min Y) + min Z)), and fl(v^2) is monotonic in |v|, so per axis the
         // candidate of smallest magnitude among p - L, p, p + L is squared once
+        // Both points are wrapped into the cell, so |p| < L and p + sign(p) L is never the
+        // shortest: the candidates are p and q = p - sign(p) L.
         const double pre[3] = {p0, p1, p2};
         double sq[3];
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-            const double L = g.axis_len[c];
-            const double v = fmin(fmin(fabs(pre[c] - L), fabs(pre[c])), fabs(pre[c] + L));
+            const double q = pre[c] - copysign(g.axis_len[c], pre[c]);
+            const double v = fabs(pre[c]) <= fabs(q) ? pre[c] : q;
             sq[c] = v * v;
         }
         return (sq[0] + sq[1]) + sq[2];

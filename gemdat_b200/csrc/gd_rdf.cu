@@ -15,17 +15,15 @@
 //
 // One CTA per (frame, slice of the sources); the frame's targets sit in shared memory wrapped
 // to [0,1); one warp per source, lanes over targets, a warp-private shared-memory histogram
-// flushed to the global uint64 table per (source, target tile).  The kernel is fp64-pipe
-// bound: ~300 fp64 instructions per pair for a general cell (the 27 images share their 27
-// products and 27 partial sums), ~35 for a diagonal cell, where the minimum separates per axis
-// (rounding is monotonic, so min over images of fl(fl(X+Y)+Z) = fl(fl(minX+minY)+minZ)).
+// flushed to the global uint64 table per (source, target tile).  Distances come from gd_pbc.cuh
+// (targets staged as Cartesian coordinates of the LLL-reduced, wrapped point): 27 image sums for a
+// general cell, one candidate per axis for an axis-aligned one.  Pairs beyond the last edge -- the
+// bulk when the cell is larger than max_dist -- are counted in registers; the others find their
+// bin from an fp32 guess corrected against exact per-edge thresholds on d2.
 #include "gd_common.cuh"
 #include "gd_pbc.cuh"
 
-// Tuning knobs for A/B builds (tools/rdf_variants.sh); the defaults are the measured ones.
-#ifndef GD_RDF_DIAG_SELECT
-#define GD_RDF_DIAG_SELECT 0
-#endif
+// Tuning knob for A/B builds (tools/rdf_variants.sh).
 #ifdef GD_RDF_MIN_CTAS  // resident CTAs per SM the register allocation must allow
 #define GD_RDF_BOUNDS __launch_bounds__(8 * 32, GD_RDF_MIN_CTAS)
 #else
@@ -70,25 +68,39 @@ __device__ double sqrt_threshold(double e, bool strict) {
     return x;
 }
 
+constexpr int kOverGroups = 4;  // groups whose beyond-the-last-edge pairs are counted in registers
+
 __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int nb = p.n_edges + 1;
     const int hist_len = p.n_group * nb;
     double *s_b = reinterpret_cast<double *>(smem);                 // [tile][3]
-    double *s_edges = s_b + 3 * (size_t)p.tile;                      // [n_edges + 1] thresholds on d2
-    int32_t *s_atom = reinterpret_cast<int32_t *>(s_edges + p.n_edges + 1);  // [tile]
+    double *s_th = s_b + 3 * (size_t)p.tile;                         // [n_edges + 2] thresholds on d2
+    int32_t *s_atom = reinterpret_cast<int32_t *>(s_th + p.n_edges + 2);  // [tile]
     int32_t *s_group = s_atom + p.tile;                              // [tile]
     uint32_t *s_hist = reinterpret_cast<uint32_t *>(s_group + p.tile);   // [kWarps][hist_len]
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float inv_res = (float)p.inv_res;
     uint32_t *my_hist = s_hist + (size_t)warp * hist_len;
-    // s_edges[k] = threshold on d2 for edge k (mode 0: edge < d, mode 1: edge <= d);
-    // s_edges[n_edges] = where d2 leaves "d == last edge" (np.histogram's closed last bin)
-    for (int k = threadIdx.x; k <= p.n_edges; k += blockDim.x)
-        s_edges[k] = k < p.n_edges ? sqrt_threshold(p.edges[k], p.mode == 0)
-                                   : sqrt_threshold(p.edges[p.n_edges - 1], true);
+    // bin index = number of edges passed.  s_th[k + 1] = smallest d2 that passes edge k: mode 0
+    // (np.digitize right=True) edge < d; mode 1 (np.histogram) edge <= d, except the LAST edge,
+    // which np.histogram's closed last bin makes strict as well.  s_th[0] = -inf and
+    // s_th[n_edges + 1] = +inf close the table, so the search below needs no bounds checks.
+    for (int k = threadIdx.x; k < p.n_edges + 2; k += blockDim.x) {
+        double th;
+        if (k == 0)
+            th = -1e300;
+        else if (k == p.n_edges + 1)
+            th = 1e300;
+        else
+            th = sqrt_threshold(p.edges[k - 1], p.mode == 0 || k == p.n_edges);
+        s_th[k] = th;
+    }
     for (int k = threadIdx.x; k < kWarps * hist_len; k += blockDim.x) s_hist[k] = 0;
+    __syncthreads();
+    const double th_over = s_th[p.n_edges];  // at or above: beyond the last edge
+    const bool reg_over = p.n_group <= kOverGroups;
 
     for (int64_t t = blockIdx.x; t < p.n_frames; t += gridDim.x) {
         const double *frame = p.pos + t * (int64_t)p.n_atoms * 3;
@@ -110,17 +122,36 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                 const double *q = frame + 3 * (int64_t)atom_i;
                 double a[3];
                 gd_pbc_cart(p.pbc, q[0], q[1], q[2], a);
+                // pairs beyond the last edge are the bulk (the cell is much larger than max_dist):
+                // they are counted in registers, per group, and added once per (source, tile)
+                uint32_t over[kOverGroups] = {0, 0, 0, 0};
                 for (int k = lane; k < nt; k += 32) {
                     if (p.skip_same && s_atom[k] == atom_i) continue;
                     const double b[3] = {s_b[3 * k], s_b[3 * k + 1], s_b[3 * k + 2]};
                     const double d2 = gd_pbc_d2(p.pbc, a, b);
-                    // fp32 guess of the bin, corrected against the exact thresholds
-                    int g = (int)fminf(sqrtf((float)d2) * inv_res, (float)p.n_edges);
-                    while (g > 0 && !(s_edges[g - 1] <= d2)) --g;
-                    while (g < p.n_edges && s_edges[g] <= d2) ++g;
-                    // np.histogram closes the last bin on the right: d == last edge
-                    if (p.mode == 1 && g == p.n_edges && d2 < s_edges[p.n_edges]) g = p.n_edges - 1;
-                    atomicAdd(&my_hist[s_group[k] * nb + g], 1u);
+                    const int grp = s_group[k];
+                    if (d2 >= th_over && reg_over) {
+#pragma unroll
+                        for (int u = 0; u < kOverGroups; ++u) over[u] += (grp == u);
+                        continue;
+                    }
+                    // fp32 guess of the bin, off by at most one: corrected against the exact
+                    // thresholds of the two neighbouring edges
+                    int g = min((int)(sqrtf((float)d2) * inv_res), p.n_edges);
+                    g += (int)(s_th[g + 1] <= d2) - (int)!(s_th[g] <= d2);
+                    // (not taken for uniform edges; arbitrary edge lists stay exact, NaNs end at 0)
+                    while (g > 0 && !(s_th[g] <= d2)) --g;
+                    while (g < p.n_edges && s_th[g + 1] <= d2) ++g;
+                    atomicAdd(&my_hist[grp * nb + g], 1u);
+                }
+                if (reg_over) {
+#pragma unroll
+                    for (int u = 0; u < kOverGroups; ++u) {
+                        uint32_t v = over[u];
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                        if (lane == 0 && v && u < p.n_group) my_hist[u * nb + p.n_edges] += v;
+                    }
                 }
                 __syncwarp();
                 unsigned long long *dst = p.hist + (size_t)c * hist_len;
@@ -207,7 +238,7 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
     p.pbc = gd_pbc_build(h_lattice);
     const GdDeviceInfo &dev = gd_device_info();
     const size_t smem_cap = (size_t)(dev.max_smem_optin > 0 ? dev.max_smem_optin : 200 * 1024);
-    const size_t fixed = (size_t)(n_edges + 1) * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
+    const size_t fixed = (size_t)(n_edges + 2) * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
     GD_REQUIRE(fixed + 32 * 32 <= smem_cap, GD_ERR_CAPACITY,
                "gd_rdf_hist: %d groups x %d bins do not fit the per-warp shared-memory histograms", n_group,
                n_edges + 1);

@@ -468,18 +468,12 @@ class HotPath:
         heads = allb[:, :head].contiguous().view(torch.int64)  # [W, A + 3]
         merged = None
         if W > 1:
-            # per-atom placement of every shard's jump rows, computed on the device from offsets
-            # the host has not seen yet (the capped merge never leaves the tables)
-            offs = heads[:, : n_atoms + 1].contiguous()
-            counts = offs[:, 1:] - offs[:, :-1]                      # [W, A]
-            per_atom = counts.sum(dim=0)
-            atom_start = torch.cumsum(per_atom, dim=0) - per_atom    # rows of atoms before a
-            dst_start = (atom_start.unsqueeze(0) + torch.cumsum(counts, dim=0) - counts).contiguous()
+            # per-atom placement of every shard's jump rows, derived inside ONE kernel from offsets
+            # the host has not seen yet (rows that would leave a table are skipped)
             merged = self._tensor('jmerged', (max(W * jcap, 1), 6), torch.int32)
-            for r in range(W):
-                _lib.check(lib.gd_events_merge_capped(dv.ptr(allb[r, head:]), dv.ptr(offs[r]), dv.ptr(dst_start[r]),
-                                                      n_atoms, dv.ptr(merged), jcap, W * jcap, s))
-            launches += W
+            _lib.check(lib.gd_jumps_merge_shards(dv.ptr(allb), int(allb.shape[1]), head, W, n_atoms, jcap,
+                                                 dv.ptr(merged), W * jcap, s))
+            launches += 1
         from types import SimpleNamespace
         return SimpleNamespace(k1=k1, offsets=offsets, rows=rows, jbuf=jbuf, jumps=jumps, allb=allb, heads=heads,
                                head=head, jcap=jcap, launches=launches, merged=merged)

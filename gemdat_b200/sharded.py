@@ -84,6 +84,15 @@ class FrameShards:
         n, A = int(pos.shape[0]), int(pos.shape[1])
         work = dv.empty((int(lib.gd_unwrap_chunks(n, A)) * A * 3,), torch.int32)
         total = dv.empty((A, 3), torch.int32)
+        frac = dv.empty((n, A, 3), torch.float64) if want_frac else None
+        cart = dv.empty((n, A, 3), torch.float64) if want_cart else None
+        dist = dv.empty((A, n), torch.float64) if want_dist else None
+        speed = dv.empty((n, A), torch.float64) if want_speed else None
+        if self.world == 1:  # one shard: the fused single-read kernel
+            _lib.check(lib.gd_unwrap(dv.ptr(pos), n, A, self.lattice.ctypes.data, None, None, None,
+                                     dv.ptr(work), dv.ptr(frac), dv.ptr(cart), dv.ptr(dist), dv.ptr(speed),
+                                     dv.ptr(total), s))
+            return {'frac': frac, 'cart': cart, 'dist': dist, 'speed': speed, 'winding': total}
         prev = base_pos = base_wind = None
         if self.world > 1:
             ends = self.comm.all_gather(torch.stack([pos[0], pos[-1]]).contiguous())  # [W, 2, A, 3]
@@ -94,10 +103,6 @@ class FrameShards:
         all_totals = self.comm.all_gather(total)  # [W, A, 3]
         if self.world > 1:
             base_wind = shard_base_winding(all_totals, self.rank)
-        frac = dv.empty((n, A, 3), torch.float64) if want_frac else None
-        cart = dv.empty((n, A, 3), torch.float64) if want_cart else None
-        dist = dv.empty((A, n), torch.float64) if want_dist else None
-        speed = dv.empty((n, A), torch.float64) if want_speed else None
         _lib.check(lib.gd_unwrap_apply(dv.ptr(pos), n, A, self.lattice.ctypes.data, dv.ptr(prev),
                                        dv.ptr(base_wind), dv.ptr(base_pos), dv.ptr(work), dv.ptr(frac),
                                        dv.ptr(cart), dv.ptr(dist), dv.ptr(speed), s))

@@ -45,8 +45,12 @@ def density_device(pos: torch.Tensor, nedges: np.ndarray, grid: torch.Tensor | N
         grid = dv.zeros(shape, torch.int32)  # reinterpreted as uint32 by the kernel
     flag = dv.zeros((1,), torch.int32)
     nedges = np.ascontiguousarray(nedges, dtype=np.int32)
-    _lib.check(_lib.lib.gd_density(dv.ptr(pos), pos.numel() // 3, nedges.ctypes.data, dv.ptr(grid),
-                                   dv.ptr(flag), dv.stream_ptr()))
+    if pos.dim() == 3:  # [frames, atoms, 3]: run-length strip walker
+        _lib.check(_lib.lib.gd_density_frames(dv.ptr(pos), int(pos.shape[0]), int(pos.shape[1]),
+                                              nedges.ctypes.data, dv.ptr(grid), dv.ptr(flag), dv.stream_ptr()))
+    else:
+        _lib.check(_lib.lib.gd_density(dv.ptr(pos), pos.numel() // 3, nedges.ctypes.data, dv.ptr(grid),
+                                       dv.ptr(flag), dv.stream_ptr()))
     return grid, flag
 
 

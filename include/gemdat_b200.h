@@ -202,6 +202,16 @@ gd_status_t gd_events_merge_capped(const int32_t *d_src_rows, const int64_t *d_s
                                    const int64_t *d_dst_start, int32_t n_atoms, int32_t *d_dst_rows,
                                    int64_t src_capacity, int64_t dst_capacity, void *stream);
 
+/* All shards' jump tables -> the merged table in ONE launch.  d_gathered: the all-gather of every
+ * shard's buffer, `stride_words` int32 apart; each buffer starts with `head_words` int32 whose
+ * first n_atoms + 1 int64 are the shard's per-atom row offsets, followed by its rows (6 int32
+ * each, src_capacity rows).  The placement (rows of atoms < a, then earlier shards' rows of a) is
+ * derived from the offsets inside the kernel; offsets that would leave a table are skipped like
+ * in gd_events_merge_capped. */
+gd_status_t gd_jumps_merge_shards(const int32_t *d_gathered, int64_t stride_words, int32_t head_words,
+                                  int32_t world, int32_t n_atoms, int64_t src_capacity,
+                                  int32_t *d_dst_rows, int64_t dst_capacity, void *stream);
+
 /* The fill for rows staged by gd_site_states_staged: copies every (frame chunk, atom)
  * segment's rows to their place in the table (same layout and order as gd_events_fill) and
  * adds frame0 to the time column.  d_work / d_changed_global / d_atom_offsets as left by
@@ -558,6 +568,14 @@ gd_status_t gd_msd_direct(const double *d_soa, int64_t n_frames, int32_t n_atoms
  * if any coordinate is outside [0,1) (the reference asserts). */
 gd_status_t gd_density(const double *d_pos_frac, int64_t n_atom_frames, const int32_t *h_nedges,
                        uint32_t *d_grid, int32_t *d_range_flag, void *stream);
+
+/* The same histogram for positions known as [n_frames,n_atoms,3] (the product path).  A lane
+ * follows one atom through consecutive frames and counts runs inside one voxel in registers:
+ * one RED per run instead of one per atom-frame; when the whole grid fits the CTA's shared
+ * memory (<= 48k voxels) the runs go to a CTA-private copy first (shared-memory atomics). */
+gd_status_t gd_density_frames(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                              const int32_t *h_nedges, uint32_t *d_grid, int32_t *d_range_flag,
+                              void *stream);
 
 /* ------------------------------------------------------------------------- *
  * helpers

@@ -156,7 +156,9 @@ def test_density_rejects_out_of_range():
     from gemdat_b200 import Trajectory
 
     pos = np.full((3, 2, 3), 0.5)
-    pos[1, 1, 2] = 1.0
+    # np.mod(-1e-20, 1) == 1.0: the one way a coordinate survives to_positions outside [0, 1)
+    # (a plain 1.0 is wrapped to 0.0 by trajectory.py:126-127 before volume.py:476-477 sees it)
+    pos[1, 1, 2] = -1e-20
     traj = Trajectory(species=['Li'] * 2, coords=pos, lattice=np.eye(3) * 4, time_step=1.0)
     traj.coords_are_displacement = False
     with pytest.raises(AssertionError):
@@ -1211,7 +1213,7 @@ def test_default_radius_route_keeps_the_time_axis_on_the_device(monkeypatch):
     real = dv.to_host
 
     def spy(t):
-        if t.numel() >= 3000:
+        if 3000 in t.shape or t.numel() >= 3000 * 48:  # anything with a frame axis
             big.append(tuple(t.shape))
         return real(t)
 

@@ -5,6 +5,7 @@ Prints CUDA-event times per call; run it plain first, then under
 `ncu --set full -k regex:k_density|k_unwrap|k_msd|k_fill|k_occupancy|k_residence ...`.
 """
 import ctypes as C
+import os
 import sys
 
 sys.path.insert(0, '.')
@@ -26,10 +27,17 @@ s = dv.stream_ptr()
 lat = np.ascontiguousarray(rec.lattice, dtype=np.float64)
 
 
+REPS = int(os.environ.get('PROBE_REPS', '2'))  # 0 under ncu: one launch per kernel
+
+
 def timed(name, fn, unit_bytes=None, reps=2):
+    reps = min(reps, REPS)
     fn()
     torch.cuda.synchronize()
     best = 1e30
+    if reps == 0:
+        print(f'{name}: launched once', flush=True)
+        return 1.0
     for _ in range(reps):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
@@ -55,6 +63,19 @@ timed('K0 unwrap -> cart', lambda: _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, l
 timed('K0 unwrap -> dist', lambda: _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None,
       dv.ptr(work), None, None, dv.ptr(dist), None, dv.ptr(wind), s)), 32)
 del dist
+speed = dv.empty((T, A), torch.float64)
+timed('K0 unwrap -> speed', lambda: _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None,
+      dv.ptr(work), None, None, None, dv.ptr(speed), dv.ptr(wind), s)), 32)
+awork = dv.empty((int(lib.gd_amplitudes_work_bytes(T, A)),), torch.uint8)
+aoff = dv.empty((A + 1,), torch.int64)
+n_amp = C.c_int64(0)
+timed('a4 amplitudes count', lambda: _lib.check(lib.gd_amplitudes_count(dv.ptr(speed), T, A, dv.ptr(awork), dv.ptr(aoff),
+      C.byref(n_amp), s)), 8)
+amp = dv.empty((n_amp.value,), torch.float64)
+timed('a4 amplitudes fill', lambda: _lib.check(lib.gd_amplitudes_fill(dv.ptr(speed), T, A, dv.ptr(awork), dv.ptr(aoff),
+      dv.ptr(amp), s)), 8 + 8 * n_amp.value / (T * A))
+print(f'  amplitudes: {n_amp.value} ({n_amp.value / (T * A):.3f} per atom-frame)', flush=True)
+del speed, amp, awork
 
 # K5
 nedges = grid_edges(Lattice(rec.lattice), 0.1)
