@@ -179,10 +179,9 @@ __device__ __forceinline__ CompactJob compact_job(int64_t item, const int2 *__re
     return j;
 }
 
-// kLanes lanes own one segment at a time and walk the segments grid-stride.  A segment's copy
-// hangs on a chain of three dependent look-ups (skip flag -> chunk offsets -> atom offset)
-// before its first payload load can start, so the NEXT segment's look-ups are issued before the
-// current segment is copied: the chain overlaps the copy instead of preceding it.
+// kLanes lanes own one segment at a time (grid-stride when the grid is capped; then the NEXT
+// segment's look-ups -- skip flag -> chunk offsets -> atom offset, a chain of three dependent
+// loads -- are issued before the current segment is copied).
 __global__ void __launch_bounds__(256)
     k_events_compact(const int2 *__restrict__ stage, int32_t cap, Geometry g,
                      const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
@@ -514,11 +513,13 @@ extern "C" gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_c
     Geometry g = geometry(n_frames, n_atoms);
     const GdDeviceInfo &dev = gd_device_info();
     GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");
-    // persistent-style grid: every lane group walks ~items / groups segments
+    // One segment per lane group by default: measured on C3 (profiles/r2e_step_ab.txt) a capped,
+    // persistent grid with the next segment's look-ups prefetched is SLOWER (8 CTAs/SM: 1.37 ms,
+    // 16: 1.13, uncapped: 1.10) -- the copy wants all the parallelism it can get.
+    // GD_COMPACT_CTAS_PER_SM caps the grid for A/B runs.
     int64_t blocks = gd_ceil_div(g.n_chunks * g.n_atoms * kCompactLanes, 256);
-    int per_sm = 8;
-    if (const char *e = getenv("GD_COMPACT_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
-    if (blocks > (int64_t)dev.sm_count * per_sm) blocks = (int64_t)dev.sm_count * per_sm;
+    if (const char *e = getenv("GD_COMPACT_CTAS_PER_SM"))
+        if (atoi(e) > 0 && blocks > (int64_t)dev.sm_count * atoi(e)) blocks = (int64_t)dev.sm_count * atoi(e);
     k_events_compact<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const int2 *>(d_stage), stage_cap, g, d_work, d_changed_global,
         d_atom_offsets, (int32_t)frame0, reinterpret_cast<int2 *>(d_events),

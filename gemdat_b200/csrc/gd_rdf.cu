@@ -70,15 +70,22 @@ __device__ double sqrt_threshold(double e, bool strict) {
 
 constexpr int kOverGroups = 4;  // groups whose beyond-the-last-edge pairs are counted in registers
 
+// kOneGroup: all targets count in one table row (species RDF): no group look-ups, one register
+// counter.  When the edges are k * resolution (np.arange from 0) the fp32 bin guess is off by at
+// most one and a single comparison with each neighbouring threshold is exact; other edge lists
+// (checked once per CTA) keep the search loops.
+template <bool kOneGroup>
 __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int nb = p.n_edges + 1;
     const int hist_len = p.n_group * nb;
-    double *s_b = reinterpret_cast<double *>(smem);                 // [tile][3]
-    double *s_th = s_b + 3 * (size_t)p.tile;                         // [n_edges + 2] thresholds on d2
-    int32_t *s_atom = reinterpret_cast<int32_t *>(s_th + p.n_edges + 2);  // [tile]
-    int32_t *s_group = s_atom + p.tile;                              // [tile]
-    uint32_t *s_hist = reinterpret_cast<uint32_t *>(s_group + p.tile);   // [kWarps][hist_len]
+    // targets of the tile, structure of arrays (conflict-free 8-byte reads, no index arithmetic)
+    double *s_x = reinterpret_cast<double *>(smem);                  // [tile]
+    double *s_y = s_x + p.tile;
+    double *s_z = s_y + p.tile;
+    double *s_th = s_z + p.tile;                                     // [n_edges + 2] thresholds on d2
+    int32_t *s_ag = reinterpret_cast<int32_t *>(s_th + p.n_edges + 2);   // [tile] atom | group << 24
+    uint32_t *s_hist = reinterpret_cast<uint32_t *>(s_ag + p.tile);  // [kWarps][hist_len]
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float inv_res = (float)p.inv_res;
@@ -98,9 +105,15 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
         s_th[k] = th;
     }
     for (int k = threadIdx.x; k < kWarps * hist_len; k += blockDim.x) s_hist[k] = 0;
+    __shared__ int s_irregular;
+    if (threadIdx.x == 0) s_irregular = 0;
     __syncthreads();
+    for (int k = threadIdx.x; k < p.n_edges; k += blockDim.x)
+        if (!(fabs(p.edges[k] * p.inv_res - (double)k) <= 1e-6)) s_irregular = 1;
+    __syncthreads();
+    const bool uniform = s_irregular == 0;
     const double th_over = s_th[p.n_edges];  // at or above: beyond the last edge
-    const bool reg_over = p.n_group <= kOverGroups;
+    const bool reg_over = kOneGroup || p.n_group <= kOverGroups;
 
     for (int64_t t = blockIdx.x; t < p.n_frames; t += gridDim.x) {
         const double *frame = p.pos + t * (int64_t)p.n_atoms * 3;
@@ -109,44 +122,60 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
             __syncthreads();
             for (int k = threadIdx.x; k < nt; k += blockDim.x) {
                 const int32_t atom = p.idx2[j0 + k];
-                s_atom[k] = atom;
-                s_group[k] = p.group ? p.group[j0 + k] : 0;
+                const int32_t grp = (!kOneGroup && p.group) ? p.group[j0 + k] : 0;
+                s_ag[k] = atom | (grp << 24);
                 const double *q = frame + 3 * (int64_t)atom;
-                gd_pbc_cart(p.pbc, q[0], q[1], q[2], s_b + 3 * k);
+                double c[3];
+                gd_pbc_cart(p.pbc, q[0], q[1], q[2], c);
+                s_x[k] = c[0];
+                s_y[k] = c[1];
+                s_z[k] = c[2];
             }
             __syncthreads();
             for (int i = blockIdx.y * kWarps + warp; i < p.n1; i += gridDim.y * kWarps) {
-                const int32_t c = p.cls ? p.cls[t * p.n1 + i] : 0;
-                if (c < 0) continue;
-                const int32_t atom_i = p.idx1[i];
-                const double *q = frame + 3 * (int64_t)atom_i;
+                const int32_t cls = p.cls ? p.cls[t * p.n1 + i] : 0;
+                if (cls < 0) continue;
+                // a pair of an atom with itself is recognised by the atom index; -1 never matches
+                const int32_t self = p.skip_same ? p.idx1[i] : -1;
+                const double *q = frame + 3 * (int64_t)p.idx1[i];
                 double a[3];
                 gd_pbc_cart(p.pbc, q[0], q[1], q[2], a);
                 // pairs beyond the last edge are the bulk (the cell is much larger than max_dist):
                 // they are counted in registers, per group, and added once per (source, tile)
                 uint32_t over[kOverGroups] = {0, 0, 0, 0};
-                for (int k = lane; k < nt; k += 32) {
-                    if (p.skip_same && s_atom[k] == atom_i) continue;
-                    const double b[3] = {s_b[3 * k], s_b[3 * k + 1], s_b[3 * k + 2]};
+                auto pair = [&](int k) {
+                    const int32_t ag = s_ag[k];
+                    const double b[3] = {s_x[k], s_y[k], s_z[k]};
                     const double d2 = gd_pbc_d2(p.pbc, a, b);
-                    const int grp = s_group[k];
+                    if ((ag & 0xFFFFFF) == self) return;
+                    const int grp = kOneGroup ? 0 : ag >> 24;
                     if (d2 >= th_over && reg_over) {
+                        if (kOneGroup) {
+                            ++over[0];
+                        } else {
 #pragma unroll
-                        for (int u = 0; u < kOverGroups; ++u) over[u] += (grp == u);
-                        continue;
+                            for (int u = 0; u < kOverGroups; ++u) over[u] += (grp == u);
+                        }
+                        return;
                     }
-                    // fp32 guess of the bin, off by at most one: corrected against the exact
-                    // thresholds of the two neighbouring edges
+                    // fp32 guess of the bin, corrected against the exact thresholds
                     int g = min((int)(sqrtf((float)d2) * inv_res), p.n_edges);
                     g += (int)(s_th[g + 1] <= d2) - (int)!(s_th[g] <= d2);
-                    // (not taken for uniform edges; arbitrary edge lists stay exact, NaNs end at 0)
-                    while (g > 0 && !(s_th[g] <= d2)) --g;
-                    while (g < p.n_edges && s_th[g + 1] <= d2) ++g;
+                    if (!uniform) {  // (NaNs end at 0)
+                        while (g > 0 && !(s_th[g] <= d2)) --g;
+                        while (g < p.n_edges && s_th[g + 1] <= d2) ++g;
+                    }
                     atomicAdd(&my_hist[grp * nb + g], 1u);
+                };
+                int k = lane;
+                for (; k + 32 < nt; k += 64) {  // two pairs per trip: half the loop overhead
+                    pair(k);
+                    pair(k + 32);
                 }
+                if (k < nt) pair(k);
                 if (reg_over) {
 #pragma unroll
-                    for (int u = 0; u < kOverGroups; ++u) {
+                    for (int u = 0; u < (kOneGroup ? 1 : kOverGroups); ++u) {
                         uint32_t v = over[u];
 #pragma unroll
                         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -154,12 +183,12 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                     }
                 }
                 __syncwarp();
-                unsigned long long *dst = p.hist + (size_t)c * hist_len;
-                for (int k = lane; k < hist_len; k += 32) {
-                    const uint32_t n = my_hist[k];
+                unsigned long long *dst = p.hist + (size_t)cls * hist_len;
+                for (int k2 = lane; k2 < hist_len; k2 += 32) {
+                    const uint32_t n = my_hist[k2];
                     if (n) {
-                        atomicAdd(dst + k, (unsigned long long)n);
-                        my_hist[k] = 0;
+                        atomicAdd(dst + k2, (unsigned long long)n);
+                        my_hist[k2] = 0;
                     }
                 }
                 __syncwarp();
@@ -212,6 +241,8 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
                                    const int32_t *d_group, int32_t n2, int32_t n_group,
                                    const double *d_edges, int32_t n_edges, double resolution, int32_t mode,
                                    int32_t skip_same_atom, unsigned long long *d_hist, void *stream) {
+    GD_REQUIRE(n_atoms < (1 << 24) && n_group < 128, GD_ERR_INVALID,
+               "gd_rdf_hist: at most 2^24 atoms and 127 groups");
     GD_REQUIRE(n_frames >= 0 && n_atoms > 0 && n1 >= 0 && n2 >= 0 && n_class > 0 && n_group > 0 && n_edges >= 2 &&
                    (mode == 0 || mode == 1) && resolution > 0.0,
                GD_ERR_INVALID, "gd_rdf_hist: bad argument");
@@ -247,7 +278,6 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
     if (tile > 4096) tile = 4096;
     p.tile = (int32_t)tile;
     const size_t smem = (size_t)p.tile * 32 + fixed;
-    GD_CUDA_CHECK(cudaFuncSetAttribute(k_rdf_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int sms = dev.sm_count > 0 ? dev.sm_count : 148;
     int64_t gy = gd_ceil_div((int64_t)sms * 4, n_frames);
     const int64_t gy_max = gd_ceil_div(n1, kWarps);
@@ -255,7 +285,15 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
     if (gy < 1) gy = 1;
     int64_t gx = n_frames < (int64_t)sms * 64 ? n_frames : (int64_t)sms * 64;
     dim3 grid((unsigned)gx, (unsigned)gy);
-    k_rdf_hist<<<grid, kWarps * 32, smem, (cudaStream_t)stream>>>(p);
+    const bool one_group = n_group == 1;
+    auto launch = [&](auto kernel) -> gd_status_t {
+        GD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kernel<<<grid, kWarps * 32, smem, (cudaStream_t)stream>>>(p);
+        return GD_OK;
+    };
+    gd_status_t rc;
+    rc = one_group ? launch(k_rdf_hist<true>) : launch(k_rdf_hist<false>);
+    if (rc != GD_OK) return rc;
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

@@ -46,7 +46,7 @@ namespace {
 constexpr uint32_t kMagic = 0x47534447u;  // "GDSG"
 constexpr uint32_t kBlobVersion = 4;
 constexpr int kMaxGroups = 64;
-// tuning knobs (scratch/k1_variants.sh builds A/B libraries with -D overrides)
+// tuning knobs (tools/k1_variants.sh builds A/B libraries with -D overrides)
 #ifndef GD_K1_WARPS
 #define GD_K1_WARPS 4
 #endif
@@ -1049,7 +1049,7 @@ extern "C" gd_status_t gd_site_states_staged(const double *d_pos_frac, int64_t n
 
     const size_t vis_bytes = 2 * (size_t)h->n_sites_total;
     p.vis_mode = d_visited == nullptr ? 0 : (vis_bytes <= (size_t)kVisSmemMax ? 1 : 2);
-#ifdef GD_K1_PROBE_NO_VIS  // scratch/k1_variants.sh: upper bound of what the visited marks cost
+#ifdef GD_K1_PROBE_NO_VIS  // tools/k1_variants.sh: upper bound of what the visited marks cost
     p.vis_mode = 0;
 #endif
     p.g0 = *reinterpret_cast<const GdGroupRec *>(static_cast<const unsigned char *>(h_blob) + h->off_groups);

@@ -1,5 +1,5 @@
 """Times gd_site_states alone (CUDA events) on a C3 window for tuning knobs given in the env.
-usage: python scratch/k1_sweep.py [frames]   (GD_GRID_K / GD_K1_SPG are read by the library)"""
+usage: python tools/k1_sweep.py [frames]   (GD_GRID_K / GD_K1_SPG are read by the library)"""
 import json, os, sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))

@@ -1,6 +1,6 @@
 #!/bin/bash
 # Builds A/B variants of libgemdat_b200.so that differ only in tuning knobs (-D overrides).
-# usage: bash scratch/k1_variants.sh   -> gemdat_b200/csrc/_variants/lib_<name>.so
+# usage: bash tools/k1_variants.sh   -> gemdat_b200/csrc/_variants/lib_<name>.so
 set -euo pipefail
 cd "$(dirname "$0")/../gemdat_b200/csrc"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
