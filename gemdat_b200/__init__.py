@@ -1,9 +1,11 @@
 """gemdat_b200 -- B200-native implementation of GEMDAT's data-parallel hot path.
 
 Site assignment -> transition events -> jumps, the displacement / MSD path and the
-density histogram, behind GEMDAT's own Python API.  All arithmetic runs in
-hand-written sm_100a CUDA kernels (``csrc/``, C ABI in ``include/gemdat_b200.h``);
-there is no CPU fallback.
+density histogram, behind GEMDAT's own Python API.  Everything O(frames x atoms) on
+the path runs in hand-written sm_100a CUDA kernels (``csrc/``, C ABI in
+``include/gemdat_b200.h``); library code appears only on secondary paths (CUB sort / scan
+in the collective-jump search, cuFFT in ``attempt_frequency``).
+There is no CPU fallback.
 """
 
 from __future__ import annotations

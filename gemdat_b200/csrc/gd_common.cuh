@@ -128,6 +128,12 @@ __device__ __forceinline__ void gd_tma_load_1d(void *smem_dst, const void *gmem_
         : "memory");
 }
 
+// 1-D bulk prefetch global -> L2 (no destination, no completion to wait for): src 16-byte
+// aligned, bytes a multiple of 16.  SASS: UBLKPF.
+__device__ __forceinline__ void gd_prefetch_l2(const void *gmem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
+
 // 1-D TMA bulk copy shared -> global (bulk async-group completion).
 __device__ __forceinline__ void gd_tma_store_1d(void *gmem_dst, const void *smem_src,
                                                 uint32_t bytes) {

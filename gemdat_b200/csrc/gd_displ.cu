@@ -231,6 +231,7 @@ struct FusedGeom {
     int32_t n_atoms;
     int32_t n_strips;
     int64_t n_tchunks;  // tiles along the frame axis
+    int32_t prefetch;   // rows are 16-byte aligned: bulk L2 prefetch of the tile
 };
 
 __device__ __forceinline__ uint32_t st_pack(int32_t v, uint32_t state) {
@@ -260,6 +261,14 @@ __global__ void __launch_bounds__(kTileWarps * 32)
     const int64_t t0 = tc * kTileF + (int64_t)warp * kTileWarpF;
     const int64_t t1 = min(g.n_frames, t0 + kTileWarpF);
 
+    // The tile's rows are asked for at once (bulk prefetch into L2, one row per thread), so the
+    // bytes in flight from HBM are the whole tile and not what a lane's registers can hold; the
+    // loads of pass 1 then mostly find their rows in L2.
+    if (g.prefetch) {
+        const int64_t t = tc * kTileF + threadIdx.x;
+        const int r = min(32, g.n_atoms - strip * 32);
+        if (t < g.n_frames) gd_prefetch_l2(pos + t * A3 + (int64_t)strip * 96, (uint32_t)(r * 24));
+    }
     // previous position of this warp's first frame
     double px = 0.0, py = 0.0, pz = 0.0;
     bool first_is_zero = false;  // global frame 0 without a halo row: d[0] = 0
@@ -469,6 +478,7 @@ FusedGeom fused_geometry(int64_t n_frames, int32_t n_atoms) {
     g.n_atoms = n_atoms;
     g.n_strips = (n_atoms + 31) / 32;
     g.n_tchunks = gd_ceil_div(n_frames, kTileF);
+    g.prefetch = 0;
     return g;
 }
 // int32 words of d_work the fused kernel needs: ticket (padded) + 96 status words per tile
@@ -538,16 +548,21 @@ extern "C" gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int
     const bool fused = !(env && atoi(env) == 0) && (d_cum_frac || d_cum_cart || d_dist || d_speed) &&
                        n_frames < ((int64_t)1 << 29);
     if (fused) {
-        const FusedGeom fg = fused_geometry(n_frames, n_atoms);
+        FusedGeom fg = fused_geometry(n_frames, n_atoms);
+        // GD_UNWRAP_PREFETCH=0 switches the L2 prefetch off (A/B)
+        const char *pf = getenv("GD_UNWRAP_PREFETCH");
+        fg.prefetch = (n_atoms % 2 == 0) && (reinterpret_cast<uintptr_t>(d_pos_frac) & 15) == 0 &&
+                      !(pf && atoi(pf) == 0);
         const int64_t tiles = fg.n_tchunks * fg.n_strips;
         GD_REQUIRE(tiles < ((int64_t)1 << 31), GD_ERR_INVALID, "gd_unwrap: too many tiles");
         uint32_t *words = reinterpret_cast<uint32_t *>(d_work);
         GD_CUDA_CHECK(cudaMemsetAsync(words, 0, (size_t)fused_work_words(fg) * 4, st));
         const Mat9 L = make_mat(h_lattice);
         // resident tiles must stay in L2 between the two passes (96 KB each): the dynamic
-        // shared memory request only caps the CTAs per SM (GD_UNWRAP_CTAS_PER_SM, default 4:
-        // 148 x 4 x 96 KB = 57 MB of the 126 MB L2)
-        int per_sm = 4;
+        // shared memory request only caps the CTAs per SM (GD_UNWRAP_CTAS_PER_SM, default 5:
+        // 148 x 5 x 96 KB = 71 MB of the 126 MB L2; measured 3 / 4 / 5 / 6 / 8 per SM: 3749 /
+        // 5026 / 5301 / 4745 / 4365 GB/s, profiles/r2h_k0_sweep.txt)
+        int per_sm = 5;
         if (const char *e = getenv("GD_UNWRAP_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
         const GdDeviceInfo &dev = gd_device_info();
         GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");

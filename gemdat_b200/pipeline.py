@@ -216,6 +216,23 @@ class HotPath:
     def _all_gather(self, t: torch.Tensor) -> torch.Tensor:
         return self.comm.all_gather(t)
 
+    def _pinned(self, name: str, n_bytes: int) -> torch.Tensor:
+        """Persistent page-locked host buffer (its address is baked into the captured graph)."""
+        t = self._buf.get(name)
+        if t is None or t.numel() != n_bytes:
+            t = torch.empty((n_bytes,), dtype=torch.uint8, pin_memory=True)
+            self._buf[name] = t
+        return t
+
+    def _needs_remap(self, visited_bytes: np.ndarray) -> bool:
+        """integer_remap quirk (Q2) needed for these visited flags?  The flags rarely change from
+        one pass to the next, so the answer is remembered per flag pattern."""
+        key = visited_bytes.tobytes()
+        if getattr(self, '_remap_key', None) != key:
+            vis = np.frombuffer(key, dtype=np.uint8).astype(bool).reshape(2, self.n_sites)
+            self._remap_key, self._remap_needed = key, any(self.grid.remap_lut(v) is not None for v in vis)
+        return self._remap_needed
+
     def _mark(self, name: str) -> None:
         if not self.profile_phases:
             return
@@ -474,9 +491,16 @@ class HotPath:
             _lib.check(lib.gd_jumps_merge_shards(dv.ptr(allb), int(allb.shape[1]), head, W, n_atoms, jcap,
                                                  dv.ptr(merged), W * jcap, s))
             launches += 1
+        # everything the host decides on -- every rank's offsets + status words, and the OR-ed flag
+        # buffer -- leaves in ONE copy into a persistent pinned buffer (part of the graph)
+        tail = torch.cat([heads.reshape(-1).view(torch.uint8), k1.pack])
+        host_tail = self._pinned('host_tail', tail.numel())
+        host_tail.copy_(tail, non_blocking=True)
+        launches += 1
         from types import SimpleNamespace
         return SimpleNamespace(k1=k1, offsets=offsets, rows=rows, jbuf=jbuf, jumps=jumps, allb=allb, heads=heads,
-                               head=head, jcap=jcap, launches=launches, merged=merged)
+                               head=head, jcap=jcap, launches=launches, merged=merged, host_tail=host_tail,
+                               n_head_bytes=int(heads.numel()) * 8)
 
     def _run_optimistic(self, pos: torch.Tensor):
         """Optimistic pass = `_enqueue_optimistic` (eagerly the first time, then replayed as ONE
@@ -510,8 +534,10 @@ class HotPath:
         s = dv.stream_ptr()
         k1, offsets, rows, jumps, allb, head, jcap = st.k1, st.offsets, st.rows, st.jumps, st.allb, st.head, st.jcap
         n_atoms, launches = k1.n_atoms, st.launches
-        all_off = dv.to_host(st.heads)  # <- the one synchronisation
-        host = dv.to_host(k1.pack)
+        torch.cuda.current_stream().synchronize()  # <- the one synchronisation
+        raw = st.host_tail.numpy()
+        all_off = raw[: st.n_head_bytes].view(np.int64).reshape(W, n_atoms + 3)
+        host = raw[st.n_head_bytes:]
         self._mark('k3_jumps')
         status, k2_err = all_off[:, n_atoms + 1], all_off[:, n_atoms + 2]
         n_jumps_rank = all_off[:, n_atoms]
@@ -528,7 +554,7 @@ class HotPath:
             why = 'event staging overflow'
         elif not host[k1.o_chg: k1.o_chg + n_atoms].any():
             why = 'no outer state change'
-        elif any(self.grid.remap_lut(v) is not None for v in vis):
+        elif self._needs_remap(host[: k1.n_vis]):
             why = 'Q2 remap'
         self.last_optimistic_reject = why
         if why is not None:

@@ -46,8 +46,10 @@ ms = best(run)
 ref = cart.clone()
 print(f'three-pass: {ms:.3f} ms  {48 * T * A / ms / 1e6:.0f} GB/s (48 B/atom-frame)', flush=True)
 os.environ['GD_UNWRAP_FUSED'] = '1'
-for per_sm in (2, 3, 4, 5, 6, 8, 12):
-    os.environ['GD_UNWRAP_CTAS_PER_SM'] = str(per_sm)
-    ms = best(run)
-    print(f'fused, {per_sm} CTAs/SM: {ms:.3f} ms  {48 * T * A / ms / 1e6:.0f} GB/s  equal={bool(torch.equal(cart, ref))}',
-          flush=True)
+for prefetch in ('0', '1'):
+    os.environ['GD_UNWRAP_PREFETCH'] = prefetch
+    for per_sm in (3, 4, 5, 6, 8, 12):
+        os.environ['GD_UNWRAP_CTAS_PER_SM'] = str(per_sm)
+        ms = best(run)
+        print(f'fused, L2 prefetch {prefetch}, {per_sm} CTAs/SM: {ms:.3f} ms  {48 * T * A / ms / 1e6:.0f} GB/s  '
+              f'equal={bool(torch.equal(cart, ref))}', flush=True)
