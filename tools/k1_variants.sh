@@ -1,18 +1,23 @@
 #!/bin/bash
-# Builds A/B variants of libgemdat_b200.so that differ only in tuning knobs (-D overrides).
+# Builds A/B variants of libgemdat_b200.so that differ only in tuning knobs (-D overrides) or in
+# the source of one translation unit.
 # usage: bash tools/k1_variants.sh   -> gemdat_b200/csrc/_variants/lib_<name>.so
 set -euo pipefail
 cd "$(dirname "$0")/../gemdat_b200/csrc"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
-FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 --fmad=false -Xcompiler -fPIC,-ffp-contract=off)
+FLAGS=(-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 --fmad=false -Xcompiler -fPIC,-ffp-contract=off -I.)
 mkdir -p _variants
-build() { # name, source stem (gd_states | gd_events | gd_jumps), defines...
-  local name=$1 stem=$2; shift 2
-  "$NVCC" "${FLAGS[@]}" "$@" -Xptxas -v -c $stem.cu -o _variants/${stem}_$name.o > _variants/$name.log 2>&1
-  objs=$(ls _build/gd_*.o | grep -v $stem.o)
+rm -f _variants/lib_*.so
+build() { # name, source file, source stem it replaces (gd_states | gd_events | gd_jumps), defines...
+  local name=$1 src=$2 stem=$3; shift 3
+  "$NVCC" "${FLAGS[@]}" "$@" -Xptxas -v -c $src -o _variants/${stem}_$name.o > _variants/$name.log 2>&1
+  objs=$(ls _build/gd_*.o | grep -v "/$stem.o")
   "$NVCC" -shared -o _variants/lib_$name.so _variants/${stem}_$name.o $objs -lcudart
-  echo "$name built"
+  echo "$name built: $(grep -A1 'k_site_statesILb1ELb1ELb1ELb1' _variants/$name.log | grep -o 'Used [0-9]* registers' | head -1)"
 }
-build base gd_states &
-build novis gd_states -DGD_K1_PROBE_NO_VIS=1 &
+git show HEAD:gemdat_b200/csrc/gd_states.cu > _variants/gd_states_head.cu
+build head _variants/gd_states_head.cu gd_states &
+build new6 gd_states.cu gd_states &
+build new7 gd_states.cu gd_states -DGD_K1_MIN_CTAS=7 &
+build head7 _variants/gd_states_head.cu gd_states -DGD_K1_MIN_CTAS=7 &
 wait

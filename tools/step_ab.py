@@ -43,6 +43,6 @@ def phases(label):
           '  '.join(f'{k} {v:.3f}' for k, v in acc.items()), flush=True)
 
 
-for per_sm in ('4', '8', '16', '32', '100000'):
+for per_sm in (os.environ.get("GD_COMPACT_CTAS_PER_SM", "100000"),):
     os.environ['GD_COMPACT_CTAS_PER_SM'] = per_sm
     phases(f'compact CTAs/SM {per_sm}')
