@@ -665,7 +665,8 @@ def run_ours(args):
         b.record()
         barrier()
         first_ms.append(max_over_ranks(a.elapsed_time(b)))
-        assert hp1.last_pass == 'checked' and r1['n_jumps'] == res['n_jumps']
+        assert r1['n_jumps'] == res['n_jumps']
+        first_pass = hp1.last_pass
         del hp1, r1
     first_call_ms = float(np.median(first_ms))
 
@@ -729,8 +730,10 @@ def run_ours(args):
             'clocks': sampler.summary(),
             'results': {'n_events': int(res['n_events']), 'n_jumps': int(res['n_jumps'])},
             'first_call': {'ms': first_call_ms, 'value': n_af_total / (first_call_ms * 1e-3), 'unit': UNIT,
-                           'what': 'checked pass of a fresh HotPath (no remembered table sizes, no CUDA graph), '
-                                   'median of 3, CUDA events, max over ranks'},
+                           'pass': first_pass,
+                           'what': 'first call of a fresh HotPath (no remembered table sizes, no CUDA graph): the '
+                                   'one-synchronisation pass with upper-bound table sizes, or the checked pass if '
+                                   'that was rejected; median of 3, CUDA events, max over ranks'},
             'sustained': sustained,
         }
 

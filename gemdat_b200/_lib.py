@@ -131,6 +131,7 @@ SIGNATURES = {
     'gd_amplitudes_fill': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p]),
     'gd_mean_std_work_bytes': (_i64, []),
     'gd_mean_std': (C.c_int, [_p, _i64, _p, C.POINTER(C.c_double), C.POINTER(C.c_double), _p]),
+    'gd_meanfreq': (C.c_int, [_p, _i64, _i32, C.c_double, _p, _p]),
     'gd_transpose_f64': (C.c_int, [_p, _i64, _i64, _p, _p]),
     'gd_wrap_unit': (C.c_int, [_p, _p, _i64, _p, _p]),
     'gd_transpose_soa': (C.c_int, [_p, _i64, _i32, _p, _p]),

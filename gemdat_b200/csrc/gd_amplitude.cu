@@ -231,7 +231,47 @@ __global__ void __launch_bounds__(kRedThreads)
     }
 }
 
+// ---------------------------------------------------------------- spectral moments (N2)
+//
+// meanfreq of utils.py:128-160 from the one-sided spectrum X[atom, k] (k = 0 .. n/2, complex128,
+// one row per atom -- the layout a batched real-to-complex transform leaves): with
+// P_k = w_k |X_k|^2 (w = 2 except for DC and, for even n, Nyquist: scipy.signal.periodogram's
+// one-sided scaling) the mean frequency is sum_k f_k P_k / sum_k P_k, f_k = k fs / n -- the
+// common factors 1/(fs n) and (f_1 - f_0) of the reference cancel in the ratio.  The DC bin is
+// skipped: after the constant detrend of the periodogram it holds |sum(x - mean)|^2, rounding
+// noise.  One pass over the spectrum, one CTA per atom, fixed-order reduction (deterministic).
+__global__ void __launch_bounds__(kRedThreads)
+    k_spec_meanfreq(const double2 *__restrict__ spec, int64_t n_bins, int64_t n, double scale,
+                    double *__restrict__ out) {
+    const double2 *row = spec + (int64_t)blockIdx.x * n_bins;
+    double m0 = 0.0, m1 = 0.0;
+    for (int64_t k = 1 + threadIdx.x; k < n_bins; k += kRedThreads) {
+        const double2 x = row[k];
+        const double w = (2 * k == n) ? 1.0 : 2.0;
+        const double pwr = w * fma(x.x, x.x, x.y * x.y);
+        m0 += pwr;
+        m1 = fma((double)k, pwr, m1);
+    }
+    m0 = block_sum(m0);
+    m1 = block_sum(m1);
+    if (threadIdx.x == 0) out[blockIdx.x] = (m1 / m0) * scale;
+}
+
 }  // namespace
+
+extern "C" gd_status_t gd_meanfreq(const double *d_spectrum, int64_t n_samples, int32_t n_atoms,
+                                   double sampling_frequency, double *d_meanfreq, void *stream) {
+    GD_REQUIRE(d_spectrum && d_meanfreq && n_samples > 0 && n_atoms > 0, GD_ERR_INVALID,
+               "gd_meanfreq: bad argument");
+    GD_REQUIRE((reinterpret_cast<uintptr_t>(d_spectrum) & 15) == 0, GD_ERR_ALIGNMENT,
+               "gd_meanfreq: the spectrum must be 16-byte aligned");
+    const int64_t n_bins = n_samples / 2 + 1;
+    k_spec_meanfreq<<<(unsigned)n_atoms, kRedThreads, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const double2 *>(d_spectrum), n_bins, n_samples,
+        sampling_frequency / (double)n_samples, d_meanfreq);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
 
 extern "C" int64_t gd_amplitudes_work_bytes(int64_t n_frames, int32_t n_atoms) {
     if (n_frames <= 0 || n_atoms <= 0) return 64;

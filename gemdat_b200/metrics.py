@@ -9,7 +9,7 @@ sign flips and sum the pieces, ``gd_mean_std`` reduces them -- ``vibration_ampli
 ``attempt_frequency`` (:167-188) runs on the same device array: the per-atom
 spectrum comes from cuFFT through ``torch.fft`` (a library transform, not one of this
 package's kernels), the periodogram weighting and the mean-frequency reductions of
-``utils.py:128-160`` follow it on the device.  Conductivity, Haven ratio and the Arrhenius
+``utils.py:128-160`` are one pass of ``gd_meanfreq`` over it.  Conductivity, Haven ratio and the Arrhenius
 helpers are out of scope.
 """
 
@@ -67,27 +67,24 @@ class TrajectoryMetrics:
     def _meanfreq(self) -> np.ndarray:
         """utils.py:128-160 on the device: mean frequency of every atom's speed, [A, 1].
 
-        ``scipy.signal.periodogram`` defaults restated: constant detrend, boxcar window,
-        density scaling 1/(fs N), one-sided spectrum with every bin but DC (and Nyquist for
-        even N) doubled; ``mnfreq = sum(P f) / sum(P)`` with ``P = Pxx (f[1] - f[0])``.
+        ``scipy.signal.periodogram`` defaults restated: constant detrend, boxcar window, one-sided
+        spectrum with every bin but DC (and Nyquist for even N) doubled; ``mnfreq = sum(P f) /
+        sum(P)``.  The transform is cuFFT (``torch.fft.rfft`` of one row per atom, a library
+        call); everything after it -- weighting, both sums, the ratio -- is one
+        pass of ``gd_meanfreq`` over the spectrum.  A constant offset only lands in the DC bin,
+        which the kernel skips, so no detrended copy of the array is made.
         """
-        speed = self._speed_tm()  # [T, A]
-        n = int(speed.shape[0])
-        fs = float(self.trajectory.sampling_frequency)
-        x = speed - speed.mean(dim=0, keepdim=True)
-        spec = torch.fft.rfft(x, dim=0)
-        del x
-        pxx = (spec.real * spec.real + spec.imag * spec.imag) * (1.0 / (fs * n))
-        del spec
-        if n % 2 == 0:
-            pxx[1:-1] *= 2.0
-        else:
-            pxx[1:] *= 2.0
-        f = torch.fft.rfftfreq(n, d=1.0 / fs, dtype=torch.float64, device=pxx.device)
-        width = (f[1] - f[0]) if n > 1 else f.new_tensor(float('nan'))
-        p = pxx * width
-        mnfreq = (f.reshape(1, -1) @ p) / p.sum(dim=0, keepdim=True)
-        return dv.to_host(mnfreq.reshape(-1, 1))
+        tm = self._speed_tm()  # [T, A]
+        n, n_atoms = int(tm.shape[0]), int(tm.shape[1])
+        lib, s = _lib.lib, dv.stream_ptr()
+        rows = dv.empty((n_atoms, n), torch.float64)  # one row per atom: what the batched FFT wants
+        _lib.check(lib.gd_transpose_f64(dv.ptr(tm), n, n_atoms, dv.ptr(rows), s))
+        spec = torch.fft.rfft(rows, dim=1)  # [A, n // 2 + 1] complex128
+        del rows
+        out = dv.empty((n_atoms,), torch.float64)
+        _lib.check(lib.gd_meanfreq(dv.ptr(spec), n, n_atoms, float(self.trajectory.sampling_frequency),
+                                   dv.ptr(out), s))
+        return dv.to_host(out).reshape(-1, 1)
 
     @weak_lru_cache()
     def attempt_frequency(self) -> tuple[FloatWithUnit, FloatWithUnit]:

@@ -185,6 +185,9 @@ class HotPath:
         self._cap_events = 0  # event rows of this rank's table, remembered for the optimistic pass
         # GD_OPTIMISTIC=0: always the checked pass (A/B)
         self.optimistic = os.environ.get('GD_OPTIMISTIC', '1') not in ('', '0')
+        # GD_FIRST_CALL_BOUND=0: the first call takes the checked pass (A/B)
+        self.first_call_bound = os.environ.get('GD_FIRST_CALL_BOUND', '1') not in ('', '0')
+        self._caps_are_bounds = False
         self.last_pass = 'none'
         self.last_optimistic_reject = None
         # GD_GRAPH=0: launch the optimistic pass kernel by kernel instead of replaying a CUDA graph
@@ -316,10 +319,25 @@ class HotPath:
         if next_pos_row is not None and self.rank + 1 < self.world:
             self._next_row = next_pos_row.contiguous()
         self._own_halo = next_pos_row is not None or self.world == 1
+        if (self.optimistic and self.stage_events and self._cap_events == 0 and self.first_call_bound
+                and not self.k3_exchange):
+            # very first call: no table sizes are known yet.  Instead of the checked pass (a host
+            # synchronisation for every count) the one-synchronisation pass runs with UPPER BOUNDS:
+            # the event table gets as many rows as K1's staging area can hold (more would set the
+            # overflow flag anyway), the jump table a generous guess that the status word checks.
+            n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+            cap = (int(os.environ.get('GD_EVENTS_STAGE_CAP', '0'))
+                   or int(_lib.lib.gd_events_stage_cap(n_frames, n_atoms)))  # as in _launch_k1
+            self._cap_events = int(_lib.lib.gd_events_stage_elems(n_frames, n_atoms, cap)) // 6
+            # (frame-sharded, the jump rows of all ranks travel in the final all-gather: keep it small)
+            self._jump_cap = max(65536, 64 * n_atoms) if self.world > 1 else max(1 << 20, 64 * n_atoms)
+            self._caps_are_bounds = True
         if self.optimistic and self._cap_events > 0:
             res = self._run_optimistic(pos)
             if res is not None:
                 return res
+            if self._caps_are_bounds:  # e.g. more jumps than guessed: size everything exactly
+                self._cap_events, self._jump_cap, self._caps_are_bounds = 0, 0, False
         return self._run_checked(pos)
 
     def _run_checked(self, pos: torch.Tensor) -> dict:
@@ -569,8 +587,14 @@ class HotPath:
         else:
             jumps_out = jumps[: int(n_jumps_rank[0])]
         self._mark('k3_merge')
-        self._cap_events = max(self._cap_events, n_local + n_local // 8 + 1024)
         most = int(n_jumps_rank.max())
+        if self._caps_are_bounds:
+            # sizes are known now: the next pass uses tables that fit (and becomes the graph); the
+            # bound-sized tables of this pass live on only as long as the caller keeps its result
+            self._cap_events, self._jump_cap, self._caps_are_bounds = 0, 0, False
+            for name in ('rows_cap', 'jwork', 'jbuf_opt', 'jmerged'):
+                self._buf.pop(name, None)
+        self._cap_events = max(self._cap_events, n_local + n_local // 8 + 1024)
         self._jump_cap = max(self._jump_cap, most + most // 4 + 16)
         self.last_n_local_events = n_local
         self.last_events_route = 'staged'

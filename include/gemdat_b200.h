@@ -536,6 +536,21 @@ gd_status_t gd_mean_std(const double *d_x, int64_t n, void *d_work, double *h_me
                         void *stream);
 
 /* ------------------------------------------------------------------------- *
+ * N2  attempt frequency: mean frequency of every atom's speed
+ * replaces: meanfreq, src/gemdat/utils.py:128-160 (the weighting of
+ *           scipy.signal.periodogram's one-sided spectrum and the np.dot / np.sum
+ *           reductions), called from TrajectoryMetrics.attempt_frequency, metrics.py:167-188
+ * ------------------------------------------------------------------------- */
+
+/* d_spectrum [n_atoms, n_samples/2 + 1] complex128 (interleaved re, im): the one-sided DFT of
+ * every atom's speed row (the transform itself is the caller's: cuFFT; gd_transpose_f64 turns
+ * the time-major speed array of gd_unwrap into rows per atom).  d_meanfreq [n_atoms] =
+ * sum_k f_k P_k / sum_k P_k in Hz with P_k = |X_k|^2, doubled except at DC and Nyquist,
+ * f_k = k * sampling_frequency / n_samples; the DC bin is skipped (constant detrend). */
+gd_status_t gd_meanfreq(const double *d_spectrum, int64_t n_samples, int32_t n_atoms,
+                        double sampling_frequency, double *d_meanfreq, void *stream);
+
+/* ------------------------------------------------------------------------- *
  * K4  all-lag mean squared displacement
  * replaces: Trajectory.mean_squared_displacement, src/gemdat/trajectory.py:896-933
  *           (numpy FFT autocorrelation); computed here by direct summation.

@@ -811,10 +811,21 @@ def test_hotpath_optimistic_pass_equals_checked_pass(monkeypatch):
                  site_inner_fraction=0.5, minimal_residence=3, n_frames_total=6000)
     with warnings.catch_warnings():
         warnings.simplefilter('ignore')
-        first = hp.run(pos)
-        assert hp.last_pass == 'checked'
-        ref = {k: first[k].cpu().numpy().copy() for k in ('outer', 'inner', 'events', 'jumps')}
+        # reference tables from the checked pass (every count read back where it is needed)
+        monkeypatch.setenv('GD_FIRST_CALL_BOUND', '0')
+        hp0 = HotPath(sites=rec.sites, lattice=rec.lattice, n_atoms=rec.n_atoms, site_radius=0.6,
+                      site_inner_fraction=0.5, minimal_residence=3, n_frames_total=6000)
+        checked = hp0.run(pos)
+        assert hp0.last_pass == 'checked'
+        ref = {k: checked[k].cpu().numpy().copy() for k in ('outer', 'inner', 'events', 'jumps')}
         assert len(ref['events']) > 500 and len(ref['jumps']) > 5
+        monkeypatch.delenv('GD_FIRST_CALL_BOUND')
+        # the very first call of a fresh object already takes the one-synchronisation pass, with
+        # upper bounds for the table sizes
+        first = hp.run(pos)
+        assert hp.last_pass == 'optimistic' and hp.last_launch_mode == 'eager', hp.last_optimistic_reject
+        for k, v in ref.items():
+            assert_array_equal(first[k].cpu().numpy(), v)
         second = hp.run(pos)
         assert hp.last_pass == 'optimistic', hp.last_optimistic_reject
         for k, v in ref.items():

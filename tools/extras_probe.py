@@ -122,3 +122,17 @@ timed('ffill', lambda: _lib.check(lib.gd_fill_states(dv.ptr(outer), T, A, 1, Non
 if hasattr(lib, 'gd_occupancy'):
     occ = dv.zeros((len(frac) + 1,), torch.int64)
     timed('N1 occupancy', lambda: _lib.check(lib.gd_occupancy(dv.ptr(outer), T * A, len(frac), dv.ptr(occ), s)), 4)
+
+# N2: attempt frequency (K0 speed -> cuFFT spectrum -> mean frequency), against the K0 pass that feeds it
+from gemdat_b200 import Trajectory, TrajectoryMetrics
+
+del outer, inner, filled
+traj = Trajectory(species=['Li'] * A, coords=pos, lattice=rec.lattice, time_step=2e-15)
+traj._unit_wrapped = True
+
+
+def n2():
+    TrajectoryMetrics(traj)._meanfreq()
+
+
+timed('N2 attempt frequency (K0 speed + cuFFT + reductions)', n2, reps=2)
