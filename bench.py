@@ -159,10 +159,10 @@ def cpu_reference_pass(rec, frame0, n_frames):
         warnings.simplefilter('ignore')
         so = ostates.calculate_atom_states(**kw, site_inner_fraction={'': 1.0})
         si = ostates.calculate_atom_states(**kw, site_inner_fraction={'': INNER})
-    ev = oevents.calculate_transition_events(so, si)
-    try:
+    try:  # (the reference's own error paths for degenerate windows: transitions.py:451,470, jumps.py:107)
+        ev = oevents.calculate_transition_events(so, si)
         ojumps.transitions_to_jumps(ev, n_frames, MIN_RES)
-    except ValueError:
+    except (ValueError, IndexError):
         pass
     return time.perf_counter() - t0, pos.shape[0] * pos.shape[1]
 

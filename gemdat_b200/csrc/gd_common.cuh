@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/gemdat_b200.h"
 
@@ -62,7 +63,12 @@ static inline GdChunks gd_chunks(int64_t n_frames, int32_t n_atoms) {
     GdChunks g;
     g.n_frames = n_frames;
     g.n_atoms = n_atoms;
-    const int64_t want = (n_frames * (int64_t)n_atoms) >> 20;
+    // GD_CHUNK_SHIFT (default 20) moves the size at which chunks grow (A/B runs)
+    static const int shift = [] {
+        const char *e = getenv("GD_CHUNK_SHIFT");
+        return e && atoi(e) > 0 ? atoi(e) : 20;
+    }();
+    const int64_t want = (n_frames * (int64_t)n_atoms) >> shift;
     int32_t f = 32;
     while (f < want && f < 256) f <<= 1;
     g.f = f;

@@ -1465,3 +1465,58 @@ def test_density_at_a_tenth_of_an_angstrom_on_a_c3_window():
     assert vol.data.shape == want.shape == (389, 389, 259)
     assert int(vol.data.sum()) == n * rec.n_atoms
     assert_array_equal(vol.data, want)
+
+
+# ------------------------------------------------------------------ smaller kernels against numpy
+
+
+@pytest.mark.parametrize('n_frames,n_atoms,cell,res', [
+    (64, 5, (4.0, 5.0, 6.0), 0.5),        # 8 x 10 x 12 voxels: CTA-private grid in shared memory
+    (700, 33, (9.0, 10.5, 12.25), 0.5),   # partial strip, shared-memory route
+    (300, 64, (19.8, 9.9, 9.9), 0.1),     # 1.9e6 voxels: runs go to the global grid
+    (1, 1, (3.0, 3.0, 3.0), 0.2),
+])
+def test_density_routes_agree_and_match_numpy(n_frames, n_atoms, cell, res):
+    """gd_density_frames (run-length strip walker; shared-memory grid when it fits) and gd_density
+    (flat point list, one RED per point) against np.digitize + np.unique (volume.py:471-503) on
+    slowly moving atoms (long runs in one voxel) mixed with jumps across the cell."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200.lattice import Lattice
+    from gemdat_b200.volume import density_device, grid_edges
+    from oracle import volume as ovolume
+
+    rng = np.random.default_rng(n_frames * 7 + n_atoms)
+    pos = np.mod(rng.random((1, n_atoms, 3)) + np.cumsum(rng.normal(scale=0.004, size=(n_frames, n_atoms, 3)), axis=0), 1)
+    jump = rng.random((n_frames, n_atoms)) < 0.02
+    pos[jump] = rng.random((int(jump.sum()), 3))
+    pos[0, 0] = [0.0, 0.0, 0.0]
+    pos[-1, -1] = [1.0 - 2**-53] * 3
+    lat = np.diag(cell)
+    want = ovolume.trajectory_to_volume(pos, lat, res)
+    nedges = grid_edges(Lattice(lat), res)
+    d_pos = dv.to_device(pos)
+    by_frames, flag = density_device(d_pos, nedges)
+    assert int(flag.item()) == 0
+    assert_array_equal(by_frames.cpu().numpy().view(np.uint32).astype(np.int64), want)
+    flat, flag = density_device(d_pos.reshape(-1, 3), nedges)
+    assert int(flag.item()) == 0
+    assert_array_equal(flat.cpu().numpy().view(np.uint32).astype(np.int64), want)
+
+
+@pytest.mark.parametrize('n,n_atoms', [(2, 1), (5, 3), (64, 2), (777, 5), (4096, 48)])
+def test_meanfreq_kernel_vs_periodogram_restatement(n, n_atoms):
+    """gd_meanfreq (weights, both spectral sums, ratio; DC bin skipped) on cuFFT's one-sided
+    spectrum against the numpy restatement of scipy.signal.periodogram + utils.py:128-160, for
+    even and odd lengths, with a constant offset on every row (only the DC bin sees it)."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from oracle import spectrum
+
+    rng = np.random.default_rng(n + n_atoms)
+    x = rng.normal(size=(n_atoms, n)) + rng.normal(size=(n_atoms, 1))
+    fs = 5e14
+    want = spectrum.meanfreq(x, fs)[:, 0]
+    spec = torch.fft.rfft(dv.to_device(x), dim=1)
+    out = dv.empty((n_atoms,), torch.float64)
+    _lib.check(_lib.lib.gd_meanfreq(dv.ptr(spec), n, n_atoms, fs, dv.ptr(out), dv.stream_ptr()))
+    assert_allclose(out.cpu().numpy(), want, rtol=1e-10, equal_nan=True)
