@@ -15,9 +15,8 @@ build() { # name, source file, source stem it replaces (gd_states | gd_events | 
   "$NVCC" -shared -o _variants/lib_$name.so _variants/${stem}_$name.o $objs -lcudart
   echo "$name built: $(grep -A1 'k_site_statesILb1ELb1ELb1ELb1' _variants/$name.log | grep -o 'Used [0-9]* registers' | head -1)"
 }
-git show HEAD:gemdat_b200/csrc/gd_states.cu > _variants/gd_states_head.cu
-build head _variants/gd_states_head.cu gd_states &
-build new6 gd_states.cu gd_states &
-build new7 gd_states.cu gd_states -DGD_K1_MIN_CTAS=7 &
-build head7 _variants/gd_states_head.cu gd_states -DGD_K1_MIN_CTAS=7 &
+build base gd_states.cu gd_states &
+build min7 gd_states.cu gd_states -DGD_K1_MIN_CTAS=7 &
+build min8 gd_states.cu gd_states -DGD_K1_MIN_CTAS=8 &
+build min8w2 gd_states.cu gd_states -DGD_K1_MIN_CTAS=16 -DGD_K1_WARPS=2 &
 wait
