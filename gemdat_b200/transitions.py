@@ -18,6 +18,7 @@ results in numpy / pandas.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import typing
 from dataclasses import dataclass
 from itertools import combinations_with_replacement
@@ -209,6 +210,41 @@ def _wants_pipeline(trajectory, count_events: bool) -> bool:
     return coords.nbytes >= PIPELINE_MIN_BYTES and coords.flags.c_contiguous
 
 
+_STAGING: dict = {}
+_COPY_POOL = None
+COPY_THREADS = 8
+COPY_MIN_BYTES = 4 << 20  # per thread
+
+
+def _staging_buffers(n_elems: int):
+    """Two page-locked float64 buffers of at least ``n_elems``, kept for the process (page
+    locking costs more than the copy it serves)."""
+    have = _STAGING.get('buf')
+    if have is None or have[0].numel() < n_elems:
+        have = [torch.empty((n_elems,), dtype=torch.float64, pin_memory=True) for _ in range(2)]
+        _STAGING['buf'] = have
+    return have
+
+
+def _threaded_copy(dst: np.ndarray, src: np.ndarray) -> None:
+    """dst[...] = src over the leading axis with several host threads (numpy releases the GIL
+    inside the copy loop; one thread does not fill the host memory bandwidth)."""
+    global _COPY_POOL
+    n = len(src)
+    n_threads = min(COPY_THREADS, os.cpu_count() or 1, max(1, src.nbytes // max(1, COPY_MIN_BYTES)))
+    if n_threads <= 1:
+        np.copyto(dst, src)
+        return
+    if _COPY_POOL is None:
+        from concurrent.futures import ThreadPoolExecutor
+
+        _COPY_POOL = ThreadPoolExecutor(max_workers=COPY_THREADS, thread_name_prefix='gd-stage')
+    cuts = [n * i // n_threads for i in range(n_threads + 1)]
+    jobs = [_COPY_POOL.submit(np.copyto, dst[a:b], src[a:b]) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
+    for j in jobs:
+        j.result()
+
+
 class HostStates:
     """int64 host copies of the two state arrays, arriving through a side stream."""
 
@@ -255,15 +291,31 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
     uploaded = [torch.cuda.Event(enable_timing=trace is not None) for _ in range(n_parts)]
     staged_free = [None, None]
 
+    # pageable source: the driver would bounce every part through its own small staging buffer
+    # on one host thread; copy the part into one of two page-locked buffers with several host
+    # threads instead, then let the copy engine take it from there
+    pageable = not src.is_pinned()
+    bounce = _staging_buffers(part_max * n_atoms * 3) if pageable else None
+    bounce_free = [None, None]
+
     def upload(k):
+        f0, f1 = bounds[k], bounds[k + 1]
+        part = src[f0:f1]
+        if pageable:
+            if bounce_free[k % 2] is not None:
+                bounce_free[k % 2].synchronize()
+            part = bounce[k % 2][: (f1 - f0) * n_atoms * 3].view(f1 - f0, n_atoms, 3)
+            _threaded_copy(part.numpy(), coords[f0:f1])
         with torch.cuda.stream(up):
-            pos[bounds[k]:bounds[k + 1]].copy_(src[bounds[k]:bounds[k + 1]], non_blocking=True)
+            pos[f0:f1].copy_(part, non_blocking=True)
             uploaded[k].record(up)
+            if pageable:
+                bounce_free[k % 2] = uploaded[k]
 
     upload(0)
     done = torch.cuda.Event()
     for k in range(n_parts):
-        if k + 1 < n_parts:
+        if k + 1 < n_parts and not pageable:
             upload(k + 1)
         f0, f1 = bounds[k], bounds[k + 1]
         main.wait_event(uploaded[k])
@@ -290,6 +342,8 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
             staged_free[k % 2] = free
         if trace is not None:
             trace.append((uploaded[k], ready, free))
+        if k + 1 < n_parts and pageable:
+            upload(k + 1)  # the host-side copy runs while the device works on part k
     done.record(down)
     # later work on the current stream (and the allocator's reuse of the staging buffers) is
     # ordered after both side streams

@@ -852,15 +852,20 @@ def test_hotpath_optimistic_pass_equals_checked_pass(monkeypatch):
         assert_array_equal(fifth['events'].cpu().numpy(), ref['events'])
 
 
+@pytest.mark.parametrize('pinned', [False, True])
 @pytest.mark.parametrize('n_atoms', [48, 33])
-def test_pipelined_host_path_equals_resident_path(monkeypatch, n_atoms):
+def test_pipelined_host_path_equals_resident_path(monkeypatch, n_atoms, pinned):
     """Host numpy input large enough for the upload / K1 / download pipeline (forced here) gives
-    the same states, events and jumps as the single-launch path on a device-resident copy."""
+    the same states, events and jumps as the single-launch path on a device-resident copy;
+    pageable input goes through the threaded page-locked staging buffers."""
     import gemdat_b200.transitions as gt
     from gemdat_b200 import Sites, Trajectory, synth
 
     rec = synth.config_c2(n_frames=4001, seed=5)
     pos = rec.host_positions(0, 4001)[:, :n_atoms].copy()
+    if pinned:
+        pos = torch.from_numpy(pos).pin_memory().numpy()
+    monkeypatch.setattr(gt, 'COPY_MIN_BYTES', 1 << 14)  # several host threads per part even here
     kw = dict(site_radius=0.9, site_inner_fraction=0.5)
     ref = Trajectory(species=['Li'] * n_atoms, coords=torch.from_numpy(pos).cuda(), lattice=rec.lattice,
                      time_step=2e-15).transitions_between_sites(rec.sites, 'Li', **kw)
