@@ -97,6 +97,7 @@ SIGNATURES = {
     'gd_events_merge_capped': (C.c_int, [_p, _p, _p, _i32, _p, _i64, _i64, _p]),
     'gd_jumps_merge_shards': (C.c_int, [_p, _i64, _i32, _i32, _i32, _i64, _p, _i64, _p]),
     'gd_fill_states': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p, _p]),
+    'gd_fill_states_noalloc': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p]),
     'gd_fill_last_valid': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p]),
     'gd_fill_apply': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p]),
     'gd_occupancy': (C.c_int, [_p, _i64, _i32, _p, _p]),

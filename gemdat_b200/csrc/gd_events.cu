@@ -18,6 +18,8 @@
 // atom-frames (24 B each).
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "gd_common.cuh"
 
 namespace {
@@ -616,6 +618,71 @@ extern "C" gd_status_t gd_jumps_merge_shards(const int32_t *d_gathered, int64_t 
     k_merge_shards<<<grid, 128, 0, (cudaStream_t)stream>>>(d_gathered, stride_words, head_words, world,
                                                           n_atoms, src_capacity, d_dst_rows,
                                                           dst_capacity);
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+// ---------------------------------------------------------------- allocation-free ffill / bfill
+//
+// gd_fill_states for callers that cannot allocate (code under CUDA graph capture, tight serving
+// loops, harnesses that forbid cudaMalloc): the per-(frame chunk, atom) carries live in a
+// file-scope device array instead of a caller-provided d_work.  Every GPU that loads the library
+// holds the array (16 MiB) until exit.  All calls share it: calls that overlap on the GPU race.
+// Nothing in it has to start at zero -- k_fill_summary overwrites every slot the later two
+// kernels read -- so it is not cleared; it keeps the last call's carries.
+constexpr int64_t kFillStaticElems = GD_FILL_NOALLOC_MAX_WORK_ELEMS;
+static __device__ __align__(256) int32_t g_fill_scratch[kFillStaticElems];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_fill_scratch_mutex;
+int32_t *g_fill_scratch_ptr[kMaxDevices];  // device address of g_fill_scratch, per device
+
+// In host code `g_fill_scratch` is a host-side stand-in, not a device address: the address the
+// kernels get comes from cudaGetSymbolAddress, looked up once per device with that device current.
+gd_status_t fill_scratch_address(int32_t **out) {
+    int dev = -1;
+    GD_CUDA_CHECK(cudaGetDevice(&dev));
+    GD_REQUIRE(dev >= 0 && dev < kMaxDevices, GD_ERR_INVALID,
+               "gd_fill_states_noalloc: device ordinal %d not supported (max %d)", dev, kMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_fill_scratch_mutex);
+    if (g_fill_scratch_ptr[dev] == nullptr) {
+        void *p = nullptr;
+        GD_CUDA_CHECK(cudaGetSymbolAddress(&p, g_fill_scratch));
+        GD_REQUIRE(p != nullptr, GD_ERR_CUDA, "gd_fill_states_noalloc: no address for the scratch array");
+        g_fill_scratch_ptr[dev] = static_cast<int32_t *>(p);
+    }
+    *out = g_fill_scratch_ptr[dev];
+    return GD_OK;
+}
+
+}  // namespace
+
+extern "C" gd_status_t gd_fill_states_noalloc(const int32_t *d_states, int64_t n_frames,
+                                              int32_t n_atoms, int direction,
+                                              const int32_t *d_carry_in, int32_t *d_carry_out,
+                                              int32_t *d_out, void *stream) {
+    GD_REQUIRE(d_states && d_out, GD_ERR_INVALID, "gd_fill_states_noalloc: null argument");
+    GD_REQUIRE(n_frames > 0 && n_atoms > 0, GD_ERR_INVALID, "gd_fill_states_noalloc: empty input");
+    GD_REQUIRE(direction == 1 || direction == -1, GD_ERR_INVALID,
+               "gd_fill_states_noalloc: direction must be +1 (ffill) or -1 (bfill)");
+    const Geometry g = geometry(n_frames, n_atoms);
+    const int64_t items = g.n_chunks * g.n_atoms;
+    GD_REQUIRE(items <= kFillStaticElems, GD_ERR_CAPACITY,
+               "gd_fill_states_noalloc: %lld frames x %d atoms need %lld scratch slots, the static "
+               "array holds %lld (use gd_fill_states with a caller-provided d_work)",
+               (long long)n_frames, (int)n_atoms, (long long)items, (long long)kFillStaticElems);
+    int32_t *work = nullptr;
+    const gd_status_t st_addr = fill_scratch_address(&work);
+    if (st_addr != GD_OK) return st_addr;
+    cudaStream_t st = (cudaStream_t)stream;
+    k_fill_summary<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, work);
+    GD_LAUNCH_CHECK();
+    k_fill_carry<<<blocks_for((int64_t)n_atoms * 32, 128), 128, 0, st>>>(g, direction, d_carry_in,
+                                                                         d_carry_out, work);
+    GD_LAUNCH_CHECK();
+    k_fill_apply<<<blocks_for(items, 256), 256, 0, st>>>(d_states, g, direction, work, nullptr, d_out);
     GD_LAUNCH_CHECK();
     return GD_OK;
 }

@@ -231,6 +231,23 @@ gd_status_t gd_fill_states(const int32_t *d_states, int64_t n_frames, int32_t n_
                            const int32_t *d_carry_in, int32_t *d_carry_out, int32_t *d_work,
                            int32_t *d_out, void *stream);
 
+/* gd_fill_states without a caller-provided d_work and without any allocation.  NO COUNTERPART
+ * IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The per-(frame chunk, atom) carries live in a file-scope `static __device__` array of
+ * GD_FILL_NOALLOC_MAX_WORK_ELEMS int32 (16 MiB, held by every GPU that loads the library until
+ * exit; one BASELINE config-3 trajectory, 10^6 frames x 1008 atoms, needs 3 938 256 slots).  The
+ * call makes no cudaMalloc / cudaFree and calls no allocating routine; inputs and outputs are
+ * the caller's.  Shapes whose gd_events_work_elems(n_frames, n_atoms) - 16 exceeds the maximum
+ * are rejected with GD_ERR_CAPACITY (use gd_fill_states).  All calls share the one array per
+ * device, which keeps the last call's carries (every slot read is overwritten first, nothing
+ * needs clearing): calls that overlap on the GPU -- different streams, or two threads -- RACE;
+ * order them on one stream or with events.  Same arguments and results as gd_fill_states. */
+#define GD_FILL_NOALLOC_MAX_WORK_ELEMS (1 << 22)
+gd_status_t gd_fill_states_noalloc(const int32_t *d_states, int64_t n_frames, int32_t n_atoms,
+                                   int direction, const int32_t *d_carry_in, int32_t *d_carry_out,
+                                   int32_t *d_out, void *stream);
+
 /* The same fill in two steps, for frame shards (one pass over the states less than calling
  * gd_fill_states twice):
  *   1. gd_fill_last_valid: d_last_valid [n_atoms] = last valid state of this shard in scan
