@@ -140,6 +140,9 @@ __global__ void __launch_bounds__(256)
 #define GD_COMPACT_ATOM_MAJOR 0
 #endif
 constexpr int kCompactLanes = GD_COMPACT_LANES;
+#ifndef GD_COMPACT_WARP_DEFAULT
+#define GD_COMPACT_WARP_DEFAULT 1
+#endif
 
 // where a (chunk, atom) segment's rows go: n_words 8-byte words from `src` to `dst` (0 = nothing)
 struct CompactJob {
@@ -221,6 +224,93 @@ __global__ void __launch_bounds__(256)
             dst[k] = v;
         }
         cur = nxt;
+    }
+}
+
+// Warp-cooperative variant (GD_COMPACT_WARP, default): a warp owns 32 consecutive (atom, chunk)
+// segments in ATOM-major order.  The look-ups of the 32 segments (skip flag, chunk offsets, atom
+// offset -- independent loads, coalesced over the chunks) are issued at once, one per lane; the
+// rows of consecutive chunks of an atom are consecutive in the table, so the warp then writes one
+// contiguous run of words, lane by lane (32 x 8 B per store instruction), each lane finding the
+// segment its word comes from in a small shared table.  Four loads per lane are in flight before
+// the first store.  Against the 16-lanes-per-segment kernel: one dependent load latency instead
+// of three before the copy starts, full-width stores, no lanes idle in the last trip of a segment.
+constexpr int kCwWarps = 8;
+
+__global__ void __launch_bounds__(kCwWarps * 32)
+    k_events_compact_warp(const int2 *__restrict__ stage, int32_t cap, Geometry g,
+                          const int32_t *__restrict__ work, const uint8_t *__restrict__ changed_global,
+                          const int64_t *__restrict__ atom_offsets, int32_t frame0,
+                          int2 *__restrict__ events, int64_t row_capacity) {
+    __shared__ int s_prefix[kCwWarps][33];
+    __shared__ const int2 *s_src[kCwWarps][32];
+    __shared__ int2 *s_dst[kCwWarps][32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t n_items = g.n_chunks * g.n_atoms;
+    const int64_t item = ((int64_t)blockIdx.x * kCwWarps + wid) * 32 + lane;
+    int n_words = 0;
+    const int2 *src = nullptr;
+    int2 *dst = nullptr;
+    if (item < n_items) {
+        const int32_t a = (int32_t)(item / g.n_chunks);
+        const int64_t c = item - (int64_t)a * g.n_chunks;
+        const int32_t *w = work + item;  // == work[a * n_chunks + c]
+        const bool last_chunk = c + 1 == g.n_chunks;
+        // independent loads: all issued before the first use
+        const uint8_t keep = changed_global[a];
+        const int32_t first = w[0];
+        const int32_t nxt = last_chunk ? 0 : w[1];
+        const int64_t off = atom_offsets[a];
+        const int64_t off1 = atom_offsets[a + 1];
+        const int32_t last = last_chunk ? (int32_t)(off1 - off) : nxt;
+        if (keep && last > first && off + last <= row_capacity) {
+            src = stage + (c * g.n_atoms + a) * (int64_t)cap * 3;
+            dst = events + (off + first) * 3;
+            n_words = 3 * (last - first);
+        }
+    }
+    int incl = n_words;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += up;
+    }
+    s_prefix[wid][lane + 1] = incl;
+    if (lane == 0) s_prefix[wid][0] = 0;
+    s_src[wid][lane] = src;
+    s_dst[wid][lane] = dst;
+    __syncwarp();
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    const int *prefix = s_prefix[wid];
+    int j = 0, lo = 0, hi = prefix[1];  // segment of the lane's current word: words [lo, hi)
+    constexpr int kAhead = 4;
+    for (int w0 = lane; w0 < total; w0 += 32 * kAhead) {
+        int2 v[kAhead];
+        int2 *to[kAhead];
+        int kind[kAhead];
+#pragma unroll
+        for (int u = 0; u < kAhead; ++u) {
+            const int wd = w0 + 32 * u;
+            to[u] = nullptr;
+            if (wd < total) {
+                while (wd >= hi) {
+                    ++j;
+                    lo = hi;
+                    hi = prefix[j + 1];
+                }
+                const int local = wd - lo;
+                v[u] = __ldcs(s_src[wid][j] + local);
+                to[u] = s_dst[wid][j] + local;
+                kind[u] = local % 3;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kAhead; ++u) {
+            if (to[u] != nullptr) {
+                if (kind[u] == 2) v[u].y += frame0;  // (destination inner site, time)
+                *to[u] = v[u];
+            }
+        }
     }
 }
 
@@ -519,6 +609,19 @@ extern "C" gd_status_t gd_events_compact(const int32_t *d_stage, int32_t stage_c
     // persistent grid with the next segment's look-ups prefetched is SLOWER (8 CTAs/SM: 1.37 ms,
     // 16: 1.13, uncapped: 1.10) -- the copy wants all the parallelism it can get.
     // GD_COMPACT_CTAS_PER_SM caps the grid for A/B runs.
+    static const int use_warp = [] {
+        const char *e = getenv("GD_COMPACT_WARP");
+        return e ? atoi(e) : GD_COMPACT_WARP_DEFAULT;
+    }();
+    if (use_warp) {
+        const int64_t wblocks = gd_ceil_div(g.n_chunks * g.n_atoms, (int64_t)kCwWarps * 32);
+        k_events_compact_warp<<<(unsigned)wblocks, kCwWarps * 32, 0, (cudaStream_t)stream>>>(
+            reinterpret_cast<const int2 *>(d_stage), stage_cap, g, d_work, d_changed_global,
+            d_atom_offsets, (int32_t)frame0, reinterpret_cast<int2 *>(d_events),
+            row_capacity > 0 ? row_capacity : INT64_MAX);
+        GD_LAUNCH_CHECK();
+        return GD_OK;
+    }
     int64_t blocks = gd_ceil_div(g.n_chunks * g.n_atoms * kCompactLanes, 256);
     if (const char *e = getenv("GD_COMPACT_CTAS_PER_SM"))
         if (atoi(e) > 0 && blocks > (int64_t)dev.sm_count * atoi(e)) blocks = (int64_t)dev.sm_count * atoi(e);
