@@ -45,4 +45,4 @@ def phases(label):
 
 for per_sm in (os.environ.get("GD_COMPACT_CTAS_PER_SM", "100000"),):
     os.environ['GD_COMPACT_CTAS_PER_SM'] = per_sm
-    phases(f'compact CTAs/SM {per_sm} warp-compaction {os.environ.get("GD_COMPACT_WARP", "default")}')
+    phases(f'compact CTAs/SM {per_sm} warp-compaction {os.environ.get("GD_COMPACT_WARP", "default")} tiled-spec {os.environ.get("GD_K3_SPEC_TILED", "default")}')
