@@ -6,8 +6,11 @@ DataFrame]``.  The default method is the CUDA state machine (``gd_jumps_count`` 
 ``gd_jumps_fill``, K3) standing in for the pandas ``groupby``/``iterrows`` loop of
 ``_generic_transitions_to_jumps`` (:24-119).  ``matrix`` (:212-221) and
 ``jump_diffusivity`` (:185-210) follow the reference formulae.  ``collective`` (:223-251)
-hands the device table to ``gemdat_b200.collective.Collective``.  Rates, activation
-energies and graphs are consumers of this table and out of scope (DESIGN.md "next rows").
+hands the device table to ``gemdat_b200.collective.Collective``.  ``rates`` (:435-462),
+``activation_energies`` (:253-308), ``to_graph`` (:364-410) and
+``activation_energy_between_sites`` (:340-362) are the consumers the N1 / N2 rows exist for:
+a few scalars per site pair on the host, fed by ``Transitions.split`` / ``atom_locations`` /
+``occupancy`` (device reductions), the per-part jump tables (K3) and the attempt frequency (N2).
 """
 
 from __future__ import annotations
@@ -154,6 +157,88 @@ class Jumps:
     @weak_lru_cache()
     def _counter(self) -> Counter:
         return Counter(zip(self.data['start site'], self.data['destination site']))
+
+    def _part_counters(self, n_parts: int) -> list[Counter]:
+        return [part.counter() for part in self.split(n_parts)]
+
+    @weak_lru_cache()
+    def rates(self, n_parts: int = 10) -> pd.DataFrame:
+        """jumps.py:435-462: jumps per second and per floating atom between site labels, mean and
+        sample standard deviation (ddof=1) over ``n_parts`` consecutive parts of the run."""
+        counters = self._part_counters(n_parts)
+        denom = self.n_floating * (self.trajectory.total_time / n_parts)
+        table = {}
+        for pair in dict.fromkeys(self.site_pairs):  # the reference visits duplicates again: same value
+            n_jumps = [c[pair] for c in counters]
+            table[pair] = float(np.mean(n_jumps) / denom), float(np.std(n_jumps, ddof=1) / denom)
+        df = pd.DataFrame(table).T
+        df.columns = ('rates', 'std')
+        return df
+
+    @weak_lru_cache()
+    def activation_energies(self, n_parts: int = 10) -> pd.DataFrame:
+        """jumps.py:253-308: E_act = -ln(rate / attempt frequency) k_B T in eV per pair of site
+        labels, mean and sample standard deviation over ``n_parts`` parts.  The rate of a part is
+        its jump count over (time the atoms spend on the start label: ``atom_locations`` of the
+        part x n_floating x part duration); A->A jumps are halved (:293-296)."""
+        from scipy.constants import Boltzmann, elementary_charge
+
+        from .metrics import TrajectoryMetrics
+
+        trajectory = self.trajectory
+        attempt_freq, _ = TrajectoryMetrics(trajectory).attempt_frequency()
+        temperature = trajectory.metadata['temperature']
+        locations = [part.atom_locations() for part in self.transitions.split(n_parts)]
+        counters = self._part_counters(n_parts)
+        n_floating = self.n_floating
+        part_time = trajectory.total_time / n_parts
+        table = {}
+        for start, stop in dict.fromkeys(self.site_pairs):
+            n_jumps = np.array([c[start, stop] for c in counters])
+            share = np.array([loc[start] for loc in locations])
+            eff_rate = n_jumps / (share * n_floating * part_time)
+            if start == stop:
+                eff_rate /= 2
+            e_act = -np.log(eff_rate / attempt_freq) * (Boltzmann * temperature) / elementary_charge
+            table[start, stop] = np.mean(e_act), np.std(e_act, ddof=1)
+        df = pd.DataFrame(table).T
+        df.columns = ('energy', 'std')
+        return df
+
+    def activation_energy_between_sites(self, start, stop) -> float:
+        """jumps.py:340-362: the ``e_act`` attribute of the graph edge start -> stop."""
+        edge = self.to_graph().get_edge_data(start, stop)
+        if not edge:
+            raise IndexError(f'No jumps between ({start}) and ({stop})')
+        return edge['e_act']
+
+    @weak_lru_cache()
+    def to_graph(self, min_e_act: float | None = None, max_e_act: float | None = None):
+        """jumps.py:364-410: networkx DiGraph, one node per site (attribute ``label``), one edge
+        per (start site, destination site) that has jumps, weighted by the activation energy from
+        the whole run: rate = jumps / (site occupancy x total time)."""
+        import networkx as nx
+        from scipy.constants import Boltzmann, elementary_charge
+
+        from .metrics import TrajectoryMetrics
+
+        lo = min_e_act if min_e_act else float('-inf')
+        hi = max_e_act if max_e_act else float('inf')
+        occupancy = self.transitions.occupancy().occupancies
+        attempt_freq, _ = TrajectoryMetrics(self.trajectory).attempt_frequency()
+        kBT = Boltzmann * self.trajectory.metadata['temperature']
+        total_time = self.trajectory.total_time
+        _, labels, _ = site_arrays(self.sites)
+        graph = nx.DiGraph()
+        for i, label in enumerate(labels):
+            graph.add_node(i, label=label)
+        for (start, stop), n_jumps in self._counter().items():
+            eff_rate = n_jumps / (occupancy[start] * total_time)
+            e_act = -np.log(eff_rate / attempt_freq) * kBT
+            e_act /= elementary_charge
+            if lo <= e_act <= hi:
+                graph.add_edge(start, stop, e_act=e_act)
+        return graph
 
     def split(self, n_parts: int) -> list['Jumps']:
         """jumps.py:412-433."""

@@ -1136,6 +1136,56 @@ def test_n1_vs_reference_golden(name):
         assert_array_equal(df.index.to_numpy(), g[f'{name}/split{n}/{i}/events_index'])
 
 
+@pytest.mark.parametrize('name', N1_CASES)
+def test_rates_activation_energies_graph_vs_reference_golden(name):
+    """The consumers of N1 / N2: Jumps.rates / activation_energies / to_graph /
+    activation_energy_between_sites against the outputs of the reference's jumps.py:253-308,
+    340-462 (tests/golden/make_golden_rates.py).  Floating point: 1e-10 relative (the attempt
+    frequency comes from cuFFT instead of scipy's periodogram; everything else is exact)."""
+    from conftest import load_golden
+    from gemdat_b200 import Jumps
+
+    g = load_golden('rates')
+    c, tr = _n1_transitions(name)
+    jumps = Jumps(tr, minimal_residence=int(g[f'{name}/minimal_residence']))
+    freq, freq_std = jumps.trajectory.metrics().attempt_frequency()
+    assert_allclose([float(freq), float(freq_std)], g[f'{name}/attempt_frequency'], rtol=1e-9)
+    for n in g[f'{name}/part_counts'].tolist():
+        if f'{name}/parts{n}/error' in g:  # some part holds no jump: ValueError('No jumps found')
+            with pytest.raises(ValueError, match=str(g[f'{name}/parts{n}/error'])):
+                jumps.rates(n_parts=n)
+            with pytest.raises(ValueError, match=str(g[f'{name}/parts{n}/error'])):
+                jumps.activation_energies(n_parts=n)
+            continue
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')  # log(0) for pairs without jumps, like the reference
+            rates, eact = jumps.rates(n_parts=n), jumps.activation_energies(n_parts=n)
+        assert list(rates.columns) == ['rates', 'std'] and list(eact.columns) == ['energy', 'std']
+        assert [list(k) for k in rates.index] == g[f'{name}/rates{n}/keys'].tolist()
+        assert [list(k) for k in eact.index] == g[f'{name}/eact{n}/keys'].tolist()
+        assert_allclose(rates.to_numpy(dtype=float), g[f'{name}/rates{n}/values'], rtol=1e-12)
+        assert_allclose(eact.to_numpy(dtype=float), g[f'{name}/eact{n}/values'], rtol=1e-10, equal_nan=True)
+    graph = jumps.to_graph()
+    assert [d['label'] for _, d in graph.nodes(data=True)] == [str(x) for x in g[f'{name}/graph_nodes']]
+    edges = np.array([(a, b, d['e_act']) for a, b, d in graph.edges(data=True)], dtype=float).reshape(-1, 3)
+    want = g[f'{name}/graph_edges']
+    assert_array_equal(edges[:, :2], want[:, :2])  # same edges in the same order
+    assert_allclose(edges[:, 2], want[:, 2], rtol=1e-10)
+    lo, hi = g[f'{name}/graph_cut'].tolist()
+    cut = jumps.to_graph(min_e_act=lo, max_e_act=hi)
+    cut_edges = np.array([(a, b, d['e_act']) for a, b, d in cut.edges(data=True)], dtype=float).reshape(-1, 3)
+    # an edge whose energy equals a bound to the last bit may fall on either side at 1e-10
+    want_cut = g[f'{name}/graph_cut_edges']
+    inner = (want_cut[:, 2] > lo * (1 + 1e-9)) & (want_cut[:, 2] < hi * (1 - 1e-9))
+    have = {(int(a), int(b)) for a, b, _ in cut_edges}
+    assert {(int(a), int(b)) for a, b, _ in want_cut[inner]} <= have
+    assert have <= {(int(a), int(b)) for a, b, _ in want[(want[:, 2] >= lo * (1 - 1e-9)) & (want[:, 2] <= hi * (1 + 1e-9))]}
+    a, b, e = g[f'{name}/between'].tolist()
+    assert_allclose(jumps.activation_energy_between_sites(int(a), int(b)), e, rtol=1e-10)
+    with pytest.raises(IndexError):
+        jumps.activation_energy_between_sites(int(a), int(a))
+
+
 @pytest.mark.parametrize('n_frames,n_atoms,n_sites', [(1, 1, 3), (257, 5, 7), (4099, 33, 64), (1000, 17, 60_000)])
 def test_n1_kernels_random_vs_oracle(n_frames, n_atoms, n_sites):
     """gd_occupancy (shared-memory bins; global atomics beyond 48k bins; unaligned input) and the
