@@ -309,6 +309,39 @@ def run_extras(args, rec, world, rank, peaks, jumps=None):
                                           '(72 B moved)')
     got.clear()
 
+    # ---- drift correction and centre of mass (callers on the input side): gd_drift (24 B read) ->
+    # summed drift -> K0 cumulative displacements (48 B) -> gd_drift_correct in place (48 B), and
+    # gd_frame_mean over the same array (24 B).  One shard only (the summed drift is not carried
+    # across ranks here).
+    if world == 1:
+        def drift_correction():
+            d = dv.empty((n_own, 3), torch.float64)
+            _lib.check(lib.gd_drift(dv.ptr(pos), n_own, A, None, A, None, dv.ptr(d), s))
+            summed = dv.empty((n_own, 3), torch.float64)
+            scan_work = dv.empty((int(lib.gd_cumsum_frames3_work_bytes(n_own)),), torch.uint8)
+            _lib.check(lib.gd_cumsum_frames3(dv.ptr(d), n_own, dv.ptr(scan_work), dv.ptr(summed), s))
+            cum = fs.unwrap(pos, want_frac=True)['frac']
+            base = pos[0].clone()
+            _lib.check(lib.gd_drift_correct(dv.ptr(cum), dv.ptr(base), dv.ptr(summed), n_own, A, dv.ptr(cum), s))
+            got['corrected'] = (cum, base)
+
+        ms = timed(drift_correction, reps=2)
+        cum, base = got['corrected']
+        out['drift_correction'] = hbm_line(ms, 24 + 48 + 48, in_unit_cell=bool(
+            float(cum.min().item()) >= 0.0 and float(cum.max().item()) < 1.0),
+            note='Trajectory.apply_drift_correction on device-resident positions: drift 24 B + K0 48 B + '
+                 'correct-in-place 48 B per atom-frame')
+        weights = torch.ones((A,), dtype=torch.float64, device=pos.device)
+        com = dv.empty((n_own, 3), torch.float64)
+
+        def frame_mean():
+            _lib.check(lib.gd_frame_mean(dv.ptr(cum), dv.ptr(base), dv.ptr(weights), n_own, A, dv.ptr(com), s))
+
+        ms = timed(frame_mean)
+        out['center_of_mass'] = hbm_line(ms, 24, note='gd_frame_mean: weighted mean over the atoms of every frame')
+        del cum, base, com
+        got.clear()
+
     # ---- a4: speed (K0) -> amplitudes -> std, the site_radius=None route (nothing O(T) downloaded)
     def a4():
         sp = fs.unwrap(pos, want_speed=True)['speed']

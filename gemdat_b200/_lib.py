@@ -101,6 +101,11 @@ SIGNATURES = {
     'gd_fill_last_valid': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p]),
     'gd_fill_apply': (C.c_int, [_p, _i64, _i32, C.c_int, _p, _p, _p, _p]),
     'gd_occupancy': (C.c_int, [_p, _i64, _i32, _p, _p]),
+    'gd_frame_mean': (C.c_int, [_p, _p, _p, _i64, _i32, _p, _p]),
+    'gd_drift': (C.c_int, [_p, _i64, _i32, _p, _i32, _p, _p, _p]),
+    'gd_cumsum_frames3_work_bytes': (_i64, [_i64]),
+    'gd_cumsum_frames3': (C.c_int, [_p, _i64, _p, _p, _p]),
+    'gd_drift_correct': (C.c_int, [_p, _p, _p, _i64, _i32, _p, _p]),
     'gd_residence_work_bytes': (_i64, [_i64]),
     'gd_residence_count': (C.c_int, [_p, _i64, _p, C.POINTER(_i64), _p]),
     'gd_residence_fill': (C.c_int, [_p, _i64, _p, _p, _p]),

@@ -12,7 +12,7 @@
 // frame's atoms are contiguous: one CTA per frame, coalesced) or an elementwise pass: HBM bound.
 //   k_frame_mean     24 B read per atom-frame                    -> [T, 3]
 //   k_drift          24 B read per selected atom-frame (the row before comes from L2) -> [T, 3]
-//   k_cumsum3        the [T, 3] drift summed along T (one CTA, carried tile by tile)
+//   k_cumsum3_*      the [T, 3] drift summed along T (block scans + carries, three small launches)
 //   k_drift_correct  24 B read + 24 B write per atom-frame: mod(base + cum - D, 1)
 // The reference accumulates (d_t - drift_t) per atom sequentially in float64; here the cumulative
 // displacement comes from K0 (x_t - x_0 - integer winding, exact up to one rounding) and the
@@ -115,63 +115,127 @@ __global__ void __launch_bounds__(kThreads)
     }
 }
 
-// one CTA: inclusive sum of v[T, 3] along T, tile by tile (1024 frames) with a running carry
-__global__ void __launch_bounds__(1024) k_cumsum3(const double *__restrict__ v, int64_t n_frames,
-                                                  double *__restrict__ out) {
+// Inclusive sum of v[T, 3] along T in three small launches (all loads coalesced):
+//   k_cumsum3_local  every CTA scans its own block of 1024 frames into `out`, block total -> totals
+//   k_cumsum3_carry  one CTA turns the block totals into carries (exclusive scan, tile by tile)
+//   k_cumsum3_add    every CTA adds its carry
+constexpr int kScanBlock = 1024;
+
+// inclusive scan of one value per thread over the CTA (1024 threads), three channels at once;
+// returns the CTA total in tot[]
+__device__ __forceinline__ void block_scan3(double incl[3], double tot[3]) {
     __shared__ double warp_tot[3][32];
-    __shared__ double carry[3];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const double up = __shfl_up_sync(0xffffffffu, incl[c], o);
+            if (lane >= o) incl[c] += up;
+        }
+    }
+    if (lane == 31) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) warp_tot[c][warp] = incl[c];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        double before = 0.0, all = 0.0;
+        for (int w = 0; w < 32; ++w) {
+            const double x = warp_tot[c][w];
+            if (w < warp) before += x;
+            all += x;
+        }
+        incl[c] += before;
+        tot[c] = all;
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kScanBlock)
+    k_cumsum3_local(const double *__restrict__ v, int64_t n_frames, double *__restrict__ out,
+                    double *__restrict__ totals) {
+    const int64_t t = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+    double incl[3], tot[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) incl[c] = t < n_frames ? v[3 * t + c] : 0.0;
+    block_scan3(incl, tot);
+    if (t < n_frames) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) out[3 * t + c] = incl[c];
+    }
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) totals[3 * (int64_t)blockIdx.x + c] = tot[c];
+    }
+}
+
+// totals[nb, 3] -> exclusive sums in place (one CTA, tiles of 1024 blocks with a running carry)
+__global__ void __launch_bounds__(kScanBlock) k_cumsum3_carry(double *__restrict__ totals, int64_t nb) {
+    __shared__ double carry[3];
+    __shared__ double s_incl[3][kScanBlock];
     if (threadIdx.x < 3) carry[threadIdx.x] = 0.0;
     __syncthreads();
-    for (int64_t base = 0; base < n_frames; base += 1024) {
-        const int64_t t = base + threadIdx.x;
-        double incl[3];
+    for (int64_t base = 0; base < nb; base += kScanBlock) {
+        const int64_t b = base + threadIdx.x;
+        double incl[3], tot[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) incl[c] = t < n_frames ? v[3 * t + c] : 0.0;
+        for (int c = 0; c < 3; ++c) incl[c] = b < nb ? totals[3 * b + c] : 0.0;
+        block_scan3(incl, tot);
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
+        for (int c = 0; c < 3; ++c) s_incl[c][threadIdx.x] = incl[c];
+        __syncthreads();
+        if (b < nb) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const double up = __shfl_up_sync(0xffffffffu, incl[c], o);
-                if (lane >= o) incl[c] += up;
-            }
-        }
-        if (lane == 31) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) warp_tot[c][warp] = incl[c];
+            for (int c = 0; c < 3; ++c)  // exclusive value: the inclusive one of the block before
+                totals[3 * b + c] = threadIdx.x == 0 ? carry[c] : carry[c] + s_incl[c][threadIdx.x - 1];
         }
         __syncthreads();
-        double before[3] = {carry[0], carry[1], carry[2]};
-        for (int w = 0; w < warp; ++w) {
+        if (threadIdx.x == 0) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) before[c] += warp_tot[c][w];
-        }
-        if (t < n_frames) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) out[3 * t + c] = before[c] + incl[c];
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) carry[c] = before[c] + incl[c];
+            for (int c = 0; c < 3; ++c) carry[c] += tot[c];
         }
         __syncthreads();
     }
+}
+
+__global__ void __launch_bounds__(kScanBlock)
+    k_cumsum3_add(double *__restrict__ out, int64_t n_frames, const double *__restrict__ carries) {
+    if (blockIdx.x == 0) return;  // carry 0
+    const int64_t t = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+    if (t >= n_frames) return;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) out[3 * t + c] = carries[3 * (int64_t)blockIdx.x + c] + out[3 * t + c];
 }
 
 // out[t, a, c] = np.mod(base[a, c] + cum[t, a, c] - D[t, c], 1)      (out may alias cum)
 __global__ void __launch_bounds__(256)
     k_drift_correct(const double *cum, const double *__restrict__ base,
                     const double *__restrict__ shift, int64_t n_frames, int32_t n_atoms, double *out) {
-    const int64_t row = (int64_t)n_atoms * 3;
-    const int64_t n = n_frames * row;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const int64_t t = i / row;
-        const int64_t k = i - t * row;  // 3 a + c
-        const int c = (int)(k % 3);
-        const double x = base[k] + (cum[i] - shift[3 * t + c]);
-        out[i] = x - floor(x);
+    const int row = n_atoms * 3;
+    constexpr int kAhead = 4;  // loads in flight per thread
+    for (int64_t t = blockIdx.x; t < n_frames; t += gridDim.x) {
+        const double s0 = shift[3 * t], s1 = shift[3 * t + 1], s2 = shift[3 * t + 2];
+        const double *in = cum + t * (int64_t)row;
+        double *o = out + t * (int64_t)row;
+        for (int k0 = threadIdx.x; k0 < row; k0 += 256 * kAhead) {
+            double v[kAhead];
+#pragma unroll
+            for (int u = 0; u < kAhead; ++u) {
+                const int k = k0 + 256 * u;
+                v[u] = k < row ? __ldcs(in + k) : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < kAhead; ++u) {
+                const int k = k0 + 256 * u;
+                if (k < row) {
+                    const int c = k % 3;
+                    const double x = base[k] + (v[u] - (c == 0 ? s0 : (c == 1 ? s1 : s2)));
+                    __stcs(o + k, x - floor(x));
+                }
+            }
+        }
     }
 }
 
@@ -204,11 +268,25 @@ extern "C" gd_status_t gd_drift(const double *d_pos, int64_t n_frames, int32_t n
     return GD_OK;
 }
 
-extern "C" gd_status_t gd_cumsum_frames3(const double *d_in, int64_t n_frames, double *d_out,
-                                         void *stream) {
-    GD_REQUIRE(d_in && d_out && n_frames > 0, GD_ERR_INVALID, "gd_cumsum_frames3: bad argument");
-    k_cumsum3<<<1, 1024, 0, (cudaStream_t)stream>>>(d_in, n_frames, d_out);
+extern "C" int64_t gd_cumsum_frames3_work_bytes(int64_t n_frames) {
+    return (n_frames > 0 ? gd_ceil_div(n_frames, (int64_t)kScanBlock) : 1) * 3 * (int64_t)sizeof(double);
+}
+
+extern "C" gd_status_t gd_cumsum_frames3(const double *d_in, int64_t n_frames, void *d_work,
+                                         double *d_out, void *stream) {
+    GD_REQUIRE(d_in && d_out && d_work && n_frames > 0, GD_ERR_INVALID, "gd_cumsum_frames3: bad argument");
+    GD_REQUIRE(d_in != d_out, GD_ERR_INVALID, "gd_cumsum_frames3: d_out must not alias d_in");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t nb = gd_ceil_div(n_frames, (int64_t)kScanBlock);
+    double *totals = static_cast<double *>(d_work);
+    k_cumsum3_local<<<(unsigned)nb, kScanBlock, 0, st>>>(d_in, n_frames, d_out, totals);
     GD_LAUNCH_CHECK();
+    if (nb > 1) {
+        k_cumsum3_carry<<<1, kScanBlock, 0, st>>>(totals, nb);
+        GD_LAUNCH_CHECK();
+        k_cumsum3_add<<<(unsigned)nb, kScanBlock, 0, st>>>(d_out, n_frames, totals);
+        GD_LAUNCH_CHECK();
+    }
     return GD_OK;
 }
 
@@ -217,12 +295,8 @@ extern "C" gd_status_t gd_drift_correct(const double *d_cumulative, const double
                                         int32_t n_atoms, double *d_out, void *stream) {
     GD_REQUIRE(d_cumulative && d_base && d_cumulative_drift && d_out && n_frames > 0 && n_atoms > 0,
                GD_ERR_INVALID, "gd_drift_correct: bad argument");
-    const GdDeviceInfo &dev = gd_device_info();
-    GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");
-    const int64_t n = n_frames * n_atoms * 3;
-    int64_t blocks = gd_ceil_div(n, 256);
-    if (blocks > (int64_t)dev.sm_count * 16) blocks = (int64_t)dev.sm_count * 16;
-    k_drift_correct<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+    GD_REQUIRE((int64_t)n_atoms * 3 < INT32_MAX, GD_ERR_INVALID, "gd_drift_correct: too many atoms");
+    k_drift_correct<<<frame_grid(n_frames), 256, 0, (cudaStream_t)stream>>>(
         d_cumulative, d_base, d_cumulative_drift, n_frames, n_atoms, d_out);
     GD_LAUNCH_CHECK();
     return GD_OK;

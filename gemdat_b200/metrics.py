@@ -9,8 +9,10 @@ sign flips and sum the pieces, ``gd_mean_std`` reduces them -- ``vibration_ampli
 ``attempt_frequency`` (:167-188) runs on the same device array: the per-atom
 spectrum comes from cuFFT through ``torch.fft`` (a library transform, not one of this
 package's kernels), the periodogram weighting and the mean-frequency reductions of
-``utils.py:128-160`` are one pass of ``gd_meanfreq`` over it.  Conductivity, Haven ratio and the Arrhenius
-helpers are out of scope.
+``utils.py:128-160`` are one pass of ``gd_meanfreq`` over it.  ``mol_per_liter`` (:64-74), ``tracer_diffusivity_center_of_mass``
+(:99-120), ``haven_ratio`` (:122-137) and ``tracer_conductivity`` (:140-165) are scalars on top of
+these; the multi-trajectory statistics (``TrajectoryMetricsStd``) and the Arrhenius helpers are out
+of scope.
 """
 
 from __future__ import annotations
@@ -96,6 +98,35 @@ class TrajectoryMetrics:
     def particle_density(self) -> FloatWithUnit:
         volume_m3 = self.trajectory.get_lattice().volume * ANGSTROM**3
         return FloatWithUnit(len(self.trajectory.species) / volume_m3, 'm^-3')
+
+    @weak_lru_cache()
+    def mol_per_liter(self) -> FloatWithUnit:
+        """metrics.py:64-74."""
+        from scipy.constants import Avogadro
+
+        return FloatWithUnit((self.particle_density() * 1e-3) / Avogadro, 'mol l^-1')
+
+    @weak_lru_cache()
+    def tracer_diffusivity_center_of_mass(self, *, dimensions: int = 3) -> FloatWithUnit:
+        """metrics.py:99-120: tracer diffusivity of the centre of mass (one pseudo atom)."""
+        return TrajectoryMetrics(self.trajectory.center_of_mass()).tracer_diffusivity(dimensions=dimensions)
+
+    @weak_lru_cache()
+    def haven_ratio(self, *, dimensions: int = 3) -> float:
+        """metrics.py:122-137."""
+        return self.tracer_diffusivity(dimensions=dimensions) / self.tracer_diffusivity_center_of_mass(
+            dimensions=dimensions)
+
+    @weak_lru_cache()
+    def tracer_conductivity(self, *, z_ion: int, dimensions: int = 3) -> FloatWithUnit:
+        """metrics.py:140-165: e^2 z^2 D n / (k_B T), S/m."""
+        from scipy.constants import Boltzmann, elementary_charge
+
+        temperature = self.trajectory.metadata['temperature']
+        tracer_diff = self.tracer_diffusivity(dimensions=dimensions)
+        conductivity = ((elementary_charge**2) * (z_ion**2) * tracer_diff * self.particle_density()) / (
+            Boltzmann * temperature)
+        return FloatWithUnit(conductivity, 'S m^-1')
 
     @weak_lru_cache()
     def tracer_diffusivity(self, *, dimensions: int = 3) -> FloatWithUnit:

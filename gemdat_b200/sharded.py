@@ -109,6 +109,50 @@ class FrameShards:
         return {'frac': frac, 'cart': cart, 'dist': dist, 'speed': speed,
                 'winding': all_totals.sum(dim=0, dtype=torch.int32)}
 
+    # -------------------------------------------------------------- drift / centre of mass
+    def drift_correction(self, pos: torch.Tensor, selected: np.ndarray | None = None) -> torch.Tensor:
+        """Drift-corrected, wrapped positions of this rank's frames [n, A, 3]
+        (``Trajectory.apply_drift_correction``): the local drift needs the row before the shard
+        (halo), its running sum the totals of the shards before (all-gather of [W, 3], added in
+        shard order), K0 the usual winding exchange.  Equal to one shard up to the rounding of
+        the summed drift (the sums are grouped by shard)."""
+        lib, s = _lib.lib, dv.stream_ptr()
+        n, A = int(pos.shape[0]), int(pos.shape[1])
+        prev, base_pos = None, pos[0].contiguous()
+        if self.world > 1:
+            ends = self.comm.all_gather(torch.stack([pos[0], pos[-1]]).contiguous())  # [W, 2, A, 3]
+            base_pos = ends[0, 0].contiguous()
+            if self.rank:
+                prev = ends[self.rank - 1, 1].contiguous()
+        d_sel = None if selected is None else dv.to_device(np.ascontiguousarray(selected, dtype=np.int32))
+        n_sel = A if selected is None else int(len(selected))
+        drift = dv.empty((n, 3), torch.float64)
+        _lib.check(lib.gd_drift(dv.ptr(pos), n, A, dv.ptr(d_sel), n_sel, dv.ptr(prev), dv.ptr(drift), s))
+        summed = dv.empty((n, 3), torch.float64)
+        scan_work = dv.empty((int(lib.gd_cumsum_frames3_work_bytes(n)),), torch.uint8)
+        _lib.check(lib.gd_cumsum_frames3(dv.ptr(drift), n, dv.ptr(scan_work), dv.ptr(summed), s))
+        if self.world > 1:
+            totals = self.comm.all_gather(summed[-1].contiguous())  # [W, 3]
+            for r in range(self.rank):  # shard order: the same grouping on every rank
+                summed += totals[r]
+        cum = self.unwrap(pos, want_frac=True)['frac']
+        _lib.check(lib.gd_drift_correct(dv.ptr(cum), dv.ptr(base_pos), dv.ptr(summed), n, A, dv.ptr(cum), s))
+        return cum
+
+    def center_of_mass(self, pos: torch.Tensor, weights: np.ndarray | None = None) -> torch.Tensor:
+        """[n, 3] weighted mean of the unwrapped positions of this rank's frames
+        (``Trajectory.center_of_mass``): K0 + one reduction per frame, no further exchange."""
+        n, A = int(pos.shape[0]), int(pos.shape[1])
+        base_pos = pos[0].contiguous()
+        if self.world > 1:
+            base_pos = self.comm.all_gather(base_pos)[0].contiguous()
+        cum = self.unwrap(pos, want_frac=True)['frac']
+        d_w = None if weights is None else dv.to_device(np.ascontiguousarray(weights, dtype=np.float64))
+        out = dv.empty((n, 3), torch.float64)
+        _lib.check(_lib.lib.gd_frame_mean(dv.ptr(cum), dv.ptr(base_pos), dv.ptr(d_w), n, A, dv.ptr(out),
+                                          dv.stream_ptr()))
+        return out
+
     # -------------------------------------------------------------- ffill / bfill
     def fill(self, states: torch.Tensor, direction: int) -> torch.Tensor:
         """states_prev (direction +1) / states_next (-1) of this rank's frames [n, A] int32."""

@@ -301,6 +301,91 @@ class Trajectory:
         g = Lattice(self.lattice).metric_tensor
         return np.einsum('ij,ij->i', frac @ g, frac)
 
+    # ------------------------------------------------------------------ per-frame averages, drift
+    def _selected_atoms(self, fixed_species, floating_species) -> np.ndarray:
+        """Atom numbers the drift is averaged over (trajectory.py:778-789: the fixed species, or
+        every species that is not floating, or all atoms)."""
+        symbols = [_symbol(sp) for sp in self.species]
+        if fixed_species:
+            wanted = [fixed_species] if isinstance(fixed_species, str) else fixed_species
+            wanted = {_symbol(s) for s in wanted}
+            keep = [s in wanted for s in symbols]
+        elif floating_species:
+            keep = [s not in floating_species for s in symbols]  # (`in` on a str: like the reference)
+        else:
+            keep = [True] * len(symbols)
+        return np.nonzero(keep)[0].astype(np.int32)
+
+    def _drift_device(self, fixed_species, floating_species) -> torch.Tensor | None:
+        """float64 [n_frames, 3] on the device, None when no atom is selected."""
+        sel = self._selected_atoms(fixed_species, floating_species)
+        if sel.size == 0:
+            return None
+        pos = self._device_positions()
+        n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+        out = dv.empty((n_frames, 3), torch.float64)
+        d_sel = None if sel.size == n_atoms else dv.to_device(sel)
+        _lib.check(_lib.lib.gd_drift(dv.ptr(pos), n_frames, n_atoms, dv.ptr(d_sel), int(sel.size), None,
+                                     dv.ptr(out), dv.stream_ptr()))
+        return out
+
+    def drift(self, *, fixed_species=None, floating_species=None) -> np.ndarray:
+        """trajectory.py:751-791: mean wrapped step of the fixed atoms per frame, [n_frames, 1, 3]
+        (``gd_drift``: one CTA per frame)."""
+        out = self._drift_device(fixed_species, floating_species)
+        if out is None:
+            import warnings
+
+            warnings.warn('Mean of empty slice.', RuntimeWarning, stacklevel=2)  # numpy's, over 0 atoms
+            return np.full((len(self), 1, 3), np.nan)
+        return dv.to_host(out)[:, None, :]
+
+    def apply_drift_correction(self, *, fixed_species=None, floating_species=None) -> 'Trajectory':
+        """trajectory.py:793-830: subtract the drift from every atom's steps.
+
+        The reference returns the corrected steps in displacement form and sums them along the
+        frames when positions are asked for; here the corrected, wrapped POSITIONS come back
+        directly (K0's cumulative displacements minus the summed drift, ``gd_drift_correct``),
+        on the device when the input was: the same trajectory up to rounding of the running sum.
+        """
+        drift = self._drift_device(fixed_species, floating_species)
+        n_frames, n_atoms = len(self), len(self.species)
+        if drift is None:
+            raise ValueError('no atoms selected to compute the drift from')
+        lib, s = _lib.lib, dv.stream_ptr()
+        summed = dv.empty((n_frames, 3), torch.float64)
+        scan_work = dv.empty((int(lib.gd_cumsum_frames3_work_bytes(n_frames)),), torch.uint8)
+        _lib.check(lib.gd_cumsum_frames3(dv.ptr(drift), n_frames, dv.ptr(scan_work), dv.ptr(summed), s))
+        was_device = dv.is_device(self.coords)
+        base = dv.to_device(np.ascontiguousarray(self._host_base_positions()), torch.float64)
+        cum = self._unwrap(want_frac=True, keep_on_device=True)['frac']
+        _lib.check(lib.gd_drift_correct(dv.ptr(cum), dv.ptr(base), dv.ptr(summed), n_frames, n_atoms,
+                                        dv.ptr(cum), s))
+        out = self.__class__(species=self.species, coords=cum if was_device else dv.to_host(cum),
+                             lattice=self.lattice, metadata=self.metadata, time_step=self.time_step)
+        out._unit_wrapped = True
+        return out
+
+    def _host_base_positions(self) -> np.ndarray:
+        base = self.base_positions
+        return dv.to_host(base) if dv.is_device(base) else np.asarray(base, dtype=np.float64)
+
+    def center_of_mass(self) -> 'Trajectory':
+        """trajectory.py:732-749: one pseudo atom 'X' at the mass-weighted mean of the unwrapped
+        positions (base positions + K0's cumulative displacements, ``gd_frame_mean``)."""
+        from .elements import atomic_mass
+
+        weights = np.array([atomic_mass(sp) for sp in self.species], dtype=np.float64)
+        cum = self._unwrap(want_frac=True, keep_on_device=True)['frac']
+        n_frames, n_atoms = int(cum.shape[0]), int(cum.shape[1])
+        base = dv.to_device(np.ascontiguousarray(self._host_base_positions()), torch.float64)
+        d_weights = dv.to_device(weights)
+        out = dv.empty((n_frames, 3), torch.float64)
+        _lib.check(_lib.lib.gd_frame_mean(dv.ptr(cum), dv.ptr(base), dv.ptr(d_weights), n_frames, n_atoms,
+                                          dv.ptr(out), dv.stream_ptr()))
+        return self.__class__(species=['X'], coords=dv.to_host(out)[:, None, :], lattice=self.lattice,
+                              metadata=self.metadata, time_step=self.time_step)
+
     # ------------------------------------------------------------------ K4: MSD
     def mean_squared_displacement(self, lags: tuple[int, int] | None = None) -> np.ndarray:
         """trajectory.py:896-933: per-atom MSD for every lag, [n_atoms, n_frames] Angstrom^2.

@@ -525,6 +525,44 @@ gd_status_t gd_unwrap_apply(const double *d_pos_frac, int64_t n_frames, int32_t 
                             double *d_dist, double *d_speed, void *stream);
 
 /* ------------------------------------------------------------------------- *
+ * Per-frame averages over atoms and the drift correction (callers on the input side of K0)
+ * replaces: Trajectory.center_of_mass (src/gemdat/trajectory.py:732-749: np.average of
+ *           base_positions + cumulative_displacements over the atoms, weights = masses),
+ *           Trajectory.drift (:751-791: np.mean of the fixed species' displacements per
+ *           frame) and Trajectory.apply_drift_correction (:793-830: displacements - drift,
+ *           later summed along the frames and wrapped by to_positions, :121-127).
+ * ------------------------------------------------------------------------- */
+
+/* d_out [n_frames,3] = sum_a w[a] (base[a] + x[t,a]) / sum_a w[a].  d_x [n_frames,n_atoms,3];
+ * d_base [n_atoms,3] or NULL (nothing added); d_weights [n_atoms] or NULL (plain mean).
+ * One CTA per frame, fixed reduction order (deterministic). */
+gd_status_t gd_frame_mean(const double *d_x, const double *d_base, const double *d_weights,
+                          int64_t n_frames, int32_t n_atoms, double *d_out, void *stream);
+
+/* d_drift [n_frames,3] = mean over the selected atoms of the wrapped step
+ * (x[t] - x[t-1]) - rint(x[t] - x[t-1]) of the fractional positions d_pos [n_frames,n_atoms,3].
+ * d_selected [n_selected] atom numbers, or NULL with n_selected == n_atoms (all atoms).
+ * Frame 0 has step 0 (pymatgen to_displacements) unless d_prev_row [n_atoms,3], the last
+ * row of the frame shard before this one, is given. */
+gd_status_t gd_drift(const double *d_pos, int64_t n_frames, int32_t n_atoms,
+                     const int32_t *d_selected, int32_t n_selected, const double *d_prev_row,
+                     double *d_drift, void *stream);
+
+/* inclusive sum along the frames of d_in [n_frames,3] -> d_out [n_frames,3] (block scans of
+ * 1024 frames + carries).  d_work: gd_cumsum_frames3_work_bytes(n_frames) bytes, 8-byte
+ * aligned; d_out must not alias d_in. */
+int64_t gd_cumsum_frames3_work_bytes(int64_t n_frames);
+gd_status_t gd_cumsum_frames3(const double *d_in, int64_t n_frames, void *d_work, double *d_out,
+                              void *stream);
+
+/* d_out [n_frames,n_atoms,3] = np.mod(d_base[a] + d_cumulative[t,a] - d_cumulative_drift[t], 1):
+ * the drift-corrected positions from K0's cumulative displacements (gd_unwrap d_cum_frac) and
+ * the summed drift.  d_out may be d_cumulative (in place). */
+gd_status_t gd_drift_correct(const double *d_cumulative, const double *d_base,
+                             const double *d_cumulative_drift, int64_t n_frames, int32_t n_atoms,
+                             double *d_out, void *stream);
+
+/* ------------------------------------------------------------------------- *
  * a4  vibration amplitudes
  * replaces: TrajectoryMetrics.amplitudes (src/gemdat/metrics.py:209-231: Python loop over
  *           atoms, np.sign / np.roll / np.array_split / np.sum) and the np.mean / np.std of

@@ -56,6 +56,14 @@ class Element:
     def __repr__(self):
         return f'Element {self.symbol}'
 
+    @property
+    def atomic_mass(self):
+        # pymatgen's periodic_table.json value [recalled]: the same table the product uses, so a
+        # golden made through this stub pins the centre-of-mass ARITHMETIC, not the table
+        from gemdat_b200.elements import ATOMIC_MASS
+
+        return ATOMIC_MASS[self.symbol]
+
 
 class Species(Element):
     pass

@@ -1186,6 +1186,143 @@ def test_rates_activation_energies_graph_vs_reference_golden(name):
         jumps.activation_energy_between_sites(int(a), int(a))
 
 
+# ------------------------------------------------------------------ drift / centre of mass
+def _mod1_close(a, b, atol):
+    """positions agree modulo 1 (a value next to 0 may come out next to 1)."""
+    d = np.abs(np.asarray(a) - np.asarray(b))
+    return np.minimum(d, 1.0 - d).max() <= atol
+
+
+DRIFT_CASES = {
+    # tag -> (kwargs of the call, golden tag).  floating_species: the reference averages over
+    # zero atoms there (tests/golden/make_golden_drift.py); the product follows the docstring,
+    # i.e. equals the fixed_species call with the complementary species
+    'all': ({}, 'all'),
+    'fixed_P_S': ({'fixed_species': ('P', 'S')}, 'fixed_P_S'),
+    'fixed_Br': ({'fixed_species': 'Br'}, 'fixed_Br'),
+    'floating_Li': ({'floating_species': 'Li'}, 'fixed_P_S_Br'),
+    'floating_Li_Br': ({'floating_species': ('Li', 'Br')}, 'fixed_P_S'),
+}
+
+
+@pytest.mark.parametrize('device_input', [False, True])
+@pytest.mark.parametrize('tag', list(DRIFT_CASES))
+def test_drift_correction_vs_reference_golden(tag, device_input):
+    """Trajectory.drift / apply_drift_correction (trajectory.py:751-830) against the reference's
+    outputs.  drift: 1e-12 relative (a mean over atoms in another order); corrected positions:
+    1e-11 absolute modulo 1 (the reference sums d - drift per atom sequentially, the kernels
+    subtract the summed drift from K0's cumulative displacement)."""
+    from conftest import load_golden
+    from gemdat_b200 import Trajectory, TrajectoryMetrics
+
+    g = load_golden('drift')
+    kw, gtag = DRIFT_CASES[tag]
+    coords = torch.from_numpy(g['coords']).cuda() if device_input else g['coords']
+    traj = Trajectory(species=[str(s) for s in g['species']], coords=coords, lattice=g['lattice'],
+                      metadata={'temperature': float(g['temperature'])}, time_step=float(g['time_step']))
+    drift = traj.drift(**kw)
+    assert drift.shape == g[f'drift/{gtag}'].shape
+    assert_allclose(drift, g[f'drift/{gtag}'], rtol=1e-12, atol=1e-18)
+    corrected = traj.apply_drift_correction(**kw)
+    pos = corrected.positions
+    assert dv_is_device(pos) == device_input
+    pos = pos.cpu().numpy() if device_input else pos
+    assert pos.min() >= 0.0 and pos.max() < 1.0
+    assert _mod1_close(pos, g[f'corrected/{gtag}/positions'], 1e-11)
+    d_li = TrajectoryMetrics(corrected.filter('Li')).tracer_diffusivity(dimensions=3)
+    assert_allclose(corrected.displacements, g[f'corrected/{gtag}/displacements'], rtol=0, atol=1e-11)
+    assert_allclose(float(d_li), float(g[f'corrected/{gtag}/tracer_diffusivity_Li']), rtol=1e-9)
+
+
+def dv_is_device(x):
+    return isinstance(x, torch.Tensor) and x.is_cuda
+
+
+def test_center_of_mass_and_scalar_metrics_vs_reference_golden():
+    """Trajectory.center_of_mass (trajectory.py:732-749) and TrajectoryMetrics.mol_per_liter /
+    tracer_diffusivity_center_of_mass / haven_ratio / tracer_conductivity (metrics.py:64-165)
+    against the reference's outputs, 1e-10 relative."""
+    from conftest import load_golden
+    from gemdat_b200 import Trajectory, TrajectoryMetrics
+
+    g = load_golden('drift')
+    species = [str(s) for s in g['species']]
+    traj = Trajectory(species=species, coords=g['coords'], lattice=g['lattice'],
+                      metadata={'temperature': float(g['temperature'])}, time_step=float(g['time_step']))
+    com = traj.center_of_mass()
+    assert com.species == ['X'] and com.coords.shape == g['com/coords'].shape
+    assert_allclose(com.coords, g['com/coords'], rtol=1e-12, atol=1e-13)
+    assert _mod1_close(traj.center_of_mass().positions, g['com/positions'], 1e-12)
+    li = traj.filter('Li')
+    assert_allclose(li.center_of_mass().coords, g['com_Li/coords'], rtol=1e-12, atol=1e-13)
+    m = TrajectoryMetrics(li)
+    assert_allclose(float(m.mol_per_liter()), float(g['metrics/mol_per_liter']), rtol=1e-12)
+    assert_allclose(float(m.tracer_diffusivity(dimensions=3)), float(g['metrics/tracer_diffusivity']), rtol=1e-10)
+    assert_allclose(float(m.tracer_diffusivity_center_of_mass(dimensions=3)),
+                    float(g['metrics/tracer_diffusivity_com']), rtol=1e-9)
+    assert_allclose(float(m.haven_ratio(dimensions=3)), float(g['metrics/haven_ratio']), rtol=1e-9)
+    assert_allclose(float(m.tracer_conductivity(z_ion=1, dimensions=3)), float(g['metrics/tracer_conductivity']),
+                    rtol=1e-10)
+    assert_allclose(float(m.tracer_conductivity(z_ion=2, dimensions=2)),
+                    float(g['metrics/tracer_conductivity_2d']), rtol=1e-10)
+    assert m.tracer_conductivity(z_ion=1).unit == 'S m^-1' and m.mol_per_liter().unit == 'mol l^-1'
+
+
+@pytest.mark.parametrize('n_frames,n_atoms', [(1, 5), (2, 1), (3001, 37), (20000, 300)])
+def test_drift_kernels_random_vs_oracle(n_frames, n_atoms):
+    """gd_drift / gd_cumsum_frames3 / gd_drift_correct / gd_frame_mean through the C ABI against
+    oracle/drift.py on random walks, incl. one frame, one atom, a ragged atom count."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+    from oracle import drift as odrift
+
+    rng = np.random.default_rng(n_frames + n_atoms)
+    steps = rng.normal(scale=0.01, size=(n_frames, n_atoms, 3)) + rng.normal(scale=0.003, size=(n_frames, 1, 3))
+    steps[0] = 0
+    pos = np.mod(rng.random((n_atoms, 3)) + np.cumsum(steps, axis=0), 1.0)
+    sel = np.sort(rng.choice(n_atoms, size=max(1, n_atoms // 2), replace=False)).astype(np.int32)
+    lib, s = _lib.lib, dv.stream_ptr()
+    # (every device buffer keeps a name until the end: a temporary would be freed, and its block
+    # handed to the next allocation, before the kernel that reads it runs)
+    d_pos = dv.to_device(pos)
+    d_sel = dv.to_device(sel)
+    d_base = dv.to_device(pos[0].copy())
+    d_drift = dv.empty((n_frames, 3), torch.float64)
+    _lib.check(lib.gd_drift(dv.ptr(d_pos), n_frames, n_atoms, dv.ptr(d_sel), len(sel), None, dv.ptr(d_drift), s))
+    want = odrift.drift(pos, sel)[:, 0]
+    assert_allclose(d_drift.cpu().numpy(), want, rtol=1e-12, atol=1e-18)
+    d_sum = dv.empty((n_frames, 3), torch.float64)
+    d_scan = dv.empty((int(lib.gd_cumsum_frames3_work_bytes(n_frames)),), torch.uint8)
+    _lib.check(lib.gd_cumsum_frames3(dv.ptr(d_drift), n_frames, dv.ptr(d_scan), dv.ptr(d_sum), s))
+    assert_allclose(d_sum.cpu().numpy(), np.cumsum(d_drift.cpu().numpy(), axis=0), rtol=1e-12, atol=1e-15)
+    # a frame shard: the row before the shard supplies frame 0's step
+    if n_frames > 10:
+        cut = n_frames // 3
+        part = dv.empty((n_frames - cut, 3), torch.float64)
+        _lib.check(lib.gd_drift(dv.ptr(d_pos[cut:]), n_frames - cut, n_atoms, dv.ptr(d_sel), len(sel),
+                                dv.ptr(d_pos[cut - 1]), dv.ptr(part), s))
+        assert_array_equal(part.cpu().numpy(), d_drift[cut:].cpu().numpy())
+    # corrected positions from the cumulative displacements
+    cum = np.cumsum(odrift.displacements(pos), axis=0)
+    d_cum = dv.to_device(cum)
+    d_out = dv.empty((n_frames, n_atoms, 3), torch.float64)
+    _lib.check(lib.gd_drift_correct(dv.ptr(d_cum), dv.ptr(d_base), dv.ptr(d_sum), n_frames, n_atoms, dv.ptr(d_out), s))
+    got = d_out.cpu().numpy()
+    assert got.min() >= 0.0 and got.max() < 1.0
+    assert _mod1_close(got, odrift.corrected_positions(pos, sel), 1e-11)
+    # weighted mean over the atoms of a frame
+    w = rng.random(n_atoms) + 0.5
+    d_w = dv.to_device(w)
+    d_mean = dv.empty((n_frames, 3), torch.float64)
+    _lib.check(lib.gd_frame_mean(dv.ptr(d_cum), dv.ptr(d_base), dv.ptr(d_w), n_frames, n_atoms, dv.ptr(d_mean), s))
+    assert_allclose(d_mean.cpu().numpy(), odrift.center_of_mass(pos, w)[:, 0], rtol=1e-12, atol=1e-13)
+    # in place
+    _lib.check(lib.gd_drift_correct(dv.ptr(d_cum), dv.ptr(d_base), dv.ptr(d_sum), n_frames, n_atoms, dv.ptr(d_cum), s))
+    assert_array_equal(d_cum.cpu().numpy(), got)
+    _lib.check(lib.gd_frame_mean(dv.ptr(d_pos), None, None, n_frames, n_atoms, dv.ptr(d_mean), s))
+    assert_allclose(d_mean.cpu().numpy(), pos.mean(axis=1), rtol=1e-12, atol=1e-15)
+
+
 @pytest.mark.parametrize('n_frames,n_atoms,n_sites', [(1, 1, 3), (257, 5, 7), (4099, 33, 64), (1000, 17, 60_000)])
 def test_n1_kernels_random_vs_oracle(n_frames, n_atoms, n_sites):
     """gd_occupancy (shared-memory bins; global atomics beyond 48k bins; unaligned input) and the

@@ -413,7 +413,9 @@ def _gpu_shards_worker(rank: int, world: int, port: int, out_path: str):
                  grid=fs.density(d_pos, grid_edges(Lattice(lat), 0.5)).cpu().numpy(),
                  counts=fs.site_counts(d_states, 7).cpu().numpy(),
                  msd=msd.cpu().numpy(), block=np.array([a_lo, a_hi]), curve=curve.cpu().numpy(),
-                 rdf=fs.species_rdf_counts(d_pos, idx, idx, bins, 0.25, True).cpu().numpy())
+                 rdf=fs.species_rdf_counts(d_pos, idx, idx, bins, 0.25, True).cpu().numpy(),
+                 corrected=fs.drift_correction(d_pos, np.arange(0, A, 2)).cpu().numpy(),
+                 com=fs.center_of_mass(d_pos, np.linspace(1.0, 2.0, A)).cpu().numpy())
     finally:
         dist.destroy_process_group()
 
@@ -422,7 +424,7 @@ def _gpu_shards_worker(rank: int, world: int, port: int, out_path: str):
 @pytest.mark.parametrize('world', [2, 3])
 def test_frame_shards_equal_one(tmp_path, world):
     """K0, ffill/bfill, K5, N1 counts, K4 (frames regrouped by atom, per-lag partial sums
-    all-reduced) and the species RDF over frame shards (ranks sharing cuda:0, gloo transport)
+    all-reduced), drift correction / centre of mass and the species RDF over frame shards (ranks sharing cuda:0, gloo transport)
     against one shard: bit-identical, the atom-averaged MSD curve to 1e-12."""
     from gemdat_b200.sharded import FrameShards
     from gemdat_b200.volume import grid_edges
@@ -455,3 +457,10 @@ def test_frame_shards_equal_one(tmp_path, world):
         np.testing.assert_array_equal(r['rdf'], rdf)
         np.testing.assert_allclose(r['curve'], curve.cpu().numpy(), rtol=1e-12)
     assert int(grid.sum()) == T * A and int(counts.sum()) == T * A
+    # drift correction: the summed drift is grouped by shard, so equal up to its rounding (mod 1)
+    want = fs.drift_correction(d_pos, np.arange(0, A, 2)).cpu().numpy()
+    got = np.vstack([r['corrected'] for r in ranks])
+    diff = np.abs(got - want)
+    assert np.minimum(diff, 1.0 - diff).max() < 1e-12
+    np.testing.assert_array_equal(np.vstack([r['com'] for r in ranks]),
+                                  fs.center_of_mass(d_pos, np.linspace(1.0, 2.0, A)).cpu().numpy())

@@ -414,3 +414,27 @@ def test_library_lll_equals_oracle_lll():
         assert_array_equal(mapping.reshape(3, 3), want_map)
         assert_allclose(lll.reshape(3, 3), want_lll, rtol=1e-12, atol=1e-12)
         assert abs(abs(np.linalg.det(mapping.reshape(3, 3))) - 1.0) < 1e-9
+
+
+# ------------------------------------------------------------------ drift / centre of mass
+DRIFT_SELECTIONS = {'all': None, 'fixed_P_S': {'P', 'S'}, 'fixed_Br': {'Br'}, 'fixed_P_S_Br': {'P', 'S', 'Br'}}
+
+
+def test_oracle_drift_equals_reference_golden():
+    """oracle/drift.py against the reference's Trajectory.drift / apply_drift_correction /
+    center_of_mass (trajectory.py:732-830; tests/golden/make_golden_drift.py): bit-exact."""
+    from conftest import load_golden
+    from gemdat_b200.elements import ATOMIC_MASS
+    from oracle import drift as odrift
+
+    g = load_golden('drift')
+    species = [str(s) for s in g['species']]
+    pos = g['coords']
+    for tag, names in DRIFT_SELECTIONS.items():
+        sel = [i for i, s in enumerate(species) if names is None or s in names]
+        assert_array_equal(odrift.drift(pos, sel), g[f'drift/{tag}'])
+        assert_array_equal(odrift.corrected_steps(pos, sel), g[f'corrected/{tag}/displacements'])
+        assert_array_equal(odrift.corrected_positions(pos, sel), g[f'corrected/{tag}/positions'])
+    assert_array_equal(odrift.center_of_mass(pos, [ATOMIC_MASS[s] for s in species]), g['com/coords'])
+    # the reference's floating_species route averages over zero atoms (see the generator's header)
+    assert np.isnan(g['drift/floating_Li'][1:]).all() and np.isnan(g['drift/floating_Li_Br'][1:]).all()

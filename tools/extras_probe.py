@@ -77,6 +77,23 @@ timed('a4 amplitudes fill', lambda: _lib.check(lib.gd_amplitudes_fill(dv.ptr(spe
 print(f'  amplitudes: {n_amp.value} ({n_amp.value / (T * A):.3f} per atom-frame)', flush=True)
 del speed, amp, awork
 
+# drift correction / centre of mass
+if hasattr(lib, 'gd_drift'):
+    d_drift = dv.empty((T, 3), torch.float64)
+    d_sum = dv.empty((T, 3), torch.float64)
+    frac = dv.empty((T, A, 3), torch.float64)
+    base = pos[0].clone()
+    com = dv.empty((T, 3), torch.float64)
+    timed('gd_drift (all atoms)', lambda: _lib.check(lib.gd_drift(dv.ptr(pos), T, A, None, A, None, dv.ptr(d_drift), s)), 24)
+    d_scan = dv.empty((int(lib.gd_cumsum_frames3_work_bytes(T)),), torch.uint8)
+    timed('gd_cumsum_frames3', lambda: _lib.check(lib.gd_cumsum_frames3(dv.ptr(d_drift), T, dv.ptr(d_scan), dv.ptr(d_sum), s)))
+    timed('K0 unwrap -> frac', lambda: _lib.check(lib.gd_unwrap(dv.ptr(pos), T, A, lat.ctypes.data, None, None, None,
+          dv.ptr(work), dv.ptr(frac), None, None, None, dv.ptr(wind), s)), 48)
+    timed('gd_frame_mean', lambda: _lib.check(lib.gd_frame_mean(dv.ptr(frac), dv.ptr(base), None, T, A, dv.ptr(com), s)), 24)
+    timed('gd_drift_correct (in place)', lambda: _lib.check(lib.gd_drift_correct(dv.ptr(frac), dv.ptr(base), dv.ptr(d_sum),
+          T, A, dv.ptr(frac), s)), 48)
+    del frac, com
+
 # K5
 nedges = grid_edges(Lattice(rec.lattice), 0.1)
 grid, flag = density_device(pos, nedges)
