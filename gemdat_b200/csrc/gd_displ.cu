@@ -232,6 +232,7 @@ struct FusedGeom {
     int32_t n_strips;
     int64_t n_tchunks;  // tiles along the frame axis
     int32_t prefetch;   // rows are 16-byte aligned: bulk L2 prefetch of the tile
+    int32_t dist_tile;  // the dynamic shared memory holds a 32 x 33 tile per warp: dist leaves transposed
 };
 
 __device__ __forceinline__ uint32_t st_pack(int32_t v, uint32_t state) {
@@ -246,6 +247,7 @@ __global__ void __launch_bounds__(kTileWarps * 32)
                    const __grid_constant__ Mat9 L, double *__restrict__ cum_frac,
                    double *__restrict__ cum_cart, double *__restrict__ dist,
                    double *__restrict__ speed, int32_t *__restrict__ winding_out) {
+    extern __shared__ double s_dyn[];  // requested to cap the CTAs per SM; holds the dist tiles
     __shared__ uint32_t s_tile;
     __shared__ int32_t s_agg[kTileWarps][3][32];
     __shared__ int32_t s_base[3][32];
@@ -389,6 +391,7 @@ __global__ void __launch_bounds__(kTileWarps * 32)
                     __dsub_rn(__dsub_rn(pz, bz), (double)wz));
     const double *q = pos + t0 * A3 + 3 * (int64_t)a;
     constexpr int kAhead2 = 4;
+    double *dist_tile = (dist && g.dist_tile) ? s_dyn + warp * (32 * 33) : nullptr;
     auto apply = [&](double x, double y, double z, int64_t t) {
         if (!(first_is_zero && t == 0)) {
             wx += winding(x, px);
@@ -416,10 +419,16 @@ __global__ void __launch_bounds__(kTileWarps * 32)
         }
         if (dist || speed) {
             const double d = length(cx, cy, cz);
-            if (on) {
-                if (dist) dist[(int64_t)a * g.n_frames + t] = d;
-                if (speed) speed[t * (int64_t)g.n_atoms + a] = d - pd;
+            if (dist) {
+                // dist is atom-major [A, T]: with lane = atom a direct store touches 32 rows per
+                // instruction.  The warp's 32 x 32 values go through shared memory instead and
+                // leave as 256-byte runs of one atom's row (below).
+                if (dist_tile)
+                    dist_tile[(int)(t - t0) * 33 + lane] = d;
+                else if (on)
+                    dist[(int64_t)a * g.n_frames + t] = d;
             }
+            if (speed && on) speed[t * (int64_t)g.n_atoms + a] = d - pd;
             pd = d;
         }
     };
@@ -439,6 +448,14 @@ __global__ void __launch_bounds__(kTileWarps * 32)
     for (; t < t1; ++t) {
         apply(q[0], q[1], q[2], t);
         q += A3;
+    }
+    if (dist_tile) {
+        __syncwarp();
+        const int n_t = (int)(t1 - t0);
+        const int n_a = min(32, g.n_atoms - strip * 32);
+        double *row = dist + (int64_t)strip * 32 * g.n_frames + t0 + lane;
+        for (int i = 0; i < n_a; ++i, row += g.n_frames)
+            if (lane < n_t) __stcs(row, dist_tile[lane * 33 + i]);
     }
 }
 
@@ -479,6 +496,7 @@ FusedGeom fused_geometry(int64_t n_frames, int32_t n_atoms) {
     g.n_strips = (n_atoms + 31) / 32;
     g.n_tchunks = gd_ceil_div(n_frames, kTileF);
     g.prefetch = 0;
+    g.dist_tile = 0;
     return g;
 }
 // int32 words of d_work the fused kernel needs: ticket (padded) + 96 status words per tile
@@ -568,6 +586,7 @@ extern "C" gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int
         GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");
         int smem = dev.max_smem_optin / per_sm - 2048;
         if (smem < 0) smem = 0;
+        fg.dist_tile = smem >= (int)(kTileWarps * 32 * 33 * sizeof(double));
         GD_CUDA_CHECK(cudaFuncSetAttribute(k_unwrap_fused, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            smem));
         k_unwrap_fused<<<(unsigned)tiles, kTileWarps * 32, (size_t)smem, st>>>(
