@@ -175,6 +175,9 @@ class HotPath:
                              site_radius=r, site_inner_fraction=f)
         self.n_atoms = n_atoms
         self.n_sites = len(frac)
+        # the visited-site flags only feed the integer_remap quirk (Q2), which exists for labelled
+        # radius groups; with the single group '' K1 is not asked for them (2.4 % of its time)
+        self._visited_needed = any(key is not None for key in self.grid.group_keys)
         self.minimal_residence = int(minimal_residence)
         self.n_frames_total = int(n_frames_total)
         self.frame0 = int(frame0)
@@ -294,7 +297,9 @@ class HotPath:
             e0.record()
         _lib.check(lib.gd_site_states_staged(dv.ptr(pos), n_frames, n_atoms, dv.ptr(next_pos),
                                              dv.ptr(self.grid.d_blob), self.grid.h_blob.ctypes.data,
-                                             dv.ptr(outer), dv.ptr(inner), dv.ptr(visited), dv.ptr(band),
+                                             dv.ptr(outer), dv.ptr(inner),
+                                             dv.ptr(visited) if self._visited_needed else None,
+                                             dv.ptr(band),
                                              dv.ptr(work), dv.ptr(changed), dv.ptr(stage), cap,
                                              dv.ptr(overflow) if stage is not None else None, s))
         if timed:
@@ -413,7 +418,7 @@ class HotPath:
         # event, so each shard runs its own slice and only the per-atom machine STATE crosses the
         # shard boundary (40 B per atom, `_jumps_frame_sharded`); the events never move.  Event
         # tables that are not state-consistent fall back to exchanging the rows by atom block.
-        res = {'outer': outer, 'inner': inner, 'visited': vis, 'band': band}
+        res = {'outer': outer, 'inner': inner, 'visited': vis if self._visited_needed else None, 'band': band}
         if self.world == 1:
             jumps, k3_launches = self._jumps_local(rows, offsets, n_atoms)
             res.update(events=rows, atom_offsets=offsets, events_layout='whole', jumps=jumps,
@@ -600,7 +605,7 @@ class HotPath:
         self.last_events_route = 'staged'
         self.launches_per_run = launches
         self.last_pass = 'optimistic'
-        return {'outer': k1.outer, 'inner': k1.inner, 'visited': vis, 'band': k1.band,
+        return {'outer': k1.outer, 'inner': k1.inner, 'visited': vis if self._visited_needed else None, 'band': k1.band,
                 'events': rows[:n_local], 'atom_offsets': offsets,
                 'events_layout': 'frame_shard' if W > 1 else 'whole', 'jumps': jumps_out,
                 'n_events': int((status >> 8).sum()), 'n_jumps': int(jumps_out.shape[0])}
