@@ -342,3 +342,30 @@ def test_sqrt_threshold_argument_of_the_rdf_binning():
                         continue
                     d = np.sqrt(d2)
                     assert (d > e if strict else d >= e) == (x <= d2), (e, strict, d2)
+
+
+def test_drift_selection_and_atomic_masses_host_logic():
+    """Host side of Trajectory.drift / center_of_mass (no device needed): which atoms the drift is
+    averaged over (trajectory.py:778-789; `floating_species` follows the docstring, see
+    tests/golden/make_golden_drift.py) and the mass look-up."""
+    from gemdat_b200 import Trajectory
+    from gemdat_b200.elements import atomic_mass
+
+    species = ['Li', 'Li+', 'P', 'S', 'S2-', 'Br']
+    traj = Trajectory(species=species, coords=np.zeros((2, 6, 3)), lattice=np.eye(3) * 10, time_step=1e-15)
+    assert traj._selected_atoms(None, None).tolist() == [0, 1, 2, 3, 4, 5]
+    assert traj._selected_atoms('S', None).tolist() == [3, 4]
+    assert traj._selected_atoms(('P', 'Br'), None).tolist() == [2, 5]
+    assert traj._selected_atoms(None, 'Li').tolist() == [2, 3, 4, 5]
+    assert traj._selected_atoms(None, ('Li', 'S')).tolist() == [2, 5]
+    assert traj._selected_atoms('P', 'Li').tolist() == [2]  # fixed_species wins, like the reference
+    assert traj._selected_atoms('Xe', None).size == 0
+    assert atomic_mass('Li') == atomic_mass('Li+') == 6.941
+    assert atomic_mass('S2-') == 32.065
+
+    class WithMass:
+        atomic_mass = 12.5
+
+    assert atomic_mass(WithMass()) == 12.5
+    with pytest.raises(KeyError):
+        atomic_mass('Qq')
