@@ -580,7 +580,10 @@ extern "C" gd_status_t gd_unwrap(const double *d_pos_frac, int64_t n_frames, int
         // shared memory request only caps the CTAs per SM (GD_UNWRAP_CTAS_PER_SM, default 5:
         // 148 x 5 x 96 KB = 71 MB of the 126 MB L2; measured 3 / 4 / 5 / 6 / 8 per SM: 3749 /
         // 5026 / 5301 / 4745 / 4365 GB/s, profiles/r2h_k0_sweep.txt)
-        int per_sm = 5;
+        // (with only the 8-byte outputs -- distance, speed -- 6 per SM is the optimum:
+        // 4 / 5 / 6 / 7 per SM: 3.61 / 2.99 / 2.74 / 2.74 ms per 4e8 atom-frames for the speed, and
+        // 6 is the most the distance tile fits, profiles/r2zf_k0_persm.txt)
+        int per_sm = (d_cum_frac || d_cum_cart) ? 5 : 6;
         if (const char *e = getenv("GD_UNWRAP_CTAS_PER_SM")) per_sm = atoi(e) > 0 ? atoi(e) : per_sm;
         const GdDeviceInfo &dev = gd_device_info();
         GD_REQUIRE(dev.sm_count > 0, GD_ERR_CUDA, "no CUDA device");

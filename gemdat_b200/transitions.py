@@ -126,20 +126,25 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
     and the "state ever changes" flags K2 needs (``info['event_work']``, ``info['changed']``).
     """
     site_frac, site_labels, _ = site_arrays(sites)
-    grid = SiteGrid(
-        lattice_matrix=trajectory.get_lattice().matrix,
-        site_frac=site_frac,
-        site_labels=site_labels,
-        site_radius=site_radius,
-        site_inner_fraction=site_inner_fraction,
-    )
+
+    def make_grid():
+        return SiteGrid(
+            lattice_matrix=trajectory.get_lattice().matrix,
+            site_frac=site_frac,
+            site_labels=site_labels,
+            site_radius=site_radius,
+            site_inner_fraction=site_inner_fraction,
+        )
+
     host_future = None
     resident = True
-    if _wants_pipeline(trajectory, count_events):
+    pipelined = _wants_pipeline(trajectory, count_events)
+    grid = None if pipelined else make_grid()
+    if pipelined:
         # host-resident input: upload, K1 and the download of the int64 states run as a
         # three-stage pipeline over frame parts (PCIe is full duplex); events are counted by the
         # stand-alone pass afterwards (it re-reads 8 B/atom-frame from HBM, noise next to PCIe)
-        pos, outer, inner, visited, band, host_future, outside = _pipelined_states(trajectory, grid)
+        pos, outer, inner, visited, band, host_future, outside, grid = _pipelined_states(trajectory, make_grid)
         n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
         work = changed = None
         # some coordinate was outside [0, 1): the device copy was wrapped afterwards (np.mod of
@@ -196,7 +201,7 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
 
 
 PIPELINE_MIN_BYTES = 64 << 20
-PIPELINE_PARTS = 16
+PIPELINE_PARTS = 32  # 16: 59.2 ms, 32: 57.6, 48: 57.0 per 1e5 C3 frames (profiles/r2zh_e2e_parts.txt)
 
 
 def _wants_pipeline(trajectory, count_events: bool) -> bool:
@@ -260,19 +265,21 @@ class HostStates:
         return self._inner.numpy()
 
 
-def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
+def _pipelined_states(trajectory, grid, trace: list | None = None):
     """K1 over frame parts with upload (copy stream), compute (current stream) and the
-    download of the widened states (second copy stream) overlapped."""
+    download of the widened states (second copy stream) overlapped.
+
+    ``grid`` is a ``SiteGrid`` or a callable that builds one: the build runs on the host
+    (~7 ms for the 2160 sites of C3) and is started AFTER the first uploads are queued, so it hides
+    behind the copies instead of delaying them."""
     lib = _lib.lib
     dev = dv.require_cuda()
     coords = trajectory.coords
     n_frames, n_atoms = int(coords.shape[0]), int(coords.shape[1])
-    d_blob = grid.d_blob  # small table upload first: it shares the H2D engine with the parts below
     src = torch.from_numpy(coords)
     pos = dv.empty((n_frames, n_atoms, 3), torch.float64)
     outer = dv.empty((n_frames, n_atoms), torch.int32)
     inner = dv.empty((n_frames, n_atoms), torch.int32)
-    visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
     band = dv.zeros((4,), torch.int64)
     outside = dv.zeros((1,), torch.int32)  # set when a coordinate lies outside [0, 1)
     host_o = torch.empty((n_frames, n_atoms), dtype=torch.int64, pin_memory=True)
@@ -312,11 +319,24 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
             if pageable:
                 bounce_free[k % 2] = uploaded[k]
 
-    upload(0)
+    # page-locked source: uploads are queued `ahead` parts in front of the compute, enough copy
+    # time to cover the host-side build of the site grid; its small table then queues behind
+    # those parts only.  Pageable source: every upload costs host time, one part ahead.
+    ahead = 1 if pageable or not callable(grid) else max(1, min(n_parts, n_parts // 5))
+    for k in range(ahead):
+        upload(k)
+    if callable(grid):
+        try:
+            grid = grid()
+        except Exception:
+            up.synchronize()  # queued copies still write into `pos`: let them finish before it is freed
+            raise
+    d_blob = grid.d_blob
+    visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
     done = torch.cuda.Event()
     for k in range(n_parts):
-        if k + 1 < n_parts and not pageable:
-            upload(k + 1)
+        if k + ahead < n_parts and not pageable:
+            upload(k + ahead)
         f0, f1 = bounds[k], bounds[k + 1]
         main.wait_event(uploaded[k])
         _lib.check(lib.gd_wrap_unit(dv.ptr(pos[f0:f1]), None, (f1 - f0) * n_atoms * 3, dv.ptr(outside),
@@ -354,7 +374,7 @@ def _pipelined_states(trajectory, grid: 'SiteGrid', trace: list | None = None):
         _lib.check(lib.gd_wrap_unit(dv.ptr(pos), dv.ptr(pos), pos.numel(), dv.ptr(outside), main.cuda_stream))
     holder = trajectory.__dict__.setdefault('_dev_holder', {})
     holder['pos'] = (coords, pos)
-    return pos, outer, inner, visited, band, HostStates(host_o, host_i, done), was_outside
+    return pos, outer, inner, visited, band, HostStates(host_o, host_i, done), was_outside, grid
 
 
 def widen_to_host(t: torch.Tensor) -> np.ndarray:

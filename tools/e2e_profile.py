@@ -22,7 +22,7 @@ def step():
     torch.cuda.synchronize()
     t3 = time.perf_counter()
     return np.array([t1 - t0, t2 - t1, t3 - t2, t3 - t0]) * 1e3
-for parts in (0, 4, 8, 16):
+for parts in (8, 16, 24, 32, 48, 64):
     gt.PIPELINE_MIN_BYTES = (1 << 60) if parts == 0 else 0
     gt.PIPELINE_PARTS = max(parts, 1)
     for _ in range(3): step()
