@@ -382,6 +382,7 @@ __global__ void __launch_bounds__(1024) k_scan_atoms(int64_t *__restrict__ off, 
 }
 
 // ---------------------------------------------------------------- ffill / bfill
+constexpr int kFillAhead = 8;
 
 // phase 1: last valid state of every (chunk, atom) segment, in scan direction
 __global__ void __launch_bounds__(256)
@@ -393,18 +394,22 @@ __global__ void __launch_bounds__(256)
     const int32_t a = (int32_t)(item - c * g.n_atoms);
     const int64_t t0 = c * g.f, t1 = min(g.n_frames, t0 + g.f);
     int32_t last = GD_NOSITE;
-    if (direction > 0) {
-#pragma unroll 4
-        for (int64_t t = t0; t < t1; ++t) {
-            const int32_t v = s[t * g.n_atoms + a];
-            last = v != GD_NOSITE ? v : last;
-        }
-    } else {
-#pragma unroll 4
-        for (int64_t t = t1 - 1; t >= t0; --t) {
-            const int32_t v = s[t * g.n_atoms + a];
-            last = v != GD_NOSITE ? v : last;
-        }
+    // kFillAhead rows are in flight per thread (the loads do not depend on `last`)
+    const int64_t A = g.n_atoms;
+    const int64_t step = direction > 0 ? A : -A;
+    const int32_t *q = s + (direction > 0 ? t0 : t1 - 1) * A + a;
+    int64_t left = t1 - t0;
+    for (; left >= kFillAhead; left -= kFillAhead) {
+        int32_t v[kFillAhead];
+#pragma unroll
+        for (int j = 0; j < kFillAhead; ++j) v[j] = __ldcs(q + j * step);
+        q += kFillAhead * step;
+#pragma unroll
+        for (int j = 0; j < kFillAhead; ++j) last = v[j] != GD_NOSITE ? v[j] : last;
+    }
+    for (; left > 0; --left, q += step) {
+        const int32_t v = __ldcs(q);
+        last = v != GD_NOSITE ? v : last;
     }
     work[c * g.n_atoms + a] = last;
 }
@@ -454,20 +459,28 @@ __global__ void __launch_bounds__(256)
     // chunk carries computed without knowing the neighbouring shard: where no valid state was
     // seen yet inside this shard, the state carried over the shard boundary applies
     if (shard_carry && last == GD_NOSITE) last = shard_carry[a];
-    if (direction > 0) {
-#pragma unroll 4
-        for (int64_t t = t0; t < t1; ++t) {
-            const int32_t v = s[t * g.n_atoms + a];
-            last = v != GD_NOSITE ? v : last;
-            out[t * g.n_atoms + a] = last;
+    const int64_t A = g.n_atoms;
+    const int64_t step = direction > 0 ? A : -A;
+    const int64_t first = (direction > 0 ? t0 : t1 - 1) * A + a;
+    const int32_t *q = s + first;
+    int32_t *o = out + first;
+    int64_t left = t1 - t0;
+    for (; left >= kFillAhead; left -= kFillAhead) {
+        int32_t v[kFillAhead];
+#pragma unroll
+        for (int j = 0; j < kFillAhead; ++j) v[j] = __ldcs(q + j * step);
+        q += kFillAhead * step;
+#pragma unroll
+        for (int j = 0; j < kFillAhead; ++j) {
+            last = v[j] != GD_NOSITE ? v[j] : last;
+            __stcs(o + j * step, last);
         }
-    } else {
-#pragma unroll 4
-        for (int64_t t = t1 - 1; t >= t0; --t) {
-            const int32_t v = s[t * g.n_atoms + a];
-            last = v != GD_NOSITE ? v : last;
-            out[t * g.n_atoms + a] = last;
-        }
+        o += kFillAhead * step;
+    }
+    for (; left > 0; --left, q += step, o += step) {
+        const int32_t v = __ldcs(q);
+        last = v != GD_NOSITE ? v : last;
+        __stcs(o, last);
     }
 }
 

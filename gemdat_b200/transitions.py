@@ -100,6 +100,17 @@ class SiteGrid:
             self._d_blob = dv.to_device(self.h_blob)
         return self._d_blob
 
+    def upload_async(self) -> torch.Tensor:
+        """Device copy of the table queued on the current stream from a page-locked staging copy,
+        without blocking the host (the upload pipeline has part copies in flight at that point)."""
+        if self._d_blob is None:
+            self._pinned_blob = torch.empty((self.h_blob.nbytes,), dtype=torch.uint8, pin_memory=True)
+            self._pinned_blob.numpy()[:] = self.h_blob
+            d = dv.empty((self.h_blob.nbytes,), torch.uint8)
+            d.copy_(self._pinned_blob, non_blocking=True)
+            self._d_blob = d
+        return self._d_blob
+
     def remap_lut(self, visited: np.ndarray) -> np.ndarray | None:
         """LUT natural index -> reported index for the integer_remap quirk, None if identity.
 
@@ -201,6 +212,12 @@ def _site_states_device(*, sites, trajectory, site_radius: dict, site_inner_frac
 
 
 PIPELINE_MIN_BYTES = 64 << 20
+# parts whose upload is queued before the site grid is built (and kept in front of the compute).
+# Measured on B200 / PCIe 5 (profiles/r2zl_e2e_ahead.txt): 1 / 2 / 4 / 6 ahead = 56.1 / 55.2 / 52.8 /
+# 51.1 ms per 1e5 C3 frames with the 7 ms grid build of 2160 sites, but with a fast build (200 sites)
+# 50.2 / 48.8 / 73.4 / 73.8 ms: once several uploads are still queued when the first downloads are
+# issued, the two directions stop overlapping (48 + 25 ms).  2 is safe in both regimes.
+PIPELINE_AHEAD = 2
 PIPELINE_PARTS = 32  # 16: 59.2 ms, 32: 57.6, 48: 57.0 per 1e5 C3 frames (profiles/r2zh_e2e_parts.txt)
 
 
@@ -319,10 +336,10 @@ def _pipelined_states(trajectory, grid, trace: list | None = None):
             if pageable:
                 bounce_free[k % 2] = uploaded[k]
 
-    # page-locked source: uploads are queued `ahead` parts in front of the compute, enough copy
-    # time to cover the host-side build of the site grid; its small table then queues behind
-    # those parts only.  Pageable source: every upload costs host time, one part ahead.
-    ahead = 1 if pageable or not callable(grid) else max(1, min(n_parts, n_parts // 5))
+    # page-locked source: uploads are queued `ahead` parts in front of the compute and the
+    # host-side build of the site grid runs while they are in flight; its small table then queues
+    # behind those parts only.  Pageable source: every upload costs host time, one part ahead.
+    ahead = 1 if pageable or not callable(grid) else max(1, min(n_parts, PIPELINE_AHEAD))
     for k in range(ahead):
         upload(k)
     if callable(grid):
@@ -331,7 +348,7 @@ def _pipelined_states(trajectory, grid, trace: list | None = None):
         except Exception:
             up.synchronize()  # queued copies still write into `pos`: let them finish before it is freed
             raise
-    d_blob = grid.d_blob
+    d_blob = grid.upload_async()
     visited = dv.zeros((2 * grid.n_sites,), torch.uint8)
     done = torch.cuda.Event()
     for k in range(n_parts):
