@@ -29,21 +29,34 @@ constexpr int kWin = kBT + kLagsPerBlock;  // r[t+k] window elements per tile
 __host__ __device__ constexpr int padded(int j) { return j + (j >> 3); }
 constexpr int kWinPad = kWin + (kWin >> 3) + 8;
 
-// [T, A, 3] -> [A, 3, T] through 32x32 shared tiles (rows = frames, cols = atom*3+c)
+// [T, A, 3] -> [A, 3, T] through shared tiles of kTrT frames x 32 columns (column = atom*3+c):
+// eight loads per thread are in flight before the first store, output runs are kTrT * 8 bytes
+constexpr int kTrT = 64;
 __global__ void __launch_bounds__(256)
     k_to_soa(const double *__restrict__ in, int64_t n_frames, int64_t n_cols,
              double *__restrict__ out) {
-    __shared__ double tile[32][33];
-    const int64_t t0 = (int64_t)blockIdx.x * 32, c0 = (int64_t)blockIdx.y * 32;
+    __shared__ double tile[kTrT][33];
+    const int64_t t0 = (int64_t)blockIdx.x * kTrT, c0 = (int64_t)blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-    for (int r = ty; r < 32; r += 8) {
-        const int64_t t = t0 + r, c = c0 + tx;
-        if (t < n_frames && c < n_cols) tile[r][tx] = in[t * n_cols + c];
+    double v[kTrT / 8];
+#pragma unroll
+    for (int k = 0; k < kTrT / 8; ++k) {
+        const int64_t t = t0 + ty + 8 * k, c = c0 + tx;
+        v[k] = (t < n_frames && c < n_cols) ? __ldcs(in + t * n_cols + c) : 0.0;
     }
+#pragma unroll
+    for (int k = 0; k < kTrT / 8; ++k) tile[ty + 8 * k][tx] = v[k];
     __syncthreads();
-    for (int r = ty; r < 32; r += 8) {
-        const int64_t c = c0 + r, t = t0 + tx;
-        if (t < n_frames && c < n_cols) out[c * n_frames + t] = tile[tx][r];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int r = ty + 8 * k;  // column of the tile = row of the output
+        const int64_t c = c0 + r;
+        if (c >= n_cols) continue;
+#pragma unroll
+        for (int h = 0; h < kTrT / 32; ++h) {
+            const int64_t t = t0 + tx + 32 * h;
+            if (t < n_frames) __stcs(out + c * n_frames + t, tile[tx + 32 * h][r]);
+        }
     }
 }
 
@@ -138,7 +151,7 @@ extern "C" gd_status_t gd_transpose_soa(const double *d_in, int64_t n_frames, in
     GD_REQUIRE(d_in && d_out && n_frames > 0 && n_atoms > 0, GD_ERR_INVALID,
                "gd_transpose_soa: bad argument");
     const int64_t n_cols = (int64_t)n_atoms * 3;
-    dim3 grid((unsigned)gd_ceil_div(n_frames, 32), (unsigned)gd_ceil_div(n_cols, 32));
+    dim3 grid((unsigned)gd_ceil_div(n_frames, kTrT), (unsigned)gd_ceil_div(n_cols, 32));
     GD_REQUIRE(grid.y <= 65535, GD_ERR_INVALID, "gd_transpose_soa: too many atoms");
     k_to_soa<<<grid, 256, 0, (cudaStream_t)stream>>>(d_in, n_frames, n_cols, d_out);
     GD_LAUNCH_CHECK();
@@ -149,7 +162,7 @@ extern "C" gd_status_t gd_transpose_f64(const double *d_in, int64_t n_rows, int6
                                         double *d_out, void *stream) {
     GD_REQUIRE(d_in && d_out && n_rows > 0 && n_cols > 0, GD_ERR_INVALID,
                "gd_transpose_f64: bad argument");
-    dim3 grid((unsigned)gd_ceil_div(n_rows, 32), (unsigned)gd_ceil_div(n_cols, 32));
+    dim3 grid((unsigned)gd_ceil_div(n_rows, kTrT), (unsigned)gd_ceil_div(n_cols, 32));
     GD_REQUIRE(grid.y <= 65535, GD_ERR_INVALID, "gd_transpose_f64: too many columns");
     k_to_soa<<<grid, 256, 0, (cudaStream_t)stream>>>(d_in, n_rows, n_cols, d_out);
     GD_LAUNCH_CHECK();

@@ -161,6 +161,12 @@ class Jumps:
     def _part_counters(self, n_parts: int) -> list[Counter]:
         return [part.counter() for part in self.split(n_parts)]
 
+    def _unique_site_pairs(self) -> list[tuple[str, str]]:
+        """``site_pairs`` without its repetitions, in the same order of first appearance (the
+        reference walks all n_sites^2 pairs and overwrites equal keys with equal values)."""
+        _, labels, _ = site_arrays(self.sites)
+        return list(product(dict.fromkeys(labels), repeat=2))
+
     @weak_lru_cache()
     def rates(self, n_parts: int = 10) -> pd.DataFrame:
         """jumps.py:435-462: jumps per second and per floating atom between site labels, mean and
@@ -168,7 +174,7 @@ class Jumps:
         counters = self._part_counters(n_parts)
         denom = self.n_floating * (self.trajectory.total_time / n_parts)
         table = {}
-        for pair in dict.fromkeys(self.site_pairs):  # the reference visits duplicates again: same value
+        for pair in self._unique_site_pairs():
             n_jumps = [c[pair] for c in counters]
             table[pair] = float(np.mean(n_jumps) / denom), float(np.std(n_jumps, ddof=1) / denom)
         df = pd.DataFrame(table).T
@@ -193,7 +199,7 @@ class Jumps:
         n_floating = self.n_floating
         part_time = trajectory.total_time / n_parts
         table = {}
-        for start, stop in dict.fromkeys(self.site_pairs):
+        for start, stop in self._unique_site_pairs():
             n_jumps = np.array([c[start, stop] for c in counters])
             share = np.array([loc[start] for loc in locations])
             eff_rate = n_jumps / (share * n_floating * part_time)
