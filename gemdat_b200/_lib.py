@@ -128,6 +128,9 @@ SIGNATURES = {
     'gd_rdf_classes': (C.c_int, [_p, _p, _p, _i64, _i32, _p, _i32, _i32, _p, _p, _p, _p]),
     'gd_rdf_hist': (C.c_int, [_p, _i64, _i32, _p, _p, _i32, _p, _i32, _p, _p, _i32, _i32, _p, _i32,
                               C.c_double, _i32, _i32, _p, _p]),
+    'gd_rdf_frames_work_bytes': (_i64, [_i64]),
+    'gd_rdf_hist_frames': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _i32, _p, _p, _p, _i32, _i32, _p, _i32,
+                                     C.c_double, _i32, _i32, _p, _p]),
     'gd_unwrap_chunks': (_i64, [_i64, _i32]),
     'gd_unwrap': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     'gd_unwrap_windings': (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p]),

@@ -20,6 +20,8 @@
 // general cell, one candidate per axis for an axis-aligned one.  Pairs beyond the last edge -- the
 // bulk when the cell is larger than max_dist -- are counted in registers; the others find their
 // bin from an fp32 guess corrected against exact per-edge thresholds on d2.
+#include <vector>
+
 #include "gd_common.cuh"
 #include "gd_pbc.cuh"
 
@@ -52,7 +54,8 @@ struct RdfParams {
     int32_t tile;  // targets per shared-memory tile
     double inv_res;
     GdPbc pbc;
-    unsigned long long *hist;  // [n_class, n_group, n_edges + 1]
+    const GdPbc *pbc_frames;   // kPerFrame: one cell per frame (the lattice changes along the run)
+    unsigned long long *hist;  // [n_class, n_group, n_edges + 1]; kPerFrame: [n_frames, n_group, n_edges + 1]
 };
 
 // Smallest x >= 0 whose correctly rounded square root is >= e (strict: > e).  sqrt is monotonic,
@@ -74,7 +77,10 @@ constexpr int kOverGroups = 4;  // groups whose beyond-the-last-edge pairs are c
 // counter.  When the edges are k * resolution (np.arange from 0) the fp32 bin guess is off by at
 // most one and a single comparison with each neighbouring threshold is exact; other edge lists
 // (checked once per CTA) keep the search loops.
-template <bool kOneGroup>
+// kPerFrame: the cell of frame t is pbc_frames[t] (copied to shared memory once per frame) and the
+// counts of frame t go to their own table hist[t] -- the caller weights them with the frame's volume
+// (rdf.py:248-261); d_class then only marks sources to skip (< 0).
+template <bool kOneGroup, bool kPerFrame>
 __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int nb = p.n_edges + 1;
@@ -106,6 +112,7 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
     }
     for (int k = threadIdx.x; k < kWarps * hist_len; k += blockDim.x) s_hist[k] = 0;
     __shared__ int s_irregular;
+    __shared__ GdPbc s_pbc;
     if (threadIdx.x == 0) s_irregular = 0;
     __syncthreads();
     for (int k = threadIdx.x; k < p.n_edges; k += blockDim.x)
@@ -117,6 +124,14 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
 
     for (int64_t t = blockIdx.x; t < p.n_frames; t += gridDim.x) {
         const double *frame = p.pos + t * (int64_t)p.n_atoms * 3;
+        if (kPerFrame) {
+            __syncthreads();  // the frame before is done with s_pbc
+            const int *src = reinterpret_cast<const int *>(p.pbc_frames + t);
+            int *dst = reinterpret_cast<int *>(&s_pbc);
+            for (int k = threadIdx.x; k < (int)(sizeof(GdPbc) / sizeof(int)); k += blockDim.x) dst[k] = src[k];
+            // (the __syncthreads at the top of the tile loop publishes it)
+        }
+        const GdPbc &P = kPerFrame ? s_pbc : p.pbc;
         for (int j0 = 0; j0 < p.n2; j0 += p.tile) {
             const int nt = min(p.tile, p.n2 - j0);
             __syncthreads();
@@ -126,7 +141,7 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                 s_ag[k] = atom | (grp << 24);
                 const double *q = frame + 3 * (int64_t)atom;
                 double c[3];
-                gd_pbc_cart(p.pbc, q[0], q[1], q[2], c);
+                gd_pbc_cart(P, q[0], q[1], q[2], c);
                 s_x[k] = c[0];
                 s_y[k] = c[1];
                 s_z[k] = c[2];
@@ -139,14 +154,14 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                 const int32_t self = p.skip_same ? p.idx1[i] : -1;
                 const double *q = frame + 3 * (int64_t)p.idx1[i];
                 double a[3];
-                gd_pbc_cart(p.pbc, q[0], q[1], q[2], a);
+                gd_pbc_cart(P, q[0], q[1], q[2], a);
                 // pairs beyond the last edge are the bulk (the cell is much larger than max_dist):
                 // they are counted in registers, per group, and added once per (source, tile)
                 uint32_t over[kOverGroups] = {0, 0, 0, 0};
                 auto pair = [&](int k) {
                     const int32_t ag = s_ag[k];
                     const double b[3] = {s_x[k], s_y[k], s_z[k]};
-                    const double d2 = gd_pbc_d2(p.pbc, a, b);
+                    const double d2 = gd_pbc_d2(P, a, b);
                     if ((ag & 0xFFFFFF) == self) return;
                     const int grp = kOneGroup ? 0 : ag >> 24;
                     if (d2 >= th_over && reg_over) {
@@ -183,7 +198,7 @@ __global__ void GD_RDF_BOUNDS k_rdf_hist(const __grid_constant__ RdfParams p) {
                     }
                 }
                 __syncwarp();
-                unsigned long long *dst = p.hist + (size_t)cls * hist_len;
+                unsigned long long *dst = p.hist + (size_t)(kPerFrame ? t : (int64_t)cls) * hist_len;
                 for (int k2 = lane; k2 < hist_len; k2 += 32) {
                     const uint32_t n = my_hist[k2];
                     if (n) {
@@ -235,6 +250,49 @@ extern "C" gd_status_t gd_rdf_classes(const int32_t *d_states, const int32_t *d_
     return GD_OK;
 }
 
+namespace {
+
+// common part of gd_rdf_hist / gd_rdf_hist_frames: shared-memory budget, grid, launch
+gd_status_t rdf_launch(RdfParams &p, bool per_frame, void *stream) {
+    const int64_t n_frames = p.n_frames;
+    const int32_t n1 = p.n1, n2 = p.n2, n_group = p.n_group, n_edges = p.n_edges;
+    const GdDeviceInfo &dev = gd_device_info();
+    const size_t smem_cap = (size_t)(dev.max_smem_optin > 0 ? dev.max_smem_optin : 200 * 1024) -
+                            (per_frame ? 1024 : 0);  // (room for the static copy of the frame's cell)
+    const size_t fixed = (size_t)(n_edges + 2) * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
+    GD_REQUIRE(fixed + 32 * 32 <= smem_cap, GD_ERR_CAPACITY,
+               "gd_rdf_hist: %d groups x %d bins do not fit the per-warp shared-memory histograms", n_group,
+               n_edges + 1);
+    int64_t tile = (int64_t)((smem_cap - fixed) / 32);
+    if (tile > n2) tile = n2;
+    if (tile > 4096) tile = 4096;
+    p.tile = (int32_t)tile;
+    const size_t smem = (size_t)p.tile * 32 + fixed;
+    const int sms = dev.sm_count > 0 ? dev.sm_count : 148;
+    int64_t gy = gd_ceil_div((int64_t)sms * 4, n_frames);
+    const int64_t gy_max = gd_ceil_div(n1, kWarps);
+    if (gy > gy_max) gy = gy_max;
+    if (gy < 1) gy = 1;
+    int64_t gx = n_frames < (int64_t)sms * 64 ? n_frames : (int64_t)sms * 64;
+    dim3 grid((unsigned)gx, (unsigned)gy);
+    const bool one_group = n_group == 1;
+    auto launch = [&](auto kernel) -> gd_status_t {
+        GD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kernel<<<grid, kWarps * 32, smem, (cudaStream_t)stream>>>(p);
+        return GD_OK;
+    };
+    gd_status_t rc;
+    if (per_frame)
+        rc = one_group ? launch(k_rdf_hist<true, true>) : launch(k_rdf_hist<false, true>);
+    else
+        rc = one_group ? launch(k_rdf_hist<true, false>) : launch(k_rdf_hist<false, false>);
+    if (rc != GD_OK) return rc;
+    GD_LAUNCH_CHECK();
+    return GD_OK;
+}
+
+}  // namespace
+
 extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
                                    const double *h_lattice, const int32_t *d_idx1, int32_t n1,
                                    const int32_t *d_class, int32_t n_class, const int32_t *d_idx2,
@@ -267,33 +325,55 @@ extern "C" gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, i
     p.inv_res = 1.0 / resolution;
     p.hist = d_hist;
     p.pbc = gd_pbc_build(h_lattice);
-    const GdDeviceInfo &dev = gd_device_info();
-    const size_t smem_cap = (size_t)(dev.max_smem_optin > 0 ? dev.max_smem_optin : 200 * 1024);
-    const size_t fixed = (size_t)(n_edges + 2) * 8 + (size_t)kWarps * n_group * (n_edges + 1) * 4 + 64;
-    GD_REQUIRE(fixed + 32 * 32 <= smem_cap, GD_ERR_CAPACITY,
-               "gd_rdf_hist: %d groups x %d bins do not fit the per-warp shared-memory histograms", n_group,
-               n_edges + 1);
-    int64_t tile = (int64_t)((smem_cap - fixed) / 32);
-    if (tile > n2) tile = n2;
-    if (tile > 4096) tile = 4096;
-    p.tile = (int32_t)tile;
-    const size_t smem = (size_t)p.tile * 32 + fixed;
-    const int sms = dev.sm_count > 0 ? dev.sm_count : 148;
-    int64_t gy = gd_ceil_div((int64_t)sms * 4, n_frames);
-    const int64_t gy_max = gd_ceil_div(n1, kWarps);
-    if (gy > gy_max) gy = gy_max;
-    if (gy < 1) gy = 1;
-    int64_t gx = n_frames < (int64_t)sms * 64 ? n_frames : (int64_t)sms * 64;
-    dim3 grid((unsigned)gx, (unsigned)gy);
-    const bool one_group = n_group == 1;
-    auto launch = [&](auto kernel) -> gd_status_t {
-        GD_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kernel<<<grid, kWarps * 32, smem, (cudaStream_t)stream>>>(p);
-        return GD_OK;
-    };
-    gd_status_t rc;
-    rc = one_group ? launch(k_rdf_hist<true>) : launch(k_rdf_hist<false>);
-    if (rc != GD_OK) return rc;
-    GD_LAUNCH_CHECK();
-    return GD_OK;
+    p.pbc_frames = nullptr;
+    return rdf_launch(p, false, stream);
+}
+
+extern "C" int64_t gd_rdf_frames_work_bytes(int64_t n_frames) {
+    return (n_frames > 0 ? n_frames : 1) * (int64_t)sizeof(GdPbc);
+}
+
+extern "C" gd_status_t gd_rdf_hist_frames(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                                          const double *h_lattices, void *d_work, const int32_t *d_idx1,
+                                          int32_t n1, const int32_t *d_skip, const int32_t *d_idx2,
+                                          const int32_t *d_group, int32_t n2, int32_t n_group,
+                                          const double *d_edges, int32_t n_edges, double resolution,
+                                          int32_t mode, int32_t skip_same_atom, unsigned long long *d_hist,
+                                          void *stream) {
+    GD_REQUIRE(n_atoms < (1 << 24) && n_group < 128, GD_ERR_INVALID,
+               "gd_rdf_hist_frames: at most 2^24 atoms and 127 groups");
+    GD_REQUIRE(n_frames >= 0 && n_atoms > 0 && n1 >= 0 && n2 >= 0 && n_group > 0 && n_edges >= 2 &&
+                   (mode == 0 || mode == 1) && resolution > 0.0,
+               GD_ERR_INVALID, "gd_rdf_hist_frames: bad argument");
+    if (n_frames == 0 || n1 == 0 || n2 == 0) return GD_OK;
+    GD_REQUIRE(d_pos_frac && h_lattices && d_work && d_idx1 && d_idx2 && d_edges && d_hist, GD_ERR_INVALID,
+               "gd_rdf_hist_frames: null pointer");
+    GD_REQUIRE((reinterpret_cast<uintptr_t>(d_work) & 7) == 0, GD_ERR_ALIGNMENT,
+               "gd_rdf_hist_frames: d_work must be 8-byte aligned");
+    // one reduced cell per frame, built on the host (3x3 LLL each) and copied once
+    std::vector<GdPbc> cells((size_t)n_frames);
+    for (int64_t t = 0; t < n_frames; ++t) cells[(size_t)t] = gd_pbc_build(h_lattices + 9 * t);
+    cudaStream_t st = (cudaStream_t)stream;
+    GD_CUDA_CHECK(cudaMemcpyAsync(d_work, cells.data(), cells.size() * sizeof(GdPbc), cudaMemcpyHostToDevice, st));
+    GD_CUDA_CHECK(cudaStreamSynchronize(st));  // `cells` is freed on return
+    RdfParams p;
+    p.pos = d_pos_frac;
+    p.n_frames = n_frames;
+    p.n_atoms = n_atoms;
+    p.idx1 = d_idx1;
+    p.n1 = n1;
+    p.cls = d_skip;
+    p.idx2 = d_idx2;
+    p.group = d_group;
+    p.n2 = n2;
+    p.n_group = n_group;
+    p.edges = d_edges;
+    p.n_edges = n_edges;
+    p.mode = mode;
+    p.skip_same = skip_same_atom;
+    p.inv_res = 1.0 / resolution;
+    p.hist = d_hist;
+    p.pbc = cells[0];
+    p.pbc_frames = static_cast<const GdPbc *>(d_work);
+    return rdf_launch(p, true, stream);
 }

@@ -138,14 +138,31 @@ def radial_distribution(*, transitions, floating_specie: str, max_dist: float = 
     return ret
 
 
+def _hist_frames(pos: torch.Tensor, lattices: np.ndarray, idx1, idx2, bins: np.ndarray, resolution: float,
+                 skip_same: bool) -> np.ndarray:
+    """uint64 counts [n_frames, len(bins) + 1] of gd_rdf_hist_frames (one cell per frame, np.histogram
+    binning, one group), host copy."""
+    n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
+    lib = _lib.lib
+    d_idx1 = dv.to_device(np.ascontiguousarray(idx1, dtype=np.int32))
+    d_idx2 = dv.to_device(np.ascontiguousarray(idx2, dtype=np.int32))
+    d_edges = dv.to_device(np.ascontiguousarray(bins, dtype=np.float64))
+    work = dv.empty((int(lib.gd_rdf_frames_work_bytes(n_frames)),), torch.uint8)
+    hist = dv.zeros((n_frames, len(bins) + 1), torch.int64)
+    _lib.check(lib.gd_rdf_hist_frames(
+        dv.ptr(pos), n_frames, n_atoms, lattices.ctypes.data, dv.ptr(work), dv.ptr(d_idx1), len(idx1), None,
+        dv.ptr(d_idx2), None, len(idx2), 1, dv.ptr(d_edges), len(bins), float(resolution), 1, int(skip_same),
+        dv.ptr(hist), dv.stream_ptr()))
+    return dv.to_host(hist)
+
+
 def radial_distribution_between_species(*, trajectory, specie_1: str | Collection[str],
                                         specie_2: str | Collection[str], max_dist: float = 5.0,
                                         resolution: float = 0.1) -> RDFData:
-    """Drop-in for rdf.py:193-268 (constant lattice)."""
+    """Drop-in for rdf.py:193-268; with ``constant_lattice=False`` every frame has its own cell
+    (``gd_rdf_hist_frames``: per-frame counts, normalised with the frame's volume like :248-261)."""
     if trajectory.lattice is None:
         raise RuntimeError('trajectory.lattice unexpectedly None')
-    if not getattr(trajectory, 'constant_lattice', True):
-        raise NotImplementedError('per-frame lattices are not supported on the device path')
     symbols = [_symbol(sp) for sp in trajectory.species]
 
     def select(species):
@@ -159,17 +176,26 @@ def radial_distribution_between_species(*, trajectory, specie_1: str | Collectio
     num_time_steps = int(pos.shape[0])
     bins = np.arange(0, max_dist + resolution, resolution)
     same = specie_1 == specie_2
+    str1 = specie_1 if isinstance(specie_1, str) else '/'.join(specie_1)
+    str2 = specie_2 if isinstance(specie_2, str) else '/'.join(specie_2)
+    shell = (bins + resolution) ** 3 - bins**3
+    if not getattr(trajectory, 'constant_lattice', True):
+        lattices = np.ascontiguousarray(trajectory.lattice, dtype=np.float64).reshape(num_time_steps, 9)
+        per_frame = _hist_frames(pos, lattices, idx1, idx2, bins, resolution, same)  # [T, len(bins) + 1]
+        hist_t = per_frame[:, 1:len(bins)].astype(float)
+        volumes = np.abs(np.linalg.det(lattices.reshape(-1, 3, 3)))
+        # hist_t / norm_t with norm_t = (n1 n2 / V_t) (4/3) pi shell, summed over the frames
+        particle_vol = num_atoms_2 * num_atoms_1 / volumes
+        norm = particle_vol[:, None] * ((4 / 3) * np.pi * shell)[None, :-1]
+        counts = (hist_t / norm).sum(axis=0) / num_time_steps
+        return RDFData(x=bins[:-1], y=counts, label=f'{str1}-{str2}', state='')
     hist = _hist(pos, trajectory.get_lattice(), idx1, None, 1, idx2, None, 1, bins, resolution, 1, same)
     hist_total = hist[0, 0, 1:len(bins)].astype(float)
 
     lat = trajectory.get_lattice()
-    shell = (bins + resolution) ** 3 - bins**3
     particle_vol = num_atoms_2 * num_atoms_1 / lat.volume
     norm = (particle_vol * (4 / 3) * np.pi * shell)[:-1]
     # sum over frames of hist_t / norm with one norm for a constant lattice (fp64; the reference
     # divides frame by frame, agreement ~1e-15 relative)
     counts = hist_total / norm / num_time_steps
-
-    str1 = specie_1 if isinstance(specie_1, str) else '/'.join(specie_1)
-    str2 = specie_2 if isinstance(specie_2, str) else '/'.join(specie_2)
     return RDFData(x=bins[:-1], y=counts, label=f'{str1}-{str2}', state='')

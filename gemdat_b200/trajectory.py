@@ -68,19 +68,23 @@ class Trajectory:
         base_positions=None,
         **_ignored,
     ):
-        if not constant_lattice:
-            raise NotImplementedError(
-                'only constant-lattice trajectories are on the accelerated path '
-                '(the reference calls get_lattice() without an index, transitions.py:769)'
-            )
         self.species = list(species)
         self.coords = coords if dv.is_device(coords) else np.asarray(coords, dtype=np.float64)
         if self.coords.ndim != 3 or self.coords.shape[2] != 3:
             raise ValueError('coords must have shape [n_frames, n_atoms, 3]')
         if self.coords.shape[1] != len(self.species):
             raise ValueError('len(species) must equal coords.shape[1]')
-        self.lattice = as_lattice_matrix(lattice)
-        self.constant_lattice = True
+        self.constant_lattice = bool(constant_lattice)
+        if self.constant_lattice:
+            self.lattice = as_lattice_matrix(lattice)
+        else:
+            # one cell per frame.  Only `radial_distribution_between_species` walks them
+            # (rdf.py:232-261); everything else on the path asks for THE lattice, like the
+            # reference, whose get_lattice() without an index is meaningless here
+            # (trajectory.py:686-703, transitions.py:769)
+            self.lattice = np.ascontiguousarray(np.asarray(lattice, dtype=np.float64).reshape(-1, 3, 3))
+            if len(self.lattice) != self.coords.shape[0]:
+                raise ValueError('constant_lattice=False needs one 3x3 lattice per frame')
         self.metadata = metadata if metadata else {}
         self.time_step = time_step
         self.coords_are_displacement = coords_are_displacement
@@ -102,7 +106,8 @@ class Trajectory:
         return self.__class__(
             species=self.species,
             coords=self.coords[frames],
-            lattice=self.lattice,
+            lattice=self.lattice if self.constant_lattice else self.lattice[frames],
+            constant_lattice=self.constant_lattice,
             metadata=self.metadata,
             time_step=self.time_step,
         )
@@ -110,7 +115,8 @@ class Trajectory:
     def __repr__(self):
         return (
             f'Trajectory({len(self.species)} sites, {len(self)} time steps, '
-            f'abc={Lattice(self.lattice).lengths}, device_resident={dv.is_device(self.coords)})'
+            f'abc={Lattice(self.lattice if self.constant_lattice else self.lattice[0]).lengths}, '
+            f'constant_lattice={self.constant_lattice}, device_resident={dv.is_device(self.coords)})'
         )
 
     # ------------------------------------------------------------------ representations
@@ -214,7 +220,14 @@ class Trajectory:
         return 1 / self.time_step
 
     def get_lattice(self, idx: int | None = None) -> Lattice:
-        return Lattice(self.lattice)
+        """trajectory.py:686-703: the lattice, or the one of frame ``idx`` when it is not constant."""
+        if self.constant_lattice:
+            return Lattice(self.lattice)
+        if idx is None:
+            raise NotImplementedError(
+                'this trajectory has one lattice per frame: only radial_distribution_between_species '
+                'supports that (the rest of the path uses a single lattice, like the reference)')
+        return Lattice(self.lattice[idx])
 
     # ------------------------------------------------------------------ selection
     def filter(self, species: str | Collection[str]) -> 'Trajectory':
@@ -240,6 +253,7 @@ class Trajectory:
             species=[sp for sp, keep in zip(self.species, idx) if keep],
             coords=new_coords,
             lattice=self.lattice,
+            constant_lattice=self.constant_lattice,
             metadata=self.metadata,
             time_step=self.time_step,
         )
@@ -262,6 +276,7 @@ class Trajectory:
                 keep_on_device=False):
         """K0.  ``speed`` comes out TIME-major [n_frames, n_atoms] (the layout the amplitude
         kernels stream); ``dist`` atom-major like the reference's array."""
+        lattice = self.get_lattice().matrix  # (raises for one lattice per frame)
         pos = self._device_positions()
         n_frames, n_atoms = int(pos.shape[0]), int(pos.shape[1])
         n_chunks = int(_lib.lib.gd_unwrap_chunks(n_frames, n_atoms))
@@ -273,7 +288,7 @@ class Trajectory:
         wind = dv.empty((n_atoms, 3), torch.int32)
         _lib.check(
             _lib.lib.gd_unwrap(
-                dv.ptr(pos), n_frames, n_atoms, self.lattice.ctypes.data, None, None, None,
+                dv.ptr(pos), n_frames, n_atoms, lattice.ctypes.data, None, None, None,
                 dv.ptr(work), dv.ptr(frac), dv.ptr(cart), dv.ptr(dist), dv.ptr(speed), dv.ptr(wind),
                 dv.stream_ptr(),
             )
@@ -298,7 +313,7 @@ class Trajectory:
         pos = res['pos']
         first, last = dv.to_host(pos[0]), dv.to_host(pos[-1])
         frac = (last - first) - dv.to_host(res['winding']).astype(np.float64)
-        g = Lattice(self.lattice).metric_tensor
+        g = self.get_lattice().metric_tensor
         return np.einsum('ij,ij->i', frac @ g, frac)
 
     # ------------------------------------------------------------------ per-frame averages, drift

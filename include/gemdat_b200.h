@@ -480,6 +480,23 @@ gd_status_t gd_rdf_hist(const double *d_pos_frac, int64_t n_frames, int32_t n_at
                         const double *d_edges, int32_t n_edges, double resolution, int32_t mode,
                         int32_t skip_same_atom, unsigned long long *d_hist, void *stream);
 
+/* The same histograms for a trajectory whose lattice changes from frame to frame
+ * (radial_distribution_between_species with constant_lattice=False, rdf.py:232-261).
+ * h_lattices [n_frames,9] row-major; the reduced cell of every frame is built on the host and
+ * copied into d_work (gd_rdf_frames_work_bytes(n_frames) bytes, 8-byte aligned; the call
+ * synchronises the stream once for that copy).  The counts of frame t go to their own table:
+ * d_hist [n_frames,n_group,n_edges+1] uint64 is ADDED to -- the reference normalises every
+ * frame with its own volume, which the caller does on these per-frame counts.  d_skip
+ * [n_frames,n1] (NULL: none): a negative entry drops that source in that frame. */
+int64_t gd_rdf_frames_work_bytes(int64_t n_frames);
+gd_status_t gd_rdf_hist_frames(const double *d_pos_frac, int64_t n_frames, int32_t n_atoms,
+                               const double *h_lattices, void *d_work, const int32_t *d_idx1,
+                               int32_t n1, const int32_t *d_skip, const int32_t *d_idx2,
+                               const int32_t *d_group, int32_t n2, int32_t n_group,
+                               const double *d_edges, int32_t n_edges, double resolution,
+                               int32_t mode, int32_t skip_same_atom, unsigned long long *d_hist,
+                               void *stream);
+
 /* ------------------------------------------------------------------------- *
  * K0  displacement / unwrap
  * replaces: pymatgen Trajectory.to_displacements via Trajectory.displacements

@@ -91,20 +91,24 @@ def radial_distribution(*, positions, symbols, floating_specie, codes, unique_la
 
 
 def between_species(*, coords_1, coords_2, same: bool, lattice, max_dist=5.0, resolution=0.1):
-    """(x, y) of rdf.py:193-268 for a constant lattice."""
+    """(x, y) of rdf.py:193-268; ``lattice`` is one 3x3 matrix or one per frame [T, 3, 3]
+    (``constant_lattice=False``: every frame has its own distances and its own normalisation)."""
     coords_1 = np.asarray(coords_1, dtype=np.float64)
     coords_2 = np.asarray(coords_2, dtype=np.float64)
-    lat = Lattice(lattice)
     n_t, n2, _ = coords_2.shape
     n1 = coords_1.shape[1]
+    lattices = np.asarray(lattice, dtype=np.float64)
+    if lattices.ndim == 2:
+        lattices = np.array([lattices] * n_t)
     bins = np.arange(0, max_dist + resolution, resolution)
     shell = (bins + resolution) ** 3 - bins**3
-    norm = ((n2 * n1 / lat.volume) * (4 / 3) * np.pi * shell)[:-1]
     counts = np.zeros(len(bins) - 1, dtype=float)
     for t in range(n_t):
+        lat = Lattice(lattices[t])
         d = lat.get_all_distances(coords_1[t], coords_2[t])
         d = d[~np.eye(n1, dtype=bool)] if same else d.ravel()
         hist, _ = np.histogram(d, bins=bins, density=False)
+        norm = ((n2 * n1 / lat.volume) * (4 / 3) * np.pi * shell)[:-1]
         counts += hist / norm
     counts /= n_t
     return bins[:-1], counts

@@ -1037,6 +1037,74 @@ def test_radial_distribution_between_species_vs_reference_golden(n):
     assert_allclose(d.y, g[f'{t}_y'], rtol=1e-12, atol=0)
 
 
+@pytest.mark.parametrize('device_input', [False, True])
+@pytest.mark.parametrize('name', ['diag', 'sheared', 'skewed'])
+def test_species_rdf_with_per_frame_lattices_vs_reference_golden(name, device_input):
+    """radial_distribution_between_species on a constant_lattice=False trajectory (rdf.py:232-261):
+    gd_rdf_hist_frames counts every frame in its own cell (axis-aligned, sheared, strongly
+    skewed), the host normalises each frame with its own volume.  Integer counts exact, curve to
+    1e-12 relative against the reference's own output (tests/golden/make_golden_rdf_frames.py)."""
+    from conftest import load_golden
+    from gemdat_b200 import Trajectory
+
+    g = load_golden('rdf_frames')
+    coords = torch.from_numpy(g['positions']).cuda() if device_input else g['positions']
+    traj = Trajectory(species=[str(s) for s in g['species']], coords=coords, lattice=g[f'{name}_lattices'],
+                      constant_lattice=False, time_step=2e-15)
+    for n in (0, 1, 2):
+        t = f'{name}_between{n}'
+        s1, s2 = g[f'{t}_specie_1'].tolist(), g[f'{t}_specie_2'].tolist()
+        d = traj.radial_distribution_between_species(specie_1=s1, specie_2=s2, max_dist=float(g[f'{t}_max_dist']),
+                                                     resolution=float(g[f'{t}_resolution']))
+        assert d.label == str(g[f'{t}_label']) and d.state == ''
+        assert_array_equal(d.x, g[f'{t}_x'])
+        assert_allclose(d.y, g[f'{t}_y'], rtol=1e-12, atol=0)
+    # the rest of the path asks for THE lattice, which such a trajectory does not have
+    with pytest.raises(NotImplementedError):
+        traj.get_lattice()
+    with pytest.raises(NotImplementedError):
+        traj.distances_from_base_position()
+    assert traj.get_lattice(3).matrix.shape == (3, 3) and traj[2:10].lattice.shape == (8, 3, 3)
+
+
+def test_rdf_hist_frames_equals_one_launch_per_frame():
+    """gd_rdf_hist_frames through the C ABI: the table of frame t equals gd_rdf_hist run on that
+    frame alone with its lattice (bit-exact), with several groups and a skip table."""
+    from gemdat_b200 import _device as dv
+    from gemdat_b200 import _lib
+
+    rng = np.random.default_rng(12)
+    T, N = 9, 70
+    pos = rng.random((T, N, 3)) * 1.6 - 0.3  # also outside [0, 1)
+    lattices = np.stack([np.diag([9.0, 10.0, 11.0]) @ (np.eye(3) + rng.uniform(-0.05, 0.05, (3, 3))) for _ in range(T)])
+    lattices[0] = np.diag([9.0, 10.0, 11.0])  # an axis-aligned frame among general ones
+    idx1 = np.arange(0, 30, dtype=np.int32)
+    idx2 = np.arange(20, N, dtype=np.int32)
+    group = (idx2 % 3).astype(np.int32)
+    skip = np.zeros((T, len(idx1)), dtype=np.int32)
+    skip[rng.random(skip.shape) < 0.2] = -1
+    bins = np.arange(0, 4.0 + 0.2, 0.2)
+    lib, s = _lib.lib, dv.stream_ptr()
+    d_pos, d_idx1, d_idx2, d_group = dv.to_device(pos), dv.to_device(idx1), dv.to_device(idx2), dv.to_device(group)
+    d_skip, d_edges = dv.to_device(skip), dv.to_device(bins)
+    flat = np.ascontiguousarray(lattices.reshape(T, 9))
+    for mode in (0, 1):
+        work = dv.empty((int(lib.gd_rdf_frames_work_bytes(T)),), torch.uint8)
+        got = dv.zeros((T, 3, len(bins) + 1), torch.int64)
+        _lib.check(lib.gd_rdf_hist_frames(dv.ptr(d_pos), T, N, flat.ctypes.data, dv.ptr(work), dv.ptr(d_idx1),
+                                          len(idx1), dv.ptr(d_skip), dv.ptr(d_idx2), dv.ptr(d_group), len(idx2), 3,
+                                          dv.ptr(d_edges), len(bins), 0.2, mode, 1, dv.ptr(got), s))
+        for t in range(T):
+            want = dv.zeros((1, 3, len(bins) + 1), torch.int64)
+            cls = dv.to_device(skip[t:t + 1].copy())
+            _lib.check(lib.gd_rdf_hist(dv.ptr(d_pos[t:t + 1]), 1, N, flat[t].ctypes.data, dv.ptr(d_idx1), len(idx1),
+                                       dv.ptr(cls), 1, dv.ptr(d_idx2), dv.ptr(d_group), len(idx2), 3,
+                                       dv.ptr(d_edges), len(bins), 0.2, mode, 1, dv.ptr(want), s))
+            assert_array_equal(got[t].cpu().numpy(), want[0].cpu().numpy())
+        n_pairs = int((skip >= 0).sum()) * len(idx2) - int(sum((skip[t] >= 0)[20:30].sum() for t in range(T)))
+        assert int(got.sum().item()) == n_pairs
+
+
 @pytest.mark.parametrize('triclinic', [False, True])
 def test_rdf_hist_random_vs_oracle(triclinic):
     """gd_rdf_hist on a random mixed-species trajectory (general and diagonal cell, several target

@@ -438,3 +438,31 @@ def test_oracle_drift_equals_reference_golden():
     assert_array_equal(odrift.center_of_mass(pos, [ATOMIC_MASS[s] for s in species]), g['com/coords'])
     # the reference's floating_species route averages over zero atoms (see the generator's header)
     assert np.isnan(g['drift/floating_Li'][1:]).all() and np.isnan(g['drift/floating_Li_Br'][1:]).all()
+
+
+# ------------------------------------------------------------------ species RDF, one lattice per frame
+RDF_FRAME_CASES = ['diag', 'sheared', 'skewed']
+
+
+@pytest.mark.parametrize('name', RDF_FRAME_CASES)
+def test_oracle_species_rdf_with_per_frame_lattices_equals_reference_golden(name):
+    """oracle/rdf.py::between_species with one cell per frame against the reference's
+    radial_distribution_between_species on a constant_lattice=False trajectory
+    (rdf.py:232-261; tests/golden/make_golden_rdf_frames.py)."""
+    from conftest import load_golden
+    from oracle import rdf as orf
+
+    g = load_golden('rdf_frames')
+    species = [str(s) for s in g['species']]
+    pos = g['positions']
+    sel = lambda want: pos[:, [s in want for s in species]]  # noqa: E731
+    for n in (0, 1, 2):
+        t = f'{name}_between{n}'
+        s1, s2 = g[f'{t}_specie_1'].tolist(), g[f'{t}_specie_2'].tolist()
+        w1 = [s1] if isinstance(s1, str) else s1
+        w2 = [s2] if isinstance(s2, str) else s2
+        x, y = orf.between_species(coords_1=sel(w1), coords_2=sel(w2), same=(s1 == s2),
+                                   lattice=g[f'{name}_lattices'], max_dist=float(g[f'{t}_max_dist']),
+                                   resolution=float(g[f'{t}_resolution']))
+        np.testing.assert_array_equal(x, g[f'{t}_x'])
+        np.testing.assert_allclose(y, g[f'{t}_y'], rtol=1e-13)
