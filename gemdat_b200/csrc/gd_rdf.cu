@@ -29,7 +29,13 @@
 #ifdef GD_RDF_MIN_CTAS  // resident CTAs per SM the register allocation must allow
 #define GD_RDF_BOUNDS __launch_bounds__(8 * 32, GD_RDF_MIN_CTAS)
 #else
-#define GD_RDF_BOUNDS __launch_bounds__(8 * 32)
+// (per-frame cells live in shared memory and the compiler keeps all 27 image vectors in registers,
+// 245 of them, one CTA per SM.  Capping them is worse: general cell, 2000 x 1008 x 1007 pairs:
+// 45.3 ms at 1 CTA/SM, 79.7 at 2 (128 registers, spills), 116.7 at 3; profiles/r2zs_rdf_frames_time.txt)
+#define GD_RDF_BOUNDS __launch_bounds__(8 * 32, kPerFrame ? GD_RDF_FRAMES_MIN_CTAS : 0)
+#endif
+#ifndef GD_RDF_FRAMES_MIN_CTAS
+#define GD_RDF_FRAMES_MIN_CTAS 1
 #endif
 
 namespace {
