@@ -119,6 +119,35 @@ class Trajectory:
             f'constant_lattice={self.constant_lattice}, device_resident={dv.is_device(self.coords)})'
         )
 
+    # ------------------------------------------------------------------ pickling / cache files
+    def __getstate__(self):
+        """Host data only: the cached device copy is dropped, device-resident coords are
+        downloaded (trajectory.py:110-119 drops its runtime-only caches the same way)."""
+        state = self.__dict__.copy()
+        state.pop('_dev_holder', None)
+        for key in ('coords', 'base_positions'):
+            if dv.is_device(state.get(key)):
+                state[key] = dv.to_host(state[key])
+        return state
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+
+    def to_cache(self, cache) -> None:
+        """trajectory.py:208-217: pickle the trajectory to ``cache``."""
+        import pickle
+
+        with open(cache, 'wb') as f:
+            pickle.dump(self, f)
+
+    @classmethod
+    def from_cache(cls, cache) -> 'Trajectory':
+        """trajectory.py:195-206: load a trajectory pickled by ``to_cache``."""
+        import pickle
+
+        with open(cache, 'rb') as f:
+            return pickle.load(f)
+
     # ------------------------------------------------------------------ representations
     def to_positions(self):
         """trajectory.py:121-127: positions representation, then ``np.mod(coords, 1)``.

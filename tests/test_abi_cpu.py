@@ -369,3 +369,28 @@ def test_drift_selection_and_atomic_masses_host_logic():
     assert atomic_mass(WithMass()) == 12.5
     with pytest.raises(KeyError):
         atomic_mass('Qq')
+
+
+def test_trajectory_cache_round_trip(tmp_path):
+    """Trajectory.to_cache / from_cache (trajectory.py:195-217): a pickle of the host data; the
+    cached device copy does not travel."""
+    from gemdat_b200 import Trajectory
+
+    rng = np.random.default_rng(3)
+    traj = Trajectory(species=['Li', 'Li', 'S'], coords=rng.random((7, 3, 3)), lattice=np.diag([9.0, 10.0, 11.0]),
+                      metadata={'temperature': 600.0}, time_step=2e-15)
+    traj.__dict__['_dev_holder'] = {'pos': ('would be a device tensor',)}
+    path = tmp_path / 'traj.cache'
+    traj.to_cache(path)
+    back = Trajectory.from_cache(path)
+    assert '_dev_holder' not in back.__dict__
+    assert back.species == traj.species and back.metadata == traj.metadata and back.time_step == traj.time_step
+    np.testing.assert_array_equal(back.coords, traj.coords)
+    np.testing.assert_array_equal(back.lattice, traj.lattice)
+    np.testing.assert_array_equal(back.base_positions, traj.base_positions)
+    assert back.constant_lattice and not back.coords_are_displacement and len(back) == 7
+    lat = np.stack([np.eye(3) * (10 + t) for t in range(7)])
+    per_frame = Trajectory(species=['Li', 'Li', 'S'], coords=rng.random((7, 3, 3)), lattice=lat,
+                           constant_lattice=False, time_step=2e-15)
+    per_frame.to_cache(path)
+    assert Trajectory.from_cache(path).get_lattice(4).matrix[0, 0] == 14.0
