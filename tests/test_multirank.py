@@ -354,6 +354,25 @@ def _shard_rules_worker(rank: int, world: int, port: int, out_path: str):
         cum = (mine - base_pos) - (base + wind)
         want = odispl.cumulative_displacements(pos)[f0:f1]
         np.testing.assert_allclose(cum, want, rtol=0, atol=1e-12)
+        # drift correction (FrameShards.drift_correction): the first step of a shard uses the row
+        # before it, the summed drift starts from the totals of the shards before (added in shard
+        # order), the corrected positions are base + cumulative displacement - summed drift, mod 1
+        from oracle import drift as odrift
+
+        sel = np.arange(0, A, 2)
+        local_steps = steps - np.rint(steps)
+        if rank == 0:
+            local_steps[0] = 0.0  # frame 0 of the trajectory has no step
+        local_drift = local_steps[:, sel].mean(axis=1)
+        summed = np.cumsum(local_drift, axis=0)
+        shard_totals = fs.comm.all_gather(torch.from_numpy(summed[-1].copy()))
+        for r in range(rank):
+            summed = summed + shard_totals[r].numpy()
+        corrected = np.mod(base_pos + cum - summed[:, None, :], 1)
+        want_pos = odrift.corrected_positions(pos, sel)[f0:f1]
+        gap = np.abs(corrected - want_pos)
+        assert np.minimum(gap, 1 - gap).max() < 1e-11
+        np.testing.assert_allclose(local_drift, odrift.drift(pos, sel)[f0:f1, 0], rtol=1e-12, atol=1e-18)
         # fills: last valid state per shard, nearest valid shard before / after
         for direction, ref in ((1, ofill.ffill), (-1, ofill.bfill)):
             st = states[f0:f1]
