@@ -134,42 +134,6 @@ __device__ __forceinline__ void gd_tma_load_1d(void *smem_dst, const void *gmem_
         : "memory");
 }
 
-// The same three operations on 32-bit shared-memory addresses computed once (gd_smem_u32):
-// inside a hot loop the generic -> shared conversion of a pointer costs several instructions
-// per use (ncu r2j: S2UR SR_CgaCtaId + UMOV + 2 ULEA per barrier access).
-__device__ __forceinline__ void gd_mbar_arrive_expect_tx_a(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void gd_mbar_wait_a(uint32_t bar, uint32_t parity) {
-    uint32_t ok;
-    do {
-        asm volatile(
-            "{\n"
-            "  .reg .pred p;\n"
-            "  mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-            "  selp.u32 %0, 1, 0, p;\n"
-            "}\n"
-            : "=r"(ok)
-            : "r"(bar), "r"(parity)
-            : "memory");
-    } while (!ok);
-}
-__device__ __forceinline__ void gd_tma_load_1d_a(uint32_t smem_dst, const void *gmem_src, uint32_t bytes,
-                                                 uint32_t bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-        ::"r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(bar)
-        : "memory");
-}
-__device__ __forceinline__ double gd_lds_f64(uint32_t addr) {
-    double v;
-    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
-    return v;
-}
-__device__ __forceinline__ void gd_sts_u8_one(uint32_t addr) {
-    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(1) : "memory");
-}
-
 // 1-D bulk prefetch global -> L2 (no destination, no completion to wait for): src 16-byte
 // aligned, bytes a multiple of 16.  SASS: UBLKPF.
 __device__ __forceinline__ void gd_prefetch_l2(const void *gmem_src, uint32_t bytes) {
