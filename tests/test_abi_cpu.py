@@ -394,3 +394,50 @@ def test_trajectory_cache_round_trip(tmp_path):
                            constant_lattice=False, time_step=2e-15)
     per_frame.to_cache(path)
     assert Trajectory.from_cache(path).get_lattice(4).matrix[0, 0] == 14.0
+
+
+def test_trajectory_with_one_lattice_per_frame_host_logic():
+    """Trajectory(constant_lattice=False): the lattice array follows frame slices and filters,
+    get_lattice(idx) picks a frame (trajectory.py:686-703), and whatever needs THE lattice says so
+    before touching the device."""
+    from gemdat_b200 import Trajectory
+
+    rng = np.random.default_rng(5)
+    lat = np.stack([np.diag([9.0, 10.0, 11.0]) * (1 + 0.01 * t) for t in range(12)])
+    traj = Trajectory(species=['Li', 'S', 'Li'], coords=rng.random((12, 3, 3)), lattice=lat, constant_lattice=False,
+                      time_step=2e-15)
+    assert traj.lattice.shape == (12, 3, 3) and not traj.constant_lattice
+    np.testing.assert_array_equal(traj.get_lattice(5).matrix, lat[5])
+    part = traj[3:9]
+    assert len(part) == 6 and not part.constant_lattice
+    np.testing.assert_array_equal(part.lattice, lat[3:9])
+    li = traj.filter('Li')
+    assert li.species == ['Li', 'Li'] and li.lattice.shape == (12, 3, 3) and not li.constant_lattice
+    assert [len(p) for p in traj.split(3)] == [3, 4, 4] and all(not p.constant_lattice for p in traj.split(3))
+    for call in (traj.get_lattice, traj.distances_from_base_position, lambda: traj.metrics().tracer_diffusivity()):
+        with pytest.raises(NotImplementedError):
+            call()
+    with pytest.raises(ValueError):
+        Trajectory(species=['Li'], coords=rng.random((4, 1, 3)), lattice=lat[:3], constant_lattice=False)
+    assert 'constant_lattice=False' in repr(traj)
+
+
+def test_drift_oracle_edge_cases():
+    """oracle/drift.py on the edges the kernels are tested against: one frame, one atom, steps that
+    cross the cell boundary, an empty selection (numpy's NaN with a warning, like the reference)."""
+    import warnings
+
+    from oracle import drift as odrift
+
+    one = np.array([[[0.2, 0.4, 0.9]]])
+    assert odrift.drift(one, [0]).shape == (1, 1, 3) and not odrift.drift(one, [0]).any()
+    np.testing.assert_array_equal(odrift.corrected_positions(one, [0]), one)
+    pos = np.array([[[0.95, 0.5, 0.05]], [[0.05, 0.5, 0.95]], [[0.15, 0.5, 0.85]]])  # wraps in x and z
+    np.testing.assert_allclose(odrift.displacements(pos)[:, 0], [[0, 0, 0], [0.1, 0, -0.1], [0.1, 0, -0.1]], atol=1e-15)
+    # drift of the only atom is its own step: the corrected atom stays where it started
+    np.testing.assert_allclose(odrift.corrected_positions(pos, [0]), np.broadcast_to(pos[0], pos.shape), atol=1e-15)
+    np.testing.assert_allclose(odrift.center_of_mass(pos, [2.0])[:, 0], [[0.95, 0.5, 0.05], [1.05, 0.5, -0.05],
+                                                                         [1.15, 0.5, -0.15]], atol=1e-15)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        assert np.isnan(odrift.drift(pos, [])).all()
