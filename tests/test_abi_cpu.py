@@ -441,3 +441,35 @@ def test_drift_oracle_edge_cases():
     with warnings.catch_warnings():
         warnings.simplefilter('ignore')
         assert np.isnan(odrift.drift(pos, [])).all()
+
+
+def test_reference_arm_contract_without_gpu_and_without_the_library():
+    """`bench.py --impl reference` (the CPU arm the driver runs beside ours): prints ONE JSON line with
+    the contract's keys, needs no GPU, and never maps libgemdat_b200.so (it times the oracle port only)."""
+    import json
+    import subprocess
+    import sys
+
+    root = Path(__file__).resolve().parents[1]
+    code = (
+        "import sys, runpy\n"
+        "sys.argv = ['bench.py', '--impl', 'reference', '--steps', '1', '--warmup', '0', '--cpu-frames', '60']\n"
+        "try:\n"
+        "    runpy.run_path('bench.py', run_name='__main__')\n"
+        "except SystemExit as e:\n"
+        "    assert not e.code, e.code\n"
+        "print('MAPPED', 'libgemdat_b200' in open('/proc/self/maps').read())\n"
+    )
+    out = subprocess.run([sys.executable, '-c', code], cwd=root, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith('{')]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d['impl'] == 'reference' and d['n_gpus'] == 1 and d['steps'] == 1 and d['warmup'] == 0
+    assert d['metric'] == 'site_assignment_plus_jumps_atom_frames_per_s' and d['unit'] == 'atom-frames/s'
+    assert d['higher_is_better'] is True and d['value'] > 0 and d['ms_per_step'] > 0
+    assert d['config']['workload'].startswith('C3 ') and d['dtype'] == 'f64' and d['data'] == 'synthetic'
+    assert d['cpu_baseline']['kind'] == 'port' and d['cpu_baseline']['cores'] >= 1
+    assert d['cpu_baseline']['value'] == d['value']
+    assert d['e2e'] == {'value': d['value'], 'unit': d['unit'], 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}
+    assert 'MAPPED False' in out.stdout
