@@ -55,6 +55,8 @@ EVENT_COLUMNS = [
 class SiteGrid:
     """Host + device copy of the search structure built by ``gd_sitegrid_build``."""
 
+    _blob_guess = 8 << 20  # bytes tried first (C3's 2160 sites need 2 MB); grows when it was too small
+
     def __init__(self, *, lattice_matrix, site_frac, site_labels, site_radius: dict,
                  site_inner_fraction: dict):
         labels = np.asarray(list(site_labels), dtype=object)
@@ -80,8 +82,15 @@ class SiteGrid:
         needed = C.c_size_t(0)
         args = (lat.ctypes.data, frac.ctypes.data, group.ctypes.data, self.n_sites,
                 radius.ctypes.data, inner.ctypes.data, len(radius))
-        st = _lib.lib.gd_sitegrid_build(*args, None, 0, C.byref(needed))
-        if st == _lib.GD_ERR_CAPACITY:
+        # one pass in the common case: the size query of gd_sitegrid_build does the whole
+        # construction, so a buffer that is large enough for most site sets is tried first (its
+        # untouched pages cost nothing) and the exact-size query only runs when it was too small
+        guess = np.zeros(SiteGrid._blob_guess, dtype=np.uint8)
+        st = _lib.lib.gd_sitegrid_build(*args, guess.ctypes.data, guess.nbytes, C.byref(needed))
+        if st == _lib.GD_OK:
+            self.h_blob = guess[:needed.value].copy()
+        elif st == _lib.GD_ERR_CAPACITY:
+            SiteGrid._blob_guess = max(SiteGrid._blob_guess, 2 * int(needed.value))
             self.h_blob = np.zeros(needed.value, dtype=np.uint8)
             st = _lib.lib.gd_sitegrid_build(*args, self.h_blob.ctypes.data, self.h_blob.nbytes,
                                             C.byref(needed))
